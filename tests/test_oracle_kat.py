@@ -1,0 +1,27 @@
+"""Pins the CPU oracle against every known-answer test the reference holds for the hot path."""
+import numpy as np
+import pytest
+
+import kat
+from oracle import golden as G
+
+
+@pytest.mark.parametrize("check", kat.ALL, ids=[c.__name__ for c in kat.ALL])
+def test_oracle_kat(check):
+    check(G)
+
+
+def test_sh_backward_ref_compat_layout_reported():
+    """Q12: with the reference's [k][axis] reading of sphericart's [axis][k] buffer, the position gradient differs
+    from the finite-difference answer; record by how much (the reference's own test tolerance is 1e-2)."""
+    xyz, g, b0, sh, fd = kat.sh_backward_case()
+    _, _, xg_ok = G.sh_backward(xyz, b0, sh, np.zeros(3, np.float32), g, 2, ref_compat_dsph=0)
+    _, _, xg_rc = G.sh_backward(xyz, b0, sh, np.zeros(3, np.float32), g, 2, ref_compat_dsph=1)
+    err_ok = float(np.abs(xg_ok - fd).max())
+    err_rc = float(np.abs(xg_rc - fd).max())
+    print(f"SH d xyz max err vs FD: correct layout {err_ok:.3e}, reference-compatible layout {err_rc:.3e}")
+    assert err_ok < 1e-3
+    # l_max = 0: both layouts coincide (dY0 = 0)
+    a = G.sh_backward(xyz, b0, None, np.zeros(3, np.float32), g, 0, ref_compat_dsph=0)[2]
+    b = G.sh_backward(xyz, b0, None, np.zeros(3, np.float32), g, 0, ref_compat_dsph=1)[2]
+    np.testing.assert_array_equal(a, b)
