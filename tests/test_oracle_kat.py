@@ -25,3 +25,17 @@ def test_sh_backward_ref_compat_layout_reported():
     a = G.sh_backward(xyz, b0, None, np.zeros(3, np.float32), g, 0, ref_compat_dsph=0)[2]
     b = G.sh_backward(xyz, b0, None, np.zeros(3, np.float32), g, 0, ref_compat_dsph=1)[2]
     np.testing.assert_array_equal(a, b)
+
+
+def test_sph_basis_pinned_to_sphericart_l3():
+    """l = 3 is pinned by no reference test: pin the oracle's closed forms and normalised gradients
+    against golden vectors produced by the vendored sphericart CPU code (oracle/gen_golden.py)."""
+    import json, os
+    with open(os.path.join(os.path.dirname(__file__), "golden", "sph_l3.json")) as f:
+        d = json.load(f)
+    xyz = np.array(d["xyz"], np.float64).reshape(-1, 3)
+    sph = np.array(d["sph"]).reshape(-1, 16)
+    dsph = np.array(d["dsph"]).reshape(-1, 3, 16)   # sphericart layout [sample][axis][k]
+    Y, dY = G.sph(xyz.astype(np.float32), 3, grad=True)
+    np.testing.assert_allclose(Y, sph, atol=2e-6)
+    np.testing.assert_allclose(dY, dsph, atol=2e-5, rtol=1e-5)
