@@ -1,0 +1,334 @@
+// binning.cu -- tile binning: exact per-Gaussian instance counts, exclusive scan, deterministic key/value
+// emission, sort, tile ranges.  Replaces the reference's coarse_binning_kernel (run twice) + generate_splats_kernel
+// + thrust temporaries + 4 blocking D2H reads (cuda/culling.cu:197-300, :386-475): the candidate window and the
+// 4-axis SAT are evaluated in registers per Gaussian, so no coarse pair list (>= 25 per Gaussian) is
+// ever materialised, and emission order is Gaussian-major so equal (tile, depth) keys come out in ascending
+// Gaussian id after the stable sort.
+#include <algorithm>
+
+#include "gsx_common.cuh"
+#include "gsx_math.cuh"
+
+namespace gsx {
+
+int sort_pairs_impl(uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                    const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
+                    int *result_in_b);
+int tile_ranges_impl(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
+                     cudaStream_t st);
+size_t sort_workspace_bytes_impl(long long n);
+
+namespace {
+
+constexpr int kBlock = 256;
+constexpr int SCAN_IPT = 8;
+constexpr int SCAN_TILE = kBlock * SCAN_IPT;
+
+// exact instance count of one Gaussian (+ its coarse candidate count, what the reference's size query returns)
+__device__ __forceinline__ int count_tiles(float u, float v, float4 r, int ntx, int nty, int *coarse) {
+  const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
+  const int nx = max(0, w.x1 - w.x0), ny = max(0, w.y1 - w.y0);
+  *coarse = nx * ny;
+  if (nx * ny == 0) return 0;
+  const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
+  int c = 0;
+  for (int tx = w.x0; tx < w.x1; ++tx)
+    for (int ty = w.y0; ty < w.y1; ++ty) c += sat_tile(s, tx, ty) ? 1 : 0;
+  return c;
+}
+
+__global__ void __launch_bounds__(kBlock) k_count(const float *__restrict__ uv, const float4 *__restrict__ radius,
+                                                  const uint8_t *__restrict__ mask, int ntx, int nty, int N,
+                                                  int *__restrict__ touched, unsigned long long *__restrict__ coarse_total) {
+  const int i = blockIdx.x * kBlock + threadIdx.x;
+  int coarse = 0, c = 0;
+  if (i < N && (!mask || mask[i])) c = count_tiles(uv[2 * i], uv[2 * i + 1], radius[i], ntx, nty, &coarse);
+  if (i < N) touched[i] = c;
+  if (coarse_total) {
+    unsigned long long s = (unsigned long long)coarse;
+    for (int off = 16; off > 0; off >>= 1) s += __shfl_down_sync(0xffffffffu, s, off);
+    if ((threadIdx.x & 31) == 0 && s) atomicAdd(coarse_total, s);
+  }
+}
+
+__global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, const float *__restrict__ depth,
+                                                 int depth_stride, const float4 *__restrict__ radius,
+                                                 const int *__restrict__ touched, const int *__restrict__ offsets,
+                                                 int ntx, int nty, int N, long long capacity,
+                                                 uint64_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+  const int i = blockIdx.x * kBlock + threadIdx.x;
+  if (i >= N) return;
+  const int cnt = touched[i];
+  if (cnt == 0) return;
+  long long o = offsets[i];
+  if (o + cnt > capacity) return;   // overflow: detected by the host through the total
+  const float u = uv[2 * i], v = uv[2 * i + 1];
+  const float4 r = radius[i];
+  const uint64_t zb = float_sort_bits(depth[(size_t)i * depth_stride]);
+  const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
+  const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
+  for (int tx = w.x0; tx < w.x1; ++tx)
+    for (int ty = w.y0; ty < w.y1; ++ty)
+      if (sat_tile(s, tx, ty)) {
+        keys[o] = ((uint64_t)(unsigned)(ty * ntx + tx) << 32) | zb;
+        vals[o] = (uint32_t)i;
+        ++o;
+      }
+}
+
+// ---- 3-kernel exclusive scan of int32 (N up to 2^31) ------------------------------------------------------
+__device__ __forceinline__ int block_reduce_sum(int v, int *s_tmp) {
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
+  if ((threadIdx.x & 31) == 0) s_tmp[threadIdx.x >> 5] = v;
+  __syncthreads();
+  int t = 0;
+  if (threadIdx.x < 32) {
+    t = threadIdx.x < (kBlock / 32) ? s_tmp[threadIdx.x] : 0;
+    for (int off = 16; off > 0; off >>= 1) t += __shfl_down_sync(0xffffffffu, t, off);
+  }
+  return t;   // valid in thread 0
+}
+
+__global__ void __launch_bounds__(kBlock) k_scan_reduce(const int *__restrict__ in, int N, int *__restrict__ block_sums) {
+  __shared__ int s_tmp[kBlock / 32];
+  const long long base = (long long)blockIdx.x * SCAN_TILE;
+  int v = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_IPT; ++k) {
+    const long long i = base + k * kBlock + threadIdx.x;
+    if (i < N) v += in[i];
+  }
+  const int t = block_reduce_sum(v, s_tmp);
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = t;
+}
+
+__global__ void __launch_bounds__(1024) k_scan_block_sums(int *__restrict__ block_sums, int nb, int *__restrict__ total) {
+  __shared__ int s[1024];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int b0 = 0; b0 < nb; b0 += 1024) {
+    const int i = b0 + threadIdx.x;
+    const int v = i < nb ? block_sums[i] : 0;
+    s[threadIdx.x] = v;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {
+      const int t = threadIdx.x >= off ? s[threadIdx.x - off] : 0;
+      __syncthreads();
+      s[threadIdx.x] += t;
+      __syncthreads();
+    }
+    if (i < nb) block_sums[i] = carry + s[threadIdx.x] - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry += s[1023];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+
+__global__ void __launch_bounds__(kBlock) k_scan_apply(const int *__restrict__ in, int N,
+                                                       const int *__restrict__ block_sums, int *__restrict__ out) {
+  __shared__ int s_warp[kBlock / 32];
+  const long long base = (long long)blockIdx.x * SCAN_TILE + (long long)threadIdx.x * SCAN_IPT;
+  int v[SCAN_IPT];
+  int sum = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_IPT; ++k) { v[k] = (base + k < N) ? in[base + k] : 0; sum += v[k]; }
+  int incl = sum;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int off = 1; off < 32; off <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, incl, off);
+    if (lane >= off) incl += t;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  int wbase = 0;
+  for (int w = 0; w < warp; ++w) wbase += s_warp[w];
+  int run = block_sums[blockIdx.x] + wbase + incl - sum;
+#pragma unroll
+  for (int k = 0; k < SCAN_IPT; ++k) {
+    if (base + k < N) out[base + k] = run;
+    run += v[k];
+  }
+}
+
+__global__ void k_copy_u32_to_i32(const uint32_t *__restrict__ in, int *__restrict__ out, long long n_host,
+                                  const int *__restrict__ n_dev) {
+  const long long n = n_dev ? min((long long)*n_dev, n_host) : n_host;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = (int)in[i];
+}
+
+}  // namespace
+
+int tile_key_bits(int n_tiles) {
+  int b = 0;
+  while ((1 << b) < n_tiles) ++b;
+  return 32 + std::max(b, 1);
+}
+
+int exclusive_scan_i32(const int *in, int N, int *out, int *block_sums, int *total_dev, cudaStream_t st) {
+  const int nb = std::max(1, ceil_div(N, SCAN_TILE));
+  k_scan_reduce<<<nb, kBlock, 0, st>>>(in, N, block_sums);
+  GSX_LAUNCH_CHECK();
+  k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nb, total_dev);
+  GSX_LAUNCH_CHECK();
+  k_scan_apply<<<nb, kBlock, 0, st>>>(in, N, block_sums, out);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+size_t scan_block_sums_count(int N) { return (size_t)std::max(1, ceil_div(N, SCAN_TILE)); }
+
+// Workspace carve-up shared by the per-function F7 entry point and the view-level context.
+struct BinLayout {
+  size_t touched, offsets, block_sums, total, keys_a, keys_b, vals_a, vals_b, sort_ws, sort_ws_bytes, bytes;
+};
+BinLayout bin_layout(int N, long long capacity) {
+  BinLayout L;
+  size_t off = 0;
+  auto take = [&](size_t b) { size_t o = off; off += align_up(std::max<size_t>(b, 16), 256); return o; };
+  L.touched = take(sizeof(int) * (size_t)N);
+  L.offsets = take(sizeof(int) * (size_t)N);
+  L.block_sums = take(sizeof(int) * scan_block_sums_count(N));
+  L.total = take(sizeof(int) * 4);
+  L.keys_a = take(sizeof(uint64_t) * (size_t)capacity);
+  L.keys_b = take(sizeof(uint64_t) * (size_t)capacity);
+  L.vals_a = take(sizeof(uint32_t) * (size_t)capacity);
+  L.vals_b = take(sizeof(uint32_t) * (size_t)capacity);
+  L.sort_ws_bytes = sort_workspace_bytes_impl(capacity);
+  L.sort_ws = take(L.sort_ws_bytes);
+  L.bytes = off;
+  return L;
+}
+
+// scan -> emit -> sort -> ranges, given touched[] already filled.  Leaves sorted keys / ids in
+// (*sorted_keys, *sorted_vals) inside the workspace; K in total_dev[0].
+int bin_sort_impl(const float *uv, const float *depth, int depth_stride, const float4 *radius, int ntx, int nty, int N,
+                  long long capacity, char *ws, const BinLayout &L, int *ranges, const uint64_t **sorted_keys,
+                  const uint32_t **sorted_vals, cudaStream_t st) {
+  int *touched = (int *)(ws + L.touched), *offsets = (int *)(ws + L.offsets);
+  int *block_sums = (int *)(ws + L.block_sums), *total = (int *)(ws + L.total);
+  uint64_t *ka = (uint64_t *)(ws + L.keys_a), *kb = (uint64_t *)(ws + L.keys_b);
+  uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
+  int rc = exclusive_scan_i32(touched, N, offsets, block_sums, total, st);
+  if (rc != GSX_OK) return rc;
+  if (N > 0) {
+    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, depth, depth_stride, radius, touched, offsets, ntx, nty, N,
+                                                   capacity, ka, va);
+    GSX_LAUNCH_CHECK();
+  }
+  int in_b = 0;
+  rc = sort_pairs_impl(ka, kb, va, vb, capacity, total, tile_key_bits(ntx * nty), ws + L.sort_ws, L.sort_ws_bytes, st,
+                       &in_b);
+  if (rc != GSX_OK) return rc;
+  *sorted_keys = in_b ? kb : ka;
+  *sorted_vals = in_b ? vb : va;
+  return tile_ranges_impl(*sorted_keys, capacity, total, ntx * nty, ranges, st);
+}
+
+int count_tiles_launch(const float *uv, const float4 *radius, const uint8_t *mask, int ntx, int nty, int N, int *touched,
+                       unsigned long long *coarse_total, cudaStream_t st) {
+  if (N <= 0) return GSX_OK;
+  k_count<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, radius, mask, ntx, nty, N, touched, coarse_total);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+int copy_ids_launch(const uint32_t *in, int *out, long long n, const int *n_dev, cudaStream_t st) {
+  if (n <= 0) return GSX_OK;
+  const int blocks = (int)std::min<long long>(kNumSMs * 8, (n + 255) / 256);
+  k_copy_u32_to_i32<<<blocks, 256, 0, st>>>(in, out, n, n_dev);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+// small cached internal workspace for callers that pass none (the reference API has no workspace argument)
+static char *g_ws = nullptr;
+static size_t g_ws_bytes = 0;
+int internal_workspace(size_t bytes, char **out) {
+  if (bytes > g_ws_bytes) {
+    if (g_ws) cudaFree(g_ws);
+    g_ws = nullptr; g_ws_bytes = 0;
+    GSX_CUDA(cudaMalloc(&g_ws, bytes));
+    g_ws_bytes = bytes;
+  }
+  *out = g_ws;
+  return GSX_OK;
+}
+
+}  // namespace gsx
+
+using namespace gsx;
+
+extern "C" {
+
+int gsx_sorted_list_size(const float *uv, const float *radius, int n_tiles_x, int n_tiles_y, int N,
+                         long long *coarse_pairs_host, long long *num_instances_host, void *stream) {
+  GSX_REQUIRE_DEV(uv); GSX_REQUIRE_DEV(radius);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (coarse_pairs_host) *coarse_pairs_host = 0;
+  if (num_instances_host) *num_instances_host = 0;
+  if (N <= 0) return GSX_OK;
+  const BinLayout L = bin_layout(N, 1);
+  char *ws;
+  int rc = internal_workspace(L.bytes + 256, &ws);
+  if (rc != GSX_OK) return rc;
+  unsigned long long *coarse = (unsigned long long *)(ws + L.bytes);
+  GSX_CUDA(cudaMemsetAsync(coarse, 0, sizeof(unsigned long long), st));
+  rc = count_tiles_launch(uv, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched), coarse, st);
+  if (rc != GSX_OK) return rc;
+  rc = exclusive_scan_i32((int *)(ws + L.touched), N, (int *)(ws + L.offsets), (int *)(ws + L.block_sums),
+                          (int *)(ws + L.total), st);
+  if (rc != GSX_OK) return rc;
+  unsigned long long hc = 0;
+  int hk = 0;
+  GSX_CUDA(cudaMemcpyAsync(&hc, coarse, sizeof(hc), cudaMemcpyDeviceToHost, st));
+  GSX_CUDA(cudaMemcpyAsync(&hk, ws + L.total, sizeof(int), cudaMemcpyDeviceToHost, st));
+  GSX_CUDA(cudaStreamSynchronize(st));
+  if (coarse_pairs_host) *coarse_pairs_host = (long long)hc;
+  if (num_instances_host) *num_instances_host = hk;
+  return GSX_OK;
+}
+
+size_t gsx_sorted_list_workspace_bytes(int N, long long capacity) {
+  return bin_layout(std::max(N, 1), std::max<long long>(capacity, 1)).bytes;
+}
+
+int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const float *radius, int n_tiles_x,
+                                 int n_tiles_y, int N, long long capacity, int *sorted_gaussians, int *ranges,
+                                 int *num_instances_dev, void *workspace, size_t workspace_bytes, void *stream) {
+  GSX_REQUIRE_DEV(uv); GSX_REQUIRE_DEV(xyz_c); GSX_REQUIRE_DEV(radius); GSX_REQUIRE_DEV(ranges);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int T = n_tiles_x * n_tiles_y;
+  if (N <= 0 || capacity <= 0) {
+    GSX_CUDA(cudaMemsetAsync(ranges, 0, sizeof(int) * (size_t)(T + 1), st));
+    if (num_instances_dev) GSX_CUDA(cudaMemsetAsync(num_instances_dev, 0, sizeof(int), st));
+    return GSX_OK;
+  }
+  GSX_REQUIRE_DEV(sorted_gaussians);
+  const BinLayout L = bin_layout(N, capacity);
+  char *ws = (char *)workspace;
+  if (!ws) {
+    int rc = internal_workspace(L.bytes, &ws);
+    if (rc != GSX_OK) return rc;
+  } else if (workspace_bytes < L.bytes) {
+    set_error("sorted-list workspace %zu < %zu", workspace_bytes, L.bytes);
+    return GSX_E_WORKSPACE;
+  }
+  int rc = count_tiles_launch(uv, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched),
+                              nullptr, st);
+  if (rc != GSX_OK) return rc;
+  const uint64_t *sk;
+  const uint32_t *sv;
+  rc = bin_sort_impl(uv, xyz_c + 2, 3, (const float4 *)radius, n_tiles_x, n_tiles_y, N, capacity, ws, L, ranges, &sk,
+                     &sv, st);
+  if (rc != GSX_OK) return rc;
+  rc = copy_ids_launch(sv, sorted_gaussians, capacity, (const int *)(ws + L.total), st);
+  if (rc != GSX_OK) return rc;
+  if (num_instances_dev)
+    GSX_CUDA(cudaMemcpyAsync(num_instances_dev, ws + L.total, sizeof(int), cudaMemcpyDeviceToDevice, st));
+  return GSX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,40 @@
+// gsx_common.cuh -- host-side helpers of libgsx.so (error codes, pointer checks, launch helpers).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/gsx.h"
+
+namespace gsx {
+
+void set_error(const char *fmt, ...);
+
+// The reference asserts every pointer is device memory (cuda/checks.cuh:17-38) and exits; the C ABI returns a
+// status instead and the C++ compat shim turns it back into exit(EXIT_FAILURE).
+int check_device_ptr(const void *p, const char *name);
+
+#define GSX_REQUIRE_DEV(p)                                   \
+  do {                                                       \
+    int _e = ::gsx::check_device_ptr((p), #p);               \
+    if (_e != GSX_OK) return _e;                             \
+  } while (0)
+
+#define GSX_CUDA(call)                                                                            \
+  do {                                                                                            \
+    cudaError_t _e = (call);                                                                      \
+    if (_e != cudaSuccess) {                                                                      \
+      ::gsx::set_error("%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(_e));      \
+      return GSX_E_CUDA;                                                                          \
+    }                                                                                             \
+  } while (0)
+
+#define GSX_LAUNCH_CHECK() GSX_CUDA(cudaGetLastError())
+
+static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+constexpr int kNumSMs = 148;  // B200
+
+}  // namespace gsx

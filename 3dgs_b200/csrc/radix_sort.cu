@@ -1,0 +1,320 @@
+// radix_sort.cu -- hand-written onesweep LSD radix sort of (uint64 key, uint32 value) pairs, plus tile-range
+// extraction.  Replaces cub::DeviceRadixSort::SortPairs<double,int> over 64 bits + find_tile_boundaries_kernel
+// (reference cuda/culling.cu:455-469, :302-343).  Keys are tile<<32 | order-preserving depth bits, so only
+// 32 + ceil(log2 T) bits are sorted (6 passes of 8 bits up to 65536 tiles instead of the reference's 8).
+//
+// Structure (one read of the keys for all histograms, then one read + one write per pass):
+//   k_histogram      : per-pass 256-bin digit histograms, shared-memory privatised, one global RED per bin/block
+//   k_scan_histogram : exclusive scan of each pass's 256 bins -> global digit bases
+//   k_onesweep       : per 4096-key tile: warp-synchronous match_any ranking (stable), decoupled look-back of the
+//                      per-digit tile prefixes through a (flag|count) status word, shared-memory reorder so the
+//                      global scatter is coalesced per digit run.  Tile ids come from an atomic ticket so a tile
+//                      only ever waits on tiles that are already resident (no deadlock).
+// HBM-bound: algorithmic bytes = 8n (histogram read) + passes * 24n.  The live count may live on the device
+// (n_dev) so the view-level path never syncs with the host.
+#include "gsx_common.cuh"
+
+namespace gsx {
+
+namespace {
+
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_IPT = 16;
+constexpr int RS_TILE = RS_THREADS * RS_IPT;   // 4096 keys per tile
+constexpr int RADIX = 256;
+constexpr int MAX_PASSES = 8;
+constexpr uint32_t FLAG_AGG = 1u << 30, FLAG_INC = 2u << 30, FLAG_MASK = 3u << 30, VAL_MASK = ~FLAG_MASK;
+
+__device__ __forceinline__ long long live_count(const int *n_dev, long long n) {
+  if (n_dev) { const long long v = *n_dev; return v < n ? v : n; }
+  return n;
+}
+
+__global__ void __launch_bounds__(256) k_histogram(const uint64_t *__restrict__ keys, long long n_host,
+                                                   const int *__restrict__ n_dev, int passes, int key_bits,
+                                                   unsigned int *__restrict__ hist /*[passes][256]*/) {
+  __shared__ unsigned int sh[MAX_PASSES * RADIX];
+  for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x) sh[i] = 0;
+  __syncthreads();
+  const long long n = live_count(n_dev, n_host);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint64_t k = keys[i];
+    for (int p = 0; p < passes; ++p) {
+      const int bits = min(8, key_bits - 8 * p);
+      const unsigned d = (unsigned)(k >> (8 * p)) & ((1u << bits) - 1u);
+      atomicAdd(&sh[p * RADIX + d], 1u);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < passes * RADIX; i += blockDim.x)
+    if (sh[i]) atomicAdd(&hist[i], sh[i]);
+}
+
+__global__ void __launch_bounds__(RADIX) k_scan_histogram(unsigned int *__restrict__ hist) {
+  __shared__ unsigned int s[RADIX];
+  unsigned int *h = hist + blockIdx.x * RADIX;
+  const unsigned v = h[threadIdx.x];
+  s[threadIdx.x] = v;
+  __syncthreads();
+  for (int off = 1; off < RADIX; off <<= 1) {
+    const unsigned t = threadIdx.x >= off ? s[threadIdx.x - off] : 0u;
+    __syncthreads();
+    s[threadIdx.x] += t;
+    __syncthreads();
+  }
+  h[threadIdx.x] = s[threadIdx.x] - v;
+}
+
+__device__ __forceinline__ unsigned ld_volatile(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_volatile(unsigned *p, unsigned v) {
+  asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+__global__ void __launch_bounds__(RS_THREADS)
+k_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
+           uint32_t *__restrict__ vals_out, long long n_host, const int *__restrict__ n_dev, int shift, int bits,
+           const unsigned int *__restrict__ digit_base /*[256] exclusive*/, unsigned int *__restrict__ status,
+           unsigned int *__restrict__ ticket) {
+  __shared__ __align__(16) uint64_t s_keys[RS_TILE];        // reused for the values
+  __shared__ unsigned int s_warp[RS_WARPS][RADIX + 1];      // per-warp digit counts -> exclusive offsets
+  __shared__ unsigned int s_excl[RADIX + 1];                // block-exclusive offset of each digit
+  __shared__ int s_gbase[RADIX];                            // global base minus local offset
+  __shared__ unsigned int s_scan[RS_WARPS];
+  __shared__ unsigned int s_tile;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+  for (int i = tid; i < RS_WARPS * (RADIX + 1); i += RS_THREADS) (&s_warp[0][0])[i] = 0;
+  __syncthreads();
+  const unsigned tile = s_tile;
+  const long long n = live_count(n_dev, n_host);
+  const long long base = (long long)tile * RS_TILE;
+  if (base >= n) return;
+  const int valid = (int)min((long long)RS_TILE, n - base);
+  const unsigned mask = (1u << bits) - 1u;
+
+  uint64_t key[RS_IPT];
+  uint32_t val[RS_IPT];
+  unsigned pos[RS_IPT];
+#pragma unroll
+  for (int i = 0; i < RS_IPT; ++i) {
+    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+    if (li < valid) { key[i] = keys_in[base + li]; val[i] = vals_in[base + li]; }
+    else { key[i] = ~0ull; val[i] = 0; }
+  }
+  // stable rank inside the warp: items in order i, lanes in order; peers found with match.any
+#pragma unroll
+  for (int i = 0; i < RS_IPT; ++i) {
+    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+    const unsigned d = li < valid ? ((unsigned)(key[i] >> shift) & mask) : (unsigned)RADIX;
+    const unsigned peers = __match_any_sync(0xffffffffu, d);
+    const unsigned lt = peers & ((1u << lane) - 1u);
+    const unsigned before = s_warp[warp][d];
+    __syncwarp();
+    if (lt == 0) s_warp[warp][d] = before + __popc(peers);
+    __syncwarp();
+    pos[i] = before + __popc(lt);
+  }
+  __syncthreads();
+  // per digit: exclusive scan over warps, total per digit
+  unsigned total = 0;   // for digit == tid
+  {
+    unsigned run = 0;
+#pragma unroll
+    for (int w = 0; w < RS_WARPS; ++w) { const unsigned t = s_warp[w][tid]; s_warp[w][tid] = run; run += t; }
+    total = run;
+    if (tid == 0) {
+      unsigned r2 = 0;
+      for (int w = 0; w < RS_WARPS; ++w) { const unsigned t = s_warp[w][RADIX]; s_warp[w][RADIX] = r2; r2 += t; }
+    }
+  }
+  // block-exclusive scan of totals over the 256 digits
+  {
+    unsigned incl = total;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const unsigned t = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += t;
+    }
+    if (lane == 31) s_scan[warp] = incl;
+    __syncthreads();
+    unsigned wbase = 0;
+    for (int w = 0; w < warp; ++w) wbase += s_scan[w];
+    s_excl[tid] = wbase + incl - total;
+    if (tid == RS_THREADS - 1) s_excl[RADIX] = wbase + incl;   // == valid
+  }
+  // decoupled look-back for digit == tid
+  {
+    unsigned *my = status + (size_t)tile * RADIX + tid;
+    unsigned excl = 0;
+    if (tile == 0) {
+      st_volatile(my, FLAG_INC | total);
+    } else {
+      st_volatile(my, FLAG_AGG | total);
+      long long t = (long long)tile - 1;
+      while (true) {
+        const unsigned s = ld_volatile(status + (size_t)t * RADIX + tid);
+        if ((s & FLAG_MASK) == 0) continue;
+        excl += s & VAL_MASK;
+        if ((s & FLAG_MASK) == FLAG_INC) break;
+        --t;
+      }
+      st_volatile(my, FLAG_INC | (excl + total));
+    }
+    s_gbase[tid] = (int)(digit_base[tid] + excl) - (int)s_excl[tid];
+  }
+  __syncthreads();
+  // local reorder through shared memory, then coalesced scatter
+#pragma unroll
+  for (int i = 0; i < RS_IPT; ++i) {
+    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+    const unsigned d = li < valid ? ((unsigned)(key[i] >> shift) & mask) : (unsigned)RADIX;
+    pos[i] += s_excl[d] + s_warp[warp][d];
+    s_keys[pos[i]] = key[i];
+  }
+  __syncthreads();
+  int gidx[RS_IPT];
+#pragma unroll
+  for (int k = 0; k < RS_IPT; ++k) {
+    const int slot = tid + k * RS_THREADS;
+    gidx[k] = -1;
+    if (slot < valid) {
+      const uint64_t kk = s_keys[slot];
+      const unsigned d = (unsigned)(kk >> shift) & mask;
+      gidx[k] = s_gbase[d] + slot;
+      keys_out[gidx[k]] = kk;
+    }
+  }
+  __syncthreads();
+  uint32_t *s_vals = reinterpret_cast<uint32_t *>(s_keys);
+#pragma unroll
+  for (int i = 0; i < RS_IPT; ++i) s_vals[pos[i]] = val[i];
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < RS_IPT; ++k)
+    if (gidx[k] >= 0) vals_out[gidx[k]] = s_vals[tid + k * RS_THREADS];
+}
+
+// ranges[t] = first i whose tile >= t ; ranges[n_tiles] = n   (reference cuda/culling.cu:302-343; exact integer
+// tile ids instead of floor(key / (max_z+1)) -- SURVEY H3).  n == 0 -> all zeros.
+__global__ void __launch_bounds__(256) k_tile_ranges(const uint64_t *__restrict__ keys, long long n_host,
+                                                     const int *__restrict__ n_dev, int n_tiles,
+                                                     int *__restrict__ ranges) {
+  const long long n = live_count(n_dev, n_host);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (n == 0) {
+    for (long long t = i0; t <= n_tiles; t += stride) ranges[t] = 0;
+    return;
+  }
+  for (long long i = i0; i < n; i += stride) {
+    int cur = (int)(keys[i] >> 32);
+    cur = min(cur, n_tiles - 1);
+    int prev = -1;
+    if (i > 0) prev = min((int)(keys[i - 1] >> 32), n_tiles - 1);
+    for (int t = prev + 1; t <= cur; ++t) ranges[t] = (int)i;
+    if (i == n - 1)
+      for (int t = cur + 1; t <= n_tiles; ++t) ranges[t] = (int)n;
+  }
+}
+
+struct SortLayout {
+  size_t hist_off, ticket_off, status_off, total;
+  int tiles;
+};
+SortLayout sort_layout(long long n) {
+  SortLayout L;
+  L.tiles = (int)((n + RS_TILE - 1) / RS_TILE);
+  if (L.tiles < 1) L.tiles = 1;
+  size_t off = 0;
+  L.hist_off = off; off += align_up(sizeof(unsigned) * MAX_PASSES * RADIX, 256);
+  L.ticket_off = off; off += align_up(sizeof(unsigned) * MAX_PASSES, 256);
+  L.status_off = off; off += align_up(sizeof(unsigned) * (size_t)MAX_PASSES * L.tiles * RADIX, 256);
+  L.total = off;
+  return L;
+}
+
+}  // namespace
+
+// Internal entry (no pointer attribute checks) used by the binning path.  Result lands in keys_out/vals_out when
+// the number of passes is odd, else back in keys_in/vals_in; *result_in_out tells which.
+int sort_pairs_impl(uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                    const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
+                    int *result_in_b) {
+  if (key_bits < 1 || key_bits > 64) { set_error("key_bits %d out of range", key_bits); return GSX_E_ARG; }
+  const int passes = (key_bits + 7) / 8;
+  *result_in_b = passes & 1;
+  if (n <= 0) return GSX_OK;
+  const SortLayout L = sort_layout(n);
+  if (workspace_bytes < L.total) { set_error("sort workspace %zu < %zu", workspace_bytes, L.total); return GSX_E_WORKSPACE; }
+  char *ws = (char *)workspace;
+  unsigned *hist = (unsigned *)(ws + L.hist_off);
+  unsigned *ticket = (unsigned *)(ws + L.ticket_off);
+  unsigned *status = (unsigned *)(ws + L.status_off);
+  GSX_CUDA(cudaMemsetAsync(ws, 0, L.status_off + sizeof(unsigned) * (size_t)passes * L.tiles * RADIX, st));
+  const int hblocks = (int)std::min<long long>(kNumSMs * 8, (n + 255) / 256);
+  k_histogram<<<hblocks, 256, 0, st>>>(keys_a, n, n_dev, passes, key_bits, hist);
+  GSX_LAUNCH_CHECK();
+  k_scan_histogram<<<passes, RADIX, 0, st>>>(hist);
+  GSX_LAUNCH_CHECK();
+  uint64_t *kin = keys_a, *kout = keys_b;
+  uint32_t *vin = vals_a, *vout = vals_b;
+  for (int p = 0; p < passes; ++p) {
+    const int bits = std::min(8, key_bits - 8 * p);
+    k_onesweep<<<L.tiles, RS_THREADS, 0, st>>>(kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX,
+                                               status + (size_t)p * L.tiles * RADIX, ticket + p);
+    GSX_LAUNCH_CHECK();
+    std::swap(kin, kout);
+    std::swap(vin, vout);
+  }
+  return GSX_OK;
+}
+
+int tile_ranges_impl(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
+                     cudaStream_t st) {
+  long long work = std::max<long long>(n, n_tiles + 1);
+  const int blocks = (int)std::min<long long>(kNumSMs * 16, (work + 255) / 256);
+  k_tile_ranges<<<std::max(blocks, 1), 256, 0, st>>>(sorted_keys, n, n_dev, n_tiles, ranges);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+size_t sort_workspace_bytes_impl(long long n) { return sort_layout(n).total; }
+
+}  // namespace gsx
+
+using namespace gsx;
+
+extern "C" {
+
+size_t gsx_sort_workspace_bytes(long long n) { return sort_workspace_bytes_impl(n); }
+
+int gsx_sort_pairs_u64(uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in, uint32_t *vals_out, long long n,
+                       const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, void *stream) {
+  GSX_REQUIRE_DEV(keys_in); GSX_REQUIRE_DEV(keys_out); GSX_REQUIRE_DEV(vals_in); GSX_REQUIRE_DEV(vals_out);
+  GSX_REQUIRE_DEV(workspace);
+  int in_b = 0;
+  int rc = sort_pairs_impl(keys_in, keys_out, vals_in, vals_out, n, n_dev, key_bits, workspace, workspace_bytes,
+                           (cudaStream_t)stream, &in_b);
+  if (rc != GSX_OK) return rc;
+  if (!in_b && n > 0) {   // even number of passes: result is in keys_in -> copy to the documented output
+    GSX_CUDA(cudaMemcpyAsync(keys_out, keys_in, sizeof(uint64_t) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    GSX_CUDA(cudaMemcpyAsync(vals_out, vals_in, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  }
+  return GSX_OK;
+}
+
+int gsx_tile_ranges(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
+                    void *stream) {
+  GSX_REQUIRE_DEV(ranges);
+  if (n > 0) GSX_REQUIRE_DEV(sorted_keys);
+  return tile_ranges_impl(sorted_keys, n, n_dev, n_tiles, ranges, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,185 @@
+/* gsx.h -- C ABI of the B200-native splatting hot path (libgsx.so).
+ *
+ * Drop-in boundary for the `gsplat_cuda` library of AndrewBoessen/3DGS: every entry point below replaces one
+ * free function declared in the reference's include/gsplat_cuda/cuda_forward.cuh / cuda_backward.cuh (cited per
+ * function, paths relative to /root/reference), or one of its two callers (cuda/raster.cu rasterize_image,
+ * cuda/trainer.cu backward_pass).  Plain pointers and sizes only; all pointers are DEVICE pointers unless the
+ * name says host; `stream` is a cudaStream_t passed as void*.  Every function returns 0 on success or a
+ * GSX_E_* code (the reference prints to stderr and exit(1)s instead, cuda/checks.cuh:17-38; the C++ compat
+ * shim include/gsplat_cuda/ restores that behaviour on top of these).
+ *
+ * Array layouts are the reference's: xyz[N][3], uv[N][2], quat[N][4] (w,x,y,z), scale[N][3] (log),
+ * opacity[N] (logit), band0[N][3], sh[N][n-1][3], sigma[N][6], J[N][6], conic[N][3], radius[N][4]
+ * (r_major,r_minor,sin,cos), view/proj row-major 4x4, image[H][W][3], weight[H][W], splats_per_pixel[H][W].
+ */
+#ifndef GSX_H_
+#define GSX_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSX_OK 0
+#define GSX_E_NULL 1      /* null pointer argument */
+#define GSX_E_NOTDEV 2    /* pointer is not device memory */
+#define GSX_E_ARG 3       /* bad scalar argument (l_max, sizes) */
+#define GSX_E_CUDA 4      /* CUDA runtime error (see gsx_last_error) */
+#define GSX_E_WORKSPACE 5 /* caller workspace too small */
+#define GSX_E_CAPACITY 6  /* instance capacity exceeded */
+
+#define GSX_TILE 16 /* TILE_SIZE_FWD / TILE_SIZE_BWD, cuda_forward.cuh:8, cuda_backward.cuh:8 */
+
+/* flags */
+#define GSX_SH_DSPH_CORRECT 1 /* F10: use sphericart's true [axis][k] derivative layout instead of the
+                                 reference's [k][axis] reading.  Default 0 = reference behaviour. */
+#define GSX_GRAD_OVERWRITE 2  /* gsx_backward: overwrite parameter gradients instead of accumulating */
+
+int gsx_version(void);
+const char *gsx_last_error(void);
+
+/* ---- F1..F8: cuda_forward.cuh ------------------------------------------------------------------------ */
+/* cuda_forward.cuh:48  compute_camera_space_points */
+int gsx_compute_camera_space_points(const float *xyz_w, const float *view, int N, float *xyz_c, void *stream);
+/* cuda_forward.cuh:61  project_to_screen */
+int gsx_project_to_screen(const float *xyz_c, const float *proj, int N, int width, int height, float *uv,
+                          void *stream);
+/* cuda_forward.cuh:76  cull_gaussians ; mask is bool[N], nonzero = keep */
+int gsx_cull_gaussians(const float *uv, const float *xyz_c, int N, float near_thresh, int padding, int width,
+                       int height, uint8_t *mask, void *stream);
+/* cuda_forward.cuh:38  compute_sigma */
+int gsx_compute_sigma(const float *quaternion, const float *scale, int N, float *sigma, void *stream);
+/* cuda_forward.cuh:26  compute_conic ; radius is float4[N] */
+int gsx_compute_conic(const float *xyz_c, const float *view, const float *sigma, float focal_x, float focal_y,
+                      float tan_fovx, float tan_fovy, float mh_dist, int N, float *J, float *conic, float *radius,
+                      void *stream);
+/* cuda_forward.cuh:107 precompute_spherical_harmonics ; xyz is the WORLD position (Q11); campos by value */
+int gsx_precompute_spherical_harmonics(const float *xyz_w, const float *sh, const float *band0, float campos_x,
+                                       float campos_y, float campos_z, int l_max, int N, float *rgb,
+                                       void *stream);
+/* cuda_forward.cuh:92  get_sorted_gaussian_list, phase 1 (sorted_gaussians == nullptr): returns the number of
+ * coarse candidate pairs C -- what the reference stores in `sorted_gaussian_bytes` -- and the exact instance
+ * count K.  Synchronises `stream` (the reference does too, culling.cu:404). */
+int gsx_sorted_list_size(const float *uv, const float *radius, int n_tiles_x, int n_tiles_y, int N,
+                         long long *coarse_pairs_host, long long *num_instances_host, void *stream);
+/* workspace bytes needed by gsx_get_sorted_gaussian_list for N Gaussians and up to `capacity` instances */
+size_t gsx_sorted_list_workspace_bytes(int N, long long capacity);
+/* cuda_forward.cuh:92  get_sorted_gaussian_list, phase 2.  sorted_gaussians has room for `capacity` ints
+ * (the reference caller allocates C of them); ranges has n_tiles+1 ints.  Writes K into *num_instances_dev
+ * (device int, may be null).  Order: (tile, depth, gaussian id) ascending -- the reference's order with its
+ * nondeterministic ties canonicalised.  workspace may be null: the library then uses an internal cached one. */
+int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const float *radius, int n_tiles_x,
+                                 int n_tiles_y, int N, long long capacity, int *sorted_gaussians, int *ranges,
+                                 int *num_instances_dev, void *workspace, size_t workspace_bytes, void *stream);
+/* cuda_forward.cuh:128 render_image */
+int gsx_render_image(const float *uv, const float *opacity, const float *conic, const float *rgb,
+                     float background, const int *sorted_splats, const int *splat_range_by_tile, int width,
+                     int height, int *splats_per_pixel, float *weight_per_pixel, float *image, void *stream);
+
+/* ---- F9..F15: cuda_backward.cuh ---------------------------------------------------------------------- */
+/* cuda_backward.cuh:118 render_image_backward ; outputs accumulated (+=) */
+int gsx_render_image_backward(const float *uv, const float *opacity, const float *conic, const float *rgb,
+                              float background, const int *sorted_splats, const int *splat_range_by_tile,
+                              const int *splats_per_pixel, const float *weight_per_pixel,
+                              const float *grad_image, int width, int height, int N, float *grad_rgb,
+                              float *grad_opacity, float *grad_uv, float *grad_conic, void *stream);
+/* cuda_backward.cuh:92  precompute_spherical_harmonics_backward ; sh_grad/band0_grad (=), xyz_grad (+=) */
+int gsx_precompute_spherical_harmonics_backward(const float *xyz_w, const float *band0, const float *sh,
+                                                float campos_x, float campos_y, float campos_z,
+                                                const float *rgb_grad, int l_max, int N, int flags,
+                                                float *sh_grad, float *band0_grad, float *xyz_grad,
+                                                void *stream);
+/* cuda_backward.cuh:62  compute_conic_backward ; J_grad, sigma_grad (+=) */
+int gsx_compute_conic_backward(const float *J, const float *sigma, const float *view, const float *conic,
+                               const float *conic_grad, int N, float *J_grad, float *sigma_grad, void *stream);
+/* cuda_backward.cuh:47  compute_projection_jacobian_backward ; xyz_c_grad (+=) */
+int gsx_compute_projection_jacobian_backward(const float *xyz_c, float focal_x, float focal_y, float tan_fovx,
+                                             float tan_fovy, const float *J_grad, int N, float *xyz_c_grad,
+                                             void *stream);
+/* cuda_backward.cuh:76  compute_sigma_backward ; quat_grad, scale_grad (=) */
+int gsx_compute_sigma_backward(const float *quaternion, const float *scale, const float *sigma_grad, int N,
+                               float *quat_grad, float *scale_grad, void *stream);
+/* cuda_backward.cuh:21  project_to_screen_backward ; xyz_c_grad (+=) */
+int gsx_project_to_screen_backward(const float *xyz_c, const float *proj, const float *uv_grad, int N, int width,
+                                   int height, float *xyz_c_grad, void *stream);
+/* cuda_backward.cuh:34  compute_camera_space_points_backward ; xyz_w_grad (+=) ; xyz_w unused */
+int gsx_compute_camera_space_points_backward(const float *xyz_w, const float *view, const float *xyz_c_grad,
+                                             int N, float *xyz_w_grad, void *stream);
+
+/* ---- standalone sort primitives (hand-written onesweep) ------------------------------------------------- */
+size_t gsx_sort_workspace_bytes(long long n);
+/* Sorts n (key,value) pairs ascending on key bits [0, key_bits); stable.  Result is left in keys_out/vals_out
+ * (keys_in/vals_in are clobbered).  n_dev, when non-null, is a device int holding the live count (<= n). */
+int gsx_sort_pairs_u64(uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in, uint32_t *vals_out, long long n,
+                       const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, void *stream);
+/* ranges[t] = first i with (keys[i] >> 32) >= t, ranges[n_tiles] = n.  n_dev as above. */
+int gsx_tile_ranges(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
+                    void *stream);
+
+/* ---- view-level fused path: replaces rasterize_image (cuda/raster.cu:12-136) and backward_pass
+ *      (cuda/trainer.cu:926-1015, minus fused_loss) without compaction copies or host round trips.
+ *      Everything is indexed by GLOBAL Gaussian id so a batch of views (and GPUs) can sum gradients. ------ */
+typedef struct gsx_view {
+  float view[16];        /* row-major world->camera, trainer.cu:1322-1332 */
+  float proj[16];        /* row-major projection, trainer.cu:1310-1320 */
+  float campos[3];       /* Image::CamPos() */
+  float focal_x, focal_y;   /* camera.params[0], params[1] (Q16) */
+  float tan_fovx, tan_fovy; /* W/(2 fx), H/(2 fy), raster.cu:92-93 */
+  int width, height;
+  float near_thresh;     /* config near_thresh */
+  int cull_padding;      /* config cull_mask_padding */
+  float mh_dist;         /* config mh_dist */
+  float background;      /* scalar grey background (Q4) */
+  int l_max;             /* 0..3 */
+  int flags;             /* GSX_SH_DSPH_CORRECT | GSX_GRAD_OVERWRITE */
+} gsx_view_t;
+
+typedef struct gsx_params {   /* GaussianParameters, cuda_data.cuh:11-24 */
+  const float *xyz, *scale, *quaternion, *opacity, *band0, *sh;
+  int sh_stride;              /* floats per Gaussian in sh: 3*((l_alloc+1)^2-1); the trainer always allocates 45 */
+} gsx_params_t;
+
+typedef struct gsx_grads {    /* GaussianGradients, cuda_data.cuh:26-46 (parameter gradients only) */
+  float *xyz, *scale, *quaternion, *opacity, *band0, *sh;
+  float *uv;                  /* optional [N][2]: screen-space gradient as F9 leaves it (densification statistic) */
+} gsx_grads_t;
+
+typedef struct gsx_ctx gsx_ctx_t;   /* persistent per-device workspace (replaces ForwardPassData) */
+
+typedef struct gsx_stats {
+  int N, P;                   /* Gaussians in, Gaussians passing the cull */
+  long long K;                /* tile instances */
+  long long capacity;         /* current instance capacity */
+} gsx_stats_t;
+
+int gsx_ctx_create(gsx_ctx_t **ctx, int max_gaussians, int max_width, int max_height, long long instance_capacity);
+int gsx_ctx_destroy(gsx_ctx_t *ctx);
+/* Forward for one view.  Fully asynchronous on `stream`; if K exceeds the context's instance capacity the
+ * overflow is detected at gsx_ctx_stats()/gsx_forward_sync and the caller re-runs after gsx_ctx_reserve. */
+int gsx_forward(gsx_ctx_t *ctx, const gsx_view_t *view_host, const gsx_params_t *params, int N, void *stream);
+/* Backward for the view last rendered by gsx_forward on this ctx.  grad_image[H][W][3] device. */
+int gsx_backward(gsx_ctx_t *ctx, const gsx_view_t *view_host, const gsx_params_t *params, int N,
+                 const float *grad_image, const gsx_grads_t *grads, void *stream);
+/* Synchronises and reports P, K; returns GSX_E_CAPACITY if the last forward overflowed. */
+int gsx_ctx_stats(gsx_ctx_t *ctx, gsx_stats_t *out_host, void *stream);
+int gsx_ctx_reserve(gsx_ctx_t *ctx, long long instance_capacity);
+/* Device views of the last forward's saved state (ForwardPassData, cuda_data.cuh:70-86), global-index. */
+typedef struct gsx_state {
+  const float *image, *weight_per_pixel; const int *splats_per_pixel;
+  const float *uv, *xyz_c, *conic_opacity /*[N][4] a,b,c,sigmoid(opacity)*/, *rgb, *radius;
+  const uint8_t *mask; const int *tiles_touched; const int *sorted_gaussians, *ranges;
+  const uint64_t *sorted_keys; const int *num_instances /* device int */;
+} gsx_state_t;
+int gsx_ctx_state(gsx_ctx_t *ctx, gsx_state_t *out_host);
+
+/* Host-buffer entry point (what bench.py's e2e leg and a host-side caller use): copies the view + grad_image
+ * from (pinned) host memory, runs forward+backward, copies the image back.  params/grads stay on the device as
+ * in the reference trainer (CudaDataManager). */
+int gsx_render_view_host(gsx_ctx_t *ctx, const gsx_view_t *view_host, const gsx_params_t *params, int N,
+                         const float *grad_image_host, float *image_host, const gsx_grads_t *grads, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSX_H_ */
