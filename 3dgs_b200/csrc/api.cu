@@ -1,0 +1,232 @@
+// api.cu -- host side of libgsx.so: error plumbing, the persistent per-device context that replaces the
+// reference's ForwardPassData (include/gsplat_cuda/cuda_data.cuh:70-86, re-allocated every view there), and the
+// view-level entry points that replace rasterize_image (cuda/raster.cu:12-136) and backward_pass
+// (cuda/trainer.cu:926-1015).  No host<->device round trip happens inside gsx_forward/gsx_backward: the instance
+// count K stays on the device and every kernel downstream of the scan reads it from there.
+#include <algorithm>
+#include <stdarg.h>
+
+#include "gsx_common.cuh"
+
+namespace gsx {
+
+static thread_local char g_err[512] = "";
+void set_error(const char *fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_device_ptr(const void *p, const char *name) {
+  if (p == nullptr) { set_error("pointer %s is null", name); return GSX_E_NULL; }
+  cudaPointerAttributes a;
+  cudaError_t e = cudaPointerGetAttributes(&a, p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    set_error("cudaPointerGetAttributes(%s) -> %s", name, cudaGetErrorString(e));
+    return GSX_E_NOTDEV;
+  }
+  if (a.type != cudaMemoryTypeDevice && a.type != cudaMemoryTypeManaged) {
+    set_error("pointer %s is not a device pointer", name);
+    return GSX_E_NOTDEV;
+  }
+  return GSX_OK;
+}
+
+// from binning.cu / composite.cu / preprocess.cu
+BinLayout bin_layout(int N, long long capacity);
+int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius, int ntx,
+                  int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
+                  const uint64_t **sorted_keys, const uint32_t **sorted_vals, cudaStream_t st);
+int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
+                         int W, int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st);
+int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
+                         int W, int H, float bg, const int *spp, const float *wpp, const float *grad_image,
+                         float *packed_grads, cudaStream_t st);
+int preprocess_fwd_launch(const gsx_view_t &v, const gsx_params_t &p, int N, float4 *r0, float4 *r1, float4 *r2,
+                          float4 *radius, float *depth, uint8_t *mask, int *touched, cudaStream_t st);
+int preprocess_bwd_launch(const gsx_view_t &v, const gsx_params_t &p, int N, const float4 *r1, const uint8_t *mask,
+                          float4 *gacc, const gsx_grads_t &g, cudaStream_t st);
+
+}  // namespace gsx
+
+using namespace gsx;
+
+struct gsx_ctx {
+  int max_n = 0, max_w = 0, max_h = 0;
+  long long capacity = 0;
+  // per-Gaussian state of the last forward
+  float4 *r0 = nullptr, *r1 = nullptr, *r2 = nullptr, *radius = nullptr;
+  float *depth = nullptr;
+  uint8_t *mask = nullptr;
+  float *gacc = nullptr;            // [N][12]
+  // binning workspace (depends on capacity)
+  char *bin_ws = nullptr;
+  BinLayout L{};
+  int *ranges = nullptr;
+  // per-pixel state
+  float *image = nullptr, *wpp = nullptr, *grad_image = nullptr;
+  int *spp = nullptr;
+  // last forward
+  const uint64_t *sorted_keys = nullptr;
+  const uint32_t *sorted_vals = nullptr;
+  int last_n = 0, last_w = 0, last_h = 0;
+  int *h_stats = nullptr;           // pinned: [0] = K, [1] = P
+  int *d_P = nullptr;
+};
+
+namespace gsx {
+__global__ void k_count_mask(const uint8_t *__restrict__ mask, int N, int *__restrict__ out) {
+  int c = 0;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) c += mask[i] ? 1 : 0;
+  for (int off = 16; off > 0; off >>= 1) c += __shfl_down_sync(0xffffffffu, c, off);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+static int alloc_bin(gsx_ctx *c, long long capacity) {
+  if (c->bin_ws) { cudaFree(c->bin_ws); c->bin_ws = nullptr; }
+  c->capacity = std::max<long long>(capacity, 1024);
+  c->L = bin_layout(c->max_n, c->capacity);
+  GSX_CUDA(cudaMalloc(&c->bin_ws, c->L.bytes));
+  return GSX_OK;
+}
+}  // namespace gsx
+
+extern "C" {
+
+int gsx_version(void) { return 1; }
+const char *gsx_last_error(void) { return g_err; }
+
+int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_height, long long instance_capacity) {
+  if (!out || max_gaussians <= 0 || max_width <= 0 || max_height <= 0) { set_error("bad ctx arguments"); return GSX_E_ARG; }
+  gsx_ctx *c = new gsx_ctx();
+  c->max_n = max_gaussians; c->max_w = max_width; c->max_h = max_height;
+  const size_t n = (size_t)max_gaussians, px = (size_t)max_width * max_height;
+  const int T = ((max_width + 15) / 16) * ((max_height + 15) / 16);
+  GSX_CUDA(cudaMalloc(&c->r0, n * sizeof(float4)));
+  GSX_CUDA(cudaMalloc(&c->r1, n * sizeof(float4)));
+  GSX_CUDA(cudaMalloc(&c->r2, n * sizeof(float4)));
+  GSX_CUDA(cudaMalloc(&c->radius, n * sizeof(float4)));
+  GSX_CUDA(cudaMalloc(&c->depth, n * sizeof(float)));
+  GSX_CUDA(cudaMalloc(&c->mask, n));
+  GSX_CUDA(cudaMalloc(&c->gacc, n * 12 * sizeof(float)));
+  GSX_CUDA(cudaMemset(c->gacc, 0, n * 12 * sizeof(float)));
+  GSX_CUDA(cudaMemset(c->mask, 0, n));
+  GSX_CUDA(cudaMalloc(&c->ranges, sizeof(int) * (size_t)(T + 1)));
+  GSX_CUDA(cudaMalloc(&c->image, px * 3 * sizeof(float)));
+  GSX_CUDA(cudaMalloc(&c->wpp, px * sizeof(float)));
+  GSX_CUDA(cudaMalloc(&c->spp, px * sizeof(int)));
+  GSX_CUDA(cudaMalloc(&c->grad_image, px * 3 * sizeof(float)));
+  GSX_CUDA(cudaMalloc(&c->d_P, sizeof(int)));
+  GSX_CUDA(cudaMallocHost(&c->h_stats, 4 * sizeof(int)));
+  if (instance_capacity <= 0) instance_capacity = 8LL * max_gaussians;
+  int rc = alloc_bin(c, instance_capacity);
+  if (rc != GSX_OK) return rc;
+  *out = c;
+  return GSX_OK;
+}
+
+int gsx_ctx_destroy(gsx_ctx_t *c) {
+  if (!c) return GSX_OK;
+  cudaFree(c->r0); cudaFree(c->r1); cudaFree(c->r2); cudaFree(c->radius); cudaFree(c->depth); cudaFree(c->mask);
+  cudaFree(c->gacc); cudaFree(c->bin_ws); cudaFree(c->ranges); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
+  cudaFree(c->grad_image); cudaFree(c->d_P); cudaFreeHost(c->h_stats);
+  delete c;
+  return GSX_OK;
+}
+
+int gsx_ctx_reserve(gsx_ctx_t *c, long long instance_capacity) {
+  if (!c) return GSX_E_NULL;
+  if (instance_capacity <= c->capacity) return GSX_OK;
+  if (instance_capacity >= (1LL << 30)) { set_error("instance capacity %lld >= 2^30", instance_capacity); return GSX_E_ARG; }
+  GSX_CUDA(cudaDeviceSynchronize());
+  return alloc_bin(c, instance_capacity);
+}
+
+int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N, void *stream) {
+  if (!c || !v || !p) { set_error("null ctx/view/params"); return GSX_E_NULL; }
+  if (N < 0 || N > c->max_n || v->width <= 0 || v->height <= 0 || v->width > c->max_w || v->height > c->max_h ||
+      (size_t)v->width * v->height > (size_t)c->max_w * c->max_h) {
+    set_error("view %dx%d / N %d exceeds the context (%d, %dx%d)", v->width, v->height, N, c->max_n, c->max_w, c->max_h);
+    return GSX_E_ARG;
+  }
+  if (v->l_max < 0 || v->l_max > 3) { set_error("l_max %d out of range 0..3", v->l_max); return GSX_E_ARG; }
+  const int shf = ((v->l_max + 1) * (v->l_max + 1) - 1) * 3;
+  if (v->l_max > 0 && p->sh_stride < shf) { set_error("sh_stride %d < %d", p->sh_stride, shf); return GSX_E_ARG; }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int ntx = (v->width + 15) / 16, nty = (v->height + 15) / 16;
+  c->last_n = N; c->last_w = v->width; c->last_h = v->height;
+  int *touched = (int *)(c->bin_ws + c->L.touched);
+  int rc = preprocess_fwd_launch(*v, *p, N, c->r0, c->r1, c->r2, c->radius, c->depth, c->mask, touched, st);
+  if (rc != GSX_OK) return rc;
+  rc = bin_sort_impl((const float *)c->r0, 4, c->depth, 1, c->radius, ntx, nty, N, c->capacity, c->bin_ws, c->L, c->ranges,
+                     &c->sorted_keys, &c->sorted_vals, st);
+  if (rc != GSX_OK) return rc;
+  return composite_fwd_packed(c->r0, c->r1, c->r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
+                              v->background, c->spp, c->wpp, c->image, st);
+}
+
+int gsx_backward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N, const float *grad_image,
+                 const gsx_grads_t *g, void *stream) {
+  if (!c || !v || !p || !g || !grad_image) { set_error("null argument"); return GSX_E_NULL; }
+  if (N != c->last_n || v->width != c->last_w || v->height != c->last_h) {
+    set_error("gsx_backward does not match the last gsx_forward on this context");
+    return GSX_E_ARG;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = composite_bwd_packed(c->r0, c->r1, c->r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
+                                v->background, c->spp, c->wpp, grad_image, c->gacc, st);
+  if (rc != GSX_OK) return rc;
+  return preprocess_bwd_launch(*v, *p, N, c->r1, c->mask, (float4 *)c->gacc, *g, st);
+}
+
+int gsx_ctx_stats(gsx_ctx_t *c, gsx_stats_t *out, void *stream) {
+  if (!c || !out) return GSX_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  GSX_CUDA(cudaMemsetAsync(c->d_P, 0, sizeof(int), st));
+  if (c->last_n > 0) {
+    k_count_mask<<<kNumSMs * 4, 256, 0, st>>>(c->mask, c->last_n, c->d_P);
+    GSX_LAUNCH_CHECK();
+  }
+  GSX_CUDA(cudaMemcpyAsync(&c->h_stats[0], c->bin_ws + c->L.total, sizeof(int), cudaMemcpyDeviceToHost, st));
+  GSX_CUDA(cudaMemcpyAsync(&c->h_stats[1], c->d_P, sizeof(int), cudaMemcpyDeviceToHost, st));
+  GSX_CUDA(cudaStreamSynchronize(st));
+  out->N = c->last_n; out->P = c->h_stats[1]; out->K = c->h_stats[0]; out->capacity = c->capacity;
+  if (out->K > c->capacity) {
+    set_error("instance capacity exceeded: K=%lld > %lld (gsx_ctx_reserve and re-run)", out->K, c->capacity);
+    return GSX_E_CAPACITY;
+  }
+  return GSX_OK;
+}
+
+int gsx_ctx_state(gsx_ctx_t *c, gsx_state_t *o) {
+  if (!c || !o) return GSX_E_NULL;
+  o->image = c->image; o->weight_per_pixel = c->wpp; o->splats_per_pixel = c->spp;
+  o->rec0 = (const float *)c->r0; o->rec1 = (const float *)c->r1; o->rec2 = (const float *)c->r2;
+  o->radius = (const float *)c->radius; o->depth = c->depth; o->mask = c->mask;
+  o->tiles_touched = (const int *)(c->bin_ws + c->L.touched);
+  o->sorted_gaussians = (const int *)c->sorted_vals; o->sorted_keys = c->sorted_keys;
+  o->ranges = c->ranges; o->num_instances = (const int *)(c->bin_ws + c->L.total);
+  o->packed_grads = c->gacc;
+  return GSX_OK;
+}
+
+int gsx_render_view_host(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N,
+                         const float *grad_image_host, float *image_host, const gsx_grads_t *g, void *stream) {
+  if (!c || !v || !p) { set_error("null argument"); return GSX_E_NULL; }
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t bytes = (size_t)v->width * v->height * 3 * sizeof(float);
+  if (grad_image_host) GSX_CUDA(cudaMemcpyAsync(c->grad_image, grad_image_host, bytes, cudaMemcpyHostToDevice, st));
+  int rc = gsx_forward(c, v, p, N, stream);
+  if (rc != GSX_OK) return rc;
+  if (image_host) GSX_CUDA(cudaMemcpyAsync(image_host, c->image, bytes, cudaMemcpyDeviceToHost, st));
+  if (grad_image_host && g) {
+    rc = gsx_backward(c, v, p, N, c->grad_image, g, stream);
+    if (rc != GSX_OK) return rc;
+  }
+  GSX_CUDA(cudaStreamSynchronize(st));
+  return GSX_OK;
+}
+
+}  // extern "C"

@@ -37,12 +37,13 @@ __device__ __forceinline__ int count_tiles(float u, float v, float4 r, int ntx, 
   return c;
 }
 
-__global__ void __launch_bounds__(kBlock) k_count(const float *__restrict__ uv, const float4 *__restrict__ radius,
+__global__ void __launch_bounds__(kBlock) k_count(const float *__restrict__ uv, int uv_stride,
+                                                  const float4 *__restrict__ radius,
                                                   const uint8_t *__restrict__ mask, int ntx, int nty, int N,
                                                   int *__restrict__ touched, unsigned long long *__restrict__ coarse_total) {
   const int i = blockIdx.x * kBlock + threadIdx.x;
   int coarse = 0, c = 0;
-  if (i < N && (!mask || mask[i])) c = count_tiles(uv[2 * i], uv[2 * i + 1], radius[i], ntx, nty, &coarse);
+  if (i < N && (!mask || mask[i])) c = count_tiles(uv[(size_t)i * uv_stride], uv[(size_t)i * uv_stride + 1], radius[i], ntx, nty, &coarse);
   if (i < N) touched[i] = c;
   if (coarse_total) {
     unsigned long long s = (unsigned long long)coarse;
@@ -51,7 +52,8 @@ __global__ void __launch_bounds__(kBlock) k_count(const float *__restrict__ uv, 
   }
 }
 
-__global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, const float *__restrict__ depth,
+__global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, int uv_stride,
+                                                 const float *__restrict__ depth,
                                                  int depth_stride, const float4 *__restrict__ radius,
                                                  const int *__restrict__ touched, const int *__restrict__ offsets,
                                                  int ntx, int nty, int N, long long capacity,
@@ -62,7 +64,7 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, c
   if (cnt == 0) return;
   long long o = offsets[i];
   if (o + cnt > capacity) return;   // overflow: detected by the host through the total
-  const float u = uv[2 * i], v = uv[2 * i + 1];
+  const float u = uv[(size_t)i * uv_stride], v = uv[(size_t)i * uv_stride + 1];
   const float4 r = radius[i];
   const uint64_t zb = float_sort_bits(depth[(size_t)i * depth_stride]);
   const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
@@ -181,9 +183,6 @@ int exclusive_scan_i32(const int *in, int N, int *out, int *block_sums, int *tot
 size_t scan_block_sums_count(int N) { return (size_t)std::max(1, ceil_div(N, SCAN_TILE)); }
 
 // Workspace carve-up shared by the per-function F7 entry point and the view-level context.
-struct BinLayout {
-  size_t touched, offsets, block_sums, total, keys_a, keys_b, vals_a, vals_b, sort_ws, sort_ws_bytes, bytes;
-};
 BinLayout bin_layout(int N, long long capacity) {
   BinLayout L;
   size_t off = 0;
@@ -204,7 +203,7 @@ BinLayout bin_layout(int N, long long capacity) {
 
 // scan -> emit -> sort -> ranges, given touched[] already filled.  Leaves sorted keys / ids in
 // (*sorted_keys, *sorted_vals) inside the workspace; K in total_dev[0].
-int bin_sort_impl(const float *uv, const float *depth, int depth_stride, const float4 *radius, int ntx, int nty, int N,
+int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius, int ntx, int nty, int N,
                   long long capacity, char *ws, const BinLayout &L, int *ranges, const uint64_t **sorted_keys,
                   const uint32_t **sorted_vals, cudaStream_t st) {
   int *touched = (int *)(ws + L.touched), *offsets = (int *)(ws + L.offsets);
@@ -214,7 +213,7 @@ int bin_sort_impl(const float *uv, const float *depth, int depth_stride, const f
   int rc = exclusive_scan_i32(touched, N, offsets, block_sums, total, st);
   if (rc != GSX_OK) return rc;
   if (N > 0) {
-    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, depth, depth_stride, radius, touched, offsets, ntx, nty, N,
+    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, depth, depth_stride, radius, touched, offsets, ntx, nty, N,
                                                    capacity, ka, va);
     GSX_LAUNCH_CHECK();
   }
@@ -227,10 +226,10 @@ int bin_sort_impl(const float *uv, const float *depth, int depth_stride, const f
   return tile_ranges_impl(*sorted_keys, capacity, total, ntx * nty, ranges, st);
 }
 
-int count_tiles_launch(const float *uv, const float4 *radius, const uint8_t *mask, int ntx, int nty, int N, int *touched,
+int count_tiles_launch(const float *uv, int uv_stride, const float4 *radius, const uint8_t *mask, int ntx, int nty, int N, int *touched,
                        unsigned long long *coarse_total, cudaStream_t st) {
   if (N <= 0) return GSX_OK;
-  k_count<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, radius, mask, ntx, nty, N, touched, coarse_total);
+  k_count<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, mask, ntx, nty, N, touched, coarse_total);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -276,7 +275,7 @@ int gsx_sorted_list_size(const float *uv, const float *radius, int n_tiles_x, in
   if (rc != GSX_OK) return rc;
   unsigned long long *coarse = (unsigned long long *)(ws + L.bytes);
   GSX_CUDA(cudaMemsetAsync(coarse, 0, sizeof(unsigned long long), st));
-  rc = count_tiles_launch(uv, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched), coarse, st);
+  rc = count_tiles_launch(uv, 2, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched), coarse, st);
   if (rc != GSX_OK) return rc;
   rc = exclusive_scan_i32((int *)(ws + L.touched), N, (int *)(ws + L.offsets), (int *)(ws + L.block_sums),
                           (int *)(ws + L.total), st);
@@ -316,12 +315,12 @@ int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const floa
     set_error("sorted-list workspace %zu < %zu", workspace_bytes, L.bytes);
     return GSX_E_WORKSPACE;
   }
-  int rc = count_tiles_launch(uv, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched),
+  int rc = count_tiles_launch(uv, 2, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched),
                               nullptr, st);
   if (rc != GSX_OK) return rc;
   const uint64_t *sk;
   const uint32_t *sv;
-  rc = bin_sort_impl(uv, xyz_c + 2, 3, (const float4 *)radius, n_tiles_x, n_tiles_y, N, capacity, ws, L, ranges, &sk,
+  rc = bin_sort_impl(uv, 2, xyz_c + 2, 3, (const float4 *)radius, n_tiles_x, n_tiles_y, N, capacity, ws, L, ranges, &sk,
                      &sv, st);
   if (rc != GSX_OK) return rc;
   rc = copy_ids_launch(sv, sorted_gaussians, capacity, (const int *)(ws + L.total), st);

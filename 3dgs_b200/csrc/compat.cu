@@ -1,0 +1,112 @@
+// compat.cu -- the 15 reference-named C++ entry points (include/gsplat_cuda/cuda_forward.cuh, cuda_backward.cuh)
+// on top of the gsx C ABI, with the reference's error convention: any failure prints and exit(EXIT_FAILURE)
+// (reference cuda/checks.cuh:17-38).
+#include <stdio.h>
+#include <stdlib.h>
+
+#include "../../include/gsplat_cuda/cuda_backward.cuh"
+#include "../../include/gsplat_cuda/cuda_forward.cuh"
+#include "../../include/gsx.h"
+
+static void gsx_or_die(int rc, const char *fn) {
+  if (rc != GSX_OK) {
+    fprintf(stderr, "Assertion failed in %s: %s (gsx status %d)\n", fn, gsx_last_error(), rc);
+    exit(EXIT_FAILURE);
+  }
+}
+#define DIE_UNLESS(call) gsx_or_die((call), __func__)
+
+void compute_conic(float *const xyz, const float *view, float *const sigma, const float focal_x, const float focal_y,
+                   const float tan_fovx, const float tan_fovy, const float mh_dist, const int N, float *J, float *conic,
+                   float4 *radius, cudaStream_t stream) {
+  DIE_UNLESS(gsx_compute_conic(xyz, view, sigma, focal_x, focal_y, tan_fovx, tan_fovy, mh_dist, N, J, conic,
+                               reinterpret_cast<float *>(radius), stream));
+}
+void compute_sigma(float *const quaternion, float *const scale, const int N, float *sigma, cudaStream_t stream) {
+  DIE_UNLESS(gsx_compute_sigma(quaternion, scale, N, sigma, stream));
+}
+void compute_camera_space_points(float *const xyz_w, const float *view, const int N, float *xyz_c, cudaStream_t stream) {
+  DIE_UNLESS(gsx_compute_camera_space_points(xyz_w, view, N, xyz_c, stream));
+}
+void project_to_screen(float *const xyz, const float *proj, const int N, const int width, const int height, float *uv,
+                       cudaStream_t stream) {
+  DIE_UNLESS(gsx_project_to_screen(xyz, proj, N, width, height, uv, stream));
+}
+void cull_gaussians(float *const uv, float *const xyz, const int N, const float near_thresh, const int padding,
+                    const int width, const int height, bool *mask, cudaStream_t stream) {
+  static_assert(sizeof(bool) == 1, "bool mask is one byte");
+  DIE_UNLESS(gsx_cull_gaussians(uv, xyz, N, near_thresh, padding, width, height, reinterpret_cast<uint8_t *>(mask), stream));
+}
+// Two-phase protocol of the reference (cuda/culling.cu:398-407): phase 1 reports the number of coarse candidate
+// pairs (an element count despite the parameter's name); phase 2 receives a buffer of that many ints.
+void get_sorted_gaussian_list(const float *uv, const float *xyz, const float4 *radius, const int n_tiles_x,
+                              const int n_tiles_y, const int N, size_t &sorted_gaussian_bytes, int *sorted_gaussians,
+                              int *splat_start_end_idx_by_tile_idx, cudaStream_t stream) {
+  if (sorted_gaussians == nullptr) {
+    long long coarse = 0, k = 0;
+    DIE_UNLESS(gsx_sorted_list_size(uv, reinterpret_cast<const float *>(radius), n_tiles_x, n_tiles_y, N, &coarse, &k,
+                                    stream));
+    sorted_gaussian_bytes = (size_t)coarse;
+    return;
+  }
+  DIE_UNLESS(gsx_get_sorted_gaussian_list(uv, xyz, reinterpret_cast<const float *>(radius), n_tiles_x, n_tiles_y, N,
+                                          (long long)sorted_gaussian_bytes, sorted_gaussians,
+                                          splat_start_end_idx_by_tile_idx, nullptr, nullptr, 0, stream));
+}
+void precompute_spherical_harmonics(const float *xyz, const float *sh_coefficients, const float *sh_coeffs_band_0,
+                                    const float3 campos, const int l_max, const int N, float *rgb, cudaStream_t stream) {
+  DIE_UNLESS(gsx_precompute_spherical_harmonics(xyz, sh_coefficients, sh_coeffs_band_0, campos.x, campos.y, campos.z,
+                                                l_max, N, rgb, stream));
+}
+void render_image(const float *uv, const float *opacity, const float *conic, const float *rgb,
+                  const float background_opacity, const int *sorted_splats, const int *splat_range_by_tile,
+                  const int image_width, const int image_height, int *splats_per_pixel, float *weight_per_pixel,
+                  float *image, cudaStream_t stream) {
+  DIE_UNLESS(gsx_render_image(uv, opacity, conic, rgb, background_opacity, sorted_splats, splat_range_by_tile,
+                              image_width, image_height, splats_per_pixel, weight_per_pixel, image, stream));
+}
+
+void project_to_screen_backward(const float *const xyz_c, const float *const proj, const float *const uv_grad_out,
+                                const int N, const int width, const int height, float *xyz_c_grad_in,
+                                cudaStream_t stream) {
+  DIE_UNLESS(gsx_project_to_screen_backward(xyz_c, proj, uv_grad_out, N, width, height, xyz_c_grad_in, stream));
+}
+void compute_camera_space_points_backward(const float *const xyz_w, const float *const view,
+                                          const float *const xyz_c_grad_out, const int N, float *xyz_w_grad_in,
+                                          cudaStream_t stream) {
+  DIE_UNLESS(gsx_compute_camera_space_points_backward(xyz_w, view, xyz_c_grad_out, N, xyz_w_grad_in, stream));
+}
+void compute_projection_jacobian_backward(const float *const xyz_c, const float focal_x, const float focal_y,
+                                          const float tan_fovx, const float tan_fovy, const float *const J_grad_out,
+                                          const int N, float *xyz_c_grad_in, cudaStream_t stream) {
+  DIE_UNLESS(gsx_compute_projection_jacobian_backward(xyz_c, focal_x, focal_y, tan_fovx, tan_fovy, J_grad_out, N,
+                                                      xyz_c_grad_in, stream));
+}
+void compute_conic_backward(const float *const J, const float *const sigma, const float *const view,
+                            const float *const conic, const float *const conic_grad_out, const int N, float *J_grad_in,
+                            float *sigma_grad_in, cudaStream_t stream) {
+  DIE_UNLESS(gsx_compute_conic_backward(J, sigma, view, conic, conic_grad_out, N, J_grad_in, sigma_grad_in, stream));
+}
+void compute_sigma_backward(const float *const quaternion, const float *const scale, const float *const sigma_grad_out,
+                            const int N, float *quaternion_grad_in, float *scale_grad_in, cudaStream_t stream) {
+  DIE_UNLESS(gsx_compute_sigma_backward(quaternion, scale, sigma_grad_out, N, quaternion_grad_in, scale_grad_in, stream));
+}
+void precompute_spherical_harmonics_backward(const float *const xyz_c, const float *const rgb_vals,
+                                             const float *const sh_coeffs, const float3 campos,
+                                             const float *const rgb_grad_out, const int l_max, const int N,
+                                             float *sh_grad_in, float *sh_grad_band_0_in, float *xyz_c_grad_in,
+                                             cudaStream_t stream) {
+  DIE_UNLESS(gsx_precompute_spherical_harmonics_backward(xyz_c, rgb_vals, sh_coeffs, campos.x, campos.y, campos.z,
+                                                         rgb_grad_out, l_max, N, 0, sh_grad_in, sh_grad_band_0_in,
+                                                         xyz_c_grad_in, stream));
+}
+void render_image_backward(const float *const uvs, const float *const opacity, const float *const conic,
+                           const float *const rgb, const float background_opacity, const int *const sorted_splats,
+                           const int *const splat_range_by_tile, const int *const num_splats_per_pixel,
+                           const float *const final_weight_per_pixel, const float *const grad_image,
+                           const int image_width, const int image_height, float *grad_rgb, float *grad_opacity,
+                           float *grad_uv, float *grad_conic, cudaStream_t stream) {
+  DIE_UNLESS(gsx_render_image_backward(uvs, opacity, conic, rgb, background_opacity, sorted_splats, splat_range_by_tile,
+                                       num_splats_per_pixel, final_weight_per_pixel, grad_image, image_width,
+                                       image_height, 0, grad_rgb, grad_opacity, grad_uv, grad_conic, stream));
+}

@@ -37,4 +37,9 @@ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; 
 
 constexpr int kNumSMs = 148;  // B200
 
+// workspace carve-up of the binning stage (binning.cu), shared with the context in api.cu
+struct BinLayout {
+  size_t touched, offsets, block_sums, total, keys_a, keys_b, vals_a, vals_b, sort_ws, sort_ws_bytes, bytes;
+};
+
 }  // namespace gsx

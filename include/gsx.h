@@ -166,10 +166,19 @@ int gsx_ctx_stats(gsx_ctx_t *ctx, gsx_stats_t *out_host, void *stream);
 int gsx_ctx_reserve(gsx_ctx_t *ctx, long long instance_capacity);
 /* Device views of the last forward's saved state (ForwardPassData, cuda_data.cuh:70-86), global-index. */
 typedef struct gsx_state {
-  const float *image, *weight_per_pixel; const int *splats_per_pixel;
-  const float *uv, *xyz_c, *conic_opacity /*[N][4] a,b,c,sigmoid(opacity)*/, *rgb, *radius;
-  const uint8_t *mask; const int *tiles_touched; const int *sorted_gaussians, *ranges;
-  const uint64_t *sorted_keys; const int *num_instances /* device int */;
+  const float *image, *weight_per_pixel; const int *splats_per_pixel;   /* [H][W][3], [H][W], [H][W] */
+  const float *rec0;    /* [N][4] u, v, ex, ey  (ex,ey: alpha>=1/255 half-extents used for warp culling) */
+  const float *rec1;    /* [N][4] conic a, b, c, sigmoid(opacity) */
+  const float *rec2;    /* [N][4] r, g, b, opa*(1-opa) */
+  const float *radius;  /* [N][4] r_major, r_minor, sin, cos */
+  const float *depth;   /* [N] camera-space z */
+  const uint8_t *mask;  /* [N] cull mask, 1 = keep */
+  const int *tiles_touched;            /* [N] exact instance count per Gaussian */
+  const int *sorted_gaussians;         /* [K] global Gaussian ids, (tile, depth, id) order */
+  const uint64_t *sorted_keys;         /* [K] tile<<32 | depth bits */
+  const int *ranges;                   /* [T+1] */
+  const int *num_instances;            /* device int: K */
+  const float *packed_grads;           /* [N][12] compositing gradients (zero between views) */
 } gsx_state_t;
 int gsx_ctx_state(gsx_ctx_t *ctx, gsx_state_t *out_host);
 
