@@ -1,0 +1,363 @@
+"""Host-side mirror of the reference's operator interface for the splatting hot path.
+
+* per-function wrappers named after the reference's `gsplat_cuda` functions
+  (include/gsplat_cuda/cuda_forward.cuh, cuda_backward.cuh), taking CUDA torch tensors in the reference's layouts;
+* `Rasterizer`: the view-level path -- what `rasterize_image` (cuda/raster.cu:12) and `TrainerImpl::backward_pass`
+  (cuda/trainer.cu:926) do in the reference -- on a persistent context, with global-index gradients.
+
+Everything goes through the C ABI of libgsx.so; torch only owns memory and streams.
+"""
+import ctypes as C
+
+import torch
+
+from . import _ffi
+from ._ffi import GsxGrads, GsxParams, GsxState, GsxStats, GsxView, check, f32, lib
+
+
+def _ptr(t):
+    if t is None:
+        return C.c_void_p(0)
+    assert t.is_cuda and t.is_contiguous(), "expected a contiguous CUDA tensor"
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _chk_f32(*ts):
+    for t in ts:
+        assert t is None or t.dtype == torch.float32
+
+
+# ------------------------------------------------------------------------------------------------ forward F1..F8
+def compute_camera_space_points(xyz_w, view, xyz_c=None):
+    n = xyz_w.shape[0]
+    xyz_c = torch.empty((n, 3), device=xyz_w.device, dtype=torch.float32) if xyz_c is None else xyz_c
+    check(lib().gsx_compute_camera_space_points(_ptr(xyz_w), _ptr(view), n, _ptr(xyz_c), _stream()))
+    return xyz_c
+
+
+def project_to_screen(xyz_c, proj, width, height, uv=None):
+    n = xyz_c.shape[0]
+    uv = torch.empty((n, 2), device=xyz_c.device, dtype=torch.float32) if uv is None else uv
+    check(lib().gsx_project_to_screen(_ptr(xyz_c), _ptr(proj), n, int(width), int(height), _ptr(uv), _stream()))
+    return uv
+
+
+def cull_gaussians(uv, xyz_c, near_thresh, padding, width, height, mask=None):
+    n = uv.shape[0]
+    mask = torch.empty(n, device=uv.device, dtype=torch.uint8) if mask is None else mask
+    check(lib().gsx_cull_gaussians(_ptr(uv), _ptr(xyz_c), n, f32(near_thresh), int(padding), int(width), int(height),
+                                   _ptr(mask), _stream()))
+    return mask
+
+
+def compute_sigma(quaternion, scale, sigma=None):
+    n = quaternion.shape[0]
+    sigma = torch.empty((n, 6), device=quaternion.device, dtype=torch.float32) if sigma is None else sigma
+    check(lib().gsx_compute_sigma(_ptr(quaternion), _ptr(scale), n, _ptr(sigma), _stream()))
+    return sigma
+
+
+def compute_conic(xyz_c, view, sigma, focal_x, focal_y, tan_fovx, tan_fovy, mh_dist):
+    n = xyz_c.shape[0]
+    dev = xyz_c.device
+    J = torch.empty((n, 6), device=dev, dtype=torch.float32)
+    conic = torch.empty((n, 3), device=dev, dtype=torch.float32)
+    radius = torch.empty((n, 4), device=dev, dtype=torch.float32)
+    check(lib().gsx_compute_conic(_ptr(xyz_c), _ptr(view), _ptr(sigma), f32(focal_x), f32(focal_y), f32(tan_fovx),
+                                  f32(tan_fovy), f32(mh_dist), n, _ptr(J), _ptr(conic), _ptr(radius), _stream()))
+    return J, conic, radius
+
+
+def precompute_spherical_harmonics(xyz_w, sh, band0, campos, l_max, rgb=None):
+    n = xyz_w.shape[0]
+    rgb = torch.empty((n, 3), device=xyz_w.device, dtype=torch.float32) if rgb is None else rgb
+    cx, cy, cz = [float(c) for c in campos]
+    check(lib().gsx_precompute_spherical_harmonics(_ptr(xyz_w), _ptr(sh if l_max > 0 else None), _ptr(band0), f32(cx),
+                                                   f32(cy), f32(cz), int(l_max), n, _ptr(rgb), _stream()))
+    return rgb
+
+
+def get_sorted_gaussian_list(uv, xyz_c, radius, n_tiles_x, n_tiles_y):
+    """Both phases of the reference protocol.  Returns dict(C, K, sorted[K], ranges[T+1])."""
+    n = uv.shape[0]
+    dev = uv.device
+    cc, kk = C.c_longlong(0), C.c_longlong(0)
+    check(lib().gsx_sorted_list_size(_ptr(uv), _ptr(radius), int(n_tiles_x), int(n_tiles_y), n, C.byref(cc),
+                                     C.byref(kk), _stream()))
+    cap = max(int(cc.value), 1)       # the reference caller allocates C ints (cuda/raster.cu:115)
+    srt = torch.zeros(cap, device=dev, dtype=torch.int32)
+    ranges = torch.zeros(n_tiles_x * n_tiles_y + 1, device=dev, dtype=torch.int32)
+    kdev = torch.zeros(1, device=dev, dtype=torch.int32)
+    check(lib().gsx_get_sorted_gaussian_list(_ptr(uv), _ptr(xyz_c), _ptr(radius), int(n_tiles_x), int(n_tiles_y), n,
+                                             C.c_longlong(cap), _ptr(srt), _ptr(ranges), _ptr(kdev), C.c_void_p(0),
+                                             C.c_size_t(0), _stream()))
+    K = int(kdev.item())
+    assert K == kk.value
+    return dict(C=int(cc.value), K=K, sorted=srt[:K], ranges=ranges)
+
+
+def render_image(uv, opacity, conic, rgb, background, sorted_splats, ranges, width, height):
+    dev = uv.device
+    spp = torch.zeros((height, width), device=dev, dtype=torch.int32)
+    wpp = torch.zeros((height, width), device=dev, dtype=torch.float32)
+    img = torch.zeros((height, width, 3), device=dev, dtype=torch.float32)
+    if sorted_splats.numel() == 0:
+        sorted_splats = torch.zeros(1, device=dev, dtype=torch.int32)
+    check(lib().gsx_render_image(_ptr(uv), _ptr(opacity), _ptr(conic), _ptr(rgb), f32(background), _ptr(sorted_splats),
+                                 _ptr(ranges), int(width), int(height), _ptr(spp), _ptr(wpp), _ptr(img), _stream()))
+    return img, wpp, spp
+
+
+# ------------------------------------------------------------------------------------------------ backward F9..F15
+def render_image_backward(uv, opacity, conic, rgb, background, sorted_splats, ranges, spp, wpp, grad_image, width,
+                          height, grads=None):
+    n = uv.shape[0]
+    dev = uv.device
+    if grads is None:
+        grads = (torch.zeros((n, 3), device=dev), torch.zeros(n, device=dev), torch.zeros((n, 2), device=dev),
+                 torch.zeros((n, 3), device=dev))
+    g_rgb, g_opa, g_uv, g_con = grads
+    if sorted_splats.numel() == 0:
+        sorted_splats = torch.zeros(1, device=dev, dtype=torch.int32)
+    check(lib().gsx_render_image_backward(_ptr(uv), _ptr(opacity), _ptr(conic), _ptr(rgb), f32(background),
+                                          _ptr(sorted_splats), _ptr(ranges), _ptr(spp), _ptr(wpp), _ptr(grad_image),
+                                          int(width), int(height), n, _ptr(g_rgb), _ptr(g_opa), _ptr(g_uv),
+                                          _ptr(g_con), _stream()))
+    return g_rgb, g_opa, g_uv, g_con
+
+
+def precompute_spherical_harmonics_backward(xyz_w, band0, sh, campos, rgb_grad, l_max, xyz_grad=None, flags=0):
+    n = xyz_w.shape[0]
+    dev = xyz_w.device
+    nc = (l_max + 1) ** 2
+    sh_grad = torch.zeros((n, max(nc - 1, 1), 3), device=dev)
+    b0_grad = torch.zeros((n, 3), device=dev)
+    xyz_grad = torch.zeros((n, 3), device=dev) if xyz_grad is None else xyz_grad
+    cx, cy, cz = [float(c) for c in campos]
+    check(lib().gsx_precompute_spherical_harmonics_backward(
+        _ptr(xyz_w), _ptr(band0), _ptr(sh if l_max > 0 else None), f32(cx), f32(cy), f32(cz), _ptr(rgb_grad),
+        int(l_max), n, int(flags), _ptr(sh_grad if l_max > 0 else None), _ptr(b0_grad), _ptr(xyz_grad), _stream()))
+    return sh_grad[:, :nc - 1], b0_grad, xyz_grad
+
+
+def compute_conic_backward(J, sigma, view, conic, conic_grad, J_grad=None, sigma_grad=None):
+    n = J.shape[0]
+    J_grad = torch.zeros((n, 6), device=J.device) if J_grad is None else J_grad
+    sigma_grad = torch.zeros((n, 6), device=J.device) if sigma_grad is None else sigma_grad
+    check(lib().gsx_compute_conic_backward(_ptr(J), _ptr(sigma), _ptr(view), _ptr(conic), _ptr(conic_grad), n,
+                                           _ptr(J_grad), _ptr(sigma_grad), _stream()))
+    return J_grad, sigma_grad
+
+
+def compute_projection_jacobian_backward(xyz_c, focal_x, focal_y, tan_fovx, tan_fovy, J_grad, xyz_c_grad=None):
+    n = xyz_c.shape[0]
+    xyz_c_grad = torch.zeros((n, 3), device=xyz_c.device) if xyz_c_grad is None else xyz_c_grad
+    check(lib().gsx_compute_projection_jacobian_backward(_ptr(xyz_c), f32(focal_x), f32(focal_y), f32(tan_fovx),
+                                                         f32(tan_fovy), _ptr(J_grad), n, _ptr(xyz_c_grad), _stream()))
+    return xyz_c_grad
+
+
+def compute_sigma_backward(quaternion, scale, sigma_grad):
+    n = quaternion.shape[0]
+    dq = torch.zeros((n, 4), device=quaternion.device)
+    ds = torch.zeros((n, 3), device=quaternion.device)
+    check(lib().gsx_compute_sigma_backward(_ptr(quaternion), _ptr(scale), _ptr(sigma_grad), n, _ptr(dq), _ptr(ds),
+                                           _stream()))
+    return dq, ds
+
+
+def project_to_screen_backward(xyz_c, proj, uv_grad, width, height, xyz_c_grad=None):
+    n = xyz_c.shape[0]
+    xyz_c_grad = torch.zeros((n, 3), device=xyz_c.device) if xyz_c_grad is None else xyz_c_grad
+    check(lib().gsx_project_to_screen_backward(_ptr(xyz_c), _ptr(proj), _ptr(uv_grad), n, int(width), int(height),
+                                               _ptr(xyz_c_grad), _stream()))
+    return xyz_c_grad
+
+
+def compute_camera_space_points_backward(xyz_w, view, xyz_c_grad, xyz_w_grad=None):
+    n = xyz_c_grad.shape[0]
+    xyz_w_grad = torch.zeros((n, 3), device=xyz_c_grad.device) if xyz_w_grad is None else xyz_w_grad
+    check(lib().gsx_compute_camera_space_points_backward(_ptr(xyz_w), _ptr(view), _ptr(xyz_c_grad), n,
+                                                         _ptr(xyz_w_grad), _stream()))
+    return xyz_w_grad
+
+
+# ------------------------------------------------------------------------------------------------ sort primitives
+def sort_pairs_u64(keys, vals, key_bits=64):
+    """keys: int64 CUDA tensor holding uint64 bit patterns, vals: int32.  Returns sorted copies."""
+    n = keys.numel()
+    dev = keys.device
+    k_in, v_in = keys.clone(), vals.clone()
+    k_out, v_out = torch.empty_like(k_in), torch.empty_like(v_in)
+    wsb = lib().gsx_sort_workspace_bytes(C.c_longlong(max(n, 1)))
+    ws = torch.empty(wsb, device=dev, dtype=torch.uint8)
+    check(lib().gsx_sort_pairs_u64(_ptr(k_in), _ptr(k_out), _ptr(v_in), _ptr(v_out), C.c_longlong(n), C.c_void_p(0),
+                                   int(key_bits), _ptr(ws), C.c_size_t(wsb), _stream()))
+    return k_out, v_out
+
+
+def tile_ranges(sorted_keys, n_tiles):
+    n = sorted_keys.numel()
+    ranges = torch.empty(n_tiles + 1, device=sorted_keys.device, dtype=torch.int32)
+    check(lib().gsx_tile_ranges(_ptr(sorted_keys) if n else C.c_void_p(0), C.c_longlong(n), C.c_void_p(0), int(n_tiles),
+                                _ptr(ranges), _stream()))
+    return ranges
+
+
+# ------------------------------------------------------------------------------------------------ view-level path
+def make_view(view, proj, campos, focal_x, focal_y, width, height, near_thresh=0.3, cull_padding=100, mh_dist=3.0,
+              background=0.0, l_max=3, flags=0):
+    """Host-side camera block.  tan_fov as cuda/raster.cu:92-93."""
+    v = GsxView()
+    v.view[:] = [float(x) for x in view.reshape(-1)]
+    v.proj[:] = [float(x) for x in proj.reshape(-1)]
+    v.campos[:] = [float(x) for x in campos]
+    v.focal_x, v.focal_y = float(focal_x), float(focal_y)
+    v.tan_fovx, v.tan_fovy = width / (2.0 * focal_x), height / (2.0 * focal_y)
+    v.width, v.height = int(width), int(height)
+    v.near_thresh, v.cull_padding, v.mh_dist = float(near_thresh), int(cull_padding), float(mh_dist)
+    v.background, v.l_max, v.flags = float(background), int(l_max), int(flags)
+    return v
+
+
+class Gaussians:
+    """Device-resident parameters (GaussianParameters, cuda_data.cuh:11-24) + global-index gradient buffers."""
+
+    def __init__(self, xyz, scale, quaternion, opacity, band0, sh, device="cuda"):
+        to = lambda a: torch.as_tensor(a, dtype=torch.float32).contiguous().to(device)
+        self.xyz, self.scale, self.quaternion = to(xyz), to(scale), to(quaternion)
+        self.opacity, self.band0 = to(opacity).reshape(-1), to(band0)
+        self.N = self.xyz.shape[0]
+        if sh is None:
+            self.sh = torch.zeros(1, device=device)
+            self.sh_stride = 0
+        else:
+            self.sh = to(sh).reshape(self.N, -1)
+            self.sh_stride = self.sh.shape[1]
+        self.grads = None
+
+    def params(self):
+        p = GsxParams()
+        p.xyz, p.scale, p.quaternion = self.xyz.data_ptr(), self.scale.data_ptr(), self.quaternion.data_ptr()
+        p.opacity, p.band0, p.sh = self.opacity.data_ptr(), self.band0.data_ptr(), self.sh.data_ptr()
+        p.sh_stride = self.sh_stride
+        return p
+
+    def zero_grads(self, with_uv=False):
+        dev = self.xyz.device
+        z = lambda *s: torch.zeros(s, device=dev, dtype=torch.float32)
+        self.grads = dict(xyz=z(self.N, 3), scale=z(self.N, 3), quaternion=z(self.N, 4), opacity=z(self.N),
+                          band0=z(self.N, 3), sh=z(self.N, max(self.sh_stride, 1)))
+        if with_uv:
+            self.grads["uv"] = z(self.N, 2)
+        return self.grads
+
+    def grads_struct(self):
+        g = GsxGrads()
+        d = self.grads
+        g.xyz, g.scale, g.quaternion = d["xyz"].data_ptr(), d["scale"].data_ptr(), d["quaternion"].data_ptr()
+        g.opacity, g.band0, g.sh = d["opacity"].data_ptr(), d["band0"].data_ptr(), d["sh"].data_ptr()
+        g.uv = d["uv"].data_ptr() if "uv" in d else None
+        return g
+
+
+class Rasterizer:
+    """Persistent context: forward (rasterize_image) + backward (backward_pass minus fused_loss)."""
+
+    def __init__(self, max_gaussians, max_width, max_height, instance_capacity=0):
+        self.h = C.c_void_p()
+        check(lib().gsx_ctx_create(C.byref(self.h), int(max_gaussians), int(max_width), int(max_height),
+                                   C.c_longlong(int(instance_capacity))))
+        self.max_gaussians, self.max_width, self.max_height = max_gaussians, max_width, max_height
+        self._view = None
+
+    def close(self):
+        if self.h:
+            lib().gsx_ctx_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def forward(self, view, g):
+        self._view, self._n = view, g.N
+        self._p = g.params()
+        check(lib().gsx_forward(self.h, C.byref(view), C.byref(self._p), g.N, _stream()))
+
+    def backward(self, view, g, grad_image):
+        if g.grads is None:
+            g.zero_grads()
+        gs = g.grads_struct()
+        p = g.params()
+        check(lib().gsx_backward(self.h, C.byref(view), C.byref(p), g.N, _ptr(grad_image), C.byref(gs), _stream()))
+
+    def stats(self, raise_on_overflow=True):
+        s = GsxStats()
+        rc = lib().gsx_ctx_stats(self.h, C.byref(s), _stream())
+        if rc != _ffi.GSX_OK and (raise_on_overflow or rc != _ffi.GSX_E_CAPACITY):
+            check(rc)
+        return dict(N=s.N, P=s.P, K=s.K, capacity=s.capacity, overflow=(rc == _ffi.GSX_E_CAPACITY))
+
+    def reserve(self, capacity):
+        check(lib().gsx_ctx_reserve(self.h, C.c_longlong(int(capacity))))
+
+    def forward_checked(self, view, g):
+        """forward + one sync to grow the instance capacity if it overflowed (first view of a scene)."""
+        self.forward(view, g)
+        st = self.stats(raise_on_overflow=False)
+        if st["overflow"]:
+            self.reserve(int(st["K"] * 1.25) + 1024)
+            self.forward(view, g)
+            st = self.stats()
+        return st
+
+    def render_view_host(self, view, g, grad_image_host, image_host):
+        """Host-buffer entry point: H2D grad_image, forward, backward, D2H image (synchronises)."""
+        if g.grads is None:
+            g.zero_grads()
+        gs = g.grads_struct()
+        p = g.params()
+        gi = C.c_void_p(grad_image_host.data_ptr()) if grad_image_host is not None else C.c_void_p(0)
+        io = C.c_void_p(image_host.data_ptr()) if image_host is not None else C.c_void_p(0)
+        check(lib().gsx_render_view_host(self.h, C.byref(view), C.byref(p), g.N, gi, io, C.byref(gs), _stream()))
+
+    def state(self):
+        """Zero-copy torch views of the saved forward state (for tests / inspection)."""
+        s = GsxState()
+        check(lib().gsx_ctx_state(self.h, C.byref(s)))
+        v = self._view
+        n, W, H = self._n, v.width, v.height
+        T = ((W + 15) // 16) * ((H + 15) // 16)
+        K = int(_from_ptr(s.num_instances, (1,), torch.int32).item())
+        out = dict(
+            image=_from_ptr(s.image, (H, W, 3), torch.float32), weight_per_pixel=_from_ptr(s.weight_per_pixel, (H, W), torch.float32),
+            splats_per_pixel=_from_ptr(s.splats_per_pixel, (H, W), torch.int32),
+            rec0=_from_ptr(s.rec0, (n, 4), torch.float32), rec1=_from_ptr(s.rec1, (n, 4), torch.float32),
+            rec2=_from_ptr(s.rec2, (n, 4), torch.float32), radius=_from_ptr(s.radius, (n, 4), torch.float32),
+            depth=_from_ptr(s.depth, (n,), torch.float32), mask=_from_ptr(s.mask, (n,), torch.uint8),
+            tiles_touched=_from_ptr(s.tiles_touched, (n,), torch.int32), ranges=_from_ptr(s.ranges, (T + 1,), torch.int32),
+            packed_grads=_from_ptr(s.packed_grads, (n, 12), torch.float32), K=K)
+        out["sorted_gaussians"] = _from_ptr(s.sorted_gaussians, (max(K, 1),), torch.int32)[:K]
+        out["sorted_keys"] = _from_ptr(s.sorted_keys, (max(K, 1),), torch.int64)[:K]
+        return out
+
+
+class _CudaArray:
+    def __init__(self, ptr, shape, dtype):
+        itemsize = torch.empty(0, dtype=dtype).element_size()
+        typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1", torch.int64: "<i8"}[dtype]
+        strides = None
+        self.__cuda_array_interface__ = dict(shape=tuple(shape), typestr=typestr, data=(int(ptr), False), version=2,
+                                             strides=strides)
+        self._itemsize = itemsize
+
+
+def _from_ptr(ptr, shape, dtype):
+    return torch.as_tensor(_CudaArray(ptr, shape, dtype), device="cuda")

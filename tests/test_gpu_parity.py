@@ -1,0 +1,416 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (3dgs_b200.host -> libgsx.so), against the
+CPU oracle on the same seeded inputs.  Discrete outputs bit-exact; floats within the tolerances in tests/util.py."""
+import numpy as np
+import pytest
+
+import kat
+import util
+from util import G, S, gs
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def B():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return gs.np_backend
+
+
+@pytest.mark.parametrize("check", kat.ALL, ids=[c.__name__ for c in kat.ALL])
+def test_reference_kats_on_gpu(B, check):
+    """every known-answer test of the reference (tests/cuda_forward_test.cpp, cuda_backward_test.cpp) through the C ABI"""
+    check(B)
+
+
+def _scene(N=20000, W=320, H=240, l_max=3, seed=11):
+    cam = S.orbit_camera(W, H, azimuth_deg=30.0)
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=seed)
+    return cam, g
+
+
+# ------------------------------------------------------------------------------------------ per-function parity
+def test_pointwise_forward_parity(B):
+    cam, g = _scene()
+    W, H = cam["width"], cam["height"]
+    xyz_c = B.camera_space_points(g["xyz"], cam["view"])
+    np.testing.assert_allclose(xyz_c, G.camera_space_points(g["xyz"], cam["view"]), rtol=1e-5, atol=1e-6)
+    uv = B.project_to_screen(xyz_c, cam["proj"], W, H)
+    np.testing.assert_allclose(uv, G.project_to_screen(xyz_c, cam["proj"], W, H), rtol=1e-5, atol=1e-3)
+    m = B.cull(uv, xyz_c, S.NEAR_THRESH, S.CULL_PADDING, W, H)
+    np.testing.assert_array_equal(m, G.cull(uv, xyz_c, S.NEAR_THRESH, S.CULL_PADDING, W, H))   # same inputs: exact
+    sig = B.sigma(g["quaternion"], g["scale"])
+    np.testing.assert_allclose(sig, G.sigma(g["quaternion"], g["scale"]), rtol=2e-5, atol=1e-9)
+    tx, ty = W / (2 * cam["fx"]), H / (2 * cam["fy"])
+    J, con, rad = B.conic(xyz_c, cam["view"], sig, cam["fx"], cam["fy"], tx, ty, S.MH_DIST)
+    Jg, cong, radg = G.conic(xyz_c, cam["view"], sig, cam["fx"], cam["fy"], tx, ty, S.MH_DIST)
+    np.testing.assert_allclose(J, Jg, rtol=1e-5, atol=1e-6)
+    util.assert_grad_close(con, cong, "conic", rtol=1e-4)
+    assert (rad[:, :2] != radg[:, :2]).mean() <= 1e-4      # ceil() radii: identical up to 1-ulp ties
+    np.testing.assert_allclose(rad[:, 2:], radg[:, 2:], atol=2e-5)
+    for l in (0, 1, 2, 3):
+        nsh = (l + 1) ** 2 - 1
+        sh = g["sh"][:, :nsh] if nsh else None
+        rgb = B.sh_forward(g["xyz"], sh, g["band0"], cam["campos"], l)
+        np.testing.assert_allclose(rgb, G.sh_forward(g["xyz"], sh, g["band0"], cam["campos"], l), rtol=1e-5, atol=2e-6)
+
+
+def test_pointwise_backward_parity(B):
+    cam, g = _scene(N=5000)
+    W, H = cam["width"], cam["height"]
+    rng = np.random.default_rng(3)
+    N = g["xyz"].shape[0]
+    xyz_c = G.camera_space_points(g["xyz"], cam["view"])
+    sig = G.sigma(g["quaternion"], g["scale"])
+    tx, ty = W / (2 * cam["fx"]), H / (2 * cam["fy"])
+    J, con, _ = G.conic(xyz_c, cam["view"], sig, cam["fx"], cam["fy"], tx, ty, S.MH_DIST)
+    gc = rng.standard_normal((N, 3)).astype(np.float32)
+    a = B.conic_backward(J, sig, cam["view"], con, gc)
+    b = G.conic_backward(J, sig, cam["view"], con, gc)
+    util.assert_grad_close(a[0], b[0], "J_grad")
+    util.assert_grad_close(a[1], b[1], "sigma_grad")
+    gJ = rng.standard_normal((N, 6)).astype(np.float32)
+    pre = rng.standard_normal((N, 3)).astype(np.float32)
+    util.assert_grad_close(B.jacobian_backward(xyz_c, cam["fx"], cam["fy"], tx, ty, gJ, pre),
+                           G.jacobian_backward(xyz_c, cam["fx"], cam["fy"], tx, ty, gJ, pre), "jacobian_backward(+=)")
+    gS = rng.standard_normal((N, 6)).astype(np.float32)
+    a = B.sigma_backward(g["quaternion"], g["scale"], gS)
+    b = G.sigma_backward(g["quaternion"], g["scale"], gS)
+    util.assert_grad_close(a[0], b[0], "quat_grad")
+    util.assert_grad_close(a[1], b[1], "scale_grad")
+    gu = rng.standard_normal((N, 2)).astype(np.float32)
+    util.assert_grad_close(B.project_to_screen_backward(xyz_c, cam["proj"], gu, W, H, pre),
+                           G.project_to_screen_backward(xyz_c, cam["proj"], gu, W, H, pre), "project_backward(+=)")
+    util.assert_grad_close(B.camera_space_points_backward(cam["view"], pre, gJ[:, :3].copy()),
+                           G.camera_space_points_backward(cam["view"], pre, gJ[:, :3].copy()), "cam_backward(+=)")
+    grgb = rng.standard_normal((N, 3)).astype(np.float32)
+    for l in (0, 1, 2, 3):
+        nsh = (l + 1) ** 2 - 1
+        sh = g["sh"][:, :nsh] if nsh else None
+        for compat in (1, 0):
+            a = B.sh_backward(g["xyz"], g["band0"], sh, cam["campos"], grgb, l, ref_compat_dsph=compat, xyz_grad=pre)
+            b = G.sh_backward(g["xyz"], g["band0"], sh, cam["campos"], grgb, l, ref_compat_dsph=compat, xyz_grad=pre)
+            if nsh:
+                util.assert_grad_close(a[0], b[0], f"sh_grad l={l}")
+            util.assert_grad_close(a[1], b[1], f"band0_grad l={l}")
+            util.assert_grad_close(a[2], b[2], f"xyz_grad l={l} compat={compat}")
+
+
+# ------------------------------------------------------------------------------------------ sort / ranges
+@pytest.mark.parametrize("n,bits", [(0, 45), (1, 45), (4095, 45), (4096, 40), (4097, 64), (100_003, 45), (1_000_000, 47)])
+def test_onesweep_sort_exact(n, bits):
+    import torch
+    H = gs.host
+    rng = np.random.default_rng(n + bits)
+    hi = rng.integers(0, 1 << (bits - 32), n, dtype=np.uint64)
+    lo = rng.integers(0, 1 << 32, n, dtype=np.uint64)
+    if n > 10:
+        lo[: n // 3] = lo[0]          # many equal keys -> stability is observable
+        hi[: n // 3] = hi[0]
+    keys = (hi << np.uint64(32)) | lo
+    vals = np.arange(n, dtype=np.int32)
+    k = torch.as_tensor(keys.view(np.int64)).cuda()
+    v = torch.as_tensor(vals).cuda()
+    ks, vs = H.sort_pairs_u64(k, v, key_bits=bits)
+    order = np.argsort(keys, kind="stable")
+    np.testing.assert_array_equal(ks.cpu().numpy().view(np.uint64), keys[order])
+    np.testing.assert_array_equal(vs.cpu().numpy(), vals[order])      # stable: ties keep input order
+    T = 1 << min(bits - 32, 14)
+    rg = H.tile_ranges(ks, T).cpu().numpy() if n else H.tile_ranges(k, T).cpu().numpy()
+    tiles = (keys[order] >> np.uint64(32)).astype(np.int64)
+    np.testing.assert_array_equal(rg, np.searchsorted(np.minimum(tiles, T - 1), np.arange(T + 1), side="left"))
+
+
+def test_sorted_list_bit_exact(B):
+    """instance set, order and ranges vs the oracle on identical (uv, depth, radius): bit-exact, incl. ragged tiles,
+    off-screen Gaussians, rotated boxes and equal depths (ties by Gaussian id)."""
+    rng = np.random.default_rng(5)
+    N, W, H = 30000, 333, 250
+    ntx, nty = (W + 15) // 16, (H + 15) // 16
+    uv = np.stack([rng.uniform(-120, W + 120, N), rng.uniform(-120, H + 120, N)], 1).astype(np.float32)
+    z = rng.uniform(0.3, 9.0, N).astype(np.float32)
+    z[::7] = 2.5                                      # equal-depth ties
+    xyz = np.stack([np.zeros(N), np.zeros(N), z], 1).astype(np.float32)
+    rmaj = np.ceil(rng.exponential(6.0, N) + 1).astype(np.float32)
+    rmin = np.ceil(rmaj * rng.uniform(0.1, 1.0, N)).astype(np.float32)
+    th = rng.uniform(-np.pi / 2, np.pi / 2, N)
+    rad = np.stack([rmaj, rmin, np.sin(th), np.cos(th)], 1).astype(np.float32)
+    uv[:50] = np.round(uv[:50] / 16) * 16            # centres exactly on tile borders (inclusive SAT)
+    rad[:50, 2:] = [0.0, 1.0]
+    a = B.sorted_list(uv, xyz, rad, ntx, nty)
+    b = G.sorted_list(uv, xyz, rad, ntx, nty)
+    assert a["C"] == b["C"] and a["K"] == b["K"] and a["K"] > N
+    np.testing.assert_array_equal(a["ranges"], b["ranges"])
+    np.testing.assert_array_equal(a["sorted"], b["sorted"])
+    # nothing on screen -> empty list, all-zero ranges (reference: 0-block launch over zero-initialised ranges, Q15)
+    uv2 = uv.copy(); uv2[:] = -5000.0
+    e = B.sorted_list(uv2, xyz, rad, ntx, nty)
+    assert e["K"] == 0 and not e["ranges"].any()
+
+
+# ------------------------------------------------------------------------------------------ compositing
+def _comp_inputs(N=4000, W=150, H=100, seed=2, big=False):
+    rng = np.random.default_rng(seed)
+    ntx, nty = (W + 15) // 16, (H + 15) // 16
+    uv = np.stack([rng.uniform(-10, W + 10, N), rng.uniform(-10, H + 10, N)], 1).astype(np.float32)
+    z = rng.uniform(0.5, 9.0, N).astype(np.float32)
+    xyz = np.stack([np.zeros(N), np.zeros(N), z], 1).astype(np.float32)
+    s1 = rng.uniform(1.0, 12.0 if big else 5.0, N); s2 = s1 * rng.uniform(0.2, 1.0, N)
+    th = rng.uniform(0, np.pi, N)
+    c, s = np.cos(th), np.sin(th)
+    cov00 = c * c * s1 ** 2 + s * s * s2 ** 2 + 0.3
+    cov11 = s * s * s1 ** 2 + c * c * s2 ** 2 + 0.3
+    cov01 = c * s * (s1 ** 2 - s2 ** 2)
+    det = cov00 * cov11 - cov01 ** 2
+    con = np.stack([cov11 / det, -cov01 / det, cov00 / det], 1).astype(np.float32)
+    mid = 0.5 * (cov00 + cov11); lt = np.sqrt(np.maximum(0.1, mid * mid - det))
+    ang = 0.5 * np.arctan2(2 * cov01, cov00 - cov11)
+    rad = np.stack([np.ceil(3 * np.sqrt(mid + lt)), np.ceil(3 * np.sqrt(mid - lt)), np.sin(ang), np.cos(ang)], 1).astype(np.float32)
+    opacity = (2.0 * rng.standard_normal(N)).astype(np.float32)
+    opacity[:20] = 30.0       # sigmoid == 1.0f exactly -> Q7 (whole entry dropped in the backward)
+    opacity[20:40] = -12.0    # never reaches 1/255
+    rgb = rng.uniform(-0.2, 1.2, (N, 3)).astype(np.float32)
+    lst = G.sorted_list(uv, xyz, rad, ntx, nty)
+    return dict(W=W, H=H, uv=uv, opacity=opacity, conic=con, rgb=rgb, sorted=lst["sorted"], ranges=lst["ranges"])
+
+
+@pytest.mark.parametrize("big,bg", [(False, 0.0), (True, 0.7)])
+def test_render_forward_parity(B, big, bg):
+    d = _comp_inputs(big=big, N=6000 if big else 4000)
+    a = B.render(d["uv"], d["opacity"], d["conic"], d["rgb"], bg, d["sorted"], d["ranges"], d["W"], d["H"])
+    b = G.render(d["uv"], d["opacity"], d["conic"], d["rgb"], bg, d["sorted"], d["ranges"], d["W"], d["H"])
+    util.assert_image_close(a[0], b[0], "image")
+    util.assert_image_close(a[1], b[1], "final transmittance")
+    assert (a[2] != b[2]).mean() <= util.OUTLIER_FRAC          # splats_per_pixel: exact up to threshold flips
+    if big:
+        assert (b[2] < (d["ranges"][1:] - d["ranges"][:-1]).max()).any()   # early termination is exercised
+
+
+@pytest.mark.parametrize("big,bg", [(False, 0.0), (True, 0.7)])
+def test_render_backward_parity(B, big, bg):
+    d = _comp_inputs(big=big, N=6000 if big else 4000, seed=9)
+    img, wpp, spp = G.render(d["uv"], d["opacity"], d["conic"], d["rgb"], bg, d["sorted"], d["ranges"], d["W"], d["H"])
+    gi = S.grad_image(d["W"], d["H"]) * 1e3
+    a = B.render_backward(d["uv"], d["opacity"], d["conic"], d["rgb"], bg, d["sorted"], d["ranges"], spp, wpp, gi, d["W"], d["H"])
+    b = G.render_backward(d["uv"], d["opacity"], d["conic"], d["rgb"], bg, d["sorted"], d["ranges"], spp, wpp, gi, d["W"], d["H"])
+    for x, y, name in zip(a, b, ("grad_rgb", "grad_opacity", "grad_uv", "grad_conic")):
+        util.assert_grad_close(x, y, name, outlier=2e-3)
+    assert not a[0][:20].any() and not a[2][:20].any()     # Q7: opa == 1 -> every gradient of the entry dropped
+    assert np.abs(b[0]).sum() > 0
+
+
+# ------------------------------------------------------------------------------------------ view-level path
+def _run_view(cam, g, l_max, background, flags=0, sh_alloc=None):
+    import torch
+    H = gs.host
+    N = g["xyz"].shape[0]
+    sh = g["sh"]
+    if sh is not None and sh_alloc is not None:          # trainer-style: 45 floats allocated, l_max bands used
+        full = np.zeros((N, (sh_alloc + 1) ** 2 - 1, 3), np.float32)
+        full[:, : sh.shape[1]] = sh
+        sh = full
+    gd = H.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], sh)
+    r = H.Rasterizer(N, cam["width"], cam["height"], instance_capacity=1024)   # forces the grow-and-retry path
+    v = util.gsx_view(cam, l_max, background, flags)
+    stats = r.forward_checked(v, gd)
+    torch.cuda.synchronize()
+    return H, gd, r, v, stats
+
+
+@pytest.mark.parametrize("l_max,sh_alloc,W,H", [(3, None, 320, 240), (1, 3, 203, 117), (0, None, 100, 80), (2, None, 64, 64)])
+def test_view_forward_chain_consistent(B, l_max, sh_alloc, W, H):
+    cam = S.orbit_camera(W, H, azimuth_deg=100.0)
+    g = S.synthetic_gaussians(20000, l_max=l_max, seed=21)
+    Hh, gd, r, v, stats = _run_view(cam, g, l_max, 0.3, sh_alloc=sh_alloc)
+    st = {k: (t.cpu().numpy() if hasattr(t, "cpu") else t) for k, t in r.state().items()}
+    gv = util.make_views(cam, l_max, 0.3)
+    o = G.forward(gv, g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+    N = g["xyz"].shape[0]
+    vis = o.i("vis")
+    mask = st["mask"].astype(bool)
+    # 1. cull mask and per-Gaussian floats vs the oracle's own chain
+    assert (mask != o.i("mask").astype(bool)).sum() <= 2
+    both = np.intersect1d(vis, np.nonzero(mask)[0])
+    comp = np.searchsorted(vis, both)
+    assert stats["P"] == mask.sum() and stats["K"] == st["K"]
+    np.testing.assert_allclose(st["rec0"][both, :2], o.f("uv").reshape(-1, 2)[both], rtol=1e-5, atol=2e-3)
+    np.testing.assert_allclose(st["depth"][both], o.f("xyz_c").reshape(-1, 3)[both, 2], rtol=1e-5, atol=1e-6)
+    util.assert_grad_close(st["rec1"][both, :3], o.f("conic").reshape(-1, 3)[comp], "conic", rtol=2e-4)
+    np.testing.assert_allclose(st["rec2"][both, :3], o.f("rgb").reshape(-1, 3)[comp], rtol=1e-5, atol=3e-6)
+    rg = o.f("radius").reshape(-1, 4)[comp]
+    assert (st["radius"][both, :2] != rg[:, :2]).mean() <= 2e-4
+    opa = 1.0 / (1.0 + np.exp(-g["opacity"][both].astype(np.float64)))
+    np.testing.assert_allclose(st["rec1"][both, 3], opa, rtol=1e-5)
+    # 2. binning + sort + ranges: bit-exact vs the oracle fed with the GPU's own per-Gaussian values
+    uv = np.where(mask[:, None], st["rec0"][:, :2], -1e6).astype(np.float32)
+    rad = np.where(mask[:, None], st["radius"], np.array([0, 0, 0, 1], np.float32)).astype(np.float32)
+    xyz_c = np.zeros((N, 3), np.float32); xyz_c[:, 2] = np.where(mask, st["depth"], 1.0)
+    ntx, nty = (W + 15) // 16, (H + 15) // 16
+    lst = G.sorted_list(uv, xyz_c, rad, ntx, nty)
+    assert lst["K"] == st["K"] and st["K"] > 0
+    np.testing.assert_array_equal(st["ranges"], lst["ranges"])
+    np.testing.assert_array_equal(st["sorted_gaussians"], lst["sorted"])
+    keys = st["sorted_keys"].view(np.uint64)
+    np.testing.assert_array_equal((keys >> np.uint64(32)).astype(np.int32), lst["tiles"])
+    assert (np.diff(keys.astype(np.uint64).view(np.int64)) >= 0).all()           # sortedness
+    np.testing.assert_array_equal(st["tiles_touched"][mask].sum(), st["K"])
+    # 3. compositing vs the oracle on the GPU's per-Gaussian values and list
+    con = st["rec1"][:, :3].copy(); rgb = st["rec2"][:, :3].copy()
+    img, wpp, spp = G.render(uv, g["opacity"], con, rgb, 0.3, lst["sorted"], lst["ranges"], W, H)
+    util.assert_image_close(st["image"], img)
+    util.assert_image_close(st["weight_per_pixel"], wpp, "final T")
+    assert (st["splats_per_pixel"] != spp).mean() <= util.OUTLIER_FRAC
+    # 4. and end to end vs the oracle's own chain (threshold flips bounded)
+    assert util.close_frac(st["image"], o.f("image").reshape(H, W, 3), 1e-3, 1e-4) <= 2e-3
+    r.close()
+
+
+@pytest.mark.parametrize("l_max,sh_alloc,flags", [(3, None, 0), (3, None, 1), (1, 3, 0), (0, None, 0)])
+def test_view_backward_parity(B, l_max, sh_alloc, flags):
+    import torch
+    W, H = 256, 192
+    cam = S.orbit_camera(W, H, azimuth_deg=200.0)
+    g = S.synthetic_gaussians(15000, l_max=l_max, seed=33)
+    Hh, gd, r, v, stats = _run_view(cam, g, l_max, 0.5, flags=flags, sh_alloc=sh_alloc)
+    st = {k: (t.cpu().numpy().copy() if hasattr(t, "cpu") else t) for k, t in r.state().items()}
+    gi = S.grad_image(W, H) * 1e3
+    gd.zero_grads(with_uv=True)
+    gi_d = torch.as_tensor(gi).cuda()
+    r.backward(v, gd, gi_d)
+    r.backward(v, gd, gi_d)          # accumulate semantics: two identical views -> exactly twice the gradient
+    torch.cuda.synchronize()
+    got = {k: t.cpu().numpy() for k, t in gd.grads.items()}
+    assert not r.state()["packed_grads"].any().item()       # the packed buffer is handed back zeroed
+    # oracle chain F9 -> F10..F15 on the GPU's forward state (chain-consistent)
+    N = g["xyz"].shape[0]
+    mask = st["mask"].astype(bool)
+    vis = np.nonzero(mask)[0]
+    uv = st["rec0"][vis, :2].copy(); con = st["rec1"][vis, :3].copy(); rgb = st["rec2"][vis, :3].copy()
+    inv = np.full(N, -1, np.int32); inv[vis] = np.arange(vis.size, dtype=np.int32)
+    srt_c = inv[st["sorted_gaussians"]]
+    assert (srt_c >= 0).all()
+    g_rgb, g_opa, g_uv, g_con = G.render_backward(uv, g["opacity"][vis], con, rgb, 0.5, srt_c, st["ranges"],
+                                                  st["splats_per_pixel"], st["weight_per_pixel"], gi, W, H)
+    nsh = (l_max + 1) ** 2 - 1
+    sh_c = g["sh"][vis, :nsh] if nsh else None
+    xyz_c = G.camera_space_points(g["xyz"][vis], cam["view"])
+    sig = G.sigma(g["quaternion"][vis], g["scale"][vis])
+    tx, ty = W / (2 * cam["fx"]), H / (2 * cam["fy"])
+    J, _, _ = G.conic(xyz_c, cam["view"], sig, cam["fx"], cam["fy"], tx, ty, S.MH_DIST)
+    shg, b0g, xyzg = G.sh_backward(g["xyz"][vis], g["band0"][vis], sh_c, cam["campos"], g_rgb, l_max, ref_compat_dsph=0 if flags & 1 else 1)
+    gJ, gS = G.conic_backward(J, sig, cam["view"], con, g_con)
+    gxc = G.jacobian_backward(xyz_c, cam["fx"], cam["fy"], tx, ty, gJ)
+    gq, gsc = G.sigma_backward(g["quaternion"][vis], g["scale"][vis], gS)
+    gxc = G.project_to_screen_backward(xyz_c, cam["proj"], g_uv, W, H, gxc)
+    xyzg = G.camera_space_points_backward(cam["view"], gxc, xyzg)
+    exp = dict(xyz=util.scatter(xyzg, vis, N), scale=util.scatter(gsc, vis, N), quaternion=util.scatter(gq, vis, N),
+               opacity=util.scatter(g_opa, vis, N), band0=util.scatter(b0g, vis, N), uv=util.scatter(g_uv, vis, N))
+    for k, e in exp.items():
+        util.assert_grad_close(got[k], 2.0 * e, f"d {k}", outlier=2e-3)
+    if nsh:
+        stride = gd.sh_stride
+        e = np.zeros((N, stride), np.float32)
+        e[vis, : nsh * 3] = shg.reshape(vis.size, -1)
+        util.assert_grad_close(got["sh"], 2.0 * e, "d sh", outlier=2e-3)
+    # overwrite mode: one call, '=' semantics, culled Gaussians get zeros
+    v2 = util.gsx_view(cam, l_max, 0.5, flags | 2)
+    for t in gd.grads.values():
+        t.fill_(123.0)
+    r.backward(v2, gd, gi_d)
+    torch.cuda.synchronize()
+    got1 = {k: t.cpu().numpy() for k, t in gd.grads.items()}
+    util.assert_grad_close(got1["xyz"], exp["xyz"], "d xyz (overwrite)", outlier=2e-3)
+    util.assert_grad_close(got1["opacity"], exp["opacity"], "d opacity (overwrite)", outlier=2e-3)
+    if (~mask).any():
+        assert not got1["scale"][~mask].any()
+    r.close()
+
+
+def test_config1_fixture_and_companion(B):
+    """C1: the reference's own COLMAP fixture (1 camera, 1 image, 1 point): the Gaussian survives the
+    padded cull, touches no tile, the image is pure background and every gradient is zero; plus the non-degenerate
+    companion (same camera, 1000 seeded Gaussians) against the oracle end to end."""
+    import torch
+    cam = S.test_data_camera()
+    g1 = S.test_data_gaussian()
+    Hh, gd, r, v, stats = _run_view(cam, g1, 0, 0.25)
+    st = r.state()
+    assert stats["P"] == 1 and stats["K"] == 0
+    np.testing.assert_allclose(st["rec0"][0, :2].cpu().numpy(), [138.03, 79.78], atol=0.02)
+    assert torch.all(st["image"] == 0.25) and not st["ranges"].any().item()
+    gd.zero_grads()
+    r.backward(v, gd, torch.ones((80, 100, 3), device="cuda"))
+    torch.cuda.synchronize()
+    assert all(not t.any().item() for t in gd.grads.values())
+    r.close()
+    g = S.frustum_gaussians(1000, cam, l_max=0, seed=4)
+    Hh, gd, r, v, stats = _run_view(cam, g, 0, 0.25)
+    gv = util.make_views(cam, 0, 0.25)
+    o = G.forward(gv, g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], None)
+    st = r.state()
+    assert stats["P"] == o.P and stats["K"] == o.K and o.K > 1000
+    np.testing.assert_array_equal(st["ranges"].cpu().numpy(), o.i("ranges"))
+    np.testing.assert_array_equal(st["sorted_gaussians"].cpu().numpy(), o.i("vis")[o.i("sorted")])
+    util.assert_image_close(st["image"].cpu().numpy(), o.f("image").reshape(80, 100, 3))
+    gi = S.grad_image(100, 80) * 1e3
+    gd.zero_grads()
+    r.backward(v, gd, torch.as_tensor(gi).cuda())
+    torch.cuda.synchronize()
+    og = G.backward(gv, o, gi)
+    for k_o, k_g in (("xyz", "xyz"), ("scale", "scale"), ("quat", "quaternion"), ("opacity", "opacity"), ("band0", "band0")):
+        util.assert_grad_close(gd.grads[k_g].cpu().numpy(), og[k_o], f"C1 companion d {k_g}", outlier=5e-3)
+    r.close()
+
+
+def test_empty_and_error_paths(B):
+    import torch
+    H = gs.host
+    cam = S.orbit_camera(64, 48)
+    g = S.synthetic_gaussians(256, l_max=0, seed=1)
+    g["xyz"][:] += 100.0                                   # everything behind / outside -> P = 0
+    Hh, gd, r, v, stats = _run_view(cam, g, 0, 0.1)
+    assert stats["P"] == 0 and stats["K"] == 0
+    assert torch.all(r.state()["image"] == 0.1)             # the reference exits here (raster.cu:38-41); we render bg
+    r.close()
+    with pytest.raises(gs._ffi.GsxError):                   # non-device pointer -> status (reference: exit(1))
+        gs._ffi.check(gs._ffi.lib().gsx_compute_sigma(None, None, 4, None, None))
+    with pytest.raises(gs._ffi.GsxError):
+        H.precompute_spherical_harmonics(torch.zeros((4, 3), device="cuda"), None, torch.zeros((4, 3), device="cuda"),
+                                         (0, 0, 0), 7)
+
+
+def test_full_size_properties_c2(B):
+    """BASELINE config 2 at full size (1M Gaussians, 1297x840, deg 3): properties that need no oracle run --
+    sortedness, ranges consistency, checksum of the id multiset, count conservation, idempotence, linearity of the
+    backward in grad_image."""
+    import torch
+    N, W, H, l_max = S.CONFIGS["C2"]
+    cam = S.orbit_camera(W, H, 0.0)
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=0x3D65 + 2)
+    Hh, gd, r, v, stats = _run_view(cam, g, l_max, 0.0)
+    st = r.state()
+    K = st["K"]
+    assert K == int(st["tiles_touched"].sum().item()) and stats["P"] == int(st["mask"].sum().item())
+    keys = st["sorted_keys"]
+    assert bool((keys[1:] >= keys[:-1]).all())
+    tiles = (keys >> 32).to(torch.int64)
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    rg = st["ranges"].to(torch.int64)
+    assert int(rg[0]) == 0 and int(rg[-1]) == K and bool((rg[1:] >= rg[:-1]).all())
+    assert torch.equal(torch.searchsorted(tiles, torch.arange(T + 1, device="cuda")), rg)
+    ids = st["sorted_gaussians"].to(torch.int64)
+    assert torch.equal(torch.bincount(ids, minlength=N).to(torch.int32), st["tiles_touched"])   # multiset of ids
+    img1 = st["image"].clone(); k1 = keys.clone()
+    r.forward(v, gd); torch.cuda.synchronize()
+    st2 = r.state()
+    assert torch.equal(st2["image"], img1) and torch.equal(st2["sorted_keys"], k1)               # idempotent / deterministic
+    assert 0.0 <= float(st2["weight_per_pixel"].min()) and float(st2["weight_per_pixel"].max()) <= 1.0
+    gi = torch.as_tensor(S.grad_image(W, H) * 1e3).cuda()
+    gd.zero_grads(); r.backward(v, gd, gi); torch.cuda.synchronize()
+    g1 = {k: t.clone() for k, t in gd.grads.items()}
+    gd.zero_grads(); r.backward(v, gd, 2.0 * gi); torch.cuda.synchronize()
+    for k in g1:                                                                                  # linearity
+        a, b = gd.grads[k], 2.0 * g1[k]
+        assert float((a - b).norm()) <= 1e-3 * float(b.norm()) + 1e-12, k
+    assert all(bool(torch.isfinite(t).all()) for t in gd.grads.values())
+    r.close()
