@@ -38,7 +38,7 @@ int check_device_ptr(const void *p, const char *name) {
 BinLayout bin_layout(int N, long long capacity);
 int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius, int ntx,
                   int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
-                  const uint64_t **sorted_keys, const uint32_t **sorted_vals, cudaStream_t st);
+                  const uint64_t **sorted_keys, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev);
 int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
                          int W, int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st);
 int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
@@ -74,6 +74,9 @@ struct gsx_ctx {
   int last_n = 0, last_w = 0, last_h = 0;
   int *h_stats = nullptr;           // pinned: [0] = K, [1] = P
   int *d_P = nullptr;
+  // optional stage timing (gsx_ctx_enable_timing): events 0..5 forward, 6..8 backward
+  bool timing = false;
+  cudaEvent_t ev[9] = {};
 };
 
 namespace gsx {
@@ -158,13 +161,17 @@ int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N,
   const int ntx = (v->width + 15) / 16, nty = (v->height + 15) / 16;
   c->last_n = N; c->last_w = v->width; c->last_h = v->height;
   int *touched = (int *)(c->bin_ws + c->L.touched);
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
   int rc = preprocess_fwd_launch(*v, *p, N, c->r0, c->r1, c->r2, c->radius, c->depth, c->mask, touched, st);
   if (rc != GSX_OK) return rc;
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[1], st));
   rc = bin_sort_impl((const float *)c->r0, 4, c->depth, 1, c->radius, ntx, nty, N, c->capacity, c->bin_ws, c->L, c->ranges,
-                     &c->sorted_keys, &c->sorted_vals, st);
+                     &c->sorted_keys, &c->sorted_vals, st, c->timing ? &c->ev[2] : nullptr);
   if (rc != GSX_OK) return rc;
-  return composite_fwd_packed(c->r0, c->r1, c->r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
-                              v->background, c->spp, c->wpp, c->image, st);
+  rc = composite_fwd_packed(c->r0, c->r1, c->r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
+                            v->background, c->spp, c->wpp, c->image, st);
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[5], st));
+  return rc;
 }
 
 int gsx_backward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N, const float *grad_image,
@@ -175,10 +182,76 @@ int gsx_backward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N
     return GSX_E_ARG;
   }
   cudaStream_t st = (cudaStream_t)stream;
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[6], st));
   int rc = composite_bwd_packed(c->r0, c->r1, c->r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
                                 v->background, c->spp, c->wpp, grad_image, c->gacc, st);
   if (rc != GSX_OK) return rc;
-  return preprocess_bwd_launch(*v, *p, N, c->r1, c->mask, (float4 *)c->gacc, *g, st);
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[7], st));
+  rc = preprocess_bwd_launch(*v, *p, N, c->r1, c->mask, (float4 *)c->gacc, *g, st);
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[8], st));
+  return rc;
+}
+
+int gsx_ctx_enable_timing(gsx_ctx_t *c, int on) {
+  if (!c) return GSX_E_NULL;
+  if (on && !c->ev[0])
+    for (int i = 0; i < 9; ++i) GSX_CUDA(cudaEventCreate(&c->ev[i]));
+  c->timing = on != 0;
+  return GSX_OK;
+}
+
+// ms_out[7]: preprocess_fwd, scan+emit, sort, ranges, composite_fwd, composite_bwd, preprocess_bwd of the last
+// forward + backward issued with timing enabled.  Synchronises the device.
+int gsx_ctx_timing(gsx_ctx_t *c, float *ms_out) {
+  if (!c || !ms_out) return GSX_E_NULL;
+  if (!c->timing) { set_error("timing not enabled"); return GSX_E_ARG; }
+  GSX_CUDA(cudaDeviceSynchronize());
+  const int a[7] = {0, 1, 2, 3, 4, 6, 7}, b[7] = {1, 2, 3, 4, 5, 7, 8};
+  for (int i = 0; i < 7; ++i) GSX_CUDA(cudaEventElapsedTime(&ms_out[i], c->ev[a[i]], c->ev[b[i]]));
+  return GSX_OK;
+}
+
+namespace gsx {
+__global__ void __launch_bounds__(256) k_fma_peak(float *out, int iters) {
+  float a0 = threadIdx.x * 1e-3f, a1 = a0 + 1.f, a2 = a0 + 2.f, a3 = a0 + 3.f, a4 = a0 + 4.f, a5 = a0 + 5.f, a6 = a0 + 6.f,
+        a7 = a0 + 7.f;
+  const float m = 0.999f, c = 1e-4f * blockIdx.x;
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      a0 = fmaf(a0, m, c); a1 = fmaf(a1, m, c); a2 = fmaf(a2, m, c); a3 = fmaf(a3, m, c);
+      a4 = fmaf(a4, m, c); a5 = fmaf(a5, m, c); a6 = fmaf(a6, m, c); a7 = fmaf(a7, m, c);
+    }
+  }
+  const float s = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+  if (s == 123.456f) out[0] = s;
+}
+}  // namespace gsx
+
+// Measured FP32 FMA peak of this device (TFLOP/s, FMA = 2 FLOP): the roofline denominator for the compositing
+// kernels (MEASURED_PEAKS.json only carries HBM and bf16 tensor numbers).
+int gsx_measure_fp32_tflops(float *tflops_host) {
+  if (!tflops_host) return GSX_E_NULL;
+  float *d = nullptr;
+  GSX_CUDA(cudaMalloc(&d, 4));
+  cudaEvent_t e0, e1;
+  GSX_CUDA(cudaEventCreate(&e0)); GSX_CUDA(cudaEventCreate(&e1));
+  const int blocks = kNumSMs * 8, iters = 4096;
+  k_fma_peak<<<blocks, 256>>>(d, 64);
+  float best = 0.f;
+  for (int rep = 0; rep < 5; ++rep) {
+    GSX_CUDA(cudaEventRecord(e0));
+    k_fma_peak<<<blocks, 256>>>(d, iters);
+    GSX_CUDA(cudaEventRecord(e1));
+    GSX_CUDA(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    GSX_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    const double flop = 2.0 * 64.0 * iters * 256.0 * blocks;
+    best = fmaxf(best, (float)(flop / (ms * 1e-3) / 1e12));
+  }
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+  *tflops_host = best;
+  return GSX_OK;
 }
 
 int gsx_ctx_stats(gsx_ctx_t *c, gsx_stats_t *out, void *stream) {

@@ -205,7 +205,8 @@ BinLayout bin_layout(int N, long long capacity) {
 // (*sorted_keys, *sorted_vals) inside the workspace; K in total_dev[0].
 int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius, int ntx, int nty, int N,
                   long long capacity, char *ws, const BinLayout &L, int *ranges, const uint64_t **sorted_keys,
-                  const uint32_t **sorted_vals, cudaStream_t st) {
+                  const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev) {
+  // ev (optional): 3 events recorded after emission, after the sort and after the ranges (stage timing)
   int *touched = (int *)(ws + L.touched), *offsets = (int *)(ws + L.offsets);
   int *block_sums = (int *)(ws + L.block_sums), *total = (int *)(ws + L.total);
   uint64_t *ka = (uint64_t *)(ws + L.keys_a), *kb = (uint64_t *)(ws + L.keys_b);
@@ -217,13 +218,17 @@ int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_
                                                    capacity, ka, va);
     GSX_LAUNCH_CHECK();
   }
+  if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
   int in_b = 0;
   rc = sort_pairs_impl(ka, kb, va, vb, capacity, total, tile_key_bits(ntx * nty), ws + L.sort_ws, L.sort_ws_bytes, st,
                        &in_b);
   if (rc != GSX_OK) return rc;
   *sorted_keys = in_b ? kb : ka;
   *sorted_vals = in_b ? vb : va;
-  return tile_ranges_impl(*sorted_keys, capacity, total, ntx * nty, ranges, st);
+  if (ev) GSX_CUDA(cudaEventRecord(ev[1], st));
+  rc = tile_ranges_impl(*sorted_keys, capacity, total, ntx * nty, ranges, st);
+  if (ev) GSX_CUDA(cudaEventRecord(ev[2], st));
+  return rc;
 }
 
 int count_tiles_launch(const float *uv, int uv_stride, const float4 *radius, const uint8_t *mask, int ntx, int nty, int N, int *touched,
@@ -321,7 +326,7 @@ int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const floa
   const uint64_t *sk;
   const uint32_t *sv;
   rc = bin_sort_impl(uv, 2, xyz_c + 2, 3, (const float4 *)radius, n_tiles_x, n_tiles_y, N, capacity, ws, L, ranges, &sk,
-                     &sv, st);
+                     &sv, st, nullptr);
   if (rc != GSX_OK) return rc;
   rc = copy_ids_launch(sv, sorted_gaussians, capacity, (const int *)(ws + L.total), st);
   if (rc != GSX_OK) return rc;

@@ -214,10 +214,9 @@ __global__ void __launch_bounds__(256) k_tile_ranges(const uint64_t *__restrict_
     return;
   }
   for (long long i = i0; i < n; i += stride) {
-    int cur = (int)(keys[i] >> 32);
-    cur = min(cur, n_tiles - 1);
+    const int cur = (int)min((unsigned)(keys[i] >> 32), (unsigned)(n_tiles - 1));   // clamp as the reference (:313)
     int prev = -1;
-    if (i > 0) prev = min((int)(keys[i - 1] >> 32), n_tiles - 1);
+    if (i > 0) prev = (int)min((unsigned)(keys[i - 1] >> 32), (unsigned)(n_tiles - 1));
     for (int t = prev + 1; t <= cur; ++t) ranges[t] = (int)i;
     if (i == n - 1)
       for (int t = cur + 1; t <= n_tiles; ++t) ranges[t] = (int)n;

@@ -191,6 +191,8 @@ def sort_pairs_u64(keys, vals, key_bits=64):
     """keys: int64 CUDA tensor holding uint64 bit patterns, vals: int32.  Returns sorted copies."""
     n = keys.numel()
     dev = keys.device
+    if n == 0:
+        return keys.clone(), vals.clone()
     k_in, v_in = keys.clone(), vals.clone()
     k_out, v_out = torch.empty_like(k_in), torch.empty_like(v_in)
     wsb = lib().gsx_sort_workspace_bytes(C.c_longlong(max(n, 1)))

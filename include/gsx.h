@@ -182,6 +182,14 @@ typedef struct gsx_state {
 } gsx_state_t;
 int gsx_ctx_state(gsx_ctx_t *ctx, gsx_state_t *out_host);
 
+/* Optional per-stage CUDA-event timing of gsx_forward/gsx_backward (used by bench.py's roofline leg, never inside
+ * the timed throughput region).  ms_out[7] = preprocess_fwd, scan+emit, sort, ranges, composite_fwd, composite_bwd,
+ * preprocess_bwd. */
+int gsx_ctx_enable_timing(gsx_ctx_t *ctx, int on);
+int gsx_ctx_timing(gsx_ctx_t *ctx, float *ms_out);
+/* Measured FP32 FMA peak of the current device in TFLOP/s (roofline denominator of the compositing kernels). */
+int gsx_measure_fp32_tflops(float *tflops_host);
+
 /* Host-buffer entry point (what bench.py's e2e leg and a host-side caller use): copies the view + grad_image
  * from (pinned) host memory, runs forward+backward, copies the image back.  params/grads stay on the device as
  * in the reference trainer (CudaDataManager). */
