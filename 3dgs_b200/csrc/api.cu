@@ -44,6 +44,8 @@ int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, c
 int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
                          int W, int H, float bg, const int *spp, const float *wpp, const float *grad_image,
                          float *packed_grads, cudaStream_t st);
+int count_work_launch(const float4 *r0, const float4 *r1, const int *sorted, const int *ranges, int W, int H,
+                      const int *spp, unsigned long long *out_dev, cudaStream_t st);
 int preprocess_fwd_launch(const gsx_view_t &v, const gsx_params_t &p, int N, float4 *r0, float4 *r1, float4 *r2,
                           float4 *radius, float *depth, uint8_t *mask, int *touched, cudaStream_t st);
 int preprocess_bwd_launch(const gsx_view_t &v, const gsx_params_t &p, int N, const float4 *r1, const uint8_t *mask,
@@ -189,6 +191,22 @@ int gsx_backward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[7], st));
   rc = preprocess_bwd_launch(*v, *p, N, c->r1, c->mask, (float4 *)c->gacc, *g, st);
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[8], st));
+  return rc;
+}
+
+// out_host[2] = {S, S+} of the last forward (work counters for the roofline arithmetic).  Synchronises.
+int gsx_ctx_count_work(gsx_ctx_t *c, unsigned long long *out_host, void *stream) {
+  if (!c || !out_host) return GSX_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long *d = nullptr;
+  GSX_CUDA(cudaMalloc(&d, 2 * sizeof(unsigned long long)));
+  GSX_CUDA(cudaMemsetAsync(d, 0, 2 * sizeof(unsigned long long), st));
+  int rc = count_work_launch(c->r0, c->r1, (const int *)c->sorted_vals, c->ranges, c->last_w, c->last_h, c->spp, d, st);
+  if (rc == GSX_OK) {
+    GSX_CUDA(cudaMemcpyAsync(out_host, d, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+    GSX_CUDA(cudaStreamSynchronize(st));
+  }
+  cudaFree(d);
   return rc;
 }
 

@@ -283,6 +283,42 @@ k_composite_bwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
   }
 }
 
+// Work counters for the roofline arithmetic (bench.py only): S = sum of splats_per_pixel (pixel-entries the
+// reference evaluates), S+ = those with alpha >= 1/255.  One thread per pixel, no staging: not a hot path.
+__global__ void __launch_bounds__(CB)
+k_count_work(const float4 *__restrict__ r0, const float4 *__restrict__ r1, const int *__restrict__ sorted,
+             const int *__restrict__ ranges, int ntx, int W, int H, const int *__restrict__ spp,
+             unsigned long long *__restrict__ out) {
+  const int tile = blockIdx.x, tid = threadIdx.x;
+  const int px = (tile % ntx) * 16 + (tid & 15), py = (tile / ntx) * 16 + (tid >> 4);
+  unsigned long long s = 0, sp = 0;
+  if (px < W && py < H) {
+    const int start = ranges[tile];
+    const int count = spp[(size_t)py * W + px];
+    s = (unsigned long long)count;
+    for (int i = 0; i < count; ++i) {
+      const int g = sorted[start + i];
+      const float4 q0 = __ldg(r0 + g), q1 = __ldg(r1 + g);
+      const float dx = q0.x - (float)px, dy = q0.y - (float)py;
+      const float power = fminf(0.0f, -0.5f * (q1.x * dx * dx + q1.z * dy * dy) - q1.y * dx * dy);
+      sp += (fminf(0.99f, q1.w * __expf(power)) >= ALPHA_MIN) ? 1ull : 0ull;
+    }
+  }
+  for (int off = 16; off > 0; off >>= 1) {
+    s += __shfl_down_sync(0xffffffffu, s, off);
+    sp += __shfl_down_sync(0xffffffffu, sp, off);
+  }
+  if ((tid & 31) == 0) { atomicAdd(out, s); atomicAdd(out + 1, sp); }
+}
+
+int count_work_launch(const float4 *r0, const float4 *r1, const int *sorted, const int *ranges, int W, int H,
+                      const int *spp, unsigned long long *out_dev, cudaStream_t st) {
+  const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
+  k_count_work<<<ntx * nty, CB, 0, st>>>(r0, r1, sorted, ranges, ntx, W, H, spp, out_dev);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
 int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
                          int W, int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st) {
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;

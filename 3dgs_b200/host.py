@@ -330,6 +330,22 @@ class Rasterizer:
         io = C.c_void_p(image_host.data_ptr()) if image_host is not None else C.c_void_p(0)
         check(lib().gsx_render_view_host(self.h, C.byref(view), C.byref(p), g.N, gi, io, C.byref(gs), _stream()))
 
+    def enable_timing(self, on=True):
+        check(lib().gsx_ctx_enable_timing(self.h, int(bool(on))))
+
+    def timing(self):
+        """ms per stage of the last timed forward+backward (synchronises)."""
+        ms = (C.c_float * 7)()
+        check(lib().gsx_ctx_timing(self.h, ms))
+        names = ("preprocess_fwd", "scan_emit", "sort", "ranges", "composite_fwd", "composite_bwd", "preprocess_bwd")
+        return dict(zip(names, [float(x) for x in ms]))
+
+    def count_work(self):
+        """(S, S+) of the last forward: evaluated pixel-entries and those with alpha >= 1/255."""
+        out = (C.c_ulonglong * 2)()
+        check(lib().gsx_ctx_count_work(self.h, out, _stream()))
+        return int(out[0]), int(out[1])
+
     def state(self):
         """Zero-copy torch views of the saved forward state (for tests / inspection)."""
         s = GsxState()
@@ -359,6 +375,12 @@ class _CudaArray:
         self.__cuda_array_interface__ = dict(shape=tuple(shape), typestr=typestr, data=(int(ptr), False), version=2,
                                              strides=strides)
         self._itemsize = itemsize
+
+
+def measure_fp32_tflops():
+    out = C.c_float(0)
+    check(lib().gsx_measure_fp32_tflops(C.byref(out)))
+    return float(out.value)
 
 
 def _from_ptr(ptr, shape, dtype):

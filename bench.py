@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""bench.py -- fwd+bwd views/s of the splatting hot path on BASELINE.json's config 4:
+synthetic 6M Gaussians, SH deg 3, 1920x1080, a batch of 8 views sharded over the GPUs with an NCCL allreduce of
+the per-Gaussian parameter gradients (one process per GPU; `python bench.py --gpus N --steps K --warmup W`, under
+torchrun for N > 1).  One step = one batch of 8 views (fwd+bwd of every view + the gradient allreduce).
+
+Prints ONE JSON line (rank 0).  `value` = views/s with inputs resident in HBM; `e2e` = the same metric through the
+host-buffer entry point (gsx_render_view_host: H2D of the view's camera block and loss-gradient image from pinned
+memory, D2H of the rendered image, every view); `roofline` = the dominant kernel against the measured peak;
+`cpu_baseline` = the CPU oracle timed on this box's host cores on a bounded sample (rank 0, N = 1 only).
+`--impl reference` times the reference's path on the host cores (the oracle port: the reference has no CPU path and
+its CUDA build is timed separately, see BASELINE.md / DESIGN.md).
+"""
+import argparse
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_VIEWS = 8
+METRIC, UNIT = "fwd+bwd views/s (6M Gaussians, SH deg 3, 1920x1080, batch of 8 views)", "views/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="C4", help="scene config from 3dgs_b200/scenes.py (C4 = the benchmarked one)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=150.0, help="budget for the CPU legs")
+    return ap.parse_args()
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled every 200 ms DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.p, self.lines, self.index = None, [], index
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms",
+                                       "200", "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL,
+                                      text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.p = None
+
+    def _read(self):
+        for ln in self.p.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.p.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, val in zip(names, f[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_scene(cfg):
+    gs = importlib.import_module("3dgs_b200")
+    S = gs.scenes
+    N, W, H, l_max = S.CONFIGS[cfg]
+    idx = int(cfg[1:])
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=0x3D65 + idx)
+    cams = [S.orbit_camera(W, H, azimuth_deg=45.0 * k) for k in range(N_VIEWS)]
+    return gs, S, N, W, H, l_max, g, cams
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs
+def cpu_view_seconds(S, g, cam, W, H, l_max, gi):
+    """one full view fwd+bwd through the CPU oracle (all host threads)"""
+    from oracle import golden as G
+    gv = G.make_view(cam["view"], cam["proj"], cam["campos"], cam["fx"], cam["fy"], W, H, near_thresh=S.NEAR_THRESH,
+                     cull_padding=S.CULL_PADDING, mh_dist=S.MH_DIST, background=0.0, l_max=l_max)
+    t0 = time.perf_counter()
+    st = G.forward(gv, g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+    G.backward(gv, st, gi)
+    return time.perf_counter() - t0, st.P, st.K
+
+
+def run_reference_arm(args):
+    """The reference's implementation of the path timed on the host cores.  The reference itself is CUDA-only (no CPU
+    path exists), so this is the oracle port (kind 'port') with every host thread.  One step = ONE view of
+    the same scene (a bounded sample of the 8-view batch); value = views/s."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import golden as G
+    gs, S, N, W, H, l_max, g, cams = make_scene(args.config)
+    cores = G.lib().gold_max_threads()
+    gi = S.grad_image(W, H)
+    for k in range(args.warmup):
+        cpu_view_seconds(S, g, cams[k % N_VIEWS], W, H, l_max, gi)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        cpu_view_seconds(S, g, cams[k % N_VIEWS], W, H, l_max, gi)
+    dt = time.perf_counter() - t0
+    v = args.steps / dt
+    sample = f"{args.steps} single views (fwd+bwd) of the {args.config} scene, one per step, {cores} OpenMP threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{args.config}: synthetic {N} Gaussians, SH deg {l_max}, {W}x{H}; one view per step on the host CPU"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "the reference has no CPU path (CUDA-only); this is the scalar C++ golden with OpenMP"}))
+
+
+# ------------------------------------------------------------------------------------------------ GPU arm
+def flat_grads(torch, N, sh_stride, device):
+    """All parameter gradients as views of ONE flat buffer so the gradient exchange is a single NCCL allreduce
+    (236 B/Gaussian at deg 3).  Segments are padded to 16 B."""
+    seg = [("xyz", 3), ("scale", 3), ("quaternion", 4), ("opacity", 1), ("band0", 3), ("sh", max(sh_stride, 1))]
+    offs, off = {}, 0
+    for nm, w in seg:
+        offs[nm] = off
+        off += (N * w + 3) // 4 * 4
+    flat = torch.zeros(off, device=device, dtype=torch.float32)
+    views = {}
+    for nm, w in seg:
+        v = flat[offs[nm]: offs[nm] + N * w]
+        views[nm] = v.view(N, w) if nm != "opacity" else v
+    return flat, views
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs CUDA devices: there is no CPU fallback for the product path"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert N_VIEWS % world == 0, "the 8-view batch shards over 1, 2, 4 or 8 GPUs"
+    gs, S, N, W, H, l_max, g, cams = make_scene(args.config)
+    Hh = gs.host
+    hbm_peak, peak_src = load_peaks()
+
+    gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"], device=dev)
+    flat, gviews = flat_grads(torch, N, gd.sh_stride, dev)
+    gd.grads = gviews
+    my_views = list(range(rank, N_VIEWS, world))                   # view sharding: rank r renders views r, r+world, ...
+    OVER = gs._ffi.GSX_GRAD_OVERWRITE
+    mk = lambda cam, flags: Hh.make_view(cam["view"], cam["proj"], cam["campos"], cam["fx"], cam["fy"], W, H,
+                                         near_thresh=S.NEAR_THRESH, cull_padding=S.CULL_PADDING, mh_dist=S.MH_DIST,
+                                         background=0.0, l_max=l_max, flags=flags)
+    # first view of the batch overwrites the gradient buffers (no 1.4 GB memset per step), the rest accumulate
+    vstructs = [mk(cams[k], OVER if i == 0 else 0) for i, k in enumerate(my_views)]
+    r = Hh.Rasterizer(N, W, H, instance_capacity=4 * N)
+    gi_host = torch.as_tensor(S.grad_image(W, H)).pin_memory()
+    img_host = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
+    gi_dev = gi_host.to(dev)
+
+    # size the instance capacity once (the only host sync of the set-up), record the work counters
+    stats = []
+    for v in vstructs:
+        stats.append(r.forward_checked(v, gd))
+    for v in vstructs:                                             # re-check after any growth
+        assert not r.forward_checked(v, gd)["overflow"]
+
+    def step():
+        for v in vstructs:
+            r.forward(v, gd)
+            r.backward(v, gd, gi_dev)
+        if world > 1:
+            dist.all_reduce(flat)
+
+    def step_e2e():
+        for v in vstructs:
+            r.render_view_host(v, gd, gi_host, img_host)
+        if world > 1:
+            dist.all_reduce(flat)
+            torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    clocks = sampler.stop() if rank == 0 else None
+
+    # e2e leg: host buffers in, host image out, every view
+    for _ in range(2):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    barrier()
+    dt_e2e = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(dt_e2e, op=dist.ReduceOp.MAX)
+    dt_e2e = float(dt_e2e.item())
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline leg (rank 0): per-stage CUDA-event timing of this rank's views, outside the timed region --------
+    r.enable_timing(True)
+    acc, reps = {}, 3
+    work = dict(P=0, K=0, S=0, Sp=0)
+    for v, st in zip(vstructs, stats):
+        for _ in range(reps):
+            r.forward(v, gd)
+            r.backward(v, gd, gi_dev)
+            for k_, x in r.timing().items():
+                acc[k_] = acc.get(k_, 0.0) + x
+        r.forward(v, gd)
+        s_, sp_ = r.count_work()
+        r.backward(v, gd, gi_dev)
+        stx = r.stats()
+        work["P"] += stx["P"]; work["K"] += stx["K"]; work["S"] += s_; work["Sp"] += sp_
+    r.enable_timing(False)
+    nv = len(vstructs)
+    stage_ms = {k_: x / (reps * nv) for k_, x in acc.items()}
+    P, K, Sx, Sp = (work[k_] / nv for k_ in ("P", "K", "S", "Sp"))
+    T = ((W + 15) // 16) * ((H + 15) // 16)
+    D = 3 * ((l_max + 1) ** 2 - 1)
+    passes = (32 + max(1, int(np.ceil(np.log2(T)))) + 7) // 8
+    fp32_peak = Hh.measure_fp32_tflops()
+    # algorithmic work per launch (SURVEY 8d / BASELINE.md section 5)
+    alg = {
+        "preprocess_fwd": ("hbm", 12 * N + (32 + 4 * D + 12) * P + 48 * P),
+        "scan_emit": ("hbm", 12 * K + 12 * N),
+        "sort": ("hbm", (8 + 24 * passes) * K),
+        "ranges": ("hbm", 8 * K + 4 * (T + 1)),
+        "composite_fwd": ("fp32", 18 * Sx),
+        "composite_bwd": ("fp32", 10 * Sx + 46 * Sp),
+        "preprocess_bwd": ("hbm", (32 + 4 * D + 12 + 36) * P + (44 + 4 * D) * P),
+    }
+    stages = {}
+    for k_, (bound, w) in alg.items():
+        t = stage_ms[k_] * 1e-3
+        if bound == "hbm":
+            a, pk, un = w / t / 1e9, hbm_peak, "GB/s"
+        else:
+            a, pk, un = w / t / 1e12, fp32_peak, "TFLOP/s"
+        stages[k_] = {"ms": round(stage_ms[k_], 4), "bound": bound, "achieved": round(a, 2), "peak": round(pk, 2),
+                      "unit": un, "frac": round(a / pk, 4)}
+    top = max(stage_ms, key=stage_ms.get)
+    roof = dict(stages[top])
+    roof.pop("ms")
+    roof.update({"kernel": top, "traffic": None, "ms": round(stage_ms[top], 4),
+                 "peak_source": peak_src if roof["bound"] == "hbm" else "FP32 FMA peak measured in this run (gsx_measure_fp32_tflops)",
+                 "share_of_view": round(stage_ms[top] / sum(stage_ms.values()), 3)})
+
+    views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
+    per_view = 15 + passes - 6 + 2                                   # kernels launched per view by libgsx
+    out = {
+        "metric": METRIC, "value": views_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "ms_per_view_per_gpu": ms_total / args.steps / len(my_views),
+        "config": {"workload": f"{args.config}: synthetic {N} Gaussians, SH deg {l_max}, {W}x{H}, batch of {N_VIEWS} views "
+                               f"sharded over {world} GPU(s), NCCL allreduce of {flat.numel() * 4 / 1e9:.2f} GB gradients",
+                   "views_per_step": N_VIEWS, "l2": "inputs larger than L2 (1.4 GB parameters + 1.4 GB gradients per view)",
+                   "visible_P": int(P), "instances_K": int(K), "pixel_entries_S": int(Sx), "contributing_Splus": int(Sp)},
+        "clocks": clocks,
+        "e2e": {"value": N_VIEWS * args.steps / dt_e2e, "unit": UNIT,
+                "h2d_bytes_per_step": N_VIEWS * (W * H * 3 * 4 + 200), "d2h_bytes_per_step": N_VIEWS * W * H * 3 * 4},
+        "gpu_launches": per_view * len(my_views) * args.steps * world,
+        "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": round(fp32_peak, 2),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import golden as G
+        cores = G.lib().gold_max_threads()
+        t, _, _ = cpu_view_seconds(S, g, cams[0], W, H, l_max, gi_host.numpy())
+        out["cpu_baseline"] = {"value": 1.0 / t, "unit": UNIT, "cores": cores, "kind": "port",
+                               "sample": f"1 view (fwd+bwd) of the same scene through oracle/libgolden.so, {cores} OpenMP threads, {t:.1f} s"}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

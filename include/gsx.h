@@ -187,6 +187,9 @@ int gsx_ctx_state(gsx_ctx_t *ctx, gsx_state_t *out_host);
  * preprocess_bwd. */
 int gsx_ctx_enable_timing(gsx_ctx_t *ctx, int on);
 int gsx_ctx_timing(gsx_ctx_t *ctx, float *ms_out);
+/* out_host[2] = {S, S+}: evaluated pixel-entries (sum of splats_per_pixel) and those with alpha >= 1/255 in the
+ * last forward -- the units of the compositing roofline.  Synchronises. */
+int gsx_ctx_count_work(gsx_ctx_t *ctx, unsigned long long *out_host, void *stream);
 /* Measured FP32 FMA peak of the current device in TFLOP/s (roofline denominator of the compositing kernels). */
 int gsx_measure_fp32_tflops(float *tflops_host);
 
