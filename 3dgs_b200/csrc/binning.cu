@@ -31,9 +31,10 @@ __device__ __forceinline__ int count_tiles(float u, float v, float4 r, int ntx, 
   *coarse = nx * ny;
   if (nx * ny == 0) return 0;
   const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
+  const TileRange tr = sat_aabb_range(s, w);
   int c = 0;
-  for (int tx = w.x0; tx < w.x1; ++tx)
-    for (int ty = w.y0; ty < w.y1; ++ty) c += sat_tile(s, tx, ty) ? 1 : 0;
+  for (int tx = tr.x0; tx <= tr.x1; ++tx)
+    for (int ty = tr.y0; ty <= tr.y1; ++ty) c += sat_tile_rot(s, tx, ty) ? 1 : 0;
   return c;
 }
 
@@ -69,9 +70,10 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
   const uint64_t zb = float_sort_bits(depth[(size_t)i * depth_stride]);
   const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
   const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
-  for (int tx = w.x0; tx < w.x1; ++tx)
-    for (int ty = w.y0; ty < w.y1; ++ty)
-      if (sat_tile(s, tx, ty)) {
+  const TileRange tr = sat_aabb_range(s, w);
+  for (int tx = tr.x0; tx <= tr.x1; ++tx)
+    for (int ty = tr.y0; ty <= tr.y1; ++ty)
+      if (sat_tile_rot(s, tx, ty)) {
         keys[o] = ((uint64_t)(unsigned)(ty * ntx + tx) << 32) | zb;
         vals[o] = (uint32_t)i;
         ++o;

@@ -272,6 +272,28 @@ __device__ __forceinline__ TileWindow candidate_window(float u, float v, float r
   return w;
 }
 
+// Exact sub-range of the candidate window that survives SAT axes 0 and 1 (the OBB's own AABB against the tile
+// rows/columns).  The reference rejects tile column tx iff  min_x > 16(tx+1) || max_x < 16 tx  (culling.cu:103-110,
+// inclusive bounds); with exact power-of-two scaling that is  ceil(min_x/16)-1 <= tx <= floor(max_x/16).  NaN
+// bounds constrain nothing (fmaxf/fminf drop them), exactly as the reference's false comparisons do.  Small
+// Gaussians thus test 1-4 tiles against axes 2 and 3 instead of >= 25.
+struct TileRange { int x0, x1, y0, y1; };   // inclusive; empty when x1 < x0 or y1 < y0
+__device__ __forceinline__ TileRange sat_aabb_range(const ObbSat &s, const TileWindow &w) {
+  TileRange r;
+  const float fx0 = (float)w.x0, fx1 = (float)(w.x1 - 1), fy0 = (float)w.y0, fy1 = (float)(w.y1 - 1);
+  r.x0 = (int)fminf(fmaxf(ceilf(s.min_x * 0.0625f) - 1.0f, fx0), fx1 + 1.0f);
+  r.x1 = (int)fmaxf(fminf(floorf(s.max_x * 0.0625f), fx1), fx0 - 1.0f);
+  r.y0 = (int)fminf(fmaxf(ceilf(s.min_y * 0.0625f) - 1.0f, fy0), fy1 + 1.0f);
+  r.y1 = (int)fmaxf(fminf(floorf(s.max_y * 0.0625f), fy1), fy0 - 1.0f);
+  return r;
+}
+// axes 2 and 3 only (axes 0/1 already decided by sat_aabb_range)
+__device__ __forceinline__ bool sat_tile_rot(const ObbSat &s, int tx, int ty) {
+  const float l = (float)tx * 16.0f, r = (float)(tx + 1) * 16.0f, t = (float)ty * 16.0f, b = (float)(ty + 1) * 16.0f;
+  if (!sat_axis(s.a2x, s.a2y, s.lo2, s.hi2, l, r, t, b)) return false;
+  return sat_axis(s.a3x, s.a3y, s.lo3, s.hi3, l, r, t, b);
+}
+
 // order-preserving map float -> uint32 (handles negative depths that only the per-function F7 can see)
 __device__ __forceinline__ uint32_t float_sort_bits(float z) {
   const uint32_t b = __float_as_uint(z);
@@ -422,7 +444,7 @@ __device__ __forceinline__ float3 cam_point_backward(const float *v, float gx, f
 // [axis][k] derivative table (Q12).
 template <int L>
 __device__ __forceinline__ float3 sh_backward(float px, float py, float pz, float3 campos, const float *band0,
-                                              const float *__restrict__ sh, float gr, float gg, float gb, bool compat,
+                                              const float *sh /* may alias sh_grad: row k is read before it is written */, float gr, float gg, float gb, bool compat,
                                               float *sh_grad, float *b0_grad, bool accumulate) {
   constexpr int n = (L + 1) * (L + 1);
   const float dx = px - campos.x, dy = py - campos.y, dz = pz - campos.z;
