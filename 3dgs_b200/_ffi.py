@@ -25,6 +25,8 @@ SYMBOLS = [
     "gsx_compute_camera_space_points_backward", "gsx_sort_workspace_bytes", "gsx_sort_pairs_u64", "gsx_tile_ranges",
     "gsx_ctx_create", "gsx_ctx_destroy", "gsx_forward", "gsx_backward", "gsx_ctx_stats", "gsx_ctx_reserve",
     "gsx_ctx_state", "gsx_render_view_host", "gsx_ctx_enable_timing", "gsx_ctx_timing", "gsx_ctx_count_work", "gsx_measure_fp32_tflops",
+    "gsx_batch_reserve", "gsx_batch_forward_params", "gsx_batch_forward_view", "gsx_batch_backward_view",
+    "gsx_batch_backward_params", "gsx_batch_render_host",
 ]
 
 

@@ -7,6 +7,7 @@
 #include <stdarg.h>
 
 #include "gsx_common.cuh"
+#include "gsx_view.cuh"
 
 namespace gsx {
 
@@ -36,9 +37,12 @@ int check_device_ptr(const void *p, const char *name) {
 
 // from binning.cu / composite.cu / preprocess.cu
 BinLayout bin_layout(int N, long long capacity);
-int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius, int ntx,
-                  int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
+int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
+                  const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
                   const uint64_t **sorted_keys, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev);
+int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, cudaStream_t st);
+int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, const gsx_grads_t &g, int flags,
+                     cudaStream_t st);
 int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
                          int W, int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st);
 int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
@@ -55,30 +59,34 @@ int preprocess_bwd_launch(const gsx_view_t &v, const gsx_params_t &p, int N, con
 
 using namespace gsx;
 
+struct gsx_slot {          // per-view state that must outlive the view inside a batch
+  SlotPtrs p{};
+  gsx_view_t view{};
+  bool allocated = false;
+};
+
 struct gsx_ctx {
   int max_n = 0, max_w = 0, max_h = 0;
   long long capacity = 0;
-  // per-Gaussian state of the last forward
-  float4 *r0 = nullptr, *r1 = nullptr, *r2 = nullptr, *radius = nullptr;
-  float *depth = nullptr;
-  uint8_t *mask = nullptr;
-  float *gacc = nullptr;            // [N][12]
-  // binning workspace (depends on capacity)
+  gsx_slot slot[GSX_MAX_BATCH];   // slot 0 is the single-view path's state
+  int n_slots = 0, cur = 0;       // cur: slot of the last forward
+  // binning workspace (depends on capacity), shared by the slots: a view's sorted list lives until the next forward
   char *bin_ws = nullptr;
   BinLayout L{};
   int *ranges = nullptr;
-  // per-pixel state
+  // per-pixel state of the last forward
   float *image = nullptr, *wpp = nullptr, *grad_image = nullptr;
   int *spp = nullptr;
-  // last forward
   const uint64_t *sorted_keys = nullptr;
   const uint32_t *sorted_vals = nullptr;
   int last_n = 0, last_w = 0, last_h = 0;
+  int batch_n = 0, batch_nv = 0, batch_lmax = 0;
   int *h_stats = nullptr;           // pinned: [0] = K, [1] = P
   int *d_P = nullptr;
-  // optional stage timing (gsx_ctx_enable_timing): events 0..5 forward, 6..8 backward
+  // optional stage timing (gsx_ctx_enable_timing): 0,1 per-Gaussian forward; 2 view start, 3 emit, 4 sort, 5 ranges,
+  // 6 compositing forward; 7,8 compositing backward; 9,10 per-Gaussian backward
   bool timing = false;
-  cudaEvent_t ev[9] = {};
+  cudaEvent_t ev[11] = {};
 };
 
 namespace gsx {
@@ -96,6 +104,60 @@ static int alloc_bin(gsx_ctx *c, long long capacity) {
   GSX_CUDA(cudaMalloc(&c->bin_ws, c->L.bytes));
   return GSX_OK;
 }
+
+static int alloc_slot(gsx_ctx *c, int k) {
+  gsx_slot &s = c->slot[k];
+  if (s.allocated) return GSX_OK;
+  const size_t n = (size_t)c->max_n;
+  GSX_CUDA(cudaMalloc(&s.p.r0, n * sizeof(float4)));
+  GSX_CUDA(cudaMalloc(&s.p.r1, n * sizeof(float4)));
+  GSX_CUDA(cudaMalloc(&s.p.r2, n * sizeof(float4)));
+  GSX_CUDA(cudaMalloc(&s.p.radius, n * sizeof(float4)));
+  GSX_CUDA(cudaMalloc(&s.p.depth, n * sizeof(float)));
+  GSX_CUDA(cudaMalloc(&s.p.mask, n));
+  GSX_CUDA(cudaMalloc(&s.p.touched, n * sizeof(int)));
+  GSX_CUDA(cudaMalloc(&s.p.gacc, n * 12 * sizeof(float)));
+  GSX_CUDA(cudaMemset(s.p.gacc, 0, n * 12 * sizeof(float)));
+  GSX_CUDA(cudaMemset(s.p.mask, 0, n));
+  GSX_CUDA(cudaMemset(s.p.touched, 0, n * sizeof(int)));
+  s.allocated = true;
+  if (k + 1 > c->n_slots) c->n_slots = k + 1;
+  return GSX_OK;
+}
+static void free_slot(gsx_slot &s) {
+  if (!s.allocated) return;
+  cudaFree(s.p.r0); cudaFree(s.p.r1); cudaFree(s.p.r2); cudaFree(s.p.radius); cudaFree(s.p.depth); cudaFree(s.p.mask);
+  cudaFree(s.p.touched); cudaFree(s.p.gacc);
+  s = gsx_slot();
+}
+
+// bin + sort + ranges + compositing forward of the view whose per-Gaussian records are in slot k
+static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
+  const gsx_slot &s = c->slot[k];
+  const gsx_view_t &v = s.view;
+  const int ntx = (v.width + 15) / 16, nty = (v.height + 15) / 16;
+  c->last_n = N; c->last_w = v.width; c->last_h = v.height; c->cur = k;
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[2], st));
+  int rc = bin_sort_impl((const float *)s.p.r0, 4, s.p.depth, 1, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, c->bin_ws,
+                         c->L, c->ranges, &c->sorted_keys, &c->sorted_vals, st, c->timing ? &c->ev[3] : nullptr);
+  if (rc != GSX_OK) return rc;
+  rc = composite_fwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, v.width, v.height, v.background,
+                            c->spp, c->wpp, c->image, st);
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[6], st));
+  return rc;
+}
+
+static int check_view(gsx_ctx *c, const gsx_view_t *v, const gsx_params_t *p, int N) {
+  if (N < 0 || N > c->max_n || v->width <= 0 || v->height <= 0 || v->width > c->max_w || v->height > c->max_h ||
+      (size_t)v->width * v->height > (size_t)c->max_w * c->max_h) {
+    set_error("view %dx%d / N %d exceeds the context (%d, %dx%d)", v->width, v->height, N, c->max_n, c->max_w, c->max_h);
+    return GSX_E_ARG;
+  }
+  if (v->l_max < 0 || v->l_max > 3) { set_error("l_max %d out of range 0..3", v->l_max); return GSX_E_ARG; }
+  const int shf = ((v->l_max + 1) * (v->l_max + 1) - 1) * 3;
+  if (v->l_max > 0 && p->sh_stride < shf) { set_error("sh_stride %d < %d", p->sh_stride, shf); return GSX_E_ARG; }
+  return GSX_OK;
+}
 }  // namespace gsx
 
 extern "C" {
@@ -107,17 +169,12 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
   if (!out || max_gaussians <= 0 || max_width <= 0 || max_height <= 0) { set_error("bad ctx arguments"); return GSX_E_ARG; }
   gsx_ctx *c = new gsx_ctx();
   c->max_n = max_gaussians; c->max_w = max_width; c->max_h = max_height;
-  const size_t n = (size_t)max_gaussians, px = (size_t)max_width * max_height;
+  const size_t px = (size_t)max_width * max_height;
   const int T = ((max_width + 15) / 16) * ((max_height + 15) / 16);
-  GSX_CUDA(cudaMalloc(&c->r0, n * sizeof(float4)));
-  GSX_CUDA(cudaMalloc(&c->r1, n * sizeof(float4)));
-  GSX_CUDA(cudaMalloc(&c->r2, n * sizeof(float4)));
-  GSX_CUDA(cudaMalloc(&c->radius, n * sizeof(float4)));
-  GSX_CUDA(cudaMalloc(&c->depth, n * sizeof(float)));
-  GSX_CUDA(cudaMalloc(&c->mask, n));
-  GSX_CUDA(cudaMalloc(&c->gacc, n * 12 * sizeof(float)));
-  GSX_CUDA(cudaMemset(c->gacc, 0, n * 12 * sizeof(float)));
-  GSX_CUDA(cudaMemset(c->mask, 0, n));
+  {
+    int rc0 = alloc_slot(c, 0);
+    if (rc0 != GSX_OK) return rc0;
+  }
   GSX_CUDA(cudaMalloc(&c->ranges, sizeof(int) * (size_t)(T + 1)));
   GSX_CUDA(cudaMalloc(&c->image, px * 3 * sizeof(float)));
   GSX_CUDA(cudaMalloc(&c->wpp, px * sizeof(float)));
@@ -134,8 +191,8 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
 
 int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (!c) return GSX_OK;
-  cudaFree(c->r0); cudaFree(c->r1); cudaFree(c->r2); cudaFree(c->radius); cudaFree(c->depth); cudaFree(c->mask);
-  cudaFree(c->gacc); cudaFree(c->bin_ws); cudaFree(c->ranges); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
+  for (int k = 0; k < GSX_MAX_BATCH; ++k) free_slot(c->slot[k]);
+  cudaFree(c->bin_ws); cudaFree(c->ranges); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
   cudaFree(c->grad_image); cudaFree(c->d_P); cudaFreeHost(c->h_stats);
   delete c;
   return GSX_OK;
@@ -151,47 +208,127 @@ int gsx_ctx_reserve(gsx_ctx_t *c, long long instance_capacity) {
 
 int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N, void *stream) {
   if (!c || !v || !p) { set_error("null ctx/view/params"); return GSX_E_NULL; }
-  if (N < 0 || N > c->max_n || v->width <= 0 || v->height <= 0 || v->width > c->max_w || v->height > c->max_h ||
-      (size_t)v->width * v->height > (size_t)c->max_w * c->max_h) {
-    set_error("view %dx%d / N %d exceeds the context (%d, %dx%d)", v->width, v->height, N, c->max_n, c->max_w, c->max_h);
-    return GSX_E_ARG;
-  }
-  if (v->l_max < 0 || v->l_max > 3) { set_error("l_max %d out of range 0..3", v->l_max); return GSX_E_ARG; }
-  const int shf = ((v->l_max + 1) * (v->l_max + 1) - 1) * 3;
-  if (v->l_max > 0 && p->sh_stride < shf) { set_error("sh_stride %d < %d", p->sh_stride, shf); return GSX_E_ARG; }
+  int rc = check_view(c, v, p, N);
+  if (rc != GSX_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  const int ntx = (v->width + 15) / 16, nty = (v->height + 15) / 16;
-  c->last_n = N; c->last_w = v->width; c->last_h = v->height;
-  int *touched = (int *)(c->bin_ws + c->L.touched);
+  gsx_slot &s = c->slot[0];
+  s.view = *v;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
-  int rc = preprocess_fwd_launch(*v, *p, N, c->r0, c->r1, c->r2, c->radius, c->depth, c->mask, touched, st);
+  rc = preprocess_fwd_launch(*v, *p, N, s.p.r0, s.p.r1, s.p.r2, s.p.radius, s.p.depth, s.p.mask, s.p.touched, st);
   if (rc != GSX_OK) return rc;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[1], st));
-  rc = bin_sort_impl((const float *)c->r0, 4, c->depth, 1, c->radius, ntx, nty, N, c->capacity, c->bin_ws, c->L, c->ranges,
-                     &c->sorted_keys, &c->sorted_vals, st, c->timing ? &c->ev[2] : nullptr);
-  if (rc != GSX_OK) return rc;
-  rc = composite_fwd_packed(c->r0, c->r1, c->r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
-                            v->background, c->spp, c->wpp, c->image, st);
-  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[5], st));
-  return rc;
+  return forward_view(c, 0, N, st);
 }
 
 int gsx_backward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N, const float *grad_image,
                  const gsx_grads_t *g, void *stream) {
   if (!c || !v || !p || !g || !grad_image) { set_error("null argument"); return GSX_E_NULL; }
-  if (N != c->last_n || v->width != c->last_w || v->height != c->last_h) {
+  if (c->cur != 0 || N != c->last_n || v->width != c->last_w || v->height != c->last_h) {
     set_error("gsx_backward does not match the last gsx_forward on this context");
     return GSX_E_ARG;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[6], st));
-  int rc = composite_bwd_packed(c->r0, c->r1, c->r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
-                                v->background, c->spp, c->wpp, grad_image, c->gacc, st);
-  if (rc != GSX_OK) return rc;
+  const gsx_slot &s = c->slot[0];
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[7], st));
-  rc = preprocess_bwd_launch(*v, *p, N, c->r1, c->mask, (float4 *)c->gacc, *g, st);
+  int rc = composite_bwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
+                                v->background, c->spp, c->wpp, grad_image, (float *)s.p.gacc, st);
+  if (rc != GSX_OK) return rc;
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[8], st));
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[9], st));
+  rc = preprocess_bwd_launch(*v, *p, N, s.p.r1, s.p.mask, s.p.gacc, *g, st);
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[10], st));
+  return rc;
+}
+
+// ---- batch path: the views of one training batch share one pass over the parameters (batch.cu) ----------------
+int gsx_batch_reserve(gsx_ctx_t *c, int n_slots) {
+  if (!c) return GSX_E_NULL;
+  if (n_slots < 1 || n_slots > GSX_MAX_BATCH) { set_error("n_slots %d out of range 1..%d", n_slots, GSX_MAX_BATCH); return GSX_E_ARG; }
+  for (int k = 0; k < n_slots; ++k) {
+    int rc = alloc_slot(c, k);
+    if (rc != GSX_OK) return rc;
+  }
+  return GSX_OK;
+}
+
+static int fill_batch_const(gsx_ctx *c, int nv, BatchConst *bc) {
+  bc->nv = nv;
+  for (int k = 0; k < nv; ++k) { bc->v[k] = make_view_const(c->slot[k].view); bc->s[k] = c->slot[k].p; }
+  return GSX_OK;
+}
+
+int gsx_batch_forward_params(gsx_ctx_t *c, const gsx_view_t *views, int n_views, const gsx_params_t *p, int N,
+                             void *stream) {
+  if (!c || !views || !p) { set_error("null ctx/views/params"); return GSX_E_NULL; }
+  if (n_views < 1 || n_views > c->n_slots) { set_error("n_views %d exceeds the reserved slots (%d)", n_views, c->n_slots); return GSX_E_ARG; }
+  for (int k = 0; k < n_views; ++k) {
+    int rc = check_view(c, &views[k], p, N);
+    if (rc != GSX_OK) return rc;
+    if (views[k].l_max != views[0].l_max) { set_error("all views of a batch must share l_max"); return GSX_E_ARG; }
+    c->slot[k].view = views[k];
+  }
+  c->batch_n = N; c->batch_nv = n_views; c->batch_lmax = views[0].l_max;
+  BatchConst bc;
+  fill_batch_const(c, n_views, &bc);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
+  int rc = batch_fwd_launch(bc, *p, N, views[0].l_max, st);
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[1], st));
+  return rc;
+}
+
+int gsx_batch_forward_view(gsx_ctx_t *c, int slot, void *stream) {
+  if (!c) return GSX_E_NULL;
+  if (slot < 0 || slot >= c->batch_nv) { set_error("slot %d outside the current batch (%d views)", slot, c->batch_nv); return GSX_E_ARG; }
+  return forward_view(c, slot, c->batch_n, (cudaStream_t)stream);
+}
+
+int gsx_batch_backward_view(gsx_ctx_t *c, int slot, const float *grad_image, void *stream) {
+  if (!c || !grad_image) { set_error("null argument"); return GSX_E_NULL; }
+  if (slot != c->cur || slot >= c->batch_nv) { set_error("gsx_batch_backward_view(%d) must follow gsx_batch_forward_view(%d)", slot, slot); return GSX_E_ARG; }
+  cudaStream_t st = (cudaStream_t)stream;
+  const gsx_slot &s = c->slot[slot];
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[7], st));
+  int rc = composite_bwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, s.view.width, s.view.height,
+                                s.view.background, c->spp, c->wpp, grad_image, (float *)s.p.gacc, st);
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[8], st));
   return rc;
+}
+
+int gsx_batch_backward_params(gsx_ctx_t *c, const gsx_params_t *p, int N, const gsx_grads_t *g, int flags, void *stream) {
+  if (!c || !p || !g) { set_error("null argument"); return GSX_E_NULL; }
+  if (N != c->batch_n || c->batch_nv < 1) { set_error("gsx_batch_backward_params does not match the current batch"); return GSX_E_ARG; }
+  BatchConst bc;
+  fill_batch_const(c, c->batch_nv, &bc);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[9], st));
+  int rc = batch_bwd_launch(bc, *p, N, c->batch_lmax, *g, flags, st);
+  if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[10], st));
+  return rc;
+}
+
+// Host-buffer batch step: per view H2D of the loss-gradient image and D2H of the rendered image (pinned host memory),
+// forward + backward of every view, one pass of parameter gradients.  Synchronises.
+int gsx_batch_render_host(gsx_ctx_t *c, const gsx_view_t *views, int n_views, const gsx_params_t *p, int N,
+                          const float *const *grad_images_host, float *const *images_host, const gsx_grads_t *g, int flags,
+                          void *stream) {
+  if (!c || !views || !p || !g || !grad_images_host) { set_error("null argument"); return GSX_E_NULL; }
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = gsx_batch_forward_params(c, views, n_views, p, N, stream);
+  if (rc != GSX_OK) return rc;
+  for (int k = 0; k < n_views; ++k) {
+    const size_t bytes = (size_t)views[k].width * views[k].height * 3 * sizeof(float);
+    GSX_CUDA(cudaMemcpyAsync(c->grad_image, grad_images_host[k], bytes, cudaMemcpyHostToDevice, st));
+    rc = gsx_batch_forward_view(c, k, stream);
+    if (rc != GSX_OK) return rc;
+    if (images_host && images_host[k]) GSX_CUDA(cudaMemcpyAsync(images_host[k], c->image, bytes, cudaMemcpyDeviceToHost, st));
+    rc = gsx_batch_backward_view(c, k, c->grad_image, stream);
+    if (rc != GSX_OK) return rc;
+  }
+  rc = gsx_batch_backward_params(c, p, N, g, flags, stream);
+  if (rc != GSX_OK) return rc;
+  GSX_CUDA(cudaStreamSynchronize(st));
+  return GSX_OK;
 }
 
 // out_host[2] = {S, S+} of the last forward (work counters for the roofline arithmetic).  Synchronises.
@@ -201,7 +338,7 @@ int gsx_ctx_count_work(gsx_ctx_t *c, unsigned long long *out_host, void *stream)
   unsigned long long *d = nullptr;
   GSX_CUDA(cudaMalloc(&d, 2 * sizeof(unsigned long long)));
   GSX_CUDA(cudaMemsetAsync(d, 0, 2 * sizeof(unsigned long long), st));
-  int rc = count_work_launch(c->r0, c->r1, (const int *)c->sorted_vals, c->ranges, c->last_w, c->last_h, c->spp, d, st);
+  int rc = count_work_launch(c->slot[c->cur].p.r0, c->slot[c->cur].p.r1, (const int *)c->sorted_vals, c->ranges, c->last_w, c->last_h, c->spp, d, st);
   if (rc == GSX_OK) {
     GSX_CUDA(cudaMemcpyAsync(out_host, d, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     GSX_CUDA(cudaStreamSynchronize(st));
@@ -213,7 +350,7 @@ int gsx_ctx_count_work(gsx_ctx_t *c, unsigned long long *out_host, void *stream)
 int gsx_ctx_enable_timing(gsx_ctx_t *c, int on) {
   if (!c) return GSX_E_NULL;
   if (on && !c->ev[0])
-    for (int i = 0; i < 9; ++i) GSX_CUDA(cudaEventCreate(&c->ev[i]));
+    for (int i = 0; i < 11; ++i) GSX_CUDA(cudaEventCreate(&c->ev[i]));
   c->timing = on != 0;
   return GSX_OK;
 }
@@ -224,8 +361,10 @@ int gsx_ctx_timing(gsx_ctx_t *c, float *ms_out) {
   if (!c || !ms_out) return GSX_E_NULL;
   if (!c->timing) { set_error("timing not enabled"); return GSX_E_ARG; }
   GSX_CUDA(cudaDeviceSynchronize());
-  const int a[7] = {0, 1, 2, 3, 4, 6, 7}, b[7] = {1, 2, 3, 4, 5, 7, 8};
-  for (int i = 0; i < 7; ++i) GSX_CUDA(cudaEventElapsedTime(&ms_out[i], c->ev[a[i]], c->ev[b[i]]));
+  const int a[7] = {0, 2, 3, 4, 5, 7, 9}, b[7] = {1, 3, 4, 5, 6, 8, 10};
+  for (int i = 0; i < 7; ++i) {   // a stage whose events were never recorded reports -1
+    if (cudaEventElapsedTime(&ms_out[i], c->ev[a[i]], c->ev[b[i]]) != cudaSuccess) { cudaGetLastError(); ms_out[i] = -1.0f; }
+  }
   return GSX_OK;
 }
 
@@ -277,7 +416,7 @@ int gsx_ctx_stats(gsx_ctx_t *c, gsx_stats_t *out, void *stream) {
   cudaStream_t st = (cudaStream_t)stream;
   GSX_CUDA(cudaMemsetAsync(c->d_P, 0, sizeof(int), st));
   if (c->last_n > 0) {
-    k_count_mask<<<kNumSMs * 4, 256, 0, st>>>(c->mask, c->last_n, c->d_P);
+    k_count_mask<<<kNumSMs * 4, 256, 0, st>>>(c->slot[c->cur].p.mask, c->last_n, c->d_P);
     GSX_LAUNCH_CHECK();
   }
   GSX_CUDA(cudaMemcpyAsync(&c->h_stats[0], c->bin_ws + c->L.total, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -294,12 +433,13 @@ int gsx_ctx_stats(gsx_ctx_t *c, gsx_stats_t *out, void *stream) {
 int gsx_ctx_state(gsx_ctx_t *c, gsx_state_t *o) {
   if (!c || !o) return GSX_E_NULL;
   o->image = c->image; o->weight_per_pixel = c->wpp; o->splats_per_pixel = c->spp;
-  o->rec0 = (const float *)c->r0; o->rec1 = (const float *)c->r1; o->rec2 = (const float *)c->r2;
-  o->radius = (const float *)c->radius; o->depth = c->depth; o->mask = c->mask;
-  o->tiles_touched = (const int *)(c->bin_ws + c->L.touched);
+  const SlotPtrs &sp = c->slot[c->cur].p;
+  o->rec0 = (const float *)sp.r0; o->rec1 = (const float *)sp.r1; o->rec2 = (const float *)sp.r2;
+  o->radius = (const float *)sp.radius; o->depth = sp.depth; o->mask = sp.mask;
+  o->tiles_touched = sp.touched;
   o->sorted_gaussians = (const int *)c->sorted_vals; o->sorted_keys = c->sorted_keys;
   o->ranges = c->ranges; o->num_instances = (const int *)(c->bin_ws + c->L.total);
-  o->packed_grads = c->gacc;
+  o->packed_grads = (const float *)sp.gacc;
   return GSX_OK;
 }
 

@@ -205,11 +205,11 @@ BinLayout bin_layout(int N, long long capacity) {
 
 // scan -> emit -> sort -> ranges, given touched[] already filled.  Leaves sorted keys / ids in
 // (*sorted_keys, *sorted_vals) inside the workspace; K in total_dev[0].
-int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius, int ntx, int nty, int N,
-                  long long capacity, char *ws, const BinLayout &L, int *ranges, const uint64_t **sorted_keys,
-                  const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev) {
+int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
+                  const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
+                  const uint64_t **sorted_keys, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev) {
   // ev (optional): 3 events recorded after emission, after the sort and after the ranges (stage timing)
-  int *touched = (int *)(ws + L.touched), *offsets = (int *)(ws + L.offsets);
+  int *offsets = (int *)(ws + L.offsets);
   int *block_sums = (int *)(ws + L.block_sums), *total = (int *)(ws + L.total);
   uint64_t *ka = (uint64_t *)(ws + L.keys_a), *kb = (uint64_t *)(ws + L.keys_b);
   uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
@@ -327,8 +327,8 @@ int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const floa
   if (rc != GSX_OK) return rc;
   const uint64_t *sk;
   const uint32_t *sv;
-  rc = bin_sort_impl(uv, 2, xyz_c + 2, 3, (const float4 *)radius, n_tiles_x, n_tiles_y, N, capacity, ws, L, ranges, &sk,
-                     &sv, st, nullptr);
+  rc = bin_sort_impl(uv, 2, xyz_c + 2, 3, (const float4 *)radius, (const int *)(ws + L.touched), n_tiles_x, n_tiles_y, N,
+                     capacity, ws, L, ranges, &sk, &sv, st, nullptr);
   if (rc != GSX_OK) return rc;
   rc = copy_ids_launch(sv, sorted_gaussians, capacity, (const int *)(ws + L.total), st);
   if (rc != GSX_OK) return rc;

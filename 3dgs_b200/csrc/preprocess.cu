@@ -12,6 +12,7 @@
 #include "gsx_common.cuh"
 #include "gsx_math.cuh"
 #include "gsx_tma.cuh"
+#include "gsx_view.cuh"
 
 namespace gsx {
 
@@ -23,17 +24,6 @@ __device__ __forceinline__ float2 alpha_extent_pre(float a, float b, float c, fl
   const float inv = tau2 / det;
   return make_float2(sqrtf(inv * c) * 1.0005f + 0.02f, sqrtf(inv * a) * 1.0005f + 0.02f);
 }
-
-struct ViewConst {     // passed by value (kernel parameter space, no device copy of the camera needed)
-  float view[12];
-  float proj[16];
-  float3 campos;
-  float fx, fy, tan_fovx, tan_fovy;
-  int width, height, ntx, nty;
-  float near_thresh;
-  int padding;
-  float mh_dist;
-};
 
 constexpr int PB = 256;
 #ifndef GSX_PRE_MINB
@@ -281,18 +271,6 @@ k_preprocess_bwd(ViewConst vc, int N, const float *__restrict__ xyz, const float
     }
   }
   if (use_tma && threadIdx.x == 0) bulk_wait_read_all();   // shared memory must outlive the bulk store
-}
-
-static ViewConst make_view_const(const gsx_view_t &v) {
-  ViewConst c;
-  for (int k = 0; k < 12; ++k) c.view[k] = v.view[k];
-  for (int k = 0; k < 16; ++k) c.proj[k] = v.proj[k];
-  c.campos = make_float3(v.campos[0], v.campos[1], v.campos[2]);
-  c.fx = v.focal_x; c.fy = v.focal_y; c.tan_fovx = v.tan_fovx; c.tan_fovy = v.tan_fovy;
-  c.width = v.width; c.height = v.height;
-  c.ntx = (v.width + 15) / 16; c.nty = (v.height + 15) / 16;
-  c.near_thresh = v.near_thresh; c.padding = v.cull_padding; c.mh_dist = v.mh_dist;
-  return c;
 }
 
 static int sh_chunk_ok(int l_max, int stride, const void *a, const void *b) {

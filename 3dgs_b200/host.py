@@ -330,6 +330,55 @@ class Rasterizer:
         io = C.c_void_p(image_host.data_ptr()) if image_host is not None else C.c_void_p(0)
         check(lib().gsx_render_view_host(self.h, C.byref(view), C.byref(p), g.N, gi, io, C.byref(gs), _stream()))
 
+    # ---- batch path (gsx_batch_*): one pass over the parameters per direction for all views of a batch ----------
+    def batch_reserve(self, n_slots):
+        check(lib().gsx_batch_reserve(self.h, int(n_slots)))
+
+    def batch_forward_params(self, views, g):
+        arr = (GsxView * len(views))(*views)
+        self._bviews, self._n = arr, g.N
+        self._p = g.params()
+        check(lib().gsx_batch_forward_params(self.h, arr, len(views), C.byref(self._p), g.N, _stream()))
+
+    def batch_forward_view(self, slot):
+        self._view = self._bviews[slot]
+        check(lib().gsx_batch_forward_view(self.h, int(slot), _stream()))
+
+    def batch_backward_view(self, slot, grad_image):
+        check(lib().gsx_batch_backward_view(self.h, int(slot), _ptr(grad_image), _stream()))
+
+    def batch_backward_params(self, g, flags=_ffi.GSX_GRAD_OVERWRITE):
+        if g.grads is None:
+            g.zero_grads()
+        gs = g.grads_struct()
+        p = g.params()
+        check(lib().gsx_batch_backward_params(self.h, C.byref(p), g.N, C.byref(gs), int(flags), _stream()))
+
+    def batch_step(self, views, g, grad_images, flags=_ffi.GSX_GRAD_OVERWRITE, on_image=None):
+        """fwd+bwd of every view of the batch, gradients summed over the views.  grad_images: one device tensor per view
+        (or a single one used for all); on_image(slot) is called after each forward (the rendered image is in state())."""
+        self.batch_forward_params(views, g)
+        for k in range(len(views)):
+            self.batch_forward_view(k)
+            if on_image is not None:
+                on_image(k)
+            gi = grad_images[k] if isinstance(grad_images, (list, tuple)) else grad_images
+            self.batch_backward_view(k, gi)
+        self.batch_backward_params(g, flags)
+
+    def batch_render_host(self, views, g, grad_images_host, images_host, flags=_ffi.GSX_GRAD_OVERWRITE):
+        """Host-buffer batch step: pinned host grad images in, pinned host images out (synchronises)."""
+        if g.grads is None:
+            g.zero_grads()
+        arr = (GsxView * len(views))(*views)
+        self._bviews, self._n = arr, g.N
+        gs, p = g.grads_struct(), g.params()
+        gi = (C.c_void_p * len(views))(*[t.data_ptr() for t in grad_images_host])
+        io = (C.c_void_p * len(views))(*[t.data_ptr() for t in images_host])
+        check(lib().gsx_batch_render_host(self.h, arr, len(views), C.byref(p), g.N, gi, io, C.byref(gs), int(flags),
+                                          _stream()))
+        self._view = arr[len(views) - 1]
+
     def enable_timing(self, on=True):
         check(lib().gsx_ctx_enable_timing(self.h, int(bool(on))))
 

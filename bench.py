@@ -190,30 +190,29 @@ def main():
     mk = lambda cam, flags: Hh.make_view(cam["view"], cam["proj"], cam["campos"], cam["fx"], cam["fy"], W, H,
                                          near_thresh=S.NEAR_THRESH, cull_padding=S.CULL_PADDING, mh_dist=S.MH_DIST,
                                          background=0.0, l_max=l_max, flags=flags)
-    # first view of the batch overwrites the gradient buffers (no 1.4 GB memset per step), the rest accumulate
-    vstructs = [mk(cams[k], OVER if i == 0 else 0) for i, k in enumerate(my_views)]
+    vstructs = [mk(cams[k], 0) for k in my_views]
+    nv = len(vstructs)
     r = Hh.Rasterizer(N, W, H, instance_capacity=4 * N)
-    gi_host = torch.as_tensor(S.grad_image(W, H)).pin_memory()
-    img_host = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
-    gi_dev = gi_host.to(dev)
+    r.batch_reserve(nv)
+    gi_host = [torch.as_tensor(S.grad_image(W, H)).pin_memory() for _ in range(nv)]
+    img_host = [torch.empty((H, W, 3), dtype=torch.float32).pin_memory() for _ in range(nv)]
+    gi_dev = gi_host[0].to(dev)
 
-    # size the instance capacity once (the only host sync of the set-up), record the work counters
-    stats = []
+    # size the instance capacity once (the only host sync of the set-up)
     for v in vstructs:
-        stats.append(r.forward_checked(v, gd))
+        r.forward_checked(v, gd)
     for v in vstructs:                                             # re-check after any growth
         assert not r.forward_checked(v, gd)["overflow"]
 
+    # One step = the rank's views of the batch through the batch path (parameters read once per direction, gradients
+    # of the rank's views summed in one pass with '=' semantics: no 1.4 GB memset) + the gradient allreduce.
     def step():
-        for v in vstructs:
-            r.forward(v, gd)
-            r.backward(v, gd, gi_dev)
+        r.batch_step(vstructs, gd, gi_dev, flags=OVER)
         if world > 1:
             dist.all_reduce(flat)
 
     def step_e2e():
-        for v in vstructs:
-            r.render_view_host(v, gd, gi_host, img_host)
+        r.batch_render_host(vstructs, gd, gi_host, img_host, flags=OVER)
         if world > 1:
             dist.all_reduce(flat)
             torch.cuda.synchronize()
@@ -262,54 +261,64 @@ def main():
     # ---- roofline leg (rank 0): per-stage CUDA-event timing of this rank's views, outside the timed region --------
     r.enable_timing(True)
     acc, reps = {}, 3
-    work = dict(P=0, K=0, S=0, Sp=0)
-    for v, st in zip(vstructs, stats):
-        for _ in range(reps):
-            r.forward(v, gd)
-            r.backward(v, gd, gi_dev)
-            for k_, x in r.timing().items():
-                acc[k_] = acc.get(k_, 0.0) + x
-        r.forward(v, gd)
-        s_, sp_ = r.count_work()
-        r.backward(v, gd, gi_dev)
-        stx = r.stats()
-        work["P"] += stx["P"]; work["K"] += stx["K"]; work["S"] += s_; work["Sp"] += sp_
+    work = dict(P=0, Pt=0, K=0, S=0, Sp=0)
+    per_view = ("scan_emit", "sort", "ranges", "composite_fwd", "composite_bwd")
+    for rep in range(reps):
+        r.batch_forward_params(vstructs, gd)
+        for k_ in range(nv):
+            r.batch_forward_view(k_)
+            if rep == 0:
+                s_, sp_ = r.count_work()
+                stx = r.stats()
+                work["P"] += stx["P"]; work["K"] += stx["K"]; work["S"] += s_; work["Sp"] += sp_
+                work["Pt"] += int((r.state()["tiles_touched"] > 0).sum().item())
+            r.batch_backward_view(k_, gi_dev)
+            t_ = r.timing()
+            for nm in per_view:
+                acc[nm] = acc.get(nm, 0.0) + t_[nm] / nv
+        r.batch_backward_params(gd, OVER)
+        t_ = r.timing()
+        for nm in ("preprocess_fwd", "preprocess_bwd"):            # batch kernels: one launch per batch
+            acc[nm] = acc.get(nm, 0.0) + t_[nm]
     r.enable_timing(False)
-    nv = len(vstructs)
-    stage_ms = {k_: x / (reps * nv) for k_, x in acc.items()}
-    P, K, Sx, Sp = (work[k_] / nv for k_ in ("P", "K", "S", "Sp"))
+    launch_ms = {k_: x / reps for k_, x in acc.items()}            # average duration of one launch (stage)
+    P, Pt, K, Sx, Sp = (work[k_] / nv for k_ in ("P", "Pt", "K", "S", "Sp"))
     T = ((W + 15) // 16) * ((H + 15) // 16)
     D = 3 * ((l_max + 1) ** 2 - 1)
     passes = (32 + max(1, int(np.ceil(np.log2(T)))) + 7) // 8
     fp32_peak = Hh.measure_fp32_tflops()
     # algorithmic work per launch (SURVEY 8d / BASELINE.md section 5)
+    PB_ = 44 + 4 * D                                                # parameter / gradient bytes per Gaussian (236 at deg 3)
     alg = {
-        "preprocess_fwd": ("hbm", 12 * N + (32 + 4 * D + 12) * P + 48 * P),
+        # batch kernels (one launch per batch of nv views): parameters once + per-view records / packed gradients
+        "preprocess_fwd": ("hbm", PB_ * N + nv * (74 * P + 5 * (N - P))),
+        "preprocess_bwd": ("hbm", PB_ * N + nv * (4 * N + 96 * Pt) + PB_ * N),
         "scan_emit": ("hbm", 12 * K + 12 * N),
         "sort": ("hbm", (8 + 24 * passes) * K),
         "ranges": ("hbm", 8 * K + 4 * (T + 1)),
         "composite_fwd": ("fp32", 18 * Sx),
         "composite_bwd": ("fp32", 10 * Sx + 46 * Sp),
-        "preprocess_bwd": ("hbm", (32 + 4 * D + 12 + 36) * P + (44 + 4 * D) * P),
     }
     stages = {}
     for k_, (bound, w) in alg.items():
-        t = stage_ms[k_] * 1e-3
+        t = launch_ms[k_] * 1e-3
         if bound == "hbm":
             a, pk, un = w / t / 1e9, hbm_peak, "GB/s"
         else:
             a, pk, un = w / t / 1e12, fp32_peak, "TFLOP/s"
-        stages[k_] = {"ms": round(stage_ms[k_], 4), "bound": bound, "achieved": round(a, 2), "peak": round(pk, 2),
-                      "unit": un, "frac": round(a / pk, 4)}
+        per_batch = k_ in ("preprocess_fwd", "preprocess_bwd")
+        stages[k_] = {"ms": round(launch_ms[k_], 4), "launches_per_batch": 1 if per_batch else nv,
+                      "ms_per_view": round(launch_ms[k_] / (nv if per_batch else 1), 4), "bound": bound,
+                      "achieved": round(a, 2), "peak": round(pk, 2), "unit": un, "frac": round(a / pk, 4)}
+    stage_ms = {k_: v_["ms_per_view"] for k_, v_ in stages.items()}
     top = max(stage_ms, key=stage_ms.get)
-    roof = dict(stages[top])
-    roof.pop("ms")
-    roof.update({"kernel": top, "traffic": None, "ms": round(stage_ms[top], 4),
+    roof = {k_: stages[top][k_] for k_ in ("bound", "achieved", "peak", "unit", "frac")}
+    roof.update({"kernel": top, "traffic": None, "ms": stages[top]["ms"],
                  "peak_source": peak_src if roof["bound"] == "hbm" else "FP32 FMA peak measured in this run (gsx_measure_fp32_tflops)",
                  "share_of_view": round(stage_ms[top] / sum(stage_ms.values()), 3)})
 
     views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
-    per_view = 15 + passes - 6 + 2                                   # kernels launched per view by libgsx
+    launches_per_view = 3 + 1 + 2 + passes + 1 + 2                   # scan x3, emit, histogram x2, onesweep, ranges, composite x2
     out = {
         "metric": METRIC, "value": views_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
@@ -318,17 +327,17 @@ def main():
         "config": {"workload": f"{args.config}: synthetic {N} Gaussians, SH deg {l_max}, {W}x{H}, batch of {N_VIEWS} views "
                                f"sharded over {world} GPU(s), NCCL allreduce of {flat.numel() * 4 / 1e9:.2f} GB gradients",
                    "views_per_step": N_VIEWS, "l2": "inputs larger than L2 (1.4 GB parameters + 1.4 GB gradients per view)",
-                   "visible_P": int(P), "instances_K": int(K), "pixel_entries_S": int(Sx), "contributing_Splus": int(Sp)},
+                   "visible_P": int(P), "touching_P": int(Pt), "instances_K": int(K), "pixel_entries_S": int(Sx), "contributing_Splus": int(Sp)},
         "clocks": clocks,
         "e2e": {"value": N_VIEWS * args.steps / dt_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": N_VIEWS * (W * H * 3 * 4 + 200), "d2h_bytes_per_step": N_VIEWS * W * H * 3 * 4},
-        "gpu_launches": per_view * len(my_views) * args.steps * world,
+        "gpu_launches": (launches_per_view * nv + 2) * args.steps * world,
         "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": round(fp32_peak, 2),
     }
     if world == 1 and not args.no_cpu_baseline:
         from oracle import golden as G
         cores = G.lib().gold_max_threads()
-        t, _, _ = cpu_view_seconds(S, g, cams[0], W, H, l_max, gi_host.numpy())
+        t, _, _ = cpu_view_seconds(S, g, cams[0], W, H, l_max, gi_host[0].numpy())
         out["cpu_baseline"] = {"value": 1.0 / t, "unit": UNIT, "cores": cores, "kind": "port",
                                "sample": f"1 view (fwd+bwd) of the same scene through oracle/libgolden.so, {cores} OpenMP threads, {t:.1f} s"}
     print(json.dumps(out))

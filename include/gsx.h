@@ -182,6 +182,31 @@ typedef struct gsx_state {
 } gsx_state_t;
 int gsx_ctx_state(gsx_ctx_t *ctx, gsx_state_t *out_host);
 
+/* ---- batch path: the n views of one training batch (n <= GSX_MAX_VIEWS) share ONE pass over the parameters in each
+ *      direction (the reference reads them twice per view, raster.cu:26-104 / trainer.cu:941-1012).  Protocol:
+ *        gsx_batch_reserve(ctx, n)                                   once
+ *        gsx_batch_forward_params(ctx, views, n, params, N, s)       F1-F6 + tile counts of all views -> per-view slots
+ *        for k in 0..n-1:
+ *          gsx_batch_forward_view(ctx, k, s)                         F7 + F8 of view k; outputs via gsx_ctx_state
+ *          gsx_batch_backward_view(ctx, k, grad_image, s)            F9 of view k (needs view k's sorted list: must
+ *                                                                    directly follow its forward_view)
+ *        gsx_batch_backward_params(ctx, params, N, grads, flags, s)  F10-F15 of all views, gradients summed over the
+ *                                                                    batch ('=' with GSX_GRAD_OVERWRITE, else '+=')
+ *      All asynchronous on `s`; no host round trip. ------------------------------------------------------------------ */
+#define GSX_MAX_VIEWS 8
+int gsx_batch_reserve(gsx_ctx_t *ctx, int n_slots);
+int gsx_batch_forward_params(gsx_ctx_t *ctx, const gsx_view_t *views_host, int n_views, const gsx_params_t *params,
+                             int N, void *stream);
+int gsx_batch_forward_view(gsx_ctx_t *ctx, int slot, void *stream);
+int gsx_batch_backward_view(gsx_ctx_t *ctx, int slot, const float *grad_image, void *stream);
+int gsx_batch_backward_params(gsx_ctx_t *ctx, const gsx_params_t *params, int N, const gsx_grads_t *grads, int flags,
+                              void *stream);
+/* Host-buffer batch step (bench.py's e2e leg): per view, H2D of grad_images_host[k] and D2H of the rendered image into
+ * images_host[k] (pinned host memory, [H][W][3] floats), then the whole protocol above.  Synchronises. */
+int gsx_batch_render_host(gsx_ctx_t *ctx, const gsx_view_t *views_host, int n_views, const gsx_params_t *params, int N,
+                          const float *const *grad_images_host, float *const *images_host, const gsx_grads_t *grads,
+                          int flags, void *stream);
+
 /* Optional per-stage CUDA-event timing of gsx_forward/gsx_backward (used by bench.py's roofline leg, never inside
  * the timed throughput region).  ms_out[7] = preprocess_fwd, scan+emit, sort, ranges, composite_fwd, composite_bwd,
  * preprocess_bwd. */

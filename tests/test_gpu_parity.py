@@ -326,6 +326,88 @@ def test_view_backward_parity(B, l_max, sh_alloc, flags):
     r.close()
 
 
+@pytest.mark.parametrize("l_max,sh_alloc,flags,overwrite", [(3, None, 0, True), (3, None, 1, False), (1, 3, 0, True), (0, None, 0, False)])
+def test_batch_path_matches_per_view_and_oracle(B, l_max, sh_alloc, flags, overwrite):
+    """gsx_batch_*: n views share one pass over the parameters per direction.  Per-view forward state must equal the
+    single-view path's, and the batch gradients the sum over the views (per-view path and oracle)."""
+    import torch
+    W, H, N = 224, 160, 12000
+    az = [10.0, 130.0, 250.0]
+    cams = [S.orbit_camera(W, H, azimuth_deg=a) for a in az]
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=44)
+    Hh = gs.host
+    sh = g["sh"]
+    if sh is not None and sh_alloc is not None:
+        full = np.zeros((N, (sh_alloc + 1) ** 2 - 1, 3), np.float32)
+        full[:, : sh.shape[1]] = sh
+        sh = full
+    gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], sh)
+    gis = [S.grad_image(W, H, seed=70 + k) * 1e3 for k in range(len(az))]
+    gis_d = [torch.as_tensor(x).cuda() for x in gis]
+    bgs = [0.0, 0.4, 1.0]
+    views = [util.gsx_view(c, l_max, bg, flags) for c, bg in zip(cams, bgs)]
+    # ---- per-view path: reference for state + summed gradients
+    r1 = Hh.Rasterizer(N, W, H, instance_capacity=8 * N)
+    gd.zero_grads(with_uv=True)
+    states = []
+    for v, gi in zip(views, gis_d):
+        r1.forward(v, gd)
+        st = {k: (t.cpu().numpy().copy() if hasattr(t, "cpu") else t) for k, t in r1.state().items()}
+        states.append(st)
+        r1.backward(v, gd, gi)
+    torch.cuda.synchronize()
+    want = {k: t.cpu().numpy().copy() for k, t in gd.grads.items()}
+    r1.close()
+    # ---- batch path
+    r = Hh.Rasterizer(N, W, H, instance_capacity=8 * N)
+    r.batch_reserve(len(views))
+    fill = 0.0 if not overwrite else 77.0
+    for t in gd.grads.values():
+        t.fill_(fill)
+    got_states = []
+
+    def grab(k):
+        got_states.append({kk: (t.cpu().numpy().copy() if hasattr(t, "cpu") else t) for kk, t in r.state().items()})
+
+    r.batch_step(views, gd, gis_d, flags=flags | (2 if overwrite else 0), on_image=grab)
+    torch.cuda.synchronize()
+    got = {k: t.cpu().numpy().copy() for k, t in gd.grads.items()}
+    for k, (a, b) in enumerate(zip(got_states, states)):
+        assert a["K"] == b["K"] and a["K"] > 0
+        np.testing.assert_array_equal(a["mask"], b["mask"])
+        np.testing.assert_array_equal(a["tiles_touched"], b["tiles_touched"])
+        np.testing.assert_array_equal(a["ranges"], b["ranges"])
+        np.testing.assert_array_equal(a["sorted_gaussians"], b["sorted_gaussians"])
+        np.testing.assert_array_equal(a["sorted_keys"], b["sorted_keys"])
+        m = b["mask"].astype(bool)
+        for nm in ("rec0", "rec1", "rec2", "radius"):
+            np.testing.assert_allclose(a[nm][m], b[nm][m], rtol=2e-6, atol=1e-6, err_msg=f"view {k} {nm}")
+        util.assert_image_close(a["image"], b["image"], f"view {k} image")
+        np.testing.assert_array_equal(a["splats_per_pixel"], b["splats_per_pixel"])
+    nsh = ((l_max + 1) ** 2 - 1) * 3
+    for k in want:
+        a_, b_ = (got[k][:, :nsh], want[k][:, :nsh]) if k == "sh" else (got[k], want[k])   # '=' writes the used bands only
+        if k == "sh" and nsh == 0:
+            continue
+        util.assert_grad_close(a_, b_, f"batch d {k} vs per-view sum", outlier=2e-3)
+    # the slots' packed gradient buffers are handed back zeroed
+    assert not r.state()["packed_grads"].any().item()
+    # ---- and against the oracle's own chain, summed over the views (threshold flips bounded: norm-wise)
+    tot = None
+    for c, bg, gi in zip(cams, bgs, gis):
+        gv = util.make_views(c, l_max, bg, flags)
+        o = G.forward(gv, g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+        tot = G.backward(gv, o, gi, grads=tot)
+    for ko, kg in (("xyz", "xyz"), ("scale", "scale"), ("quat", "quaternion"), ("opacity", "opacity"), ("band0", "band0")):
+        a, b = got[kg].reshape(-1), tot[ko].reshape(-1)
+        assert np.linalg.norm(a - b) <= 5e-3 * np.linalg.norm(b) + 1e-12, kg
+    if l_max > 0:
+        nsh = ((l_max + 1) ** 2 - 1) * 3
+        a = got["sh"][:, :nsh].reshape(-1); b = tot["sh"].reshape(N, -1)[:, :nsh].reshape(-1)
+        assert np.linalg.norm(a - b) <= 5e-3 * np.linalg.norm(b) + 1e-12
+    r.close()
+
+
 def test_config1_fixture_and_companion(B):
     """C1: the reference's own COLMAP fixture (1 camera, 1 image, 1 point): the Gaussian survives the
     padded cull, touches no tile, the image is pure background and every gradient is zero; plus the non-degenerate
