@@ -7,6 +7,7 @@
 #include <stdarg.h>
 
 #include "gsx_common.cuh"
+#include "gsx_math.cuh"
 #include "gsx_view.cuh"
 
 namespace gsx {
@@ -39,7 +40,7 @@ int check_device_ptr(const void *p, const char *name) {
 BinLayout bin_layout(int N, long long capacity);
 int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
                   const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
-                  const uint64_t **sorted_keys, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev);
+                  const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev);
 int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, cudaStream_t st);
 int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, const gsx_grads_t &g, int flags,
                      cudaStream_t st);
@@ -77,7 +78,9 @@ struct gsx_ctx {
   // per-pixel state of the last forward
   float *image = nullptr, *wpp = nullptr, *grad_image = nullptr;
   int *spp = nullptr;
-  const uint64_t *sorted_keys = nullptr;
+  const uint32_t *sorted_tiles = nullptr;
+  uint64_t *key64 = nullptr;        // tile<<32 | depth bits, rebuilt on demand by gsx_ctx_state (inspection only)
+  long long key64_cap = 0;
   const uint32_t *sorted_vals = nullptr;
   int last_n = 0, last_w = 0, last_h = 0;
   int batch_n = 0, batch_nv = 0, batch_lmax = 0;
@@ -90,6 +93,15 @@ struct gsx_ctx {
 };
 
 namespace gsx {
+// the 64-bit keys the two-level sort never materialises, for inspection: tile << 32 | order-preserving depth bits
+__global__ void k_compose_keys(const uint32_t *__restrict__ tiles, const uint32_t *__restrict__ ids,
+                               const float *__restrict__ depth, const int *__restrict__ n_dev, long long cap,
+                               uint64_t *__restrict__ out) {
+  const long long n = min((long long)*n_dev, cap);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    out[i] = ((uint64_t)tiles[i] << 32) | float_sort_bits(depth[ids[i]]);
+}
+
 __global__ void k_count_mask(const uint8_t *__restrict__ mask, int N, int *__restrict__ out) {
   int c = 0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) c += mask[i] ? 1 : 0;
@@ -99,6 +111,7 @@ __global__ void k_count_mask(const uint8_t *__restrict__ mask, int N, int *__res
 
 static int alloc_bin(gsx_ctx *c, long long capacity) {
   if (c->bin_ws) { cudaFree(c->bin_ws); c->bin_ws = nullptr; }
+  c->sorted_tiles = nullptr; c->sorted_vals = nullptr;
   c->capacity = std::max<long long>(capacity, 1024);
   c->L = bin_layout(c->max_n, c->capacity);
   GSX_CUDA(cudaMalloc(&c->bin_ws, c->L.bytes));
@@ -139,7 +152,7 @@ static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
   c->last_n = N; c->last_w = v.width; c->last_h = v.height; c->cur = k;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[2], st));
   int rc = bin_sort_impl((const float *)s.p.r0, 4, s.p.depth, 1, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, c->bin_ws,
-                         c->L, c->ranges, &c->sorted_keys, &c->sorted_vals, st, c->timing ? &c->ev[3] : nullptr);
+                         c->L, c->ranges, &c->sorted_tiles, &c->sorted_vals, st, c->timing ? &c->ev[3] : nullptr);
   if (rc != GSX_OK) return rc;
   rc = composite_fwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, v.width, v.height, v.background,
                             c->spp, c->wpp, c->image, st);
@@ -192,7 +205,7 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
 int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (!c) return GSX_OK;
   for (int k = 0; k < GSX_MAX_BATCH; ++k) free_slot(c->slot[k]);
-  cudaFree(c->bin_ws); cudaFree(c->ranges); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
+  cudaFree(c->bin_ws); if (c->key64) cudaFree(c->key64); cudaFree(c->ranges); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
   cudaFree(c->grad_image); cudaFree(c->d_P); cudaFreeHost(c->h_stats);
   delete c;
   return GSX_OK;
@@ -437,7 +450,22 @@ int gsx_ctx_state(gsx_ctx_t *c, gsx_state_t *o) {
   o->rec0 = (const float *)sp.r0; o->rec1 = (const float *)sp.r1; o->rec2 = (const float *)sp.r2;
   o->radius = (const float *)sp.radius; o->depth = sp.depth; o->mask = sp.mask;
   o->tiles_touched = sp.touched;
-  o->sorted_gaussians = (const int *)c->sorted_vals; o->sorted_keys = c->sorted_keys;
+  o->sorted_gaussians = (const int *)c->sorted_vals;
+  o->sorted_keys = nullptr;
+  if (c->sorted_tiles) {   // synchronous: inspection only, never on the hot path
+    if (c->key64_cap < c->capacity) {
+      if (c->key64) cudaFree(c->key64);
+      c->key64 = nullptr; c->key64_cap = 0;
+      GSX_CUDA(cudaMalloc(&c->key64, sizeof(uint64_t) * (size_t)c->capacity));
+      c->key64_cap = c->capacity;
+    }
+    GSX_CUDA(cudaDeviceSynchronize());
+    k_compose_keys<<<kNumSMs * 8, 256>>>(c->sorted_tiles, c->sorted_vals, sp.depth, (const int *)(c->bin_ws + c->L.total),
+                                         c->capacity, c->key64);
+    GSX_LAUNCH_CHECK();
+    GSX_CUDA(cudaDeviceSynchronize());
+    o->sorted_keys = c->key64;
+  }
   o->ranges = c->ranges; o->num_instances = (const int *)(c->bin_ws + c->L.total);
   o->packed_grads = (const float *)sp.gacc;
   return GSX_OK;

@@ -50,7 +50,7 @@ __device__ __forceinline__ void stage_rows(float *s_dst, const float *sh, int sh
     }
   } else {
     for (int k = threadIdx.x; k < rows * SHF; k += BB) {
-      const int r = k / SHF, c = k - r * SHF;
+      const int r = k / (SHF > 0 ? SHF : 1), c = k - r * SHF;
       s_dst[k] = __ldg(sh + (size_t)(row0 + r) * sh_stride + c);
     }
   }
@@ -253,7 +253,7 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     } else {
       __syncthreads();
       for (int k = threadIdx.x; k < rows * SHF; k += BB) {
-        const int r = k / SHF, c = k - r * SHF;
+        const int r = k / (SHF > 0 ? SHF : 1), c = k - r * SHF;
         float *o = out.sh + (size_t)(row0 + r) * out.sh_stride + c;
         *o = out.overwrite ? s_grad[k] : *o + s_grad[k];
       }

@@ -1,5 +1,13 @@
-// binning.cu -- tile binning: exact per-Gaussian instance counts, exclusive scan, deterministic key/value
-// emission, sort, tile ranges.  Replaces the reference's coarse_binning_kernel (run twice) + generate_splats_kernel
+// binning.cu -- tile binning: exact per-Gaussian instance counts, depth sort of the Gaussians, exclusive scan,
+// deterministic instance emission in depth order, stable tile sort, tile ranges.
+//
+// Two-level sort (B200 design; the reference sorts one 64-bit double key per instance with 8 CUB passes,
+// cuda/culling.cu:455-469): the order (tile, depth bits, Gaussian id) is produced by
+//   1. a stable 4-pass radix sort of the N Gaussians on their 32 order-preserving depth bits (ties keep ascending id),
+//   2. emitting each Gaussian's instances in that order (exclusive scan of the counts through the permutation),
+//   3. a stable radix sort of the K instances on the tile id alone: ceil(log2 T) bits = 2 passes up to 65536 tiles.
+// Per instance this moves 2 x 16 B instead of 6 x 24 B; the 64-bit tile|depth keys are never materialised (they can
+// be rebuilt for inspection, api.cu).  Result is bit-identical to sorting the 64-bit keys.  Replaces the reference's coarse_binning_kernel (run twice) + generate_splats_kernel
 // + thrust temporaries + 4 blocking D2H reads (cuda/culling.cu:197-300, :386-475): the candidate window and the
 // 4-axis SAT are evaluated in registers per Gaussian, so no coarse pair list (>= 25 per Gaussian) is
 // ever materialised, and emission order is Gaussian-major so equal (tile, depth) keys come out in ascending
@@ -14,8 +22,13 @@ namespace gsx {
 int sort_pairs_impl(uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
                     const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
                     int *result_in_b);
+int sort_pairs_u32_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                        const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
+                        int *result_in_b);
 int tile_ranges_impl(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
                      cudaStream_t st);
+int tile_ranges_u32_impl(const uint32_t *sorted_tiles, long long n, const int *n_dev, int n_tiles, int *ranges,
+                         cudaStream_t st);
 size_t sort_workspace_bytes_impl(long long n);
 
 namespace {
@@ -53,28 +66,38 @@ __global__ void __launch_bounds__(kBlock) k_count(const float *__restrict__ uv, 
   }
 }
 
-__global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, int uv_stride,
-                                                 const float *__restrict__ depth,
-                                                 int depth_stride, const float4 *__restrict__ radius,
-                                                 const int *__restrict__ touched, const int *__restrict__ offsets,
-                                                 int ntx, int nty, int N, long long capacity,
-                                                 uint64_t *__restrict__ keys, uint32_t *__restrict__ vals) {
+// depth keys of the Gaussians that touch a tile (the others sort to the end), ids as values
+__global__ void __launch_bounds__(kBlock) k_depth_keys(const float *__restrict__ depth, int depth_stride,
+                                                       const int *__restrict__ touched, int N,
+                                                       uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
   const int i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= N) return;
+  keys[i] = touched[i] > 0 ? float_sort_bits(depth[(size_t)i * depth_stride]) : 0xffffffffu;
+  vals[i] = (uint32_t)i;
+}
+
+// instance emission in depth order: thread j handles Gaussian perm[j]; its instances go to [offsets[j], +touched)
+__global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, int uv_stride,
+                                                 const float4 *__restrict__ radius, const uint32_t *__restrict__ perm,
+                                                 const int *__restrict__ touched, const int *__restrict__ offsets,
+                                                 int ntx, int nty, int N, long long capacity,
+                                                 uint32_t *__restrict__ tiles, uint32_t *__restrict__ vals) {
+  const int j = blockIdx.x * kBlock + threadIdx.x;
+  if (j >= N) return;
+  const int i = (int)perm[j];
   const int cnt = touched[i];
   if (cnt == 0) return;
-  long long o = offsets[i];
+  long long o = offsets[j];
   if (o + cnt > capacity) return;   // overflow: detected by the host through the total
   const float u = uv[(size_t)i * uv_stride], v = uv[(size_t)i * uv_stride + 1];
   const float4 r = radius[i];
-  const uint64_t zb = float_sort_bits(depth[(size_t)i * depth_stride]);
   const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
   const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
   const TileRange tr = sat_aabb_range(s, w);
   for (int tx = tr.x0; tx <= tr.x1; ++tx)
     for (int ty = tr.y0; ty <= tr.y1; ++ty)
       if (sat_tile_rot(s, tx, ty)) {
-        keys[o] = ((uint64_t)(unsigned)(ty * ntx + tx) << 32) | zb;
+        tiles[o] = (uint32_t)(ty * ntx + tx);
         vals[o] = (uint32_t)i;
         ++o;
       }
@@ -93,14 +116,20 @@ __device__ __forceinline__ int block_reduce_sum(int v, int *s_tmp) {
   return t;   // valid in thread 0
 }
 
-__global__ void __launch_bounds__(kBlock) k_scan_reduce(const int *__restrict__ in, int N, int *__restrict__ block_sums) {
+// value i of the scanned sequence: in[i], or in[perm[i]] when a permutation is given
+__device__ __forceinline__ int scan_value(const int *__restrict__ in, const uint32_t *__restrict__ perm, long long i) {
+  return perm ? in[perm[i]] : in[i];
+}
+
+__global__ void __launch_bounds__(kBlock) k_scan_reduce(const int *__restrict__ in, const uint32_t *__restrict__ perm, int N,
+                                                        int *__restrict__ block_sums) {
   __shared__ int s_tmp[kBlock / 32];
   const long long base = (long long)blockIdx.x * SCAN_TILE;
   int v = 0;
 #pragma unroll
   for (int k = 0; k < SCAN_IPT; ++k) {
     const long long i = base + k * kBlock + threadIdx.x;
-    if (i < N) v += in[i];
+    if (i < N) v += scan_value(in, perm, i);
   }
   const int t = block_reduce_sum(v, s_tmp);
   if (threadIdx.x == 0) block_sums[blockIdx.x] = t;
@@ -130,14 +159,14 @@ __global__ void __launch_bounds__(1024) k_scan_block_sums(int *__restrict__ bloc
   if (threadIdx.x == 0) *total = carry;
 }
 
-__global__ void __launch_bounds__(kBlock) k_scan_apply(const int *__restrict__ in, int N,
+__global__ void __launch_bounds__(kBlock) k_scan_apply(const int *__restrict__ in, const uint32_t *__restrict__ perm, int N,
                                                        const int *__restrict__ block_sums, int *__restrict__ out) {
   __shared__ int s_warp[kBlock / 32];
   const long long base = (long long)blockIdx.x * SCAN_TILE + (long long)threadIdx.x * SCAN_IPT;
   int v[SCAN_IPT];
   int sum = 0;
 #pragma unroll
-  for (int k = 0; k < SCAN_IPT; ++k) { v[k] = (base + k < N) ? in[base + k] : 0; sum += v[k]; }
+  for (int k = 0; k < SCAN_IPT; ++k) { v[k] = (base + k < N) ? scan_value(in, perm, base + k) : 0; sum += v[k]; }
   int incl = sum;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -172,13 +201,14 @@ int tile_key_bits(int n_tiles) {
   return 32 + std::max(b, 1);
 }
 
-int exclusive_scan_i32(const int *in, int N, int *out, int *block_sums, int *total_dev, cudaStream_t st) {
+int exclusive_scan_i32(const int *in, const uint32_t *perm, int N, int *out, int *block_sums, int *total_dev,
+                       cudaStream_t st) {
   const int nb = std::max(1, ceil_div(N, SCAN_TILE));
-  k_scan_reduce<<<nb, kBlock, 0, st>>>(in, N, block_sums);
+  k_scan_reduce<<<nb, kBlock, 0, st>>>(in, perm, N, block_sums);
   GSX_LAUNCH_CHECK();
   k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nb, total_dev);
   GSX_LAUNCH_CHECK();
-  k_scan_apply<<<nb, kBlock, 0, st>>>(in, N, block_sums, out);
+  k_scan_apply<<<nb, kBlock, 0, st>>>(in, perm, N, block_sums, out);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -193,42 +223,55 @@ BinLayout bin_layout(int N, long long capacity) {
   L.offsets = take(sizeof(int) * (size_t)N);
   L.block_sums = take(sizeof(int) * scan_block_sums_count(N));
   L.total = take(sizeof(int) * 4);
-  L.keys_a = take(sizeof(uint64_t) * (size_t)capacity);
-  L.keys_b = take(sizeof(uint64_t) * (size_t)capacity);
+  L.dk_a = take(sizeof(uint32_t) * (size_t)N);
+  L.dk_b = take(sizeof(uint32_t) * (size_t)N);
+  L.dv_a = take(sizeof(uint32_t) * (size_t)N);
+  L.dv_b = take(sizeof(uint32_t) * (size_t)N);
+  L.keys_a = take(sizeof(uint32_t) * (size_t)capacity);
+  L.keys_b = take(sizeof(uint32_t) * (size_t)capacity);
   L.vals_a = take(sizeof(uint32_t) * (size_t)capacity);
   L.vals_b = take(sizeof(uint32_t) * (size_t)capacity);
-  L.sort_ws_bytes = sort_workspace_bytes_impl(capacity);
+  L.sort_ws_bytes = sort_workspace_bytes_impl(std::max<long long>(capacity, N));
   L.sort_ws = take(L.sort_ws_bytes);
   L.bytes = off;
   return L;
 }
 
-// scan -> emit -> sort -> ranges, given touched[] already filled.  Leaves sorted keys / ids in
-// (*sorted_keys, *sorted_vals) inside the workspace; K in total_dev[0].
+// depth sort -> scan -> emit -> tile sort -> ranges, given touched[] already filled.  Leaves the sorted tile ids / Gaussian
+// ids in (*sorted_tiles, *sorted_vals) inside the workspace; K in total_dev[0].
 int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
                   const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
-                  const uint64_t **sorted_keys, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev) {
-  // ev (optional): 3 events recorded after emission, after the sort and after the ranges (stage timing)
+                  const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev) {
+  // ev (optional): 3 events recorded after emission, after the tile sort and after the ranges (stage timing)
   int *offsets = (int *)(ws + L.offsets);
   int *block_sums = (int *)(ws + L.block_sums), *total = (int *)(ws + L.total);
-  uint64_t *ka = (uint64_t *)(ws + L.keys_a), *kb = (uint64_t *)(ws + L.keys_b);
+  uint32_t *dka = (uint32_t *)(ws + L.dk_a), *dkb = (uint32_t *)(ws + L.dk_b);
+  uint32_t *dva = (uint32_t *)(ws + L.dv_a), *dvb = (uint32_t *)(ws + L.dv_b);
+  uint32_t *ka = (uint32_t *)(ws + L.keys_a), *kb = (uint32_t *)(ws + L.keys_b);
   uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
-  int rc = exclusive_scan_i32(touched, N, offsets, block_sums, total, st);
+  int in_b = 0, rc;
+  const uint32_t *perm = nullptr;
+  if (N > 0) {
+    k_depth_keys<<<ceil_div(N, kBlock), kBlock, 0, st>>>(depth, depth_stride, touched, N, dka, dva);
+    GSX_LAUNCH_CHECK();
+    rc = sort_pairs_u32_impl(dka, dkb, dva, dvb, N, nullptr, 32, ws + L.sort_ws, L.sort_ws_bytes, st, &in_b);
+    if (rc != GSX_OK) return rc;
+    perm = in_b ? dvb : dva;
+  }
+  rc = exclusive_scan_i32(touched, perm, N, offsets, block_sums, total, st);
   if (rc != GSX_OK) return rc;
   if (N > 0) {
-    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, depth, depth_stride, radius, touched, offsets, ntx, nty, N,
-                                                   capacity, ka, va);
+    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, perm, touched, offsets, ntx, nty, N, capacity, ka, va);
     GSX_LAUNCH_CHECK();
   }
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
-  int in_b = 0;
-  rc = sort_pairs_impl(ka, kb, va, vb, capacity, total, tile_key_bits(ntx * nty), ws + L.sort_ws, L.sort_ws_bytes, st,
-                       &in_b);
+  rc = sort_pairs_u32_impl(ka, kb, va, vb, capacity, total, tile_key_bits(ntx * nty) - 32, ws + L.sort_ws, L.sort_ws_bytes, st,
+                           &in_b);
   if (rc != GSX_OK) return rc;
-  *sorted_keys = in_b ? kb : ka;
+  *sorted_tiles = in_b ? kb : ka;
   *sorted_vals = in_b ? vb : va;
   if (ev) GSX_CUDA(cudaEventRecord(ev[1], st));
-  rc = tile_ranges_impl(*sorted_keys, capacity, total, ntx * nty, ranges, st);
+  rc = tile_ranges_u32_impl(*sorted_tiles, capacity, total, ntx * nty, ranges, st);
   if (ev) GSX_CUDA(cudaEventRecord(ev[2], st));
   return rc;
 }
@@ -284,7 +327,7 @@ int gsx_sorted_list_size(const float *uv, const float *radius, int n_tiles_x, in
   GSX_CUDA(cudaMemsetAsync(coarse, 0, sizeof(unsigned long long), st));
   rc = count_tiles_launch(uv, 2, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched), coarse, st);
   if (rc != GSX_OK) return rc;
-  rc = exclusive_scan_i32((int *)(ws + L.touched), N, (int *)(ws + L.offsets), (int *)(ws + L.block_sums),
+  rc = exclusive_scan_i32((int *)(ws + L.touched), nullptr, N, (int *)(ws + L.offsets), (int *)(ws + L.block_sums),
                           (int *)(ws + L.total), st);
   if (rc != GSX_OK) return rc;
   unsigned long long hc = 0;
@@ -325,7 +368,7 @@ int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const floa
   int rc = count_tiles_launch(uv, 2, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched),
                               nullptr, st);
   if (rc != GSX_OK) return rc;
-  const uint64_t *sk;
+  const uint32_t *sk;
   const uint32_t *sv;
   rc = bin_sort_impl(uv, 2, xyz_c + 2, 3, (const float4 *)radius, (const int *)(ws + L.touched), n_tiles_x, n_tiles_y, N,
                      capacity, ws, L, ranges, &sk, &sv, st, nullptr);

@@ -39,7 +39,7 @@ constexpr int kNumSMs = 148;  // B200
 
 // workspace carve-up of the binning stage (binning.cu), shared with the context in api.cu
 struct BinLayout {
-  size_t touched, offsets, block_sums, total, keys_a, keys_b, vals_a, vals_b, sort_ws, sort_ws_bytes, bytes;
+  size_t touched, offsets, block_sums, total, dk_a, dk_b, dv_a, dv_b, keys_a, keys_b, vals_a, vals_b, sort_ws, sort_ws_bytes, bytes;
 };
 
 }  // namespace gsx

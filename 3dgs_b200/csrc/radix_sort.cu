@@ -12,6 +12,8 @@
 //                      only ever waits on tiles that are already resident (no deadlock).
 // HBM-bound: algorithmic bytes = 8n (histogram read) + passes * 24n.  The live count may live on the device
 // (n_dev) so the view-level path never syncs with the host.
+// The kernels are templated on the key type: the view-level path sorts 32-bit keys twice (depth per Gaussian, then
+// tile id per instance, binning.cu) instead of one 64-bit tile|depth key per instance.
 #include "gsx_common.cuh"
 
 namespace gsx {
@@ -31,7 +33,8 @@ __device__ __forceinline__ long long live_count(const int *n_dev, long long n) {
   return n;
 }
 
-__global__ void __launch_bounds__(256) k_histogram(const uint64_t *__restrict__ keys, long long n_host,
+template <typename KeyT>
+__global__ void __launch_bounds__(256) k_histogram(const KeyT *__restrict__ keys, long long n_host,
                                                    const int *__restrict__ n_dev, int passes, int key_bits,
                                                    unsigned int *__restrict__ hist /*[passes][256]*/) {
   __shared__ unsigned int sh[MAX_PASSES * RADIX];
@@ -40,7 +43,7 @@ __global__ void __launch_bounds__(256) k_histogram(const uint64_t *__restrict__ 
   const long long n = live_count(n_dev, n_host);
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const uint64_t k = keys[i];
+    const KeyT k = keys[i];
     for (int p = 0; p < passes; ++p) {
       const int bits = min(8, key_bits - 8 * p);
       const unsigned d = (unsigned)(k >> (8 * p)) & ((1u << bits) - 1u);
@@ -76,12 +79,13 @@ __device__ __forceinline__ void st_volatile(unsigned *p, unsigned v) {
   asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
+template <typename KeyT>
 __global__ void __launch_bounds__(RS_THREADS)
-k_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
+k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
            uint32_t *__restrict__ vals_out, long long n_host, const int *__restrict__ n_dev, int shift, int bits,
            const unsigned int *__restrict__ digit_base /*[256] exclusive*/, unsigned int *__restrict__ status,
            unsigned int *__restrict__ ticket) {
-  __shared__ __align__(16) uint64_t s_keys[RS_TILE];        // reused for the values
+  __shared__ __align__(16) KeyT s_keys[RS_TILE];            // reused for the values
   __shared__ unsigned int s_warp[RS_WARPS][RADIX + 1];      // per-warp digit counts -> exclusive offsets
   __shared__ unsigned int s_excl[RADIX + 1];                // block-exclusive offset of each digit
   __shared__ int s_gbase[RADIX];                            // global base minus local offset
@@ -99,14 +103,14 @@ k_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_out
   const int valid = (int)min((long long)RS_TILE, n - base);
   const unsigned mask = (1u << bits) - 1u;
 
-  uint64_t key[RS_IPT];
+  KeyT key[RS_IPT];
   uint32_t val[RS_IPT];
   unsigned pos[RS_IPT];
 #pragma unroll
   for (int i = 0; i < RS_IPT; ++i) {
     const int li = warp * (RS_IPT * 32) + i * 32 + lane;
     if (li < valid) { key[i] = keys_in[base + li]; val[i] = vals_in[base + li]; }
-    else { key[i] = ~0ull; val[i] = 0; }
+    else { key[i] = ~(KeyT)0; val[i] = 0; }
   }
   // stable rank inside the warp: items in order i, lanes in order; peers found with match.any
 #pragma unroll
@@ -185,7 +189,7 @@ k_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_out
     const int slot = tid + k * RS_THREADS;
     gidx[k] = -1;
     if (slot < valid) {
-      const uint64_t kk = s_keys[slot];
+      const KeyT kk = s_keys[slot];
       const unsigned d = (unsigned)(kk >> shift) & mask;
       gidx[k] = s_gbase[d] + slot;
       keys_out[gidx[k]] = kk;
@@ -203,7 +207,8 @@ k_onesweep(const uint64_t *__restrict__ keys_in, uint64_t *__restrict__ keys_out
 
 // ranges[t] = first i whose tile >= t ; ranges[n_tiles] = n   (reference cuda/culling.cu:302-343; exact integer
 // tile ids instead of floor(key / (max_z+1)) -- SURVEY H3).  n == 0 -> all zeros.
-__global__ void __launch_bounds__(256) k_tile_ranges(const uint64_t *__restrict__ keys, long long n_host,
+template <typename KeyT, int SHIFT>
+__global__ void __launch_bounds__(256) k_tile_ranges(const KeyT *__restrict__ keys, long long n_host,
                                                      const int *__restrict__ n_dev, int n_tiles,
                                                      int *__restrict__ ranges) {
   const long long n = live_count(n_dev, n_host);
@@ -214,9 +219,9 @@ __global__ void __launch_bounds__(256) k_tile_ranges(const uint64_t *__restrict_
     return;
   }
   for (long long i = i0; i < n; i += stride) {
-    const int cur = (int)min((unsigned)(keys[i] >> 32), (unsigned)(n_tiles - 1));   // clamp as the reference (:313)
+    const int cur = (int)min((unsigned)(keys[i] >> SHIFT), (unsigned)(n_tiles - 1));   // clamp as the reference (:313)
     int prev = -1;
-    if (i > 0) prev = (int)min((unsigned)(keys[i - 1] >> 32), (unsigned)(n_tiles - 1));
+    if (i > 0) prev = (int)min((unsigned)(keys[i - 1] >> SHIFT), (unsigned)(n_tiles - 1));
     for (int t = prev + 1; t <= cur; ++t) ranges[t] = (int)i;
     if (i == n - 1)
       for (int t = cur + 1; t <= n_tiles; ++t) ranges[t] = (int)n;
@@ -241,12 +246,12 @@ SortLayout sort_layout(long long n) {
 
 }  // namespace
 
-// Internal entry (no pointer attribute checks) used by the binning path.  Result lands in keys_out/vals_out when
-// the number of passes is odd, else back in keys_in/vals_in; *result_in_out tells which.
-int sort_pairs_impl(uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
-                    const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
-                    int *result_in_b) {
-  if (key_bits < 1 || key_bits > 64) { set_error("key_bits %d out of range", key_bits); return GSX_E_ARG; }
+// Internal entry (no pointer attribute checks) used by the binning path.  Result lands in keys_b/vals_b when
+// the number of passes is odd, else back in keys_a/vals_a; *result_in_b tells which.
+template <typename KeyT>
+static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n, const int *n_dev,
+                        int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st, int *result_in_b) {
+  if (key_bits < 1 || key_bits > (int)sizeof(KeyT) * 8) { set_error("key_bits %d out of range", key_bits); return GSX_E_ARG; }
   const int passes = (key_bits + 7) / 8;
   *result_in_b = passes & 1;
   if (n <= 0) return GSX_OK;
@@ -258,16 +263,16 @@ int sort_pairs_impl(uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a, uint32
   unsigned *status = (unsigned *)(ws + L.status_off);
   GSX_CUDA(cudaMemsetAsync(ws, 0, L.status_off + sizeof(unsigned) * (size_t)passes * L.tiles * RADIX, st));
   const int hblocks = (int)std::min<long long>(kNumSMs * 8, (n + 255) / 256);
-  k_histogram<<<hblocks, 256, 0, st>>>(keys_a, n, n_dev, passes, key_bits, hist);
+  k_histogram<KeyT><<<hblocks, 256, 0, st>>>(keys_a, n, n_dev, passes, key_bits, hist);
   GSX_LAUNCH_CHECK();
   k_scan_histogram<<<passes, RADIX, 0, st>>>(hist);
   GSX_LAUNCH_CHECK();
-  uint64_t *kin = keys_a, *kout = keys_b;
+  KeyT *kin = keys_a, *kout = keys_b;
   uint32_t *vin = vals_a, *vout = vals_b;
   for (int p = 0; p < passes; ++p) {
     const int bits = std::min(8, key_bits - 8 * p);
-    k_onesweep<<<L.tiles, RS_THREADS, 0, st>>>(kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX,
-                                               status + (size_t)p * L.tiles * RADIX, ticket + p);
+    k_onesweep<KeyT><<<L.tiles, RS_THREADS, 0, st>>>(kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX,
+                                                     status + (size_t)p * L.tiles * RADIX, ticket + p);
     GSX_LAUNCH_CHECK();
     std::swap(kin, kout);
     std::swap(vin, vout);
@@ -275,11 +280,30 @@ int sort_pairs_impl(uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a, uint32
   return GSX_OK;
 }
 
+int sort_pairs_impl(uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                    const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
+                    int *result_in_b) {
+  return sort_pairs_t<uint64_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b);
+}
+int sort_pairs_u32_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                        const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
+                        int *result_in_b) {
+  return sort_pairs_t<uint32_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b);
+}
+
+static int ranges_grid(long long n, int n_tiles) {
+  long long work = std::max<long long>(n, n_tiles + 1);
+  return std::max((int)std::min<long long>(kNumSMs * 16, (work + 255) / 256), 1);
+}
 int tile_ranges_impl(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
                      cudaStream_t st) {
-  long long work = std::max<long long>(n, n_tiles + 1);
-  const int blocks = (int)std::min<long long>(kNumSMs * 16, (work + 255) / 256);
-  k_tile_ranges<<<std::max(blocks, 1), 256, 0, st>>>(sorted_keys, n, n_dev, n_tiles, ranges);
+  k_tile_ranges<uint64_t, 32><<<ranges_grid(n, n_tiles), 256, 0, st>>>(sorted_keys, n, n_dev, n_tiles, ranges);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+int tile_ranges_u32_impl(const uint32_t *sorted_tiles, long long n, const int *n_dev, int n_tiles, int *ranges,
+                         cudaStream_t st) {
+  k_tile_ranges<uint32_t, 0><<<ranges_grid(n, n_tiles), 256, 0, st>>>(sorted_tiles, n, n_dev, n_tiles, ranges);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }

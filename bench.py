@@ -285,7 +285,7 @@ def main():
     P, Pt, K, Sx, Sp = (work[k_] / nv for k_ in ("P", "Pt", "K", "S", "Sp"))
     T = ((W + 15) // 16) * ((H + 15) // 16)
     D = 3 * ((l_max + 1) ** 2 - 1)
-    passes = (32 + max(1, int(np.ceil(np.log2(T)))) + 7) // 8
+    passes = (max(1, int(np.ceil(np.log2(T)))) + 7) // 8            # tile-sort passes (8-bit digits over the tile id only)
     fp32_peak = Hh.measure_fp32_tflops()
     # algorithmic work per launch (SURVEY 8d / BASELINE.md section 5)
     PB_ = 44 + 4 * D                                                # parameter / gradient bytes per Gaussian (236 at deg 3)
@@ -293,9 +293,11 @@ def main():
         # batch kernels (one launch per batch of nv views): parameters once + per-view records / packed gradients
         "preprocess_fwd": ("hbm", PB_ * N + nv * (74 * P + 5 * (N - P))),
         "preprocess_bwd": ("hbm", PB_ * N + nv * (4 * N + 96 * Pt) + PB_ * N),
-        "scan_emit": ("hbm", 12 * K + 12 * N),
-        "sort": ("hbm", (8 + 24 * passes) * K),
-        "ranges": ("hbm", 8 * K + 4 * (T + 1)),
+        # depth keys (16N) + 4-pass depth sort of the Gaussians (4N + 4*16N) + scan through the permutation (20N) +
+        # emission in depth order (8N + 32 P' + 8K)
+        "scan_emit": ("hbm", 112 * N + 32 * Pt + 8 * K),
+        "sort": ("hbm", (4 + 16 * passes) * K),                    # tile sort: histogram read + passes * (8 B in + 8 B out)
+        "ranges": ("hbm", 4 * K + 4 * (T + 1)),
         "composite_fwd": ("fp32", 18 * Sx),
         "composite_bwd": ("fp32", 10 * Sx + 46 * Sp),
     }
@@ -318,7 +320,8 @@ def main():
                  "share_of_view": round(stage_ms[top] / sum(stage_ms.values()), 3)})
 
     views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
-    launches_per_view = 3 + 1 + 2 + passes + 1 + 2                   # scan x3, emit, histogram x2, onesweep, ranges, composite x2
+    # depth keys, histogram x2, depth onesweep x4, scan x3, emit, histogram x2, tile onesweep, ranges, composite x2
+    launches_per_view = 1 + 2 + 4 + 3 + 1 + 2 + passes + 1 + 2
     out = {
         "metric": METRIC, "value": views_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
