@@ -56,20 +56,52 @@ __device__ __forceinline__ void stage_rows(float *s_dst, const float *sh, int sh
   }
 }
 
+constexpr int VCW = sizeof(ViewConst) / 4;   // words per view (42: consecutive views fall on distinct banks)
+static_assert(sizeof(ViewConst) % 4 == 0, "ViewConst is word-sized");
+constexpr int NSLOT = BB * GSX_MAX_BATCH;    // (view, local Gaussian) slots of a block
+
+// Work list of a block: the active (view, Gaussian) pairs, compacted.  A thread appends all its pairs with one
+// shared-memory atomic; the order is irrelevant for the results (every pair writes to places keyed by (view, Gaussian)).
+__device__ __forceinline__ void append_pairs(unsigned bits, int t, unsigned *s_n, uint16_t *s_pair) {
+  if (!bits) return;
+  unsigned o = atomicAdd(s_n, (unsigned)__popc(bits));
+  while (bits) {
+    const int v = __ffs(bits) - 1;
+    bits &= bits - 1;
+    s_pair[o++] = (uint16_t)(v * BB + t);
+  }
+}
+
+__device__ __forceinline__ void copy_views_to_smem(const BatchConst &bc, float *s_view) {
+  const float *src = reinterpret_cast<const float *>(&bc.v[0]);
+  for (int k = threadIdx.x; k < bc.nv * VCW; k += BB) s_view[k] = src[k];
+}
+
+// Forward.  Phase A (thread = Gaussian): camera transform + cull for every view -> visibility bits; Sigma, sigmoid and
+// band 0 once per Gaussian into shared memory.  Phase B (thread = visible pair): Jacobian, conic, radius, extent, exact
+// tile count, SH colour -> the view's slot.  Only visible pairs cost anything beyond the cull.
 template <int L>
 __global__ void __launch_bounds__(BB, GSX_BATCH_MINB)
 k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restrict__ xyz, const float *__restrict__ scale,
             const float *__restrict__ quat, const float *__restrict__ opacity, const float *__restrict__ band0,
             const float *__restrict__ sh, int sh_stride, int chunk_ok) {
-  extern __shared__ __align__(16) float s_sh[];
+  extern __shared__ __align__(16) float s_mem[];
   __shared__ __align__(8) uint64_t s_bar;
+  __shared__ unsigned s_n;
   constexpr int n = (L + 1) * (L + 1);
   constexpr int SHF = (n - 1) * 3;
-  const int i = blockIdx.x * BB + threadIdx.x;
+  float *s_sh = s_mem;                               // [BB][SHF]
+  float *s_g = s_mem + BB * SHF;                     // [13][BB]: pw 3, sigma 6, opa, band0 3
+  float *s_view = s_g + 13 * BB;                     // [nv][VCW]
+  uint16_t *s_pair = reinterpret_cast<uint16_t *>(s_view + GSX_MAX_BATCH * VCW);   // [NSLOT]
+  const int t = threadIdx.x;
+  const int i = blockIdx.x * BB + t;
   const long long row0 = (long long)blockIdx.x * BB;
   const int rows = (int)min((long long)BB, (long long)N - row0);
   const bool use_tma = (L > 0) && chunk_ok && (((rows * SHF * 4) & 15) == 0);
   const int nv = bc.nv;
+  if (t == 0) { s_n = 0; if (use_tma) mbar_init(&s_bar, 1); }
+  copy_views_to_smem(bc, s_view);
   unsigned vis = 0;
   float3 pw = make_float3(0.f, 0.f, 0.f);
   if (i < N) {
@@ -81,33 +113,39 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       if (keep_gaussian(uv.x, uv.y, pc.z, vc.near_thresh, vc.padding, vc.width, vc.height)) vis |= 1u << v;
     }
   }
-  if (use_tma && threadIdx.x == 0) mbar_init(&s_bar, 1);
-  const int any = __syncthreads_or(vis != 0);
-  if (!any) {   // whole block culled in every view: no parameter traffic beyond xyz
-    if (i < N)
-      for (int v = 0; v < nv; ++v) { bc.s[v].mask[i] = 0; bc.s[v].touched[i] = 0; }
-    return;
-  }
+  const int any = __syncthreads_or(vis != 0);        // also publishes s_n = 0, the mbarrier and s_view
+  if (i < N)
+    for (int v = 0; v < nv; ++v)
+      if (!((vis >> v) & 1u)) { bc.s[v].mask[i] = 0; bc.s[v].touched[i] = 0; }
+  if (!any) return;                                  // whole block culled in every view: only xyz was read
   if (L > 0) stage_rows<SHF>(s_sh, sh, sh_stride, row0, rows, use_tma, &s_bar);
-  float sig[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, b0[3] = {0.f, 0.f, 0.f};
-  float opa = 0.f;
   if (vis) {
     const float4 q = reinterpret_cast<const float4 *>(quat)[i];
+    float sig[6];
     sigma_from_qs(q.x, q.y, q.z, q.w, scale[3 * i], scale[3 * i + 1], scale[3 * i + 2], sig);
-    opa = 1.0f / (1.0f + __expf(-opacity[i]));   // render.cu:56, once per Gaussian
-    b0[0] = band0[3 * i]; b0[1] = band0[3 * i + 1]; b0[2] = band0[3 * i + 2];
+    s_g[0 * BB + t] = pw.x; s_g[1 * BB + t] = pw.y; s_g[2 * BB + t] = pw.z;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) s_g[(3 + k) * BB + t] = sig[k];
+    s_g[9 * BB + t] = 1.0f / (1.0f + __expf(-opacity[i]));   // render.cu:56, once per Gaussian
+    s_g[10 * BB + t] = band0[3 * i]; s_g[11 * BB + t] = band0[3 * i + 1]; s_g[12 * BB + t] = band0[3 * i + 2];
+    append_pairs(vis, t, &s_n, s_pair);
   }
-  if (L > 0) {
-    if (use_tma) mbar_wait(&s_bar, 0);
-    else __syncthreads();
-  }
-  if (i >= N) return;
-  const float *shp = L > 0 ? s_sh + threadIdx.x * SHF : nullptr;
-  for (int v = 0; v < nv; ++v) {
+  __syncthreads();
+  if (L > 0 && use_tma) mbar_wait(&s_bar, 0);
+  const int np = (int)s_n;
+  for (int j = t; j < np; j += BB) {
+    const int slot = s_pair[j];
+    const int v = slot / BB, g = slot - v * BB;
+    const int gi = (int)row0 + g;
+    const ViewConst &vc = *reinterpret_cast<const ViewConst *>(s_view + v * VCW);
     const SlotPtrs &sp = bc.s[v];
-    if (!((vis >> v) & 1u)) { sp.mask[i] = 0; sp.touched[i] = 0; continue; }
-    const ViewConst &vc = bc.v[v];
-    const float3 pc = cam_point(vc.view, pw.x, pw.y, pw.z);
+    const float px = s_g[0 * BB + g], py = s_g[1 * BB + g], pz = s_g[2 * BB + g];
+    float sig[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) sig[k] = s_g[(3 + k) * BB + g];
+    const float opa = s_g[9 * BB + g];
+    const float b0[3] = {s_g[10 * BB + g], s_g[11 * BB + g], s_g[12 * BB + g]};
+    const float3 pc = cam_point(vc.view, px, py, pz);
     const float2 uv = screen_point(vc.proj, pc, vc.width, vc.height);
     float J[6], con[3];
     float4 rad;
@@ -122,14 +160,14 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       for (int tx = tr.x0; tx <= tr.x1; ++tx)
         for (int ty = tr.y0; ty <= tr.y1; ++ty) cnt += sat_tile_rot(so, tx, ty) ? 1 : 0;
     }
-    const float3 rgb = sh_to_rgb<L>(pw.x, pw.y, pw.z, vc.campos, b0, shp);
-    sp.r0[i] = make_float4(uv.x, uv.y, ext.x, ext.y);
-    sp.r1[i] = make_float4(con[0], con[1], con[2], opa);
-    sp.r2[i] = make_float4(rgb.x, rgb.y, rgb.z, opa * (1.0f - opa));
-    sp.radius[i] = rad;
-    sp.depth[i] = pc.z;
-    sp.touched[i] = cnt;
-    sp.mask[i] = 1;
+    const float3 rgb = sh_to_rgb<L>(px, py, pz, vc.campos, b0, L > 0 ? s_sh + g * SHF : nullptr);
+    sp.r0[gi] = make_float4(uv.x, uv.y, ext.x, ext.y);
+    sp.r1[gi] = make_float4(con[0], con[1], con[2], opa);
+    sp.r2[gi] = make_float4(rgb.x, rgb.y, rgb.z, opa * (1.0f - opa));
+    sp.radius[gi] = rad;
+    sp.depth[gi] = pc.z;
+    sp.touched[gi] = cnt;
+    sp.mask[gi] = 1;
   }
 }
 
@@ -141,6 +179,11 @@ struct BatchGradOut {
   int chunk_ok;      // SH rows of params and grads dense + 16-byte aligned -> bulk async copies
 };
 
+// Backward.  Phase A (thread = Gaussian): the views in which the Gaussian touched a tile AND received a non-zero packed
+// compositing gradient (all loads issued up front); their 9 gradient values go to shared-memory slots.  Phase B (thread
+// = active pair): F11, F12, F14, F15 and the position term of F10 -> d xyz_w (3) and d Sigma (6), in place in the slot.
+// Phase C (thread = Gaussian): sums its views, accumulates the SH coefficient gradients g_c * Y_k(view) in registers,
+// runs F13 once on the summed d Sigma, re-zeroes the packed gradients it consumed and writes every gradient once.
 template <int L>
 __global__ void __launch_bounds__(BB, GSX_BATCH_MINB)
 k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restrict__ xyz, const float *__restrict__ scale,
@@ -148,73 +191,125 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
             const BatchGradOut out) {
   extern __shared__ __align__(16) float s_mem[];
   __shared__ __align__(8) uint64_t s_bar;
+  __shared__ unsigned s_n;
   constexpr int n = (L + 1) * (L + 1);
   constexpr int SHF = (n - 1) * 3;
-  float *s_coef = s_mem, *s_grad = s_mem + BB * SHF;
-  const int i = blockIdx.x * BB + threadIdx.x;
+  float *s_coef = s_mem;                             // [BB][SHF] coefficients, re-used for the gradient rows
+  float *s_g = s_mem + BB * SHF;                     // [12][BB]: pw 3, sigma 6, band0 3
+  float *s_view = s_g + 12 * BB;                     // [nv][VCW]
+  float *s_stage = s_view + GSX_MAX_BATCH * VCW;     // [9][NSLOT]
+  uint16_t *s_pair = reinterpret_cast<uint16_t *>(s_stage + 9 * NSLOT);
+  const int t = threadIdx.x;
+  const int i = blockIdx.x * BB + t;
   const long long row0 = (long long)blockIdx.x * BB;
   const int rows = (int)min((long long)BB, (long long)N - row0);
   const bool use_tma = (L > 0) && out.chunk_ok && (((rows * SHF * 4) & 15) == 0);
   const int nv = bc.nv;
-  unsigned vis = 0;
-  if (i < N)
-    for (int v = 0; v < nv; ++v) vis |= (bc.s[v].touched[i] > 0 ? 1u : 0u) << v;
-  if (use_tma && threadIdx.x == 0) mbar_init(&s_bar, 1);
-  const int any = __syncthreads_or(vis != 0);
-  if (!any && !out.overwrite) return;
-  if (any && L > 0) stage_rows<SHF>(s_coef, sh, sh_stride, row0, rows, use_tma, &s_bar);
-  float *grow = s_grad + threadIdx.x * SHF;
-  if (L > 0) {
+  if (t == 0) { s_n = 0; if (use_tma) mbar_init(&s_bar, 1); }
+  copy_views_to_smem(bc, s_view);
+  // ---- phase A
+  unsigned tch = 0;
+  if (i < N) {
 #pragma unroll
-    for (int k = 0; k < SHF; ++k) grow[k] = 0.0f;
+    for (int v = 0; v < GSX_MAX_BATCH; ++v)
+      if (v < nv) tch |= (bc.s[v].touched[i] > 0 ? 1u : 0u) << v;
   }
-  float3 gxyz = make_float3(0.f, 0.f, 0.f), pw = gxyz;
-  float gs[3] = {0.f, 0.f, 0.f}, gq[4] = {0.f, 0.f, 0.f, 0.f}, gb0[3] = {0.f, 0.f, 0.f};
-  float dSt[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  float gopa = 0.0f, gu = 0.0f, gv = 0.0f;
+  const int any_t = __syncthreads_or(tch != 0);
+  if (!any_t && !out.overwrite) return;
+  if (any_t && L > 0) stage_rows<SHF>(s_coef, sh, sh_stride, row0, rows, use_tma, &s_bar);   // overlaps the loads below
+  unsigned act = 0;
+  for (int v = 0; v < nv; ++v) {
+    if (!((tch >> v) & 1u)) continue;
+    const float4 *ga = bc.s[v].gacc + 3 * (size_t)i;
+    const float4 a0 = ga[0], a1 = ga[1], a2 = ga[2];
+    const bool nz = (a0.x != 0.f) | (a0.y != 0.f) | (a0.z != 0.f) | (a0.w != 0.f) | (a1.x != 0.f) | (a1.y != 0.f) |
+                    (a1.z != 0.f) | (a1.w != 0.f) | (a2.x != 0.f);
+    if (!nz) continue;
+    act |= 1u << v;
+    float *st = s_stage + v * BB + t;
+    st[0 * NSLOT] = a0.x; st[1 * NSLOT] = a0.y; st[2 * NSLOT] = a0.z; st[3 * NSLOT] = a0.w;
+    st[4 * NSLOT] = a1.x; st[5 * NSLOT] = a1.y; st[6 * NSLOT] = a1.z; st[7 * NSLOT] = a1.w; st[8 * NSLOT] = a2.x;
+  }
+  float3 pw = make_float3(0.f, 0.f, 0.f);
   float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f, sig[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, b0[3] = {0.f, 0.f, 0.f};
-  if (vis) {
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+  if (act) {
     pw = make_float3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
     q = reinterpret_cast<const float4 *>(quat)[i];
     s0 = scale[3 * i]; s1 = scale[3 * i + 1]; s2 = scale[3 * i + 2];
-    b0[0] = band0[3 * i]; b0[1] = band0[3 * i + 1]; b0[2] = band0[3 * i + 2];
+    float sig[6];
     sigma_from_qs(q.x, q.y, q.z, q.w, s0, s1, s2, sig);
+    s_g[0 * BB + t] = pw.x; s_g[1 * BB + t] = pw.y; s_g[2 * BB + t] = pw.z;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) s_g[(3 + k) * BB + t] = sig[k];
+    s_g[9 * BB + t] = band0[3 * i]; s_g[10 * BB + t] = band0[3 * i + 1]; s_g[11 * BB + t] = band0[3 * i + 2];
+    append_pairs(act, t, &s_n, s_pair);
   }
-  if (any && L > 0) {
-    if (use_tma) mbar_wait(&s_bar, 0);
-    else __syncthreads();
-  }
-  const float *crow = s_coef + threadIdx.x * SHF;
-  for (int v = 0; v < nv; ++v) {
-    if (!((vis >> v) & 1u)) continue;
-    const ViewConst &vc = bc.v[v];
-    float4 *ga = bc.s[v].gacc + 3 * (size_t)i;
-    const float4 a0 = ga[0], a1 = ga[1], a2 = ga[2];
-    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    ga[0] = z4; ga[1] = z4; ga[2] = z4;   // the slot's packed gradients are zero again for the next batch
-    const float g_con[3] = {a1.z, a1.w, a2.x};
-    const float3 pc = cam_point(vc.view, pw.x, pw.y, pw.z);
+  __syncthreads();
+  if (any_t && L > 0 && use_tma) mbar_wait(&s_bar, 0);
+  // ---- phase B
+  const int np = (int)s_n;
+  for (int j = t; j < np; j += BB) {
+    const int slot = s_pair[j];
+    const int v = slot / BB, g = slot - v * BB;
+    const ViewConst &vc = *reinterpret_cast<const ViewConst *>(s_view + v * VCW);
+    float *st = s_stage + slot;
+    const float g_r = st[0 * NSLOT], g_g = st[1 * NSLOT], g_b = st[2 * NSLOT];
+    const float g_u = st[4 * NSLOT], g_v = st[5 * NSLOT];
+    const float g_con[3] = {st[6 * NSLOT], st[7 * NSLOT], st[8 * NSLOT]};
+    const float px = s_g[0 * BB + g], py = s_g[1 * BB + g], pz = s_g[2 * BB + g];
+    float sig[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) sig[k] = s_g[(3 + k) * BB + g];
+    const float b0[3] = {s_g[9 * BB + g], s_g[10 * BB + g], s_g[11 * BB + g]};
+    const float3 pc = cam_point(vc.view, px, py, pz);
     float J[6], con[3], dS[6], dJ[6];
     float4 rad_unused;
     projection_jacobian(pc.x, pc.y, pc.z, vc.fx, vc.fy, vc.tan_fovx, vc.tan_fovy, J);
     conic_and_radius(J, sig, vc.view, vc.mh_dist, con, &rad_unused);   // same arithmetic as the forward: same bits
     conic_backward(J, sig, vc.view, con, g_con, dS, dJ);                // F11
-    float3 gc = make_float3(0.f, 0.f, 0.f), t;
-    if (jacobian_backward(pc.x, pc.y, pc.z, vc.fx, vc.fy, vc.tan_fovx, vc.tan_fovy, dJ, &t)) { gc.x += t.x; gc.y += t.y; gc.z += t.z; }   // F12
-    if (screen_backward(vc.proj, pc.x, pc.y, pc.z, a1.x, a1.y, vc.width, vc.height, &t)) { gc.x += t.x; gc.y += t.y; gc.z += t.z; }        // F14
+    float3 gc = make_float3(0.f, 0.f, 0.f), tt;
+    if (jacobian_backward(pc.x, pc.y, pc.z, vc.fx, vc.fy, vc.tan_fovx, vc.tan_fovy, dJ, &tt)) { gc.x += tt.x; gc.y += tt.y; gc.z += tt.z; }   // F12
+    if (screen_backward(vc.proj, pc.x, pc.y, pc.z, g_u, g_v, vc.width, vc.height, &tt)) { gc.x += tt.x; gc.y += tt.y; gc.z += tt.z; }          // F14
     const float3 gw = cam_point_backward(vc.view, gc.x, gc.y, gc.z);   // F15
-    const float3 gsh = sh_backward<L>(pw.x, pw.y, pw.z, vc.campos, b0, crow, a0.x, a0.y, a0.z, out.compat_dsph != 0, grow,
-                                      gb0, true);                      // F10
-    gxyz.x += gsh.x + gw.x; gxyz.y += gsh.y + gw.y; gxyz.z += gsh.z + gw.z;
+    const float3 gsh = sh_dir_backward<L>(px, py, pz, vc.campos, b0, L > 0 ? s_coef + g * SHF : nullptr, g_r, g_g, g_b,
+                                          out.compat_dsph != 0);       // F10, position term
+    st[0 * NSLOT] = gsh.x + gw.x; st[1 * NSLOT] = gsh.y + gw.y; st[2 * NSLOT] = gsh.z + gw.z;
 #pragma unroll
-    for (int k = 0; k < 6; ++k) dSt[k] += dS[k];
-    gopa += a0.w; gu += a1.x; gv += a1.y;
+    for (int k = 0; k < 6; ++k) st[(3 + k) * NSLOT] = dS[k];
   }
-  if (vis) sigma_backward(q.x, q.y, q.z, q.w, s0, s1, s2, dSt, gq, gs);   // F13, once on the view-summed dSigma
-  if (i < N && (vis || out.overwrite)) {
+  __syncthreads();   // slots hold the pair results; the coefficient rows are free to be overwritten
+  // ---- phase C
+  float gxyz[3] = {0.f, 0.f, 0.f}, dSt[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, gb0[3] = {0.f, 0.f, 0.f};
+  float gsh[SHF > 0 ? SHF : 1];
+#pragma unroll
+  for (int k = 0; k < SHF; ++k) gsh[k] = 0.0f;
+  float gopa = 0.0f, gu = 0.0f, gv = 0.0f;
+  for (int v = 0; v < nv; ++v) {
+    if (!((act >> v) & 1u)) continue;
+    float4 *ga = bc.s[v].gacc + 3 * (size_t)i;
+    const float4 a0 = ga[0], a1 = ga[1];
+    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    ga[0] = z4; ga[1] = z4; ga[2] = z4;   // the slot's packed gradients are zero again for the next batch
+    const float *st = s_stage + v * BB + t;
+    gxyz[0] += st[0 * NSLOT]; gxyz[1] += st[1 * NSLOT]; gxyz[2] += st[2 * NSLOT];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) dSt[k] += st[(3 + k) * NSLOT];
+    gopa += a0.w; gu += a1.x; gv += a1.y;
+    float Y[n];
+    const ViewConst &vc = *reinterpret_cast<const ViewConst *>(s_view + v * VCW);
+    sh_basis_of_point<L>(pw.x, pw.y, pw.z, vc.campos, Y);
+    gb0[0] += a0.x * Y[0]; gb0[1] += a0.y * Y[0]; gb0[2] += a0.z * Y[0];
+#pragma unroll
+    for (int k = 1; k < n; ++k) {
+      gsh[3 * (k - 1) + 0] += a0.x * Y[k]; gsh[3 * (k - 1) + 1] += a0.y * Y[k]; gsh[3 * (k - 1) + 2] += a0.z * Y[k];
+    }
+  }
+  float gq[4] = {0.f, 0.f, 0.f, 0.f}, gs[3] = {0.f, 0.f, 0.f};
+  if (act) sigma_backward(q.x, q.y, q.z, q.w, s0, s1, s2, dSt, gq, gs);   // F13, once on the view-summed dSigma
+  if (i < N && (act || out.overwrite)) {
     if (out.overwrite) {
-      out.xyz[3 * i] = gxyz.x; out.xyz[3 * i + 1] = gxyz.y; out.xyz[3 * i + 2] = gxyz.z;
+      out.xyz[3 * i] = gxyz[0]; out.xyz[3 * i + 1] = gxyz[1]; out.xyz[3 * i + 2] = gxyz[2];
       out.scale[3 * i] = gs[0]; out.scale[3 * i + 1] = gs[1]; out.scale[3 * i + 2] = gs[2];
       reinterpret_cast<float4 *>(out.quat)[i] = make_float4(gq[0], gq[1], gq[2], gq[3]);
       out.opacity[i] = gopa;
@@ -229,7 +324,7 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       const float ob0 = out.band0[3 * i], ob1 = out.band0[3 * i + 1], ob2 = out.band0[3 * i + 2];
       float ou = 0.f, ov = 0.f;
       if (out.uv) { ou = out.uv[2 * i]; ov = out.uv[2 * i + 1]; }
-      out.xyz[3 * i] = ox0 + gxyz.x; out.xyz[3 * i + 1] = ox1 + gxyz.y; out.xyz[3 * i + 2] = ox2 + gxyz.z;
+      out.xyz[3 * i] = ox0 + gxyz[0]; out.xyz[3 * i + 1] = ox1 + gxyz[1]; out.xyz[3 * i + 2] = ox2 + gxyz[2];
       out.scale[3 * i] = os0 + gs[0]; out.scale[3 * i + 1] = os1 + gs[1]; out.scale[3 * i + 2] = os2 + gs[2];
       c.x += gq[0]; c.y += gq[1]; c.z += gq[2]; c.w += gq[3];
       *qq = c;
@@ -239,23 +334,26 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     }
   }
   if (L > 0) {
+    float *grow = s_coef + t * SHF;
+#pragma unroll
+    for (int k = 0; k < SHF; ++k) grow[k] = gsh[k];
     if (use_tma) {
       fence_proxy_async_smem();
       __syncthreads();
-      if (threadIdx.x == 0) {
+      if (t == 0) {
         float *dst = out.sh + row0 * SHF;
         const uint32_t bytes = (uint32_t)rows * SHF * 4u;
-        if (out.overwrite) bulk_store(dst, s_grad, bytes);
-        else bulk_reduce_add_f32(dst, s_grad, bytes);
+        if (out.overwrite) bulk_store(dst, s_coef, bytes);
+        else bulk_reduce_add_f32(dst, s_coef, bytes);
         bulk_commit();
         bulk_wait_read_all();   // shared memory must outlive the bulk store
       }
     } else {
       __syncthreads();
-      for (int k = threadIdx.x; k < rows * SHF; k += BB) {
+      for (int k = t; k < rows * SHF; k += BB) {
         const int r = k / (SHF > 0 ? SHF : 1), c = k - r * SHF;
         float *o = out.sh + (size_t)(row0 + r) * out.sh_stride + c;
-        *o = out.overwrite ? s_grad[k] : *o + s_grad[k];
+        *o = out.overwrite ? s_coef[k] : *o + s_coef[k];
       }
     }
   }
@@ -269,7 +367,7 @@ int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_m
   if (N <= 0 || bc.nv <= 0) return GSX_OK;
   const int shf = sh_floats(l_max);
   const int ok = l_max > 0 && p.sh_stride == shf && (((uintptr_t)p.sh) & 15) == 0;
-  const size_t sm = (size_t)BB * shf * sizeof(float);
+  const size_t sm = ((size_t)BB * shf + 13 * BB + GSX_MAX_BATCH * VCW) * sizeof(float) + NSLOT * sizeof(uint16_t);
   const int grid = ceil_div(N, BB);
 #define GSX_BF(L)                                                                                                     \
   do {                                                                                                                \
@@ -299,7 +397,7 @@ int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_m
   o.overwrite = (flags & GSX_GRAD_OVERWRITE) ? 1 : 0;
   o.compat_dsph = (flags & GSX_SH_DSPH_CORRECT) ? 0 : 1;
   o.chunk_ok = l_max > 0 && p.sh_stride == shf && (((uintptr_t)p.sh) & 15) == 0 && (((uintptr_t)g.sh) & 15) == 0;
-  const size_t sm = (size_t)2 * BB * shf * sizeof(float);
+  const size_t sm = ((size_t)BB * shf + 12 * BB + GSX_MAX_BATCH * VCW + 9 * NSLOT) * sizeof(float) + NSLOT * sizeof(uint16_t);
   const int grid = ceil_div(N, BB);
 #define GSX_BB(L)                                                                                                   \
   do {                                                                                                              \

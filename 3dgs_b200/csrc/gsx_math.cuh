@@ -478,4 +478,43 @@ __device__ __forceinline__ float3 sh_backward(float px, float py, float pz, floa
   return make_float3((tx - dot * dirx) / len, (ty - dot * diry) / len, (tz - dot * dirz) / len);
 }
 
+// The position term of F10 alone (cuda/spherical_harmonics_backward.cu:106-164): d xyz_w through the view direction,
+// without the coefficient gradients (the batch kernel accumulates those per Gaussian, batch.cu).  Same arithmetic
+// and order as sh_backward.
+template <int L>
+__device__ __forceinline__ float3 sh_dir_backward(float px, float py, float pz, float3 campos, const float *band0,
+                                                  const float *sh, float gr, float gg, float gb, bool compat) {
+  constexpr int n = (L + 1) * (L + 1);
+  const float dx = px - campos.x, dy = py - campos.y, dz = pz - campos.z;
+  const float len = sqrtf(dx * dx + dy * dy + dz * dz) + 1e-9f;
+  const float dirx = dx / len, diry = dy / len, dirz = dz / len;
+  float Y[n], D[3 * n];   // D = [axis][k]
+  sph_eval<L, true>(dirx, diry, dirz, Y, D, D + n, D + 2 * n);
+  float dR[3] = {0.f, 0.f, 0.f}, dG[3] = {0.f, 0.f, 0.f}, dB[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < n; ++k) {
+    float R, G, B;
+    if (k == 0) { R = band0[0]; G = band0[1]; B = band0[2]; }
+    else { R = sh[3 * (k - 1)]; G = sh[3 * (k - 1) + 1]; B = sh[3 * (k - 1) + 2]; }
+#pragma unroll
+    for (int ax = 0; ax < 3; ++ax) {
+      const float d = compat ? D[k * 3 + ax] : D[ax * n + k];
+      dR[ax] += d * R; dG[ax] += d * G; dB[ax] += d * B;
+    }
+  }
+  const float tx = gr * dR[0] + gg * dG[0] + gb * dB[0];
+  const float ty = gr * dR[1] + gg * dG[1] + gb * dB[1];
+  const float tz = gr * dR[2] + gg * dG[2] + gb * dB[2];
+  const float dot = tx * dirx + ty * diry + tz * dirz;
+  return make_float3((tx - dot * dirx) / len, (ty - dot * diry) / len, (tz - dot * dirz) / len);
+}
+
+// Y_k of the view direction of a world point (the basis values F6 and the coefficient part of F10 use)
+template <int L>
+__device__ __forceinline__ void sh_basis_of_point(float px, float py, float pz, float3 campos, float *Y) {
+  const float dx = px - campos.x, dy = py - campos.y, dz = pz - campos.z;
+  const float len = sqrtf(dx * dx + dy * dy + dz * dz) + 1e-9f;
+  sph_eval<L, false>(dx / len, dy / len, dz / len, Y, nullptr, nullptr, nullptr);
+}
+
 }  // namespace gsx
