@@ -13,6 +13,7 @@ GSX_OK = 0
 GSX_E_CAPACITY = 6
 GSX_SH_DSPH_CORRECT = 1
 GSX_GRAD_OVERWRITE = 2
+GSX_GRAD_NO_SH = 4
 
 # every symbol include/gsx.h declares (tests check the library exports all of them)
 SYMBOLS = [
@@ -26,7 +27,8 @@ SYMBOLS = [
     "gsx_ctx_create", "gsx_ctx_destroy", "gsx_forward", "gsx_backward", "gsx_ctx_stats", "gsx_ctx_reserve",
     "gsx_ctx_state", "gsx_render_view_host", "gsx_ctx_enable_timing", "gsx_ctx_timing", "gsx_ctx_count_work", "gsx_measure_fp32_tflops",
     "gsx_batch_reserve", "gsx_batch_forward_params", "gsx_batch_forward_view", "gsx_batch_backward_view",
-    "gsx_batch_backward_params", "gsx_batch_render_host",
+    "gsx_batch_backward_params", "gsx_batch_render_host", "gsx_batch_extract_view_rgb_grad",
+    "gsx_sh_grads_from_view_rgb", "gsx_ctx_build_sorted_keys",
 ]
 
 

@@ -44,6 +44,10 @@ int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_
 int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, cudaStream_t st);
 int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, const gsx_grads_t &g, int flags,
                      cudaStream_t st);
+int extract_view_rgb_launch(const float4 *gacc, const int *touched, int N, float *drgb, cudaStream_t st);
+int sh_from_view_rgb_launch(const float *xyz, int N, int l_max, const float *campos_host, int n_views, const float *drgb,
+                            size_t view_stride, float *sh_grad, int sh_stride, float *band0_grad, int flags,
+                            cudaStream_t st);
 int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
                          int W, int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st);
 int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
@@ -320,6 +324,22 @@ int gsx_batch_backward_params(gsx_ctx_t *c, const gsx_params_t *p, int N, const 
   return rc;
 }
 
+int gsx_batch_extract_view_rgb_grad(gsx_ctx_t *c, int slot, float *drgb, void *stream) {
+  if (!c || !drgb) { set_error("null argument"); return GSX_E_NULL; }
+  if (slot < 0 || slot >= c->batch_nv) { set_error("slot %d outside the current batch (%d views)", slot, c->batch_nv); return GSX_E_ARG; }
+  return extract_view_rgb_launch(c->slot[slot].p.gacc, c->slot[slot].p.touched, c->batch_n, drgb, (cudaStream_t)stream);
+}
+
+int gsx_sh_grads_from_view_rgb(const float *xyz_w, int N, int l_max, const float *campos_host, int n_views,
+                               const float *drgb, size_t view_stride, float *sh_grad, int sh_stride, float *band0_grad,
+                               int flags, void *stream) {
+  if (!campos_host) { set_error("null campos"); return GSX_E_NULL; }
+  GSX_REQUIRE_DEV(xyz_w); GSX_REQUIRE_DEV(drgb); GSX_REQUIRE_DEV(band0_grad);
+  if (l_max > 0) GSX_REQUIRE_DEV(sh_grad);
+  return sh_from_view_rgb_launch(xyz_w, N, l_max, campos_host, n_views, drgb, view_stride, sh_grad, sh_stride, band0_grad,
+                                 flags, (cudaStream_t)stream);
+}
+
 // Host-buffer batch step: per view H2D of the loss-gradient image and D2H of the rendered image (pinned host memory),
 // forward + backward of every view, one pass of parameter gradients.  Synchronises.
 int gsx_batch_render_host(gsx_ctx_t *c, const gsx_view_t *views, int n_views, const gsx_params_t *p, int N,
@@ -451,23 +471,29 @@ int gsx_ctx_state(gsx_ctx_t *c, gsx_state_t *o) {
   o->radius = (const float *)sp.radius; o->depth = sp.depth; o->mask = sp.mask;
   o->tiles_touched = sp.touched;
   o->sorted_gaussians = (const int *)c->sorted_vals;
-  o->sorted_keys = nullptr;
-  if (c->sorted_tiles) {   // synchronous: inspection only, never on the hot path
-    if (c->key64_cap < c->capacity) {
-      if (c->key64) cudaFree(c->key64);
-      c->key64 = nullptr; c->key64_cap = 0;
-      GSX_CUDA(cudaMalloc(&c->key64, sizeof(uint64_t) * (size_t)c->capacity));
-      c->key64_cap = c->capacity;
-    }
-    GSX_CUDA(cudaDeviceSynchronize());
-    k_compose_keys<<<kNumSMs * 8, 256>>>(c->sorted_tiles, c->sorted_vals, sp.depth, (const int *)(c->bin_ws + c->L.total),
-                                         c->capacity, c->key64);
-    GSX_LAUNCH_CHECK();
-    GSX_CUDA(cudaDeviceSynchronize());
-    o->sorted_keys = c->key64;
-  }
+  o->sorted_keys = nullptr;   /* never materialised by the two-level sort: gsx_ctx_build_sorted_keys */
   o->ranges = c->ranges; o->num_instances = (const int *)(c->bin_ws + c->L.total);
   o->packed_grads = (const float *)sp.gacc;
+  return GSX_OK;
+}
+
+// The 64-bit tile|depth keys of the last forward, rebuilt for inspection (tests): synchronous, never on the hot path.
+int gsx_ctx_build_sorted_keys(gsx_ctx_t *c, const uint64_t **out) {
+  if (!c || !out) return GSX_E_NULL;
+  *out = nullptr;
+  if (!c->sorted_tiles) return GSX_OK;
+  if (c->key64_cap < c->capacity) {
+    if (c->key64) cudaFree(c->key64);
+    c->key64 = nullptr; c->key64_cap = 0;
+    GSX_CUDA(cudaMalloc(&c->key64, sizeof(uint64_t) * (size_t)c->capacity));
+    c->key64_cap = c->capacity;
+  }
+  GSX_CUDA(cudaDeviceSynchronize());
+  k_compose_keys<<<kNumSMs * 8, 256>>>(c->sorted_tiles, c->sorted_vals, c->slot[c->cur].p.depth,
+                                       (const int *)(c->bin_ws + c->L.total), c->capacity, c->key64);
+  GSX_LAUNCH_CHECK();
+  GSX_CUDA(cudaDeviceSynchronize());
+  *out = c->key64;
   return GSX_OK;
 }
 

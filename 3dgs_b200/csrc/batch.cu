@@ -184,7 +184,9 @@ struct BatchGradOut {
 // = active pair): F11, F12, F14, F15 and the position term of F10 -> d xyz_w (3) and d Sigma (6), in place in the slot.
 // Phase C (thread = Gaussian): sums its views, accumulates the SH coefficient gradients g_c * Y_k(view) in registers,
 // runs F13 once on the summed d Sigma, re-zeroes the packed gradients it consumed and writes every gradient once.
-template <int L>
+// COEF = false: the SH coefficient / band-0 gradients are left out (view-parallel multi-GPU mode: they are rebuilt
+// from the all-gathered per-view colour gradients by k_sh_from_view_rgb, see below).
+template <int L, bool COEF>
 __global__ void __launch_bounds__(BB, GSX_BATCH_MINB)
 k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restrict__ xyz, const float *__restrict__ scale,
             const float *__restrict__ quat, const float *__restrict__ band0, const float *__restrict__ sh, int sh_stride,
@@ -281,9 +283,10 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
   __syncthreads();   // slots hold the pair results; the coefficient rows are free to be overwritten
   // ---- phase C
   float gxyz[3] = {0.f, 0.f, 0.f}, dSt[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, gb0[3] = {0.f, 0.f, 0.f};
-  float gsh[SHF > 0 ? SHF : 1];
+  constexpr int NG = (COEF && SHF > 0) ? SHF : 1;
+  float gsh[NG];
 #pragma unroll
-  for (int k = 0; k < SHF; ++k) gsh[k] = 0.0f;
+  for (int k = 0; k < NG; ++k) gsh[k] = 0.0f;
   float gopa = 0.0f, gu = 0.0f, gv = 0.0f;
   for (int v = 0; v < nv; ++v) {
     if (!((act >> v) & 1u)) continue;
@@ -296,13 +299,15 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
 #pragma unroll
     for (int k = 0; k < 6; ++k) dSt[k] += st[(3 + k) * NSLOT];
     gopa += a0.w; gu += a1.x; gv += a1.y;
-    float Y[n];
-    const ViewConst &vc = *reinterpret_cast<const ViewConst *>(s_view + v * VCW);
-    sh_basis_of_point<L>(pw.x, pw.y, pw.z, vc.campos, Y);
-    gb0[0] += a0.x * Y[0]; gb0[1] += a0.y * Y[0]; gb0[2] += a0.z * Y[0];
+    if (COEF) {
+      float Y[n];
+      const ViewConst &vc = *reinterpret_cast<const ViewConst *>(s_view + v * VCW);
+      sh_basis_of_point<L>(pw.x, pw.y, pw.z, vc.campos, Y);
+      gb0[0] += a0.x * Y[0]; gb0[1] += a0.y * Y[0]; gb0[2] += a0.z * Y[0];
 #pragma unroll
-    for (int k = 1; k < n; ++k) {
-      gsh[3 * (k - 1) + 0] += a0.x * Y[k]; gsh[3 * (k - 1) + 1] += a0.y * Y[k]; gsh[3 * (k - 1) + 2] += a0.z * Y[k];
+      for (int k = 1; k < n; ++k) {
+        gsh[3 * (k - 1) + 0] += a0.x * Y[k]; gsh[3 * (k - 1) + 1] += a0.y * Y[k]; gsh[3 * (k - 1) + 2] += a0.z * Y[k];
+      }
     }
   }
   float gq[4] = {0.f, 0.f, 0.f, 0.f}, gs[3] = {0.f, 0.f, 0.f};
@@ -313,7 +318,7 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       out.scale[3 * i] = gs[0]; out.scale[3 * i + 1] = gs[1]; out.scale[3 * i + 2] = gs[2];
       reinterpret_cast<float4 *>(out.quat)[i] = make_float4(gq[0], gq[1], gq[2], gq[3]);
       out.opacity[i] = gopa;
-      out.band0[3 * i] = gb0[0]; out.band0[3 * i + 1] = gb0[1]; out.band0[3 * i + 2] = gb0[2];
+      if (COEF) { out.band0[3 * i] = gb0[0]; out.band0[3 * i + 1] = gb0[1]; out.band0[3 * i + 2] = gb0[2]; }
       if (out.uv) { out.uv[2 * i] = gu; out.uv[2 * i + 1] = gv; }
     } else {
       const float ox0 = out.xyz[3 * i], ox1 = out.xyz[3 * i + 1], ox2 = out.xyz[3 * i + 2];
@@ -321,7 +326,8 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       float4 *qq = reinterpret_cast<float4 *>(out.quat) + i;
       float4 c = *qq;
       const float oo = out.opacity[i];
-      const float ob0 = out.band0[3 * i], ob1 = out.band0[3 * i + 1], ob2 = out.band0[3 * i + 2];
+      float ob0 = 0.f, ob1 = 0.f, ob2 = 0.f;
+      if (COEF) { ob0 = out.band0[3 * i]; ob1 = out.band0[3 * i + 1]; ob2 = out.band0[3 * i + 2]; }
       float ou = 0.f, ov = 0.f;
       if (out.uv) { ou = out.uv[2 * i]; ov = out.uv[2 * i + 1]; }
       out.xyz[3 * i] = ox0 + gxyz[0]; out.xyz[3 * i + 1] = ox1 + gxyz[1]; out.xyz[3 * i + 2] = ox2 + gxyz[2];
@@ -329,11 +335,11 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       c.x += gq[0]; c.y += gq[1]; c.z += gq[2]; c.w += gq[3];
       *qq = c;
       out.opacity[i] = oo + gopa;
-      out.band0[3 * i] = ob0 + gb0[0]; out.band0[3 * i + 1] = ob1 + gb0[1]; out.band0[3 * i + 2] = ob2 + gb0[2];
+      if (COEF) { out.band0[3 * i] = ob0 + gb0[0]; out.band0[3 * i + 1] = ob1 + gb0[1]; out.band0[3 * i + 2] = ob2 + gb0[2]; }
       if (out.uv) { out.uv[2 * i] = ou + gu; out.uv[2 * i + 1] = ov + gv; }
     }
   }
-  if (L > 0) {
+  if (L > 0 && COEF) {
     float *grow = s_coef + t * SHF;
 #pragma unroll
     for (int k = 0; k < SHF; ++k) grow[k] = gsh[k];
@@ -354,6 +360,82 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
         const int r = k / (SHF > 0 ? SHF : 1), c = k - r * SHF;
         float *o = out.sh + (size_t)(row0 + r) * out.sh_stride + c;
         *o = out.overwrite ? s_coef[k] : *o + s_coef[k];
+      }
+    }
+  }
+}
+
+// View-parallel multi-GPU mode.  d rgb of one view, dense [N][3] (zeros where the Gaussian got no gradient): the rank-1
+// factor of that view's SH coefficient gradient, d sh[k][c] = d rgb_c * Y_k(dir_view)
+// (cuda/spherical_harmonics_backward.cu:100-104).  12 B/Gaussian/view cross NVLink instead of 192 B/Gaussian.
+__global__ void __launch_bounds__(256) k_extract_view_rgb(const float4 *__restrict__ gacc, const int *__restrict__ touched,
+                                                          int N, float *__restrict__ drgb) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= N) return;
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (touched[i] > 0) a = gacc[3 * (size_t)i];
+  drgb[3 * (size_t)i] = a.x; drgb[3 * (size_t)i + 1] = a.y; drgb[3 * (size_t)i + 2] = a.z;
+}
+
+struct ViewCams { float campos[GSX_MAX_VIEWS_TOTAL][3]; int nv; };
+
+// SH coefficient + band-0 gradients of a whole batch from the per-view colour gradients of ALL its views (gathered
+// from every rank): out[k][c] = sum_v drgb[v][i][c] * Y_k(dir_v(i)).  One pass: reads 12 B per (view, Gaussian), writes
+// the 180 + 12 B gradient row once (rows leave through one bulk async store per block).
+template <int L>
+__global__ void __launch_bounds__(BB) k_sh_from_view_rgb(const __grid_constant__ ViewCams vc, int N,
+                                                          const float *__restrict__ xyz, const float *__restrict__ drgb,
+                                                          size_t view_stride, float *__restrict__ sh_grad, int sh_stride,
+                                                          float *__restrict__ band0_grad, int overwrite, int chunk_ok) {
+  extern __shared__ __align__(16) float s_rows[];
+  constexpr int n = (L + 1) * (L + 1);
+  constexpr int SHF = (n - 1) * 3;
+  const int t = threadIdx.x;
+  const int i = blockIdx.x * BB + t;
+  const long long row0 = (long long)blockIdx.x * BB;
+  const int rows = (int)min((long long)BB, (long long)N - row0);
+  const bool use_tma = (L > 0) && chunk_ok && (((rows * SHF * 4) & 15) == 0);
+  float gsh[SHF > 0 ? SHF : 1], gb0[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+  for (int k = 0; k < SHF; ++k) gsh[k] = 0.0f;
+  if (i < N) {
+    const float px = xyz[3 * i], py = xyz[3 * i + 1], pz = xyz[3 * i + 2];
+    for (int v = 0; v < vc.nv; ++v) {
+      const float *g = drgb + (size_t)v * view_stride + 3 * (size_t)i;
+      const float gr = g[0], gg = g[1], gb = g[2];
+      if (gr == 0.f && gg == 0.f && gb == 0.f) continue;
+      float Y[n];
+      sh_basis_of_point<L>(px, py, pz, make_float3(vc.campos[v][0], vc.campos[v][1], vc.campos[v][2]), Y);
+      gb0[0] += gr * Y[0]; gb0[1] += gg * Y[0]; gb0[2] += gb * Y[0];
+#pragma unroll
+      for (int k = 1; k < n; ++k) {
+        gsh[3 * (k - 1) + 0] += gr * Y[k]; gsh[3 * (k - 1) + 1] += gg * Y[k]; gsh[3 * (k - 1) + 2] += gb * Y[k];
+      }
+    }
+    if (overwrite) { band0_grad[3 * i] = gb0[0]; band0_grad[3 * i + 1] = gb0[1]; band0_grad[3 * i + 2] = gb0[2]; }
+    else { band0_grad[3 * i] += gb0[0]; band0_grad[3 * i + 1] += gb0[1]; band0_grad[3 * i + 2] += gb0[2]; }
+  }
+  if (L > 0) {
+    float *grow = s_rows + t * SHF;
+#pragma unroll
+    for (int k = 0; k < SHF; ++k) grow[k] = gsh[k];
+    if (use_tma) {
+      fence_proxy_async_smem();
+      __syncthreads();
+      if (t == 0) {
+        float *dst = sh_grad + row0 * SHF;
+        const uint32_t bytes = (uint32_t)rows * SHF * 4u;
+        if (overwrite) bulk_store(dst, s_rows, bytes);
+        else bulk_reduce_add_f32(dst, s_rows, bytes);
+        bulk_commit();
+        bulk_wait_read_all();
+      }
+    } else {
+      __syncthreads();
+      for (int k = t; k < rows * SHF; k += BB) {
+        const int r = k / (SHF > 0 ? SHF : 1), c = k - r * SHF;
+        float *o = sh_grad + (size_t)(row0 + r) * sh_stride + c;
+        *o = overwrite ? s_rows[k] : *o + s_rows[k];
       }
     }
   }
@@ -399,10 +481,16 @@ int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_m
   o.chunk_ok = l_max > 0 && p.sh_stride == shf && (((uintptr_t)p.sh) & 15) == 0 && (((uintptr_t)g.sh) & 15) == 0;
   const size_t sm = ((size_t)BB * shf + 12 * BB + GSX_MAX_BATCH * VCW + 9 * NSLOT) * sizeof(float) + NSLOT * sizeof(uint16_t);
   const int grid = ceil_div(N, BB);
+  const bool coef = !(flags & GSX_GRAD_NO_SH);
 #define GSX_BB(L)                                                                                                   \
   do {                                                                                                              \
-    GSX_CUDA(cudaFuncSetAttribute(k_batch_bwd<L>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));            \
-    k_batch_bwd<L><<<grid, BB, sm, st>>>(bc, N, p.xyz, p.scale, p.quaternion, p.band0, p.sh, p.sh_stride, o);         \
+    if (coef) {                                                                                                     \
+      GSX_CUDA(cudaFuncSetAttribute(k_batch_bwd<L, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));    \
+      k_batch_bwd<L, true><<<grid, BB, sm, st>>>(bc, N, p.xyz, p.scale, p.quaternion, p.band0, p.sh, p.sh_stride, o); \
+    } else {                                                                                                        \
+      GSX_CUDA(cudaFuncSetAttribute(k_batch_bwd<L, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));   \
+      k_batch_bwd<L, false><<<grid, BB, sm, st>>>(bc, N, p.xyz, p.scale, p.quaternion, p.band0, p.sh, p.sh_stride, o); \
+    }                                                                                                               \
   } while (0)
   switch (l_max) {
     case 0: GSX_BB(0); break;
@@ -412,6 +500,41 @@ int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_m
     default: set_error("l_max %d out of range 0..3", l_max); return GSX_E_ARG;
   }
 #undef GSX_BB
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+int extract_view_rgb_launch(const float4 *gacc, const int *touched, int N, float *drgb, cudaStream_t st) {
+  if (N <= 0) return GSX_OK;
+  k_extract_view_rgb<<<ceil_div(N, 256), 256, 0, st>>>(gacc, touched, N, drgb);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+int sh_from_view_rgb_launch(const float *xyz, int N, int l_max, const float *campos_host, int n_views, const float *drgb,
+                            size_t view_stride, float *sh_grad, int sh_stride, float *band0_grad, int flags,
+                            cudaStream_t st) {
+  if (N <= 0 || n_views <= 0) return GSX_OK;
+  if (n_views > GSX_MAX_VIEWS_TOTAL) { set_error("n_views %d > %d", n_views, GSX_MAX_VIEWS_TOTAL); return GSX_E_ARG; }
+  ViewCams vc;
+  vc.nv = n_views;
+  for (int v = 0; v < n_views; ++v)
+    for (int k = 0; k < 3; ++k) vc.campos[v][k] = campos_host[3 * v + k];
+  const int shf = sh_floats(l_max);
+  const int ok = l_max > 0 && sh_stride == shf && (((uintptr_t)sh_grad) & 15) == 0;
+  const int overwrite = (flags & GSX_GRAD_OVERWRITE) ? 1 : 0;
+  const size_t sm = (size_t)BB * shf * sizeof(float);
+  const int grid = ceil_div(N, BB);
+#define GSX_SV(L) \
+  k_sh_from_view_rgb<L><<<grid, BB, sm, st>>>(vc, N, xyz, drgb, view_stride, sh_grad, sh_stride, band0_grad, overwrite, ok)
+  switch (l_max) {
+    case 0: GSX_SV(0); break;
+    case 1: GSX_SV(1); break;
+    case 2: GSX_SV(2); break;
+    case 3: GSX_SV(3); break;
+    default: set_error("l_max %d out of range 0..3", l_max); return GSX_E_ARG;
+  }
+#undef GSX_SV
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }

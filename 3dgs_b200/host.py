@@ -347,6 +347,10 @@ class Rasterizer:
     def batch_backward_view(self, slot, grad_image):
         check(lib().gsx_batch_backward_view(self.h, int(slot), _ptr(grad_image), _stream()))
 
+    def batch_extract_view_rgb_grad(self, slot, drgb):
+        """dense [N][3] d rgb of the slot's view (after batch_backward_view): what ranks all-gather (dp.py)"""
+        check(lib().gsx_batch_extract_view_rgb_grad(self.h, int(slot), _ptr(drgb), _stream()))
+
     def batch_backward_params(self, g, flags=_ffi.GSX_GRAD_OVERWRITE):
         if g.grads is None:
             g.zero_grads()
@@ -395,6 +399,12 @@ class Rasterizer:
         check(lib().gsx_ctx_count_work(self.h, out, _stream()))
         return int(out[0]), int(out[1])
 
+    def state_image(self):
+        """zero-copy [H][W][3] view of the last rendered image (no synchronisation)"""
+        s = GsxState()
+        check(lib().gsx_ctx_state(self.h, C.byref(s)))
+        return _from_ptr(s.image, (self._view.height, self._view.width, 3), torch.float32)
+
     def state(self):
         """Zero-copy torch views of the saved forward state (for tests / inspection)."""
         s = GsxState()
@@ -412,7 +422,10 @@ class Rasterizer:
             tiles_touched=_from_ptr(s.tiles_touched, (n,), torch.int32), ranges=_from_ptr(s.ranges, (T + 1,), torch.int32),
             packed_grads=_from_ptr(s.packed_grads, (n, 12), torch.float32), K=K)
         out["sorted_gaussians"] = _from_ptr(s.sorted_gaussians, (max(K, 1),), torch.int32)[:K]
-        out["sorted_keys"] = _from_ptr(s.sorted_keys, (max(K, 1),), torch.int64)[:K]
+        kp = C.c_void_p()
+        check(lib().gsx_ctx_build_sorted_keys(self.h, C.byref(kp)))
+        out["sorted_keys"] = (_from_ptr(kp.value, (max(K, 1),), torch.int64)[:K] if kp.value
+                              else torch.zeros(0, dtype=torch.int64, device="cuda"))
         return out
 
 

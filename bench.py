@@ -185,7 +185,7 @@ def main():
     gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"], device=dev)
     flat, gviews = flat_grads(torch, N, gd.sh_stride, dev)
     gd.grads = gviews
-    my_views = list(range(rank, N_VIEWS, world))                   # view sharding: rank r renders views r, r+world, ...
+    my_views = gs.dp.shard_views(N_VIEWS, world, rank)             # blocked view sharding (dp.py)
     OVER = gs._ffi.GSX_GRAD_OVERWRITE
     mk = lambda cam, flags: Hh.make_view(cam["view"], cam["proj"], cam["campos"], cam["fx"], cam["fy"], W, H,
                                          near_thresh=S.NEAR_THRESH, cull_padding=S.CULL_PADDING, mh_dist=S.MH_DIST,
@@ -206,16 +206,25 @@ def main():
 
     # One step = the rank's views of the batch through the batch path (parameters read once per direction, gradients
     # of the rank's views summed in one pass with '=' semantics: no 1.4 GB memset) + the gradient allreduce.
+    all_views = [mk(c, 0) for c in cams]
+    vp = gs.dp.ViewParallel(r, gd, all_views, [c["campos"] for c in cams], l_max, world, rank)
+
     def step():
-        r.batch_step(vstructs, gd, gi_dev, flags=OVER)
-        if world > 1:
-            dist.all_reduce(flat)
+        vp.step(gi_dev)
+
+    img_dev = torch.empty((H, W, 3), device=dev, dtype=torch.float32)
 
     def step_e2e():
-        r.batch_render_host(vstructs, gd, gi_host, img_host, flags=OVER)
-        if world > 1:
-            dist.all_reduce(flat)
-            torch.cuda.synchronize()
+        if world == 1:
+            r.batch_render_host(vstructs, gd, gi_host, img_host, flags=OVER)
+            return
+        # host buffers in / out around the same exchange: per view H2D of the loss gradient, D2H of the image
+        gis = [h.to(dev, non_blocking=True) for h in gi_host]
+
+        def grab(k_):
+            img_host[k_].copy_(r.state_image(), non_blocking=True)
+        vp.step(gis, on_image=grab)
+        torch.cuda.synchronize()
 
     def barrier():
         if world > 1:
@@ -320,6 +329,12 @@ def main():
                  "share_of_view": round(stage_ms[top] / sum(stage_ms.values()), 3)})
 
     views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
+    if world > 1:
+        ga_, ar_ = vp.ex.link_bytes_per_step()
+        xbytes = (f"NCCL all-gather of {ga_ / 1e6:.0f} MB per-view d rgb + NCCL allreduce of {ar_ / 1e6:.0f} MB geometry "
+                  f"gradients (SH gradients rebuilt locally; plain allreduce would be {flat.numel() * 4 / 1e6:.0f} MB)")
+    else:
+        xbytes = "none (single GPU)"
     # depth keys, histogram x2, depth onesweep x4, scan x3, emit, histogram x2, tile onesweep, ranges, composite x2
     launches_per_view = 1 + 2 + 4 + 3 + 1 + 2 + passes + 1 + 2
     out = {
@@ -328,7 +343,7 @@ def main():
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "ms_per_view_per_gpu": ms_total / args.steps / len(my_views),
         "config": {"workload": f"{args.config}: synthetic {N} Gaussians, SH deg {l_max}, {W}x{H}, batch of {N_VIEWS} views "
-                               f"sharded over {world} GPU(s), NCCL allreduce of {flat.numel() * 4 / 1e9:.2f} GB gradients",
+                               f"sharded over {world} GPU(s); exchange per step: {xbytes}",
                    "views_per_step": N_VIEWS, "l2": "inputs larger than L2 (1.4 GB parameters + 1.4 GB gradients per view)",
                    "visible_P": int(P), "touching_P": int(Pt), "instances_K": int(K), "pixel_entries_S": int(Sx), "contributing_Splus": int(Sp)},
         "clocks": clocks,

@@ -35,6 +35,9 @@ extern "C" {
 #define GSX_SH_DSPH_CORRECT 1 /* F10: use sphericart's true [axis][k] derivative layout instead of the
                                  reference's [k][axis] reading.  Default 0 = reference behaviour. */
 #define GSX_GRAD_OVERWRITE 2  /* gsx_backward: overwrite parameter gradients instead of accumulating */
+#define GSX_GRAD_NO_SH 4      /* gsx_batch_backward_params: leave the band-0 / SH coefficient gradients out (they are
+                                 rebuilt from the gathered per-view colour gradients, gsx_sh_grads_from_view_rgb) */
+#define GSX_MAX_VIEWS_TOTAL 64 /* views of a whole (multi-GPU) batch accepted by gsx_sh_grads_from_view_rgb */
 
 int gsx_version(void);
 const char *gsx_last_error(void);
@@ -175,12 +178,15 @@ typedef struct gsx_state {
   const uint8_t *mask;  /* [N] cull mask, 1 = keep */
   const int *tiles_touched;            /* [N] exact instance count per Gaussian */
   const int *sorted_gaussians;         /* [K] global Gaussian ids, (tile, depth, id) order */
-  const uint64_t *sorted_keys;         /* [K] tile<<32 | depth bits */
+  const uint64_t *sorted_keys;         /* always NULL: the two-level sort never materialises tile<<32 | depth keys;
+                                          gsx_ctx_build_sorted_keys rebuilds them for inspection */
   const int *ranges;                   /* [T+1] */
   const int *num_instances;            /* device int: K */
   const float *packed_grads;           /* [N][12] compositing gradients (zero between views) */
 } gsx_state_t;
 int gsx_ctx_state(gsx_ctx_t *ctx, gsx_state_t *out_host);
+/* [K] tile<<32 | order-preserving depth bits of the last forward, composed on demand (synchronises the device). */
+int gsx_ctx_build_sorted_keys(gsx_ctx_t *ctx, const uint64_t **keys_dev_out);
 
 /* ---- batch path: the n views of one training batch (n <= GSX_MAX_VIEWS) share ONE pass over the parameters in each
  *      direction (the reference reads them twice per view, raster.cu:26-104 / trainer.cu:941-1012).  Protocol:
@@ -201,6 +207,18 @@ int gsx_batch_forward_view(gsx_ctx_t *ctx, int slot, void *stream);
 int gsx_batch_backward_view(gsx_ctx_t *ctx, int slot, const float *grad_image, void *stream);
 int gsx_batch_backward_params(gsx_ctx_t *ctx, const gsx_params_t *params, int N, const gsx_grads_t *grads, int flags,
                               void *stream);
+/* ---- view-parallel multi-GPU exchange.  A view's SH coefficient gradient is rank 1:
+ *      d sh[k][c] = d rgb_c * Y_k(dir_view) (cuda/spherical_harmonics_backward.cu:100-104), so instead of allreducing the
+ *      192 B/Gaussian band-0 + SH gradient, ranks all-gather the 12 B/Gaussian d rgb of each view and every rank rebuilds
+ *      the batch sum locally; only the 44 B/Gaussian geometry gradients (xyz, scale, quaternion, opacity) are allreduced.
+ *      gsx_batch_extract_view_rgb_grad: d rgb of the view in `slot` after its gsx_batch_backward_view, dense [N][3]
+ *      (zeros where no gradient arrived).  gsx_sh_grads_from_view_rgb: drgb is [n_views][view_stride floats] holding
+ *      [N][3] per view, campos_host is [n_views][3]; '=' with GSX_GRAD_OVERWRITE, else '+='. ------------------------- */
+int gsx_batch_extract_view_rgb_grad(gsx_ctx_t *ctx, int slot, float *drgb, void *stream);
+int gsx_sh_grads_from_view_rgb(const float *xyz_w, int N, int l_max, const float *campos_host, int n_views,
+                               const float *drgb, size_t view_stride, float *sh_grad, int sh_stride, float *band0_grad,
+                               int flags, void *stream);
+
 /* Host-buffer batch step (bench.py's e2e leg): per view, H2D of grad_images_host[k] and D2H of the rendered image into
  * images_host[k] (pinned host memory, [H][W][3] floats), then the whole protocol above.  Synchronises. */
 int gsx_batch_render_host(gsx_ctx_t *ctx, const gsx_view_t *views_host, int n_views, const gsx_params_t *params, int N,

@@ -408,6 +408,62 @@ def test_batch_path_matches_per_view_and_oracle(B, l_max, sh_alloc, flags, overw
     r.close()
 
 
+@pytest.mark.parametrize("l_max,sh_alloc", [(3, None), (1, 3), (0, None)])
+def test_view_parallel_split_exchange_matches_fused(B, l_max, sh_alloc):
+    """dp.py's exchange on one GPU: two emulated ranks each run their views with GSX_GRAD_NO_SH and extract the per-view
+    d rgb; geometry gradients summed + SH gradients rebuilt from all views' d rgb must equal the fused batch step."""
+    import torch
+    W, H, N = 200, 144, 9000
+    cams = [S.orbit_camera(W, H, azimuth_deg=a) for a in (5.0, 95.0, 185.0, 275.0)]
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=55)
+    Hh, dp, ffi = gs.host, gs.dp, gs._ffi
+    sh = g["sh"]
+    if sh is not None and sh_alloc is not None:
+        full = np.zeros((N, (sh_alloc + 1) ** 2 - 1, 3), np.float32)
+        full[:, : sh.shape[1]] = sh
+        sh = full
+    gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], sh)
+    gis = [torch.as_tensor(S.grad_image(W, H, seed=80 + k) * 1e3).cuda() for k in range(4)]
+    views = [util.gsx_view(c, l_max, 0.2) for c in cams]
+    r = Hh.Rasterizer(N, W, H, instance_capacity=8 * N)
+    r.batch_reserve(4)
+    gd.zero_grads()
+    r.batch_step(views, gd, gis, flags=ffi.GSX_GRAD_OVERWRITE)
+    torch.cuda.synchronize()
+    want = {k: t.clone() for k, t in gd.grads.items()}
+    drgb = torch.zeros((4, N, 3), device="cuda")
+    geom = {nm: None for nm, _ in dp.GEOM}
+    for rank in range(2):
+        mine = dp.shard_views(4, 2, rank)
+        for t in gd.grads.values():
+            t.fill_(55.0)
+        r.batch_forward_params([views[k] for k in mine], gd)
+        for j, k in enumerate(mine):
+            r.batch_forward_view(j)
+            r.batch_backward_view(j, gis[k])
+            r.batch_extract_view_rgb_grad(j, drgb[k])
+        r.batch_backward_params(gd, ffi.GSX_GRAD_OVERWRITE | ffi.GSX_GRAD_NO_SH)
+        torch.cuda.synchronize()
+        assert (gd.grads["band0"] == 55.0).all() and (gd.grads["sh"] == 55.0).all()   # left out, as documented
+        for nm in geom:
+            geom[nm] = gd.grads[nm].clone() if geom[nm] is None else geom[nm] + gd.grads[nm]
+    dp.sh_grads_from_view_rgb(gd.xyz, [c["campos"] for c in cams], drgb, l_max, gd.grads["sh"], gd.grads["band0"],
+                              gd.sh_stride, ffi.GSX_GRAD_OVERWRITE)
+    torch.cuda.synchronize()
+    nsh = ((l_max + 1) ** 2 - 1) * 3
+    for nm in geom:
+        util.assert_grad_close(geom[nm].cpu().numpy(), want[nm].cpu().numpy(), f"split d {nm}", outlier=2e-3)
+    util.assert_grad_close(gd.grads["band0"].cpu().numpy(), want["band0"].cpu().numpy(), "split d band0", outlier=2e-3)
+    if nsh:
+        util.assert_grad_close(gd.grads["sh"][:, :nsh].cpu().numpy(), want["sh"][:, :nsh].cpu().numpy(), "split d sh", outlier=2e-3)
+    # accumulate mode of the rebuild: a second call doubles
+    dp.sh_grads_from_view_rgb(gd.xyz, [c["campos"] for c in cams], drgb, l_max, gd.grads["sh"], gd.grads["band0"],
+                              gd.sh_stride, 0)
+    torch.cuda.synchronize()
+    util.assert_grad_close(gd.grads["band0"].cpu().numpy(), 2.0 * want["band0"].cpu().numpy(), "split d band0 x2", outlier=2e-3)
+    r.close()
+
+
 def test_config1_fixture_and_companion(B):
     """C1: the reference's own COLMAP fixture (1 camera, 1 image, 1 point): the Gaussian survives the
     padded cull, touches no tile, the image is pure background and every gradient is zero; plus the non-degenerate
