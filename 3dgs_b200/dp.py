@@ -104,11 +104,25 @@ class ViewParallel:
             self.ex = GradExchange(N, len(views_all), world, rank, dev, group)
             for nm, _ in GEOM:                              # the geometry gradients live in the flat allreduce buffer
                 gaussians.grads[nm] = self.ex.geom[nm]
-            self.comm = torch.cuda.Stream(device=dev)
+            self.comm = torch.cuda.Stream(device=dev, priority=-1)
             self.ev_views, self.ev_geom = torch.cuda.Event(), torch.cuda.Event()
             self.ev_gathered, self.ev_reduced = torch.cuda.Event(), torch.cuda.Event()
         else:
             self.ex = None
+        self.timing = None          # set to {} to collect per-phase CUDA-event times (ms) of the next step()
+
+    def _mark(self, name, stream):
+        if self.timing is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(stream)
+            self.timing.setdefault("_ev", {})[name] = e
+
+    def phase_ms(self):
+        """after a synchronize: durations of the phases of the last timed step"""
+        ev = self.timing["_ev"]
+        d = lambda a, b: ev[a].elapsed_time(ev[b])
+        return dict(views=d("t0", "views"), gather=d("g0", "g1"), params_bwd=d("views", "bwd"), reduce=d("r0", "r1"),
+                    sh_rebuild=d("s0", "s1"), total=d("t0", "end"))
 
     def step(self, grad_images, on_image=None):
         r, g = self.r, self.g
@@ -117,6 +131,7 @@ class ViewParallel:
             r.batch_step(self.views, g, grad_images, flags=OVER, on_image=on_image)
             return
         main = torch.cuda.current_stream()
+        self._mark("t0", main)
         r.batch_forward_params(self.views, g)
         for k in range(len(self.views)):
             r.batch_forward_view(k)
@@ -126,17 +141,26 @@ class ViewParallel:
             r.batch_backward_view(k, gi)
             r.batch_extract_view_rgb_grad(k, self.ex.local_drgb(k))
         self.ev_views.record(main)
+        self._mark("views", main)
         with torch.cuda.stream(self.comm):                  # all-gather of d rgb overlaps the per-Gaussian backward
             self.comm.wait_event(self.ev_views)
+            self._mark("g0", self.comm)
             self.ex.all_gather_drgb()
+            self._mark("g1", self.comm)
             self.ev_gathered.record(self.comm)
         r.batch_backward_params(g, OVER | NO_SH)            # geometry gradients -> flat buffer
         self.ev_geom.record(main)
+        self._mark("bwd", main)
         with torch.cuda.stream(self.comm):                  # allreduce overlaps the SH rebuild
             self.comm.wait_event(self.ev_geom)
+            self._mark("r0", self.comm)
             self.ex.all_reduce_geom()
+            self._mark("r1", self.comm)
             self.ev_reduced.record(self.comm)
         main.wait_event(self.ev_gathered)
+        self._mark("s0", main)
         sh_grads_from_view_rgb(g.xyz, self.campos_all, self.ex.drgb, self.l_max, g.grads["sh"], g.grads["band0"],
                                g.sh_stride, OVER)
+        self._mark("s1", main)
         main.wait_event(self.ev_reduced)
+        self._mark("end", main)

@@ -176,6 +176,9 @@ def main():
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL kernels on a high-priority stream: their CTAs are scheduled ahead of the (many, short) CTAs of the SH
+        # rebuild kernel they overlap with (dp.py)
+        os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1")
         dist.init_process_group("nccl", device_id=dev)
     assert N_VIEWS % world == 0, "the 8-view batch shards over 1, 2, 4 or 8 GPUs"
     gs, S, N, W, H, l_max, g, cams = make_scene(args.config)
@@ -262,6 +265,13 @@ def main():
         dist.all_reduce(dt_e2e, op=dist.ReduceOp.MAX)
     dt_e2e = float(dt_e2e.item())
 
+    exch = None
+    if world > 1:                                                  # per-phase times of one more step (outside the timed region)
+        vp.timing = {}
+        step()
+        barrier()
+        exch = {k_: round(v_, 3) for k_, v_ in vp.phase_ms().items()}
+        vp.timing = None
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -350,7 +360,7 @@ def main():
         "e2e": {"value": N_VIEWS * args.steps / dt_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": N_VIEWS * (W * H * 3 * 4 + 200), "d2h_bytes_per_step": N_VIEWS * W * H * 3 * 4},
         "gpu_launches": (launches_per_view * nv + 2) * args.steps * world,
-        "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": round(fp32_peak, 2),
+        "exchange_ms": exch, "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": round(fp32_peak, 2),
     }
     if world == 1 and not args.no_cpu_baseline:
         from oracle import golden as G
