@@ -133,41 +133,60 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
   __syncthreads();
   if (L > 0 && use_tma) mbar_wait(&s_bar, 0);
   const int np = (int)s_n;
-  for (int j = t; j < np; j += BB) {
-    const int slot = s_pair[j];
+  const int lane = t & 31;
+  for (int jb = t - lane; jb < np; jb += BB) {       // warp-uniform trip count: the tile count below is cooperative
+    const int j = jb + lane;
+    const bool active = j < np;
+    const int slot = active ? s_pair[j] : 0;
     const int v = slot / BB, g = slot - v * BB;
     const int gi = (int)row0 + g;
     const ViewConst &vc = *reinterpret_cast<const ViewConst *>(s_view + v * VCW);
     const SlotPtrs &sp = bc.s[v];
-    const float px = s_g[0 * BB + g], py = s_g[1 * BB + g], pz = s_g[2 * BB + g];
-    float sig[6];
-#pragma unroll
-    for (int k = 0; k < 6; ++k) sig[k] = s_g[(3 + k) * BB + g];
-    const float opa = s_g[9 * BB + g];
-    const float b0[3] = {s_g[10 * BB + g], s_g[11 * BB + g], s_g[12 * BB + g]};
-    const float3 pc = cam_point(vc.view, px, py, pz);
-    const float2 uv = screen_point(vc.proj, pc, vc.width, vc.height);
-    float J[6], con[3];
-    float4 rad;
-    projection_jacobian(pc.x, pc.y, pc.z, vc.fx, vc.fy, vc.tan_fovx, vc.tan_fovy, J);
-    conic_and_radius(J, sig, vc.view, vc.mh_dist, con, &rad);
-    const float2 ext = alpha_extent_b(con[0], con[1], con[2], opa);
+    ObbSat so{};
+    TileRange tr{0, -1, 0, -1};
     int cnt = 0;
-    const TileWindow w = candidate_window(uv.x, uv.y, rad.x, vc.ntx, vc.nty);
-    if (w.x1 > w.x0 && w.y1 > w.y0) {
-      const ObbSat so = obb_sat_setup(compute_obb(uv.x, uv.y, rad.x, rad.y, rad.z, rad.w));
-      const TileRange tr = sat_aabb_range(so, w);
+    if (active) {
+      const float px = s_g[0 * BB + g], py = s_g[1 * BB + g], pz = s_g[2 * BB + g];
+      float sig[6];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) sig[k] = s_g[(3 + k) * BB + g];
+      const float opa = s_g[9 * BB + g];
+      const float b0[3] = {s_g[10 * BB + g], s_g[11 * BB + g], s_g[12 * BB + g]};
+      const float3 pc = cam_point(vc.view, px, py, pz);
+      const float2 uv = screen_point(vc.proj, pc, vc.width, vc.height);
+      float J[6], con[3];
+      float4 rad;
+      projection_jacobian(pc.x, pc.y, pc.z, vc.fx, vc.fy, vc.tan_fovx, vc.tan_fovy, J);
+      conic_and_radius(J, sig, vc.view, vc.mh_dist, con, &rad);
+      const float2 ext = alpha_extent_b(con[0], con[1], con[2], opa);
+      const TileWindow w = candidate_window(uv.x, uv.y, rad.x, vc.ntx, vc.nty);
+      if (w.x1 > w.x0 && w.y1 > w.y0) {
+        so = obb_sat_setup(compute_obb(uv.x, uv.y, rad.x, rad.y, rad.z, rad.w));
+        tr = sat_aabb_range(so, w);
+      }
+      const float3 rgb = sh_to_rgb<L>(px, py, pz, vc.campos, b0, L > 0 ? s_sh + g * SHF : nullptr);
+      sp.r0[gi] = make_float4(uv.x, uv.y, ext.x, ext.y);
+      sp.r1[gi] = make_float4(con[0], con[1], con[2], opa);
+      sp.r2[gi] = make_float4(rgb.x, rgb.y, rgb.z, opa * (1.0f - opa));
+      sp.radius[gi] = rad;
+      sp.depth[gi] = pc.z;
+      sp.mask[gi] = 1;
+    }
+    // exact tile count (F7 window + SAT): small rectangles per thread, large ones by the whole warp
+    const bool big = active && rect_cells(tr) > COOP_CELLS;
+    if (active && !big) {
       for (int tx = tr.x0; tx <= tr.x1; ++tx)
         for (int ty = tr.y0; ty <= tr.y1; ++ty) cnt += sat_tile_rot(so, tx, ty) ? 1 : 0;
     }
-    const float3 rgb = sh_to_rgb<L>(px, py, pz, vc.campos, b0, L > 0 ? s_sh + g * SHF : nullptr);
-    sp.r0[gi] = make_float4(uv.x, uv.y, ext.x, ext.y);
-    sp.r1[gi] = make_float4(con[0], con[1], con[2], opa);
-    sp.r2[gi] = make_float4(rgb.x, rgb.y, rgb.z, opa * (1.0f - opa));
-    sp.radius[gi] = rad;
-    sp.depth[gi] = pc.z;
-    sp.touched[gi] = cnt;
-    sp.mask[gi] = 1;
+    unsigned bm = __ballot_sync(0xffffffffu, big);
+    while (bm) {
+      const int leader = __ffs(bm) - 1;
+      bm &= bm - 1;
+      int c = 0;
+      coop_tile_rect(leader, so, tr, [&](bool, unsigned ballot, int, int) { c += __popc(ballot); });
+      if (lane == leader) cnt = c;
+    }
+    if (active) sp.touched[gi] = cnt;
   }
 }
 

@@ -72,35 +72,65 @@ __global__ void __launch_bounds__(kBlock) k_depth_keys(const float *__restrict__
                                                        uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
   const int i = blockIdx.x * kBlock + threadIdx.x;
   if (i >= N) return;
-  keys[i] = touched[i] > 0 ? float_sort_bits(depth[(size_t)i * depth_stride]) : 0xffffffffu;
+  keys[i] = touched[i] > 0 ? min(float_sort_bits(depth[(size_t)i * depth_stride]), 0xfffffffeu) : 0xffffffffu;   // ~0 = "no instances"
   vals[i] = (uint32_t)i;
 }
 
-// instance emission in depth order: thread j handles Gaussian perm[j]; its instances go to [offsets[j], +touched)
+// instance emission in depth order: thread j handles Gaussian perm[j]; its instances go to [offsets[j], +touched).
+// Gaussians without instances were sorted to the end (key 0xffffffff): they exit on the coalesced key read without
+// touching the permutation.  Rectangles of more than COOP_CELLS tiles are expanded by the whole warp.
 __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, int uv_stride,
-                                                 const float4 *__restrict__ radius, const uint32_t *__restrict__ perm,
+                                                 const float4 *__restrict__ radius, const uint32_t *__restrict__ dkeys,
+                                                 const uint32_t *__restrict__ perm,
                                                  const int *__restrict__ touched, const int *__restrict__ offsets,
                                                  int ntx, int nty, int N, long long capacity,
                                                  uint32_t *__restrict__ tiles, uint32_t *__restrict__ vals) {
   const int j = blockIdx.x * kBlock + threadIdx.x;
-  if (j >= N) return;
-  const int i = (int)perm[j];
-  const int cnt = touched[i];
-  if (cnt == 0) return;
-  long long o = offsets[j];
-  if (o + cnt > capacity) return;   // overflow: detected by the host through the total
-  const float u = uv[(size_t)i * uv_stride], v = uv[(size_t)i * uv_stride + 1];
-  const float4 r = radius[i];
-  const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
-  const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
-  const TileRange tr = sat_aabb_range(s, w);
-  for (int tx = tr.x0; tx <= tr.x1; ++tx)
-    for (int ty = tr.y0; ty <= tr.y1; ++ty)
-      if (sat_tile_rot(s, tx, ty)) {
-        tiles[o] = (uint32_t)(ty * ntx + tx);
-        vals[o] = (uint32_t)i;
-        ++o;
+  const int lane = threadIdx.x & 31;
+  bool live = j < N && dkeys[j] != 0xffffffffu;
+  int i = 0, cnt = 0;
+  long long o = 0;
+  if (live) {
+    i = (int)perm[j];
+    cnt = touched[i];
+    o = offsets[j];
+    live = cnt > 0 && o + cnt <= capacity;   // overflow: detected by the host through the total
+  }
+  if (!__any_sync(0xffffffffu, live)) return;
+  ObbSat s{};
+  TileRange tr{0, -1, 0, -1};
+  if (live) {
+    const float u = uv[(size_t)i * uv_stride], v = uv[(size_t)i * uv_stride + 1];
+    const float4 r = radius[i];
+    const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
+    s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
+    tr = sat_aabb_range(s, w);
+  }
+  const bool big = live && rect_cells(tr) > COOP_CELLS;
+  if (live && !big) {
+    for (int tx = tr.x0; tx <= tr.x1; ++tx)
+      for (int ty = tr.y0; ty <= tr.y1; ++ty)
+        if (sat_tile_rot(s, tx, ty)) {
+          tiles[o] = (uint32_t)(ty * ntx + tx);
+          vals[o] = (uint32_t)i;
+          ++o;
+        }
+  }
+  unsigned bm = __ballot_sync(0xffffffffu, big);
+  while (bm) {
+    const int leader = __ffs(bm) - 1;
+    bm &= bm - 1;
+    long long ol = __shfl_sync(0xffffffffu, o, leader);
+    const uint32_t il = (uint32_t)__shfl_sync(0xffffffffu, i, leader);
+    coop_tile_rect(leader, s, tr, [&](bool hit, unsigned ballot, int tx, int ty) {
+      if (hit) {
+        const long long pos = ol + __popc(ballot & ((1u << lane) - 1u));
+        tiles[pos] = (uint32_t)(ty * ntx + tx);
+        vals[pos] = il;
       }
+      ol += __popc(ballot);
+    });
+  }
 }
 
 // ---- 3-kernel exclusive scan of int32 (N up to 2^31) ------------------------------------------------------
@@ -117,11 +147,15 @@ __device__ __forceinline__ int block_reduce_sum(int v, int *s_tmp) {
 }
 
 // value i of the scanned sequence: in[i], or in[perm[i]] when a permutation is given
-__device__ __forceinline__ int scan_value(const int *__restrict__ in, const uint32_t *__restrict__ perm, long long i) {
-  return perm ? in[perm[i]] : in[i];
+__device__ __forceinline__ int scan_value(const int *__restrict__ in, const uint32_t *__restrict__ perm,
+                                          const uint32_t *__restrict__ dkeys, long long i) {
+  if (!perm) return in[i];
+  if (dkeys[i] == 0xffffffffu) return 0;   // no instances: sorted to the end, no gather needed
+  return in[perm[i]];
 }
 
-__global__ void __launch_bounds__(kBlock) k_scan_reduce(const int *__restrict__ in, const uint32_t *__restrict__ perm, int N,
+__global__ void __launch_bounds__(kBlock) k_scan_reduce(const int *__restrict__ in, const uint32_t *__restrict__ perm,
+                                                        const uint32_t *__restrict__ dkeys, int N,
                                                         int *__restrict__ block_sums) {
   __shared__ int s_tmp[kBlock / 32];
   const long long base = (long long)blockIdx.x * SCAN_TILE;
@@ -129,7 +163,7 @@ __global__ void __launch_bounds__(kBlock) k_scan_reduce(const int *__restrict__ 
 #pragma unroll
   for (int k = 0; k < SCAN_IPT; ++k) {
     const long long i = base + k * kBlock + threadIdx.x;
-    if (i < N) v += scan_value(in, perm, i);
+    if (i < N) v += scan_value(in, perm, dkeys, i);
   }
   const int t = block_reduce_sum(v, s_tmp);
   if (threadIdx.x == 0) block_sums[blockIdx.x] = t;
@@ -159,14 +193,15 @@ __global__ void __launch_bounds__(1024) k_scan_block_sums(int *__restrict__ bloc
   if (threadIdx.x == 0) *total = carry;
 }
 
-__global__ void __launch_bounds__(kBlock) k_scan_apply(const int *__restrict__ in, const uint32_t *__restrict__ perm, int N,
+__global__ void __launch_bounds__(kBlock) k_scan_apply(const int *__restrict__ in, const uint32_t *__restrict__ perm,
+                                                       const uint32_t *__restrict__ dkeys, int N,
                                                        const int *__restrict__ block_sums, int *__restrict__ out) {
   __shared__ int s_warp[kBlock / 32];
   const long long base = (long long)blockIdx.x * SCAN_TILE + (long long)threadIdx.x * SCAN_IPT;
   int v[SCAN_IPT];
   int sum = 0;
 #pragma unroll
-  for (int k = 0; k < SCAN_IPT; ++k) { v[k] = (base + k < N) ? scan_value(in, perm, base + k) : 0; sum += v[k]; }
+  for (int k = 0; k < SCAN_IPT; ++k) { v[k] = (base + k < N) ? scan_value(in, perm, dkeys, base + k) : 0; sum += v[k]; }
   int incl = sum;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -201,14 +236,14 @@ int tile_key_bits(int n_tiles) {
   return 32 + std::max(b, 1);
 }
 
-int exclusive_scan_i32(const int *in, const uint32_t *perm, int N, int *out, int *block_sums, int *total_dev,
-                       cudaStream_t st) {
+int exclusive_scan_i32(const int *in, const uint32_t *perm, const uint32_t *dkeys, int N, int *out, int *block_sums,
+                       int *total_dev, cudaStream_t st) {
   const int nb = std::max(1, ceil_div(N, SCAN_TILE));
-  k_scan_reduce<<<nb, kBlock, 0, st>>>(in, perm, N, block_sums);
+  k_scan_reduce<<<nb, kBlock, 0, st>>>(in, perm, dkeys, N, block_sums);
   GSX_LAUNCH_CHECK();
   k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nb, total_dev);
   GSX_LAUNCH_CHECK();
-  k_scan_apply<<<nb, kBlock, 0, st>>>(in, perm, N, block_sums, out);
+  k_scan_apply<<<nb, kBlock, 0, st>>>(in, perm, dkeys, N, block_sums, out);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -250,18 +285,19 @@ int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_
   uint32_t *ka = (uint32_t *)(ws + L.keys_a), *kb = (uint32_t *)(ws + L.keys_b);
   uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
   int in_b = 0, rc;
-  const uint32_t *perm = nullptr;
+  const uint32_t *perm = nullptr, *dkeys = nullptr;
   if (N > 0) {
     k_depth_keys<<<ceil_div(N, kBlock), kBlock, 0, st>>>(depth, depth_stride, touched, N, dka, dva);
     GSX_LAUNCH_CHECK();
     rc = sort_pairs_u32_impl(dka, dkb, dva, dvb, N, nullptr, 32, ws + L.sort_ws, L.sort_ws_bytes, st, &in_b);
     if (rc != GSX_OK) return rc;
     perm = in_b ? dvb : dva;
+    dkeys = in_b ? dkb : dka;
   }
-  rc = exclusive_scan_i32(touched, perm, N, offsets, block_sums, total, st);
+  rc = exclusive_scan_i32(touched, perm, dkeys, N, offsets, block_sums, total, st);
   if (rc != GSX_OK) return rc;
   if (N > 0) {
-    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, perm, touched, offsets, ntx, nty, N, capacity, ka, va);
+    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, dkeys, perm, touched, offsets, ntx, nty, N, capacity, ka, va);
     GSX_LAUNCH_CHECK();
   }
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
@@ -327,7 +363,7 @@ int gsx_sorted_list_size(const float *uv, const float *radius, int n_tiles_x, in
   GSX_CUDA(cudaMemsetAsync(coarse, 0, sizeof(unsigned long long), st));
   rc = count_tiles_launch(uv, 2, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched), coarse, st);
   if (rc != GSX_OK) return rc;
-  rc = exclusive_scan_i32((int *)(ws + L.touched), nullptr, N, (int *)(ws + L.offsets), (int *)(ws + L.block_sums),
+  rc = exclusive_scan_i32((int *)(ws + L.touched), nullptr, nullptr, N, (int *)(ws + L.offsets), (int *)(ws + L.block_sums),
                           (int *)(ws + L.total), st);
   if (rc != GSX_OK) return rc;
   unsigned long long hc = 0;

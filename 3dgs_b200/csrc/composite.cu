@@ -35,6 +35,20 @@ __device__ __forceinline__ float2 alpha_extent(float a, float b, float c, float 
 
 __device__ __forceinline__ float sigmoid_fast(float x) { return 1.0f / (1.0f + __expf(-x)); }   // render.cu:56
 
+// exp(x) for x <= 0 as one MUFU.EX2 (render.cu:73 uses __expf = ex2.approx(x * log2 e) plus a denormal-range rescale;
+// results below 2^-126 flush to zero here, far under the 1/255 alpha threshold, so every kept alpha is identical)
+__device__ __forceinline__ float exp_neg(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+  return y;
+}
+// 1/x for x in [0.01, 1] (1 - alpha, alpha <= 0.99): one MUFU.RCP, no slow path
+__device__ __forceinline__ float rcp_fast(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct GaussSrc {          // where a Gaussian's compositing record comes from
   // packed (view-level path): three float4 arrays indexed by global id
   const float4 *r0, *r1, *r2;
@@ -98,7 +112,7 @@ k_composite_fwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
         const float4 q0 = s_r0[e], q1 = s_r1[e];
         const float dx = q0.x - fpx, dy = q0.y - fpy;
         const float power = fminf(0.0f, -0.5f * (q1.x * dx * dx + q1.z * dy * dy) - q1.y * dx * dy);
-        const float alpha = fminf(0.99f, q1.w * __expf(power));
+        const float alpha = fminf(0.99f, q1.w * exp_neg(power));
         if (alpha > ALPHA_MIN && !done) {
           const float4 q2 = s_r2[e];
           const float test_T = T * (1.0f - alpha);
@@ -195,7 +209,7 @@ k_composite_bwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
         const float4 q0 = s_r0[e], q1 = s_r1[e];
         const float dx = q0.x - fpx, dy = q0.y - fpy;
         const float power = fminf(0.0f, -0.5f * (q1.x * dx * dx + q1.z * dy * dy) - q1.y * dx * dy);
-        const float gg = __expf(power);
+        const float gg = exp_neg(power);
         const float alpha = fminf(0.99f, q1.w * gg);
         const bool valid = inside && (alpha >= ALPHA_MIN) && (idx < count);
         if (!__any_sync(0xffffffffu, valid)) continue;
@@ -206,13 +220,14 @@ k_composite_bwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
         if (valid) {
           const float4 q2 = s_r2[e];
           const float om = 1.0f - alpha;
-          T *= 1.0f / om;
+          const float inv_om = rcp_fast(om);   // render_backward.cu:132 divides; 1 - alpha >= 0.01
+          T *= inv_om;
           const float w = alpha * T;
           v[0] = w * gx; v[1] = w * gy; v[2] = w * gz;
           float ga = 0.0f;
           ga += (q2.x - ar) * gx; ga += (q2.y - ag) * gy; ga += (q2.z - ab) * gz;
           ga *= T;
-          ga += (-Tf / om) * bgdot;
+          ga += (-Tf * inv_om) * bgdot;
           vo = gg * ga * q2.w;                       // g * grad_alpha * opa * (1 - opa)
           ar = alpha * q2.x + om * ar; ag = alpha * q2.y + om * ag; ab = alpha * q2.z + om * ab;
           const float gp = gg * (ga * q1.w);         // d L / d power

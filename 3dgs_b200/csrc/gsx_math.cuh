@@ -294,6 +294,39 @@ __device__ __forceinline__ bool sat_tile_rot(const ObbSat &s, int tx, int ty) {
   return sat_axis(s.a3x, s.a3y, s.lo3, s.hi3, l, r, t, b);
 }
 
+// Warp-cooperative evaluation of ONE lane's tile rectangle (Gaussians covering many tiles would otherwise keep a
+// single lane busy for hundreds of SAT tests while 31 wait): the leader's SAT constants and rectangle are broadcast,
+// the 32 lanes test 32 cells per step (same tx-major order as the serial loop) and fn(c0, hit, ballot) sees each step.
+// Must be called by all 32 lanes with the same `leader`.
+constexpr int COOP_CELLS = 16;   // rectangles with more cells than this are handled cooperatively
+template <typename F>
+__device__ __forceinline__ void coop_tile_rect(int leader, const ObbSat &so, const TileRange &tr, F &&fn) {
+  const unsigned full = 0xffffffffu;
+  ObbSat b;
+  b.min_x = b.max_x = b.min_y = b.max_y = 0.0f;   // axes 0/1 were decided by sat_aabb_range
+  b.a2x = __shfl_sync(full, so.a2x, leader); b.a2y = __shfl_sync(full, so.a2y, leader);
+  b.lo2 = __shfl_sync(full, so.lo2, leader); b.hi2 = __shfl_sync(full, so.hi2, leader);
+  b.a3x = __shfl_sync(full, so.a3x, leader); b.a3y = __shfl_sync(full, so.a3y, leader);
+  b.lo3 = __shfl_sync(full, so.lo3, leader); b.hi3 = __shfl_sync(full, so.hi3, leader);
+  const int x0 = __shfl_sync(full, tr.x0, leader), y0 = __shfl_sync(full, tr.y0, leader);
+  const int ny = __shfl_sync(full, tr.y1 - tr.y0 + 1, leader);
+  const int cells = __shfl_sync(full, (tr.x1 - tr.x0 + 1) * (tr.y1 - tr.y0 + 1), leader);
+  const int lane = threadIdx.x & 31;
+  for (int c0 = 0; c0 < cells; c0 += 32) {
+    const int c = c0 + lane;
+    bool hit = false;
+    int tx = 0, ty = 0;
+    if (c < cells) {
+      tx = x0 + c / ny; ty = y0 + c - (c / ny) * ny;
+      hit = sat_tile_rot(b, tx, ty);
+    }
+    fn(hit, __ballot_sync(full, hit), tx, ty);
+  }
+}
+__device__ __forceinline__ int rect_cells(const TileRange &tr) {
+  return (tr.x1 >= tr.x0 && tr.y1 >= tr.y0) ? (tr.x1 - tr.x0 + 1) * (tr.y1 - tr.y0 + 1) : 0;
+}
+
 // order-preserving map float -> uint32 (handles negative depths that only the per-function F7 can see)
 __device__ __forceinline__ uint32_t float_sort_bits(float z) {
   const uint32_t b = __float_as_uint(z);
