@@ -36,7 +36,7 @@ int check_device_ptr(const void *p, const char *name) {
   return GSX_OK;
 }
 
-// from binning.cu / composite.cu / preprocess.cu
+// from binning.cu / composite.cu / batch.cu
 BinLayout bin_layout(int N, long long capacity);
 int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
                   const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
@@ -55,10 +55,6 @@ int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, c
                          float *packed_grads, cudaStream_t st);
 int count_work_launch(const float4 *r0, const float4 *r1, const int *sorted, const int *ranges, int W, int H,
                       const int *spp, unsigned long long *out_dev, cudaStream_t st);
-int preprocess_fwd_launch(const gsx_view_t &v, const gsx_params_t &p, int N, float4 *r0, float4 *r1, float4 *r2,
-                          float4 *radius, float *depth, uint8_t *mask, int *touched, cudaStream_t st);
-int preprocess_bwd_launch(const gsx_view_t &v, const gsx_params_t &p, int N, const float4 *r1, const uint8_t *mask,
-                          float4 *gacc, const gsx_grads_t &g, cudaStream_t st);
 
 }  // namespace gsx
 
@@ -223,15 +219,18 @@ int gsx_ctx_reserve(gsx_ctx_t *c, long long instance_capacity) {
   return alloc_bin(c, instance_capacity);
 }
 
+// Single view = a batch of one: the same pair-compacted per-Gaussian kernels (batch.cu) run with one slot.
 int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N, void *stream) {
   if (!c || !v || !p) { set_error("null ctx/view/params"); return GSX_E_NULL; }
   int rc = check_view(c, v, p, N);
   if (rc != GSX_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  gsx_slot &s = c->slot[0];
-  s.view = *v;
+  c->slot[0].view = *v;
+  c->batch_n = N; c->batch_nv = 1; c->batch_lmax = v->l_max;
+  BatchConst bc;
+  bc.nv = 1; bc.v[0] = make_view_const(*v); bc.s[0] = c->slot[0].p;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
-  rc = preprocess_fwd_launch(*v, *p, N, s.p.r0, s.p.r1, s.p.r2, s.p.radius, s.p.depth, s.p.mask, s.p.touched, st);
+  rc = batch_fwd_launch(bc, *p, N, v->l_max, st);
   if (rc != GSX_OK) return rc;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[1], st));
   return forward_view(c, 0, N, st);
@@ -240,7 +239,7 @@ int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N,
 int gsx_backward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N, const float *grad_image,
                  const gsx_grads_t *g, void *stream) {
   if (!c || !v || !p || !g || !grad_image) { set_error("null argument"); return GSX_E_NULL; }
-  if (c->cur != 0 || N != c->last_n || v->width != c->last_w || v->height != c->last_h) {
+  if (c->cur != 0 || c->batch_nv != 1 || N != c->last_n || v->width != c->last_w || v->height != c->last_h) {
     set_error("gsx_backward does not match the last gsx_forward on this context");
     return GSX_E_ARG;
   }
@@ -251,8 +250,10 @@ int gsx_backward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N
                                 v->background, c->spp, c->wpp, grad_image, (float *)s.p.gacc, st);
   if (rc != GSX_OK) return rc;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[8], st));
+  BatchConst bc;
+  bc.nv = 1; bc.v[0] = make_view_const(*v); bc.s[0] = s.p;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[9], st));
-  rc = preprocess_bwd_launch(*v, *p, N, s.p.r1, s.p.mask, s.p.gacc, *g, st);
+  rc = batch_bwd_launch(bc, *p, N, v->l_max, *g, v->flags, st);
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[10], st));
   return rc;
 }

@@ -1,6 +1,6 @@
 // pointwise.cu -- per-function mirrors of the reference's per-Gaussian kernels (F1-F6, F10-F15), exported
 // through the C ABI so the reference's gtest fixtures and trainer call sites link unchanged.  The fused
-// view-level path (preprocess.cu) uses the same device math from gsx_math.cuh.
+// view-level path (batch.cu) uses the same device math from gsx_math.cuh.
 #include "gsx_common.cuh"
 #include "gsx_math.cuh"
 
