@@ -25,7 +25,10 @@ namespace {
 
 constexpr int BB = 128;
 #ifndef GSX_BATCH_MINB
-#define GSX_BATCH_MINB 4
+#define GSX_BATCH_MINB 4   // backward; the forward kernel uses GSX_BATCH_MINB_FWD
+#endif
+#ifndef GSX_BATCH_MINB_FWD
+#define GSX_BATCH_MINB_FWD 6   // profiles/sweep_batch_minb.sh: forward gains from 6 CTAs/SM, backward loses
 #endif
 
 __device__ __forceinline__ float2 alpha_extent_b(float a, float b, float c, float opa) {   // == composite.cu
@@ -81,7 +84,7 @@ __device__ __forceinline__ void copy_views_to_smem(const BatchConst &bc, float *
 // band 0 once per Gaussian into shared memory.  Phase B (thread = visible pair): Jacobian, conic, radius, extent, exact
 // tile count, SH colour -> the view's slot.  Only visible pairs cost anything beyond the cull.
 template <int L>
-__global__ void __launch_bounds__(BB, GSX_BATCH_MINB)
+__global__ void __launch_bounds__(BB, GSX_BATCH_MINB_FWD)
 k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restrict__ xyz, const float *__restrict__ scale,
             const float *__restrict__ quat, const float *__restrict__ opacity, const float *__restrict__ band0,
             const float *__restrict__ sh, int sh_stride, int chunk_ok) {

@@ -95,6 +95,7 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_tile = atomicAdd(ticket, 1u);
   for (int i = tid; i < RS_WARPS * (RADIX + 1); i += RS_THREADS) (&s_warp[0][0])[i] = 0;
+  s_excl[tid] = 0;
   __syncthreads();
   const unsigned tile = s_tile;
   const long long n = live_count(n_dev, n_host);
@@ -104,15 +105,24 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
   const unsigned mask = (1u << bits) - 1u;
 
   KeyT key[RS_IPT];
-  uint32_t val[RS_IPT];
   unsigned pos[RS_IPT];
 #pragma unroll
   for (int i = 0; i < RS_IPT; ++i) {
     const int li = warp * (RS_IPT * 32) + i * 32 + lane;
-    if (li < valid) { key[i] = keys_in[base + li]; val[i] = vals_in[base + li]; }
-    else { key[i] = ~(KeyT)0; val[i] = 0; }
+    key[i] = li < valid ? keys_in[base + li] : ~(KeyT)0;
   }
-  // stable rank inside the warp: items in order i, lanes in order; peers found with match.any
+  // 1. tile histogram first (shared-memory integer atomics) so the tile's aggregate is published BEFORE the ranking:
+  //    successors' look-back then never waits on this tile's ranking
+#pragma unroll
+  for (int i = 0; i < RS_IPT; ++i) {
+    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+    if (li < valid) atomicAdd(&s_excl[(unsigned)(key[i] >> shift) & mask], 1u);
+  }
+  __syncthreads();
+  const unsigned total = s_excl[tid];   // for digit == tid
+  unsigned *my = status + (size_t)tile * RADIX + tid;
+  st_volatile(my, (tile == 0 ? FLAG_INC : FLAG_AGG) | total);
+  // 2. stable rank inside the warp: items in order i, lanes in order; peers found with match.any
 #pragma unroll
   for (int i = 0; i < RS_IPT; ++i) {
     const int li = warp * (RS_IPT * 32) + i * 32 + lane;
@@ -126,17 +136,11 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
     pos[i] = before + __popc(lt);
   }
   __syncthreads();
-  // per digit: exclusive scan over warps, total per digit
-  unsigned total = 0;   // for digit == tid
+  // per digit: exclusive scan over warps
   {
     unsigned run = 0;
 #pragma unroll
     for (int w = 0; w < RS_WARPS; ++w) { const unsigned t = s_warp[w][tid]; s_warp[w][tid] = run; run += t; }
-    total = run;
-    if (tid == 0) {
-      unsigned r2 = 0;
-      for (int w = 0; w < RS_WARPS; ++w) { const unsigned t = s_warp[w][RADIX]; s_warp[w][RADIX] = r2; r2 += t; }
-    }
   }
   // block-exclusive scan of totals over the 256 digits
   {
@@ -151,16 +155,11 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
     unsigned wbase = 0;
     for (int w = 0; w < warp; ++w) wbase += s_scan[w];
     s_excl[tid] = wbase + incl - total;
-    if (tid == RS_THREADS - 1) s_excl[RADIX] = wbase + incl;   // == valid
   }
-  // decoupled look-back for digit == tid
+  // 3. decoupled look-back for digit == tid (predecessors published their aggregates before ranking)
   {
-    unsigned *my = status + (size_t)tile * RADIX + tid;
     unsigned excl = 0;
-    if (tile == 0) {
-      st_volatile(my, FLAG_INC | total);
-    } else {
-      st_volatile(my, FLAG_AGG | total);
+    if (tile != 0) {
       long long t = (long long)tile - 1;
       while (true) {
         const unsigned s = ld_volatile(status + (size_t)t * RADIX + tid);
@@ -174,13 +173,15 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
     s_gbase[tid] = (int)(digit_base[tid] + excl) - (int)s_excl[tid];
   }
   __syncthreads();
-  // local reorder through shared memory, then coalesced scatter
+  // 4. local reorder through shared memory, then coalesced scatter
 #pragma unroll
   for (int i = 0; i < RS_IPT; ++i) {
     const int li = warp * (RS_IPT * 32) + i * 32 + lane;
-    const unsigned d = li < valid ? ((unsigned)(key[i] >> shift) & mask) : (unsigned)RADIX;
-    pos[i] += s_excl[d] + s_warp[warp][d];
-    s_keys[pos[i]] = key[i];
+    if (li < valid) {   // padding items (digit RADIX) are never written
+      const unsigned d = (unsigned)(key[i] >> shift) & mask;
+      pos[i] += s_excl[d] + s_warp[warp][d];
+      s_keys[pos[i]] = key[i];
+    }
   }
   __syncthreads();
   int gidx[RS_IPT];
@@ -196,9 +197,13 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
     }
   }
   __syncthreads();
+  // values are loaded only now (16 fewer live registers through the ranking)
   uint32_t *s_vals = reinterpret_cast<uint32_t *>(s_keys);
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) s_vals[pos[i]] = val[i];
+  for (int i = 0; i < RS_IPT; ++i) {
+    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+    if (li < valid) s_vals[pos[i]] = vals_in[base + li];
+  }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < RS_IPT; ++k)
