@@ -61,7 +61,8 @@ __device__ __forceinline__ void stage_rows(float *s_dst, const float *sh, int sh
 
 constexpr int VCW = sizeof(ViewConst) / 4;   // words per view (42: consecutive views fall on distinct banks)
 static_assert(sizeof(ViewConst) % 4 == 0, "ViewConst is word-sized");
-constexpr int NSLOT = BB * GSX_MAX_BATCH;    // (view, local Gaussian) slots of a block
+// (view, local Gaussian) slots of a block: BB * nv, sized at launch (a single view needs 1/8 of the 8-view staging,
+// which lifts the backward kernel from 3 to 4+ CTAs per SM)
 
 // Work list of a block: the active (view, Gaussian) pairs, compacted.  A thread appends all its pairs with one
 // shared-memory atomic; the order is irrelevant for the results (every pair writes to places keyed by (view, Gaussian)).
@@ -96,7 +97,7 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
   float *s_sh = s_mem;                               // [BB][SHF]
   float *s_g = s_mem + BB * SHF;                     // [13][BB]: pw 3, sigma 6, opa, band0 3
   float *s_view = s_g + 13 * BB;                     // [nv][VCW]
-  uint16_t *s_pair = reinterpret_cast<uint16_t *>(s_view + GSX_MAX_BATCH * VCW);   // [NSLOT]
+  uint16_t *s_pair = reinterpret_cast<uint16_t *>(s_view + GSX_MAX_BATCH * VCW);   // [BB * nv]
   const int t = threadIdx.x;
   const int i = blockIdx.x * BB + t;
   const long long row0 = (long long)blockIdx.x * BB;
@@ -221,8 +222,9 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
   float *s_coef = s_mem;                             // [BB][SHF] coefficients, re-used for the gradient rows
   float *s_g = s_mem + BB * SHF;                     // [12][BB]: pw 3, sigma 6, band0 3
   float *s_view = s_g + 12 * BB;                     // [nv][VCW]
-  float *s_stage = s_view + GSX_MAX_BATCH * VCW;     // [9][NSLOT]
-  uint16_t *s_pair = reinterpret_cast<uint16_t *>(s_stage + 9 * NSLOT);
+  const int nslot = BB * bc.nv;
+  float *s_stage = s_view + GSX_MAX_BATCH * VCW;     // [9][nslot]
+  uint16_t *s_pair = reinterpret_cast<uint16_t *>(s_stage + 9 * nslot);
   const int t = threadIdx.x;
   const int i = blockIdx.x * BB + t;
   const long long row0 = (long long)blockIdx.x * BB;
@@ -251,8 +253,8 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     if (!nz) continue;
     act |= 1u << v;
     float *st = s_stage + v * BB + t;
-    st[0 * NSLOT] = a0.x; st[1 * NSLOT] = a0.y; st[2 * NSLOT] = a0.z; st[3 * NSLOT] = a0.w;
-    st[4 * NSLOT] = a1.x; st[5 * NSLOT] = a1.y; st[6 * NSLOT] = a1.z; st[7 * NSLOT] = a1.w; st[8 * NSLOT] = a2.x;
+    st[0 * nslot] = a0.x; st[1 * nslot] = a0.y; st[2 * nslot] = a0.z; st[3 * nslot] = a0.w;
+    st[4 * nslot] = a1.x; st[5 * nslot] = a1.y; st[6 * nslot] = a1.z; st[7 * nslot] = a1.w; st[8 * nslot] = a2.x;
   }
   float3 pw = make_float3(0.f, 0.f, 0.f);
   float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
@@ -278,9 +280,9 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     const int v = slot / BB, g = slot - v * BB;
     const ViewConst &vc = *reinterpret_cast<const ViewConst *>(s_view + v * VCW);
     float *st = s_stage + slot;
-    const float g_r = st[0 * NSLOT], g_g = st[1 * NSLOT], g_b = st[2 * NSLOT];
-    const float g_u = st[4 * NSLOT], g_v = st[5 * NSLOT];
-    const float g_con[3] = {st[6 * NSLOT], st[7 * NSLOT], st[8 * NSLOT]};
+    const float g_r = st[0 * nslot], g_g = st[1 * nslot], g_b = st[2 * nslot];
+    const float g_u = st[4 * nslot], g_v = st[5 * nslot];
+    const float g_con[3] = {st[6 * nslot], st[7 * nslot], st[8 * nslot]};
     const float px = s_g[0 * BB + g], py = s_g[1 * BB + g], pz = s_g[2 * BB + g];
     float sig[6];
 #pragma unroll
@@ -298,9 +300,9 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     const float3 gw = cam_point_backward(vc.view, gc.x, gc.y, gc.z);   // F15
     const float3 gsh = sh_dir_backward<L>(px, py, pz, vc.campos, b0, L > 0 ? s_coef + g * SHF : nullptr, g_r, g_g, g_b,
                                           out.compat_dsph != 0);       // F10, position term
-    st[0 * NSLOT] = gsh.x + gw.x; st[1 * NSLOT] = gsh.y + gw.y; st[2 * NSLOT] = gsh.z + gw.z;
+    st[0 * nslot] = gsh.x + gw.x; st[1 * nslot] = gsh.y + gw.y; st[2 * nslot] = gsh.z + gw.z;
 #pragma unroll
-    for (int k = 0; k < 6; ++k) st[(3 + k) * NSLOT] = dS[k];
+    for (int k = 0; k < 6; ++k) st[(3 + k) * nslot] = dS[k];
   }
   __syncthreads();   // slots hold the pair results; the coefficient rows are free to be overwritten
   // ---- phase C
@@ -317,9 +319,9 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
     ga[0] = z4; ga[1] = z4; ga[2] = z4;   // the slot's packed gradients are zero again for the next batch
     const float *st = s_stage + v * BB + t;
-    gxyz[0] += st[0 * NSLOT]; gxyz[1] += st[1 * NSLOT]; gxyz[2] += st[2 * NSLOT];
+    gxyz[0] += st[0 * nslot]; gxyz[1] += st[1 * nslot]; gxyz[2] += st[2 * nslot];
 #pragma unroll
-    for (int k = 0; k < 6; ++k) dSt[k] += st[(3 + k) * NSLOT];
+    for (int k = 0; k < 6; ++k) dSt[k] += st[(3 + k) * nslot];
     gopa += a0.w; gu += a1.x; gv += a1.y;
     if (COEF) {
       float Y[n];
@@ -471,7 +473,7 @@ int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_m
   if (N <= 0 || bc.nv <= 0) return GSX_OK;
   const int shf = sh_floats(l_max);
   const int ok = l_max > 0 && p.sh_stride == shf && (((uintptr_t)p.sh) & 15) == 0;
-  const size_t sm = ((size_t)BB * shf + 13 * BB + GSX_MAX_BATCH * VCW) * sizeof(float) + NSLOT * sizeof(uint16_t);
+  const size_t sm = ((size_t)BB * shf + 13 * BB + GSX_MAX_BATCH * VCW) * sizeof(float) + (size_t)BB * bc.nv * sizeof(uint16_t);
   const int grid = ceil_div(N, BB);
 #define GSX_BF(L)                                                                                                     \
   do {                                                                                                                \
@@ -501,7 +503,7 @@ int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_m
   o.overwrite = (flags & GSX_GRAD_OVERWRITE) ? 1 : 0;
   o.compat_dsph = (flags & GSX_SH_DSPH_CORRECT) ? 0 : 1;
   o.chunk_ok = l_max > 0 && p.sh_stride == shf && (((uintptr_t)p.sh) & 15) == 0 && (((uintptr_t)g.sh) & 15) == 0;
-  const size_t sm = ((size_t)BB * shf + 12 * BB + GSX_MAX_BATCH * VCW + 9 * NSLOT) * sizeof(float) + NSLOT * sizeof(uint16_t);
+  const size_t sm = ((size_t)BB * shf + 12 * BB + GSX_MAX_BATCH * VCW + (size_t)9 * BB * bc.nv) * sizeof(float) + (size_t)BB * bc.nv * sizeof(uint16_t);
   const int grid = ceil_div(N, BB);
   const bool coef = !(flags & GSX_GRAD_NO_SH);
 #define GSX_BB(L)                                                                                                   \
