@@ -40,7 +40,8 @@ int check_device_ptr(const void *p, const char *name) {
 BinLayout bin_layout(int N, long long capacity);
 int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
                   const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
-                  const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev);
+                  const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
+                  uint32_t *ckey, uint32_t *cid, const int *ccount);
 int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, cudaStream_t st);
 int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, const gsx_grads_t &g, int flags,
                      cudaStream_t st);
@@ -86,6 +87,7 @@ struct gsx_ctx {
   int batch_n = 0, batch_nv = 0, batch_lmax = 0;
   int *h_stats = nullptr;           // pinned: [0] = K, [1] = P
   int *d_P = nullptr;
+  int *d_ccount = nullptr;          // [GSX_MAX_BATCH] compacted-Gaussian counters of the slots
   // optional stage timing (gsx_ctx_enable_timing): 0,1 per-Gaussian forward; 2 view start, 3 emit, 4 sort, 5 ranges,
   // 6 compositing forward; 7,8 compositing backward; 9,10 per-Gaussian backward
   bool timing = false;
@@ -130,6 +132,9 @@ static int alloc_slot(gsx_ctx *c, int k) {
   GSX_CUDA(cudaMalloc(&s.p.mask, n));
   GSX_CUDA(cudaMalloc(&s.p.touched, n * sizeof(int)));
   GSX_CUDA(cudaMalloc(&s.p.gacc, n * 12 * sizeof(float)));
+  GSX_CUDA(cudaMalloc(&s.p.ckey, n * sizeof(uint32_t)));
+  GSX_CUDA(cudaMalloc(&s.p.cid, n * sizeof(uint32_t)));
+  s.p.ccount = c->d_ccount + k;
   GSX_CUDA(cudaMemset(s.p.gacc, 0, n * 12 * sizeof(float)));
   GSX_CUDA(cudaMemset(s.p.mask, 0, n));
   GSX_CUDA(cudaMemset(s.p.touched, 0, n * sizeof(int)));
@@ -140,7 +145,7 @@ static int alloc_slot(gsx_ctx *c, int k) {
 static void free_slot(gsx_slot &s) {
   if (!s.allocated) return;
   cudaFree(s.p.r0); cudaFree(s.p.r1); cudaFree(s.p.r2); cudaFree(s.p.radius); cudaFree(s.p.depth); cudaFree(s.p.mask);
-  cudaFree(s.p.touched); cudaFree(s.p.gacc);
+  cudaFree(s.p.touched); cudaFree(s.p.gacc); cudaFree(s.p.ckey); cudaFree(s.p.cid);
   s = gsx_slot();
 }
 
@@ -152,7 +157,8 @@ static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
   c->last_n = N; c->last_w = v.width; c->last_h = v.height; c->cur = k;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[2], st));
   int rc = bin_sort_impl((const float *)s.p.r0, 4, s.p.depth, 1, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, c->bin_ws,
-                         c->L, c->ranges, &c->sorted_tiles, &c->sorted_vals, st, c->timing ? &c->ev[3] : nullptr);
+                         c->L, c->ranges, &c->sorted_tiles, &c->sorted_vals, st, c->timing ? &c->ev[3] : nullptr, s.p.ckey, s.p.cid,
+                         s.p.ccount);
   if (rc != GSX_OK) return rc;
   rc = composite_fwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, v.width, v.height, v.background,
                             c->spp, c->wpp, c->image, st);
@@ -184,6 +190,8 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
   c->max_n = max_gaussians; c->max_w = max_width; c->max_h = max_height;
   const size_t px = (size_t)max_width * max_height;
   const int T = ((max_width + 15) / 16) * ((max_height + 15) / 16);
+  GSX_CUDA(cudaMalloc(&c->d_ccount, GSX_MAX_BATCH * sizeof(int)));
+  GSX_CUDA(cudaMemset(c->d_ccount, 0, GSX_MAX_BATCH * sizeof(int)));
   {
     int rc0 = alloc_slot(c, 0);
     if (rc0 != GSX_OK) return rc0;
@@ -206,7 +214,7 @@ int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (!c) return GSX_OK;
   for (int k = 0; k < GSX_MAX_BATCH; ++k) free_slot(c->slot[k]);
   cudaFree(c->bin_ws); if (c->key64) cudaFree(c->key64); cudaFree(c->ranges); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
-  cudaFree(c->grad_image); cudaFree(c->d_P); cudaFreeHost(c->h_stats);
+  cudaFree(c->grad_image); cudaFree(c->d_P); cudaFree(c->d_ccount); cudaFreeHost(c->h_stats);
   delete c;
   return GSX_OK;
 }
@@ -230,6 +238,7 @@ int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N,
   BatchConst bc;
   bc.nv = 1; bc.v[0] = make_view_const(*v); bc.s[0] = c->slot[0].p;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
+  GSX_CUDA(cudaMemsetAsync(c->d_ccount, 0, sizeof(int), st));
   rc = batch_fwd_launch(bc, *p, N, v->l_max, st);
   if (rc != GSX_OK) return rc;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[1], st));
@@ -290,6 +299,7 @@ int gsx_batch_forward_params(gsx_ctx_t *c, const gsx_view_t *views, int n_views,
   fill_batch_const(c, n_views, &bc);
   cudaStream_t st = (cudaStream_t)stream;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
+  GSX_CUDA(cudaMemsetAsync(c->d_ccount, 0, GSX_MAX_BATCH * sizeof(int), st));
   int rc = batch_fwd_launch(bc, *p, N, views[0].l_max, st);
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[1], st));
   return rc;

@@ -149,6 +149,7 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     ObbSat so{};
     TileRange tr{0, -1, 0, -1};
     int cnt = 0;
+    float zc = 0.0f;
     if (active) {
       const float px = s_g[0 * BB + g], py = s_g[1 * BB + g], pz = s_g[2 * BB + g];
       float sig[6];
@@ -175,6 +176,7 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       sp.radius[gi] = rad;
       sp.depth[gi] = pc.z;
       sp.mask[gi] = 1;
+      zc = pc.z;
     }
     // exact tile count (F7 window + SAT): small rectangles per thread, large ones by the whole warp
     const bool big = active && rect_cells(tr) > COOP_CELLS;
@@ -191,6 +193,19 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       if (lane == leader) cnt = c;
     }
     if (active) sp.touched[gi] = cnt;
+    // Gaussians with instances are appended (warp-aggregated, unordered) to the view's compact depth-key list: the
+    // depth sort, the scan and the emission of the view then run over P' entries instead of N (binning.cu)
+    const bool app = active && cnt > 0;
+    const unsigned peers = __match_any_sync(0xffffffffu, app ? v : -1 - lane);
+    if (app) {
+      const int leader = __ffs(peers) - 1;
+      int basep = 0;
+      if (lane == leader) basep = atomicAdd(sp.ccount, __popc(peers));
+      basep = __shfl_sync(peers, basep, leader);
+      const int pos = basep + __popc(peers & ((1u << lane) - 1u));
+      sp.ckey[pos] = min(float_sort_bits(zc), 0xfffffffeu);
+      sp.cid[pos] = (uint32_t)gi;
+    }
   }
 }
 

@@ -83,10 +83,12 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
                                                  const float4 *__restrict__ radius, const uint32_t *__restrict__ dkeys,
                                                  const uint32_t *__restrict__ perm,
                                                  const int *__restrict__ touched, const int *__restrict__ offsets,
-                                                 int ntx, int nty, int N, long long capacity,
-                                                 uint32_t *__restrict__ tiles, uint32_t *__restrict__ vals) {
+                                                 int ntx, int nty, int N_host, const int *__restrict__ n_dev,
+                                                 long long capacity, uint32_t *__restrict__ tiles,
+                                                 uint32_t *__restrict__ vals) {
   const int j = blockIdx.x * kBlock + threadIdx.x;
   const int lane = threadIdx.x & 31;
+  const int N = n_dev ? min(*n_dev, N_host) : N_host;
   bool live = j < N && dkeys[j] != 0xffffffffu;
   int i = 0, cnt = 0;
   long long o = 0;
@@ -133,6 +135,26 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
   }
 }
 
+// Compacted depth keys arrive in nondeterministic order (atomic append, batch.cu), so Gaussians with EQUAL depth bits
+// leave the stable sort in that order; the canonical order breaks depth ties by ascending Gaussian id.
+// Runs of equal keys are short (a few per million): the thread at the start of a run insertion-sorts its ids.
+__global__ void __launch_bounds__(kBlock) k_fix_ties(const uint32_t *__restrict__ keys, uint32_t *__restrict__ ids,
+                                                     int N_host, const int *__restrict__ n_dev) {
+  const int n = min(*n_dev, N_host);
+  const int j = blockIdx.x * kBlock + threadIdx.x;
+  if (j >= n - 1) return;
+  const uint32_t k = keys[j];
+  if (keys[j + 1] != k || (j > 0 && keys[j - 1] == k)) return;   // not the first element of a run of >= 2
+  int e = j + 2;
+  while (e < n && keys[e] == k) ++e;
+  for (int a = j + 1; a < e; ++a) {
+    const uint32_t x = ids[a];
+    int b = a - 1;
+    while (b >= j && ids[b] > x) { ids[b + 1] = ids[b]; --b; }
+    ids[b + 1] = x;
+  }
+}
+
 // ---- 3-kernel exclusive scan of int32 (N up to 2^31) ------------------------------------------------------
 __device__ __forceinline__ int block_reduce_sum(int v, int *s_tmp) {
   for (int off = 16; off > 0; off >>= 1) v += __shfl_down_sync(0xffffffffu, v, off);
@@ -155,9 +177,10 @@ __device__ __forceinline__ int scan_value(const int *__restrict__ in, const uint
 }
 
 __global__ void __launch_bounds__(kBlock) k_scan_reduce(const int *__restrict__ in, const uint32_t *__restrict__ perm,
-                                                        const uint32_t *__restrict__ dkeys, int N,
-                                                        int *__restrict__ block_sums) {
+                                                        const uint32_t *__restrict__ dkeys, int N_host,
+                                                        const int *__restrict__ n_dev, int *__restrict__ block_sums) {
   __shared__ int s_tmp[kBlock / 32];
+  const int N = n_dev ? min(*n_dev, N_host) : N_host;
   const long long base = (long long)blockIdx.x * SCAN_TILE;
   int v = 0;
 #pragma unroll
@@ -194,9 +217,11 @@ __global__ void __launch_bounds__(1024) k_scan_block_sums(int *__restrict__ bloc
 }
 
 __global__ void __launch_bounds__(kBlock) k_scan_apply(const int *__restrict__ in, const uint32_t *__restrict__ perm,
-                                                       const uint32_t *__restrict__ dkeys, int N,
+                                                       const uint32_t *__restrict__ dkeys, int N_host,
+                                                       const int *__restrict__ n_dev,
                                                        const int *__restrict__ block_sums, int *__restrict__ out) {
   __shared__ int s_warp[kBlock / 32];
+  const int N = n_dev ? min(*n_dev, N_host) : N_host;
   const long long base = (long long)blockIdx.x * SCAN_TILE + (long long)threadIdx.x * SCAN_IPT;
   int v[SCAN_IPT];
   int sum = 0;
@@ -236,14 +261,14 @@ int tile_key_bits(int n_tiles) {
   return 32 + std::max(b, 1);
 }
 
-int exclusive_scan_i32(const int *in, const uint32_t *perm, const uint32_t *dkeys, int N, int *out, int *block_sums,
-                       int *total_dev, cudaStream_t st) {
+int exclusive_scan_i32(const int *in, const uint32_t *perm, const uint32_t *dkeys, int N, const int *n_dev, int *out,
+                       int *block_sums, int *total_dev, cudaStream_t st) {
   const int nb = std::max(1, ceil_div(N, SCAN_TILE));
-  k_scan_reduce<<<nb, kBlock, 0, st>>>(in, perm, dkeys, N, block_sums);
+  k_scan_reduce<<<nb, kBlock, 0, st>>>(in, perm, dkeys, N, n_dev, block_sums);
   GSX_LAUNCH_CHECK();
   k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nb, total_dev);
   GSX_LAUNCH_CHECK();
-  k_scan_apply<<<nb, kBlock, 0, st>>>(in, perm, dkeys, N, block_sums, out);
+  k_scan_apply<<<nb, kBlock, 0, st>>>(in, perm, dkeys, N, n_dev, block_sums, out);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -276,8 +301,11 @@ BinLayout bin_layout(int N, long long capacity) {
 // ids in (*sorted_tiles, *sorted_vals) inside the workspace; K in total_dev[0].
 int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
                   const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
-                  const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev) {
+                  const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
+                  uint32_t *ckey, uint32_t *cid, const int *ccount) {
   // ev (optional): 3 events recorded after emission, after the tile sort and after the ranges (stage timing)
+  // ckey/cid/ccount (optional, view-level path): depth keys + ids of the Gaussians that touch a tile, already compacted by
+  // the per-Gaussian kernel (unordered; *ccount entries) -- the depth sort, scan and emission then run over P' not N
   int *offsets = (int *)(ws + L.offsets);
   int *block_sums = (int *)(ws + L.block_sums), *total = (int *)(ws + L.total);
   uint32_t *dka = (uint32_t *)(ws + L.dk_a), *dkb = (uint32_t *)(ws + L.dk_b);
@@ -286,7 +314,15 @@ int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_
   uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
   int in_b = 0, rc;
   const uint32_t *perm = nullptr, *dkeys = nullptr;
-  if (N > 0) {
+  if (N > 0 && ckey) {
+    rc = sort_pairs_u32_impl(ckey, dkb, cid, dvb, N, ccount, 32, ws + L.sort_ws, L.sort_ws_bytes, st, &in_b);
+    if (rc != GSX_OK) return rc;
+    uint32_t *sk = in_b ? dkb : ckey, *sv = in_b ? dvb : cid;
+    k_fix_ties<<<ceil_div(N, kBlock), kBlock, 0, st>>>(sk, sv, N, ccount);
+    GSX_LAUNCH_CHECK();
+    perm = sv; dkeys = sk;
+  } else if (N > 0) {
+    ccount = nullptr;
     k_depth_keys<<<ceil_div(N, kBlock), kBlock, 0, st>>>(depth, depth_stride, touched, N, dka, dva);
     GSX_LAUNCH_CHECK();
     rc = sort_pairs_u32_impl(dka, dkb, dva, dvb, N, nullptr, 32, ws + L.sort_ws, L.sort_ws_bytes, st, &in_b);
@@ -294,10 +330,11 @@ int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_
     perm = in_b ? dvb : dva;
     dkeys = in_b ? dkb : dka;
   }
-  rc = exclusive_scan_i32(touched, perm, dkeys, N, offsets, block_sums, total, st);
+  rc = exclusive_scan_i32(touched, perm, dkeys, N, ccount, offsets, block_sums, total, st);
   if (rc != GSX_OK) return rc;
   if (N > 0) {
-    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, dkeys, perm, touched, offsets, ntx, nty, N, capacity, ka, va);
+    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, dkeys, perm, touched, offsets, ntx, nty, N, ccount, capacity,
+                                                   ka, va);
     GSX_LAUNCH_CHECK();
   }
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
@@ -363,7 +400,7 @@ int gsx_sorted_list_size(const float *uv, const float *radius, int n_tiles_x, in
   GSX_CUDA(cudaMemsetAsync(coarse, 0, sizeof(unsigned long long), st));
   rc = count_tiles_launch(uv, 2, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched), coarse, st);
   if (rc != GSX_OK) return rc;
-  rc = exclusive_scan_i32((int *)(ws + L.touched), nullptr, nullptr, N, (int *)(ws + L.offsets), (int *)(ws + L.block_sums),
+  rc = exclusive_scan_i32((int *)(ws + L.touched), nullptr, nullptr, N, nullptr, (int *)(ws + L.offsets), (int *)(ws + L.block_sums),
                           (int *)(ws + L.total), st);
   if (rc != GSX_OK) return rc;
   unsigned long long hc = 0;
@@ -407,7 +444,7 @@ int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const floa
   const uint32_t *sk;
   const uint32_t *sv;
   rc = bin_sort_impl(uv, 2, xyz_c + 2, 3, (const float4 *)radius, (const int *)(ws + L.touched), n_tiles_x, n_tiles_y, N,
-                     capacity, ws, L, ranges, &sk, &sv, st, nullptr);
+                     capacity, ws, L, ranges, &sk, &sv, st, nullptr, nullptr, nullptr, nullptr);
   if (rc != GSX_OK) return rc;
   rc = copy_ids_launch(sv, sorted_gaussians, capacity, (const int *)(ws + L.total), st);
   if (rc != GSX_OK) return rc;

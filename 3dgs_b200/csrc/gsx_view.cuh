@@ -37,6 +37,8 @@ struct SlotPtrs {
   uint8_t *mask;
   int *touched;
   float4 *gacc;   // [N][3] float4
+  uint32_t *ckey, *cid;   // [N] depth bits / ids of the Gaussians touching a tile, compacted (unordered)
+  int *ccount;            // device int: how many
 };
 
 struct BatchConst {

@@ -312,9 +312,9 @@ def main():
         # batch kernels (one launch per batch of nv views): parameters once + per-view records / packed gradients
         "preprocess_fwd": ("hbm", PB_ * N + nv * (74 * P + 5 * (N - P))),
         "preprocess_bwd": ("hbm", PB_ * N + nv * (4 * N + 96 * Pt) + PB_ * N),
-        # depth keys (16N) + 4-pass depth sort of the Gaussians (4N + 4*16N) + scan through the permutation (20N) +
-        # emission in depth order (8N + 32 P' + 8K)
-        "scan_emit": ("hbm", 112 * N + 32 * Pt + 8 * K),
+        # over the P' Gaussians that touch a tile (compacted by the per-Gaussian kernel): 4-pass depth sort (4 + 4*16),
+        # tie fix-up (8), scan through the permutation (20), emission in depth order (8 + 32) + 8 B per instance
+        "scan_emit": ("hbm", 136 * Pt + 8 * K),
         "sort": ("hbm", (4 + 16 * passes) * K),                    # tile sort: histogram read + passes * (8 B in + 8 B out)
         "ranges": ("hbm", 4 * K + 4 * (T + 1)),
         "composite_fwd": ("fp32", 18 * Sx),
@@ -334,7 +334,12 @@ def main():
     stage_ms = {k_: v_["ms_per_view"] for k_, v_ in stages.items()}
     top = max(stage_ms, key=stage_ms.get)
     roof = {k_: stages[top][k_] for k_ in ("bound", "achieved", "peak", "unit", "frac")}
-    roof.update({"kernel": top, "traffic": None, "ms": stages[top]["ms"],
+    try:                                                           # DRAM bytes per launch of that kernel from the committed ncu capture
+        with open(os.path.join(ROOT, "profiles", "traffic_r1.json")) as f:
+            traffic = json.load(f).get(top)
+    except Exception:
+        traffic = None
+    roof.update({"kernel": top, "traffic": traffic, "ms": stages[top]["ms"],
                  "peak_source": peak_src if roof["bound"] == "hbm" else "FP32 FMA peak measured in this run (gsx_measure_fp32_tflops)",
                  "share_of_view": round(stage_ms[top] / sum(stage_ms.values()), 3)})
 
@@ -345,7 +350,7 @@ def main():
                   f"gradients (SH gradients rebuilt locally; plain allreduce would be {flat.numel() * 4 / 1e6:.0f} MB)")
     else:
         xbytes = "none (single GPU)"
-    # depth keys, histogram x2, depth onesweep x4, scan x3, emit, histogram x2, tile onesweep, ranges, composite x2
+    # histogram x2, depth onesweep x4, tie fix-up, scan x3, emit, histogram x2, tile onesweep, ranges, composite x2
     launches_per_view = 1 + 2 + 4 + 3 + 1 + 2 + passes + 1 + 2
     out = {
         "metric": METRIC, "value": views_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,

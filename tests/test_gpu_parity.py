@@ -464,6 +464,36 @@ def test_view_parallel_split_exchange_matches_fused(B, l_max, sh_alloc):
     r.close()
 
 
+def test_view_sorted_list_depth_ties_canonical(B):
+    """Every Gaussian three times (identical depth bits): the compacted depth keys arrive unordered, so the canonical
+    tie order (ascending Gaussian id) exercises k_fix_ties.  Bit-exact against the oracle's list."""
+    W, H = 160, 128
+    cam = S.orbit_camera(W, H, azimuth_deg=70.0)
+    g0 = S.synthetic_gaussians(2500, l_max=0, seed=77)
+    rep = lambda a: None if a is None else np.concatenate([a, a, a], axis=0)
+    g = {k: rep(v) for k, v in g0.items()}
+    perm = np.random.default_rng(5).permutation(g["xyz"].shape[0])            # interleave the copies
+    g = {k: (None if v is None else np.ascontiguousarray(v[perm])) for k, v in g.items()}
+    Hh, gd, r, v, stats = _run_view(cam, g, 0, 0.0)
+    st = {k: (t.cpu().numpy() if hasattr(t, "cpu") else t) for k, t in r.state().items()}
+    N = g["xyz"].shape[0]
+    mask = st["mask"].astype(bool)
+    uv = np.where(mask[:, None], st["rec0"][:, :2], -1e6).astype(np.float32)
+    rad = np.where(mask[:, None], st["radius"], np.array([0, 0, 0, 1], np.float32)).astype(np.float32)
+    xyz_c = np.zeros((N, 3), np.float32); xyz_c[:, 2] = np.where(mask, st["depth"], 1.0)
+    lst = G.sorted_list(uv, xyz_c, rad, (W + 15) // 16, (H + 15) // 16)
+    assert lst["K"] == st["K"] and st["K"] > 0
+    np.testing.assert_array_equal(st["ranges"], lst["ranges"])
+    np.testing.assert_array_equal(st["sorted_gaussians"], lst["sorted"])
+    keys = st["sorted_keys"].view(np.uint64)
+    assert (np.diff(keys.view(np.int64)) >= 0).all()
+    d = st["depth"][st["sorted_gaussians"]]
+    same = (np.diff(keys.view(np.int64)) == 0)
+    assert same.sum() > st["K"] // 4                                           # ties really are everywhere
+    assert (np.diff(st["sorted_gaussians"])[same] > 0).all()                   # ... and broken by ascending id
+    r.close()
+
+
 def test_config1_fixture_and_companion(B):
     """C1: the reference's own COLMAP fixture (1 camera, 1 image, 1 point): the Gaussian survives the
     padded cull, touches no tile, the image is pure background and every gradient is zero; plus the non-degenerate
