@@ -113,11 +113,11 @@ def test_view_parallel_exchange_world2(tmp_path):
     for o in outs:
         # (the oracle's OpenMP reduction order differs between processes: compare to the parent's recomputation with a
         # tolerance, and the two ranks' gathered copies bit-exactly below)
-        np.testing.assert_allclose(o["drgb"], np.stack(drgb_all), rtol=1e-4, atol=1e-6 * np.abs(np.stack(drgb_all)).max())
+        np.testing.assert_allclose(o["drgb"], np.stack(drgb_all), rtol=1e-3, atol=1e-5 * np.abs(np.stack(drgb_all)).max())
         for nm, ko in (("xyz", "xyz"), ("scale", "scale"), ("quaternion", "quat"), ("opacity", "opacity")):
-            np.testing.assert_allclose(o[nm].reshape(-1), tot[ko].reshape(-1), rtol=1e-4, atol=1e-6 * np.abs(tot[ko]).max())
-        np.testing.assert_allclose(o["band0"], tot["band0"], rtol=1e-4, atol=1e-6 * np.abs(tot["band0"]).max())
-        np.testing.assert_allclose(o["sh"], tot["sh"].reshape(N, -1, 3)[:, :nsh], rtol=1e-4,
-                                   atol=1e-6 * np.abs(tot["sh"]).max())
+            np.testing.assert_allclose(o[nm].reshape(-1), tot[ko].reshape(-1), rtol=1e-3, atol=1e-5 * np.abs(tot[ko]).max())
+        np.testing.assert_allclose(o["band0"], tot["band0"], rtol=1e-3, atol=1e-5 * np.abs(tot["band0"]).max())
+        np.testing.assert_allclose(o["sh"], tot["sh"].reshape(N, -1, 3)[:, :nsh], rtol=1e-3,
+                                   atol=1e-5 * np.abs(tot["sh"]).max())
     for nm in ("drgb", "sh", "band0", "xyz", "scale", "quaternion", "opacity"):       # both ranks hold the same sums
         np.testing.assert_array_equal(outs[0][nm], outs[1][nm])
