@@ -14,6 +14,8 @@
 // Algorithmic bytes per batch at degree 3 (n views, P' = Gaussians that touch a tile in a view):
 //   forward  236 N read + 74 N n written (records, radius, depth, count, mask)
 //   backward 236 N + 4 N n + 96 P' n (packed gradients read + re-zeroed) read/written + 236 N written.
+#include <algorithm>
+
 #include "gsx_common.cuh"
 #include "gsx_math.cuh"
 #include "gsx_tma.cuh"
@@ -416,6 +418,71 @@ __global__ void __launch_bounds__(256) k_extract_view_rgb(const float4 *__restri
   drgb[3 * (size_t)i] = a.x; drgb[3 * (size_t)i + 1] = a.y; drgb[3 * (size_t)i + 2] = a.z;
 }
 
+// Fused extraction + all-gather: the same d rgb rows leave the SM straight into EVERY rank's gather buffer -- one
+// multimem.st per 16 bytes through the NVSwitch multicast address (the switch replicates; SASS STG.E.128.STRONG.SYS on a
+// multicast mapping), or one plain st.global per peer pointer (P2P over NVLink) when no multicast mapping exists.
+// The transfer overlaps the compositing of the rank's next views / the per-Gaussian backward; no NCCL call, no staging.
+struct PeerPtrs { float *p[8]; int n; };
+__device__ __forceinline__ void multimem_st_v4(float *mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__global__ void __launch_bounds__(256) k_extract_view_rgb_peers(const float4 *__restrict__ gacc,
+                                                                const int *__restrict__ touched, int N,
+                                                                float *mc /*multicast address of the view's [N][3] or null*/,
+                                                                const PeerPtrs peers) {
+  // one ADDRESS-aligned 16-byte group of the flat [3N] array per thread (a view's block may start at any 4-byte offset)
+  const float *base = mc ? mc : peers.p[0];
+  const int mis = (int)((reinterpret_cast<uintptr_t>(base) >> 2) & 3);   // identical on every rank (symmetric offsets)
+  const long long q = (long long)blockIdx.x * 256 + threadIdx.x;
+  const long long total = 3LL * N;
+  const long long first = 4 * q - mis;
+  if (first >= total) return;
+  float v[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const long long idx = first + e;
+    float x = 0.0f;
+    if (idx >= 0 && idx < total) {
+      const int i = (int)(idx / 3), c = (int)(idx - 3LL * i);
+      if (touched[i] > 0) {
+        const float4 a = gacc[3 * (size_t)i];
+        x = c == 0 ? a.x : (c == 1 ? a.y : a.z);
+      }
+    }
+    v[e] = x;
+  }
+  if (first >= 0 && first + 3 < total) {
+    const float4 o = make_float4(v[0], v[1], v[2], v[3]);
+    if (mc) multimem_st_v4(mc + first, o);
+    else
+      for (int r = 0; r < peers.n; ++r) *reinterpret_cast<float4 *>(peers.p[r] + first) = o;
+  } else {   // ragged head / tail: scalar stores to every peer
+    for (int e = 0; e < 4; ++e) {
+      const long long idx = first + e;
+      if (idx < 0 || idx >= total) continue;
+      if (mc) asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc + idx), "f"(v[e]) : "memory");
+      else
+        for (int r = 0; r < peers.n; ++r) peers.p[r][idx] = v[e];
+    }
+  }
+}
+
+// In-switch allreduce (NVLS): rank r sums its 1/world slice of the buffer over ALL ranks with multimem.ld_reduce (SASS
+// LDGMC.ADD: the NVSwitch adds the ranks' copies) and broadcasts the sums with multimem.st.  Each byte crosses a GPU's
+// links once in each direction.  Callers barrier across ranks before (inputs written) and after (outputs complete).
+__global__ void __launch_bounds__(256) k_allreduce_multimem(float *mc, long long n4_begin, long long n4_end) {
+  const long long stride = (long long)gridDim.x * 256;
+  for (long long q = n4_begin + (long long)blockIdx.x * 256 + threadIdx.x; q < n4_end; q += stride) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(mc + 4 * q)
+                 : "memory");
+    multimem_st_v4(mc + 4 * q, v);
+  }
+}
+
 struct ViewCams { float campos[GSX_MAX_VIEWS_TOTAL][3]; int nv; };
 
 // SH coefficient + band-0 gradients of a whole batch from the per-view colour gradients of ALL its views (gathered
@@ -546,6 +613,31 @@ int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_m
 int extract_view_rgb_launch(const float4 *gacc, const int *touched, int N, float *drgb, cudaStream_t st) {
   if (N <= 0) return GSX_OK;
   k_extract_view_rgb<<<ceil_div(N, 256), 256, 0, st>>>(gacc, touched, N, drgb);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+int extract_view_rgb_peers_launch(const float4 *gacc, const int *touched, int N, float *mc, float *const *peers, int n_peers,
+                                  cudaStream_t st) {
+  if (N <= 0) return GSX_OK;
+  if (!mc && (n_peers < 1 || n_peers > 8)) { set_error("n_peers %d out of range 1..8", n_peers); return GSX_E_ARG; }
+  PeerPtrs pp;
+  pp.n = mc ? 0 : n_peers;
+  for (int r = 0; r < 8; ++r) pp.p[r] = (!mc && r < n_peers) ? peers[r] : nullptr;
+  const long long groups = (3LL * N + 3 + 3) / 4;   // + up to 3 floats of head misalignment
+  k_extract_view_rgb_peers<<<ceil_div(groups, 256), 256, 0, st>>>(gacc, touched, N, mc, pp);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+int allreduce_multimem_launch(float *mc, size_t n_floats, int rank, int world, cudaStream_t st) {
+  if (!mc || world < 1 || rank < 0 || rank >= world || (n_floats & 3)) { set_error("bad multimem allreduce arguments"); return GSX_E_ARG; }
+  const long long n4 = (long long)(n_floats / 4);
+  const long long per = (n4 + world - 1) / world;
+  const long long b = std::min<long long>(n4, per * rank), e = std::min<long long>(n4, per * (rank + 1));
+  if (e <= b) return GSX_OK;
+  const int blocks = (int)std::min<long long>(kNumSMs * 4, (e - b + 255) / 256);
+  k_allreduce_multimem<<<blocks, 256, 0, st>>>(mc, b, e);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }

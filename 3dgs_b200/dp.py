@@ -10,6 +10,14 @@ d sh[k][c] = d rgb_c * Y_k(dir_view) (reference cuda/spherical_harmonics_backwar
     (gsx_sh_grads_from_view_rgb), overlapping the allreduce.
 Link bytes per Gaussian and step: 44 allreduced + 12 x views gathered, instead of 236 allreduced.
 
+Two transports for the same exchange:
+  * "nccl": NCCL all-gather + NCCL allreduce on a high-priority side stream (works everywhere);
+  * "multimem" / "p2p" (GradExchange(..., symmetric=True), used when torch symmetric memory can map the buffers): the
+    extraction kernel stores each view's d rgb straight into every rank's gather buffer through the NVSwitch multicast
+    address (multimem.st) or per-peer NVLink stores -- the all-gather is fused into the producing kernel and overlaps
+    the next views' compositing -- and the geometry gradients are summed in the switch by a hand-written NVLS kernel
+    (multimem.ld_reduce + multimem.st, gsx_allreduce_multimem_f32).  Cross-rank ordering = symmetric-memory barriers.
+
 `shard_views` and `GradExchange` are device-agnostic (the world-size-2 gloo tests drive them with CPU tensors);
 `ViewParallel` is the GPU step on top of host.Rasterizer's batch path.
 """
@@ -38,19 +46,51 @@ class GradExchange:
     """Buffers + collectives of one batch step.  drgb[v] is the dense d rgb of global view v ([N][3]); geom holds the
     allreduced arrays as views of one flat buffer (a single collective)."""
 
-    def __init__(self, N, n_views, world, rank, device, group=None):
+    def __init__(self, N, n_views, world, rank, device, group=None, symmetric=False):
         self.N, self.n_views, self.world, self.rank, self.group = N, n_views, world, rank, group
         self.mine = shard_views(n_views, world, rank)
-        self.drgb = torch.zeros((n_views, N, 3), device=device, dtype=torch.float32)
         offs, off = {}, 0
         for nm, w in GEOM:
             offs[nm] = off
             off += (N * w + 3) // 4 * 4                     # 16-byte aligned segments
-        self.geom_flat = torch.zeros(off, device=device, dtype=torch.float32)
+        n_drgb = (n_views * N * 3 + 3) // 4 * 4
+        self.transport, self.hdl, self.why_not = "nccl", None, None
+        base = None
+        if symmetric and world > 1:
+            try:                                            # one symmetric allocation: [drgb | geom_flat]
+                import torch.distributed._symmetric_memory as symm_mem
+                base = symm_mem.empty(n_drgb + off, dtype=torch.float32, device=device)
+                self.hdl = symm_mem.rendezvous(base, group if group is not None else dist.group.WORLD)
+                base.zero_()
+                self.transport = "multimem" if (self.hdl.has_multicast_support and self.hdl.multicast_ptr) else "p2p"
+            except Exception as e:                          # no symmetric memory on this system: NCCL transport
+                self.why_not, self.hdl, base = repr(e)[:200], None, None
+        if base is None:
+            base = torch.zeros(n_drgb + off, device=device, dtype=torch.float32)
+        self.base, self.n_drgb = base, n_drgb
+        self.drgb = base[: n_views * N * 3].view(n_views, N, 3)
+        self.geom_flat = base[n_drgb: n_drgb + off]
         self.geom = {}
         for nm, w in GEOM:
             v = self.geom_flat[offs[nm]: offs[nm] + N * w]
             self.geom[nm] = v.view(N, w) if w > 1 else v
+
+    # ---- symmetric-memory transport ---------------------------------------------------------------------------
+    def barrier(self, channel=0):
+        """cross-rank barrier on the current stream (device side, symmetric-memory signal pads)"""
+        self.hdl.barrier(channel=channel)
+
+    def view_targets(self, k):
+        """(multicast pointer or 0, peer pointers) of the [N][3] block of this rank's k-th view in every rank's buffer"""
+        byte_off = self.mine[k] * self.N * 3 * 4
+        if self.transport == "multimem":
+            return int(self.hdl.multicast_ptr) + byte_off, []
+        return 0, [int(p) + byte_off for p in self.hdl.buffer_ptrs]
+
+    def all_reduce_geom_multimem(self):
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        check(lib().gsx_allreduce_multimem_f32(C.c_void_p(int(self.hdl.multicast_ptr) + self.n_drgb * 4),
+                                               C.c_size_t(self.geom_flat.numel()), int(self.rank), int(self.world), st))
 
     def local_drgb(self, k):
         """buffer of this rank's k-th view"""
@@ -90,7 +130,7 @@ class ViewParallel:
     """One batch step on this rank's GPU: forward + backward of the rank's views, then the exchange above.
     `views_all` / `campos_all` describe ALL views of the batch (every rank needs every camera position)."""
 
-    def __init__(self, rasterizer, gaussians, views_all, campos_all, l_max, world=1, rank=0, group=None):
+    def __init__(self, rasterizer, gaussians, views_all, campos_all, l_max, world=1, rank=0, group=None, symmetric=True):
         self.r, self.g, self.l_max, self.world, self.rank = rasterizer, gaussians, l_max, world, rank
         self.views_all, self.campos_all = views_all, [tuple(float(x) for x in c) for c in campos_all]
         dev = gaussians.xyz.device
@@ -101,7 +141,7 @@ class ViewParallel:
         if gaussians.grads is None:
             gaussians.zero_grads()
         if world > 1:
-            self.ex = GradExchange(N, len(views_all), world, rank, dev, group)
+            self.ex = GradExchange(N, len(views_all), world, rank, dev, group, symmetric=symmetric)
             for nm, _ in GEOM:                              # the geometry gradients live in the flat allreduce buffer
                 gaussians.grads[nm] = self.ex.geom[nm]
             self.comm = torch.cuda.Stream(device=dev, priority=-1)
@@ -130,6 +170,8 @@ class ViewParallel:
         if self.world == 1:
             r.batch_step(self.views, g, grad_images, flags=OVER, on_image=on_image)
             return
+        if self.ex.transport != "nccl":
+            return self._step_symmetric(grad_images, on_image)
         main = torch.cuda.current_stream()
         self._mark("t0", main)
         r.batch_forward_params(self.views, g)
@@ -163,4 +205,47 @@ class ViewParallel:
                                g.sh_stride, OVER)
         self._mark("s1", main)
         main.wait_event(self.ev_reduced)
+        self._mark("end", main)
+
+    def _step_symmetric(self, grad_images, on_image):
+        """Same exchange with the all-gather fused into the extraction kernel (stores into every rank's buffer over
+        NVLink) and, with multicast, the geometry allreduce done in the switch by our own kernel."""
+        r, g, ex = self.r, self.g, self.ex
+        OVER, NO_SH = _ffi.GSX_GRAD_OVERWRITE, _ffi.GSX_GRAD_NO_SH
+        main = torch.cuda.current_stream()
+        st = C.c_void_p(main.cuda_stream)
+        self._mark("t0", main)
+        ex.barrier(0)                                       # every rank is done reading last step's buffers
+        r.batch_forward_params(self.views, g)
+        for k in range(len(self.views)):
+            r.batch_forward_view(k)
+            if on_image is not None:
+                on_image(k)
+            gi = grad_images[k] if isinstance(grad_images, (list, tuple)) else grad_images
+            r.batch_backward_view(k, gi)
+            mc, peers = ex.view_targets(k)
+            arr = (C.c_void_p * max(len(peers), 1))(*peers) if peers else None
+            check(lib().gsx_batch_extract_view_rgb_grad_peers(r.h, int(k), C.c_void_p(mc), arr, len(peers), st))
+        self._mark("views", main)
+        self._mark("g0", main); self._mark("g1", main)      # the gather has no phase of its own any more
+        r.batch_backward_params(g, OVER | NO_SH)            # geometry gradients -> this rank's part of the symmetric buffer
+        self._mark("bwd", main)
+        ex.barrier(1)                                       # all d rgb stores and all geometry gradients have landed
+        self.ev_geom.record(main)
+        with torch.cuda.stream(self.comm):                  # allreduce overlaps the SH rebuild
+            self.comm.wait_event(self.ev_geom)
+            self._mark("r0", self.comm)
+            if ex.transport == "multimem":
+                ex.all_reduce_geom_multimem()
+            else:
+                ex.all_reduce_geom()
+            self._mark("r1", self.comm)
+            self.ev_reduced.record(self.comm)
+        self._mark("s0", main)
+        sh_grads_from_view_rgb(g.xyz, self.campos_all, ex.drgb, self.l_max, g.grads["sh"], g.grads["band0"],
+                               g.sh_stride, OVER)
+        self._mark("s1", main)
+        main.wait_event(self.ev_reduced)
+        if ex.transport == "multimem":
+            ex.barrier(2)                                   # every rank's slice of the sums has been broadcast
         self._mark("end", main)

@@ -210,7 +210,9 @@ def main():
     # One step = the rank's views of the batch through the batch path (parameters read once per direction, gradients
     # of the rank's views summed in one pass with '=' semantics: no 1.4 GB memset) + the gradient allreduce.
     all_views = [mk(c, 0) for c in cams]
-    vp = gs.dp.ViewParallel(r, gd, all_views, [c["campos"] for c in cams], l_max, world, rank)
+    # GSX_DP_TRANSPORT=nccl forces the NCCL transport (default: symmetric memory -- multimem / p2p -- when available)
+    vp = gs.dp.ViewParallel(r, gd, all_views, [c["campos"] for c in cams], l_max, world, rank,
+                            symmetric=os.environ.get("GSX_DP_TRANSPORT", "auto") != "nccl")
 
     def step():
         vp.step(gi_dev)
@@ -346,7 +348,9 @@ def main():
     views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
     if world > 1:
         ga_, ar_ = vp.ex.link_bytes_per_step()
-        xbytes = (f"NCCL all-gather of {ga_ / 1e6:.0f} MB per-view d rgb + NCCL allreduce of {ar_ / 1e6:.0f} MB geometry "
+        how = {"nccl": "NCCL all-gather", "multimem": "in-kernel multicast stores (multimem.st)", "p2p": "in-kernel P2P stores"}[vp.ex.transport]
+        how2 = "in-switch multimem allreduce kernel" if vp.ex.transport == "multimem" else "NCCL allreduce"
+        xbytes = (f"{how} of {ga_ / 1e6:.0f} MB per-view d rgb + {how2} of {ar_ / 1e6:.0f} MB geometry "
                   f"gradients (SH gradients rebuilt locally; plain allreduce would be {flat.numel() * 4 / 1e6:.0f} MB)")
     else:
         xbytes = "none (single GPU)"
@@ -365,7 +369,7 @@ def main():
         "e2e": {"value": N_VIEWS * args.steps / dt_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": N_VIEWS * (W * H * 3 * 4 + 200), "d2h_bytes_per_step": N_VIEWS * W * H * 3 * 4},
         "gpu_launches": (launches_per_view * nv + 2) * args.steps * world,
-        "exchange_ms": exch, "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": round(fp32_peak, 2),
+        "exchange_ms": exch, "exchange_transport": (vp.ex.transport if world > 1 else None), "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": round(fp32_peak, 2),
     }
     if world == 1 and not args.no_cpu_baseline:
         from oracle import golden as G

@@ -215,6 +215,16 @@ int gsx_batch_backward_params(gsx_ctx_t *ctx, const gsx_params_t *params, int N,
  *      (zeros where no gradient arrived).  gsx_sh_grads_from_view_rgb: drgb is [n_views][view_stride floats] holding
  *      [N][3] per view, campos_host is [n_views][3]; '=' with GSX_GRAD_OVERWRITE, else '+='. ------------------------- */
 int gsx_batch_extract_view_rgb_grad(gsx_ctx_t *ctx, int slot, float *drgb, void *stream);
+/* Fused extraction + all-gather over NVLink peer memory: the view's d rgb is stored straight into every rank's gather
+ * buffer -- through the NVSwitch multicast address `multicast_drgb` (multimem.st) when non-NULL, else to each of the
+ * n_peers (<= 8) peer pointers (this rank's own buffer included) with plain P2P stores.  The pointers address the view's
+ * [N][3] block inside a symmetric allocation (cuMem/NVLS mapping owned by the caller, e.g. torch symmetric memory). */
+int gsx_batch_extract_view_rgb_grad_peers(gsx_ctx_t *ctx, int slot, float *multicast_drgb, float *const *peer_drgb_host,
+                                          int n_peers, void *stream);
+/* In-switch (NVLS) sum-allreduce of n_floats (multiple of 4, 16-byte aligned) floats of a symmetric buffer through its
+ * multicast address: rank r reduces slice r with multimem.ld_reduce and broadcasts it with multimem.st.  The caller
+ * barriers across the ranks before and after. */
+int gsx_allreduce_multimem_f32(float *multicast_ptr, size_t n_floats, int rank, int world, void *stream);
 int gsx_sh_grads_from_view_rgb(const float *xyz_w, int N, int l_max, const float *campos_host, int n_views,
                                const float *drgb, size_t view_stride, float *sh_grad, int sh_stride, float *band0_grad,
                                int flags, void *stream);

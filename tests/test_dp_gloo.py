@@ -121,3 +121,17 @@ def test_view_parallel_exchange_world2(tmp_path):
                                    atol=1e-5 * np.abs(tot["sh"]).max())
     for nm in ("drgb", "sh", "band0", "xyz", "scale", "quaternion", "opacity"):       # both ranks hold the same sums
         np.testing.assert_array_equal(outs[0][nm], outs[1][nm])
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+def test_view_parallel_multi_gpu_transports():
+    """>= 2 GPUs: dp.ViewParallel (NCCL and symmetric-memory transports) == the fused single-GPU batch (tests/dp_worker.py)."""
+    import subprocess
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    n = 2
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
+                          "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+                          os.path.join(ROOT, "tests", "dp_worker.py")], capture_output=True, text=True, timeout=580)
+    assert out.returncode == 0 and "DP_OK" in out.stdout, (out.stdout + out.stderr)[-3000:]
