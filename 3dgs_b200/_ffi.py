@@ -29,7 +29,7 @@ SYMBOLS = [
     "gsx_batch_reserve", "gsx_batch_forward_params", "gsx_batch_forward_view", "gsx_batch_backward_view",
     "gsx_batch_backward_params", "gsx_batch_render_host", "gsx_batch_extract_view_rgb_grad",
     "gsx_sh_grads_from_view_rgb", "gsx_ctx_build_sorted_keys", "gsx_batch_extract_view_rgb_grad_peers",
-    "gsx_allreduce_multimem_f32",
+    "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers",
 ]
 
 

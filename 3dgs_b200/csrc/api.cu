@@ -46,8 +46,8 @@ int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_m
 int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, const gsx_grads_t &g, int flags,
                      cudaStream_t st);
 int extract_view_rgb_launch(const float4 *gacc, const int *touched, int N, float *drgb, cudaStream_t st);
-int extract_view_rgb_peers_launch(const float4 *gacc, const int *touched, int N, float *mc, float *const *peers, int n_peers,
-                                  cudaStream_t st);
+int extract_view_rgb_peers_launch(const float4 *gacc, const int *touched, const float *src_dense, int N, float *mc,
+                                  float *const *peers, int n_peers, cudaStream_t st);
 int allreduce_multimem_launch(float *mc, size_t n_floats, int rank, int world, cudaStream_t st);
 int sh_from_view_rgb_launch(const float *xyz, int N, int l_max, const float *campos_host, int n_views, const float *drgb,
                             size_t view_stride, float *sh_grad, int sh_stride, float *band0_grad, int flags,
@@ -348,8 +348,15 @@ int gsx_batch_extract_view_rgb_grad_peers(gsx_ctx_t *c, int slot, float *multica
                                           int n_peers, void *stream) {
   if (!c || (!multicast_drgb && !peer_drgb_host)) { set_error("null argument"); return GSX_E_NULL; }
   if (slot < 0 || slot >= c->batch_nv) { set_error("slot %d outside the current batch (%d views)", slot, c->batch_nv); return GSX_E_ARG; }
-  return extract_view_rgb_peers_launch(c->slot[slot].p.gacc, c->slot[slot].p.touched, c->batch_n, multicast_drgb,
+  return extract_view_rgb_peers_launch(c->slot[slot].p.gacc, c->slot[slot].p.touched, nullptr, c->batch_n, multicast_drgb,
                                        peer_drgb_host, n_peers, (cudaStream_t)stream);
+}
+
+int gsx_push_view_rgb_peers(const float *drgb_local, int N, float *multicast_drgb, float *const *peer_drgb_host, int n_peers,
+                            void *stream) {
+  if (!drgb_local || (!multicast_drgb && !peer_drgb_host)) { set_error("null argument"); return GSX_E_NULL; }
+  return extract_view_rgb_peers_launch(nullptr, nullptr, drgb_local, N, multicast_drgb, peer_drgb_host, n_peers,
+                                       (cudaStream_t)stream);
 }
 
 int gsx_allreduce_multimem_f32(float *multicast_ptr, size_t n_floats, int rank, int world, void *stream) {

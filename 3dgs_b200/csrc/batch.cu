@@ -428,7 +428,8 @@ __device__ __forceinline__ void multimem_st_v4(float *mc, float4 v) {
                : "memory");
 }
 __global__ void __launch_bounds__(256) k_extract_view_rgb_peers(const float4 *__restrict__ gacc,
-                                                                const int *__restrict__ touched, int N,
+                                                                const int *__restrict__ touched,
+                                                                const float *__restrict__ src_dense /*or null*/, int N,
                                                                 float *mc /*multicast address of the view's [N][3] or null*/,
                                                                 const PeerPtrs peers) {
   // one ADDRESS-aligned 16-byte group of the flat [3N] array per thread (a view's block may start at any 4-byte offset)
@@ -444,10 +445,14 @@ __global__ void __launch_bounds__(256) k_extract_view_rgb_peers(const float4 *__
     const long long idx = first + e;
     float x = 0.0f;
     if (idx >= 0 && idx < total) {
-      const int i = (int)(idx / 3), c = (int)(idx - 3LL * i);
-      if (touched[i] > 0) {
-        const float4 a = gacc[3 * (size_t)i];
-        x = c == 0 ? a.x : (c == 1 ? a.y : a.z);
+      if (src_dense) {   // push of an already extracted dense block (runs on a side stream, gsx_push_view_rgb_peers)
+        x = src_dense[idx];
+      } else {
+        const int i = (int)(idx / 3), c = (int)(idx - 3LL * i);
+        if (touched[i] > 0) {
+          const float4 a = gacc[3 * (size_t)i];
+          x = c == 0 ? a.x : (c == 1 ? a.y : a.z);
+        }
       }
     }
     v[e] = x;
@@ -472,8 +477,22 @@ __global__ void __launch_bounds__(256) k_extract_view_rgb_peers(const float4 *__
 // LDGMC.ADD: the NVSwitch adds the ranks' copies) and broadcasts the sums with multimem.st.  Each byte crosses a GPU's
 // links once in each direction.  Callers barrier across ranks before (inputs written) and after (outputs complete).
 __global__ void __launch_bounds__(256) k_allreduce_multimem(float *mc, long long n4_begin, long long n4_end) {
+  // few CTAs, four independent 16-byte reductions in flight per thread: the kernel shares the GPU with the HBM-bound SH
+  // rebuild, so it should hold the links busy without occupying every SM
   const long long stride = (long long)gridDim.x * 256;
-  for (long long q = n4_begin + (long long)blockIdx.x * 256 + threadIdx.x; q < n4_end; q += stride) {
+  long long q = n4_begin + (long long)blockIdx.x * 256 + threadIdx.x;
+  for (; q + 3 * stride < n4_end; q += 4 * stride) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(v[u].x), "=f"(v[u].y), "=f"(v[u].z), "=f"(v[u].w)
+                   : "l"(mc + 4 * (q + u * stride))
+                   : "memory");
+#pragma unroll
+    for (int u = 0; u < 4; ++u) multimem_st_v4(mc + 4 * (q + u * stride), v[u]);
+  }
+  for (; q < n4_end; q += stride) {
     float4 v;
     asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
                  : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
@@ -617,15 +636,15 @@ int extract_view_rgb_launch(const float4 *gacc, const int *touched, int N, float
   return GSX_OK;
 }
 
-int extract_view_rgb_peers_launch(const float4 *gacc, const int *touched, int N, float *mc, float *const *peers, int n_peers,
-                                  cudaStream_t st) {
+int extract_view_rgb_peers_launch(const float4 *gacc, const int *touched, const float *src_dense, int N, float *mc,
+                                  float *const *peers, int n_peers, cudaStream_t st) {
   if (N <= 0) return GSX_OK;
   if (!mc && (n_peers < 1 || n_peers > 8)) { set_error("n_peers %d out of range 1..8", n_peers); return GSX_E_ARG; }
   PeerPtrs pp;
   pp.n = mc ? 0 : n_peers;
   for (int r = 0; r < 8; ++r) pp.p[r] = (!mc && r < n_peers) ? peers[r] : nullptr;
   const long long groups = (3LL * N + 3 + 3) / 4;   // + up to 3 floats of head misalignment
-  k_extract_view_rgb_peers<<<ceil_div(groups, 256), 256, 0, st>>>(gacc, touched, N, mc, pp);
+  k_extract_view_rgb_peers<<<ceil_div(groups, 256), 256, 0, st>>>(gacc, touched, src_dense, N, mc, pp);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -636,7 +655,7 @@ int allreduce_multimem_launch(float *mc, size_t n_floats, int rank, int world, c
   const long long per = (n4 + world - 1) / world;
   const long long b = std::min<long long>(n4, per * rank), e = std::min<long long>(n4, per * (rank + 1));
   if (e <= b) return GSX_OK;
-  const int blocks = (int)std::min<long long>(kNumSMs * 4, (e - b + 255) / 256);
+  const int blocks = (int)std::min<long long>(48, (e - b + 255) / 256);
   k_allreduce_multimem<<<blocks, 256, 0, st>>>(mc, b, e);
   GSX_LAUNCH_CHECK();
   return GSX_OK;

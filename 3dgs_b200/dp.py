@@ -150,6 +150,14 @@ class ViewParallel:
         else:
             self.ex = None
         self.timing = None          # set to {} to collect per-phase CUDA-event times (ms) of the next step()
+        import os
+        # symmetric transport: fuse the peer stores into the extraction kernel (1) or push from a side stream (0)
+        self.fused_extract = os.environ.get("GSX_DP_FUSED", "1") == "1"
+        # GSX_DP_GATHER=nccl: NCCL all-gather on the side stream + in-switch allreduce kernel (hybrid)
+        # (measured on 8 B200: with 8 ranks storing at once the fused stores back-pressure the views phase by 0.75 ms, while
+        # an NCCL all-gather on the side stream hides under the per-Gaussian backward: 1688 vs 1614 views/s; with <= 4
+        # ranks the fused stores overlap the next views' compositing and win)
+        self.nccl_gather = os.environ.get("GSX_DP_GATHER", "nccl" if world >= 8 else "fused") == "nccl"
 
     def _mark(self, name, stream):
         if self.timing is not None:
@@ -225,11 +233,40 @@ class ViewParallel:
             r.batch_backward_view(k, gi)
             mc, peers = ex.view_targets(k)
             arr = (C.c_void_p * max(len(peers), 1))(*peers) if peers else None
-            check(lib().gsx_batch_extract_view_rgb_grad_peers(r.h, int(k), C.c_void_p(mc), arr, len(peers), st))
+            if self.nccl_gather:
+                r.batch_extract_view_rgb_grad(k, ex.local_drgb(k))
+            elif self.fused_extract:
+                # extraction + all-gather in ONE kernel: rows go from the packed gradients straight to every rank
+                check(lib().gsx_batch_extract_view_rgb_grad_peers(r.h, int(k), C.c_void_p(mc), arr, len(peers), st))
+            else:
+                # local extraction on the main stream, peer stores on the side stream: with many ranks pushing at once the
+                # stores back-pressure (every rank receives (g-1) x 72 MB) and must not hold up the per-Gaussian backward
+                r.batch_extract_view_rgb_grad(k, ex.local_drgb(k))
+                self.ev_views.record(main)
+                with torch.cuda.stream(self.comm):
+                    self.comm.wait_event(self.ev_views)
+                    if k == 0:
+                        self._mark("g0", self.comm)
+                    check(lib().gsx_push_view_rgb_peers(C.c_void_p(ex.local_drgb(k).data_ptr()), int(ex.N), C.c_void_p(mc), arr,
+                                                        len(peers), C.c_void_p(self.comm.cuda_stream)))
         self._mark("views", main)
-        self._mark("g0", main); self._mark("g1", main)      # the gather has no phase of its own any more
+        if self.nccl_gather:
+            self.ev_views.record(main)
+            with torch.cuda.stream(self.comm):
+                self.comm.wait_event(self.ev_views)
+                self._mark("g0", self.comm)
+                ex.all_gather_drgb()
+                self._mark("g1", self.comm)
+                self.ev_gathered.record(self.comm)
+        elif self.fused_extract:
+            self._mark("g0", main); self._mark("g1", main)  # the gather has no phase of its own
+        else:
+            self._mark("g1", self.comm)
+            self.ev_gathered.record(self.comm)
         r.batch_backward_params(g, OVER | NO_SH)            # geometry gradients -> this rank's part of the symmetric buffer
         self._mark("bwd", main)
+        if self.nccl_gather or not self.fused_extract:
+            main.wait_event(self.ev_gathered)
         ex.barrier(1)                                       # all d rgb stores and all geometry gradients have landed
         self.ev_geom.record(main)
         with torch.cuda.stream(self.comm):                  # allreduce overlaps the SH rebuild

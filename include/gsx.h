@@ -221,6 +221,10 @@ int gsx_batch_extract_view_rgb_grad(gsx_ctx_t *ctx, int slot, float *drgb, void 
  * [N][3] block inside a symmetric allocation (cuMem/NVLS mapping owned by the caller, e.g. torch symmetric memory). */
 int gsx_batch_extract_view_rgb_grad_peers(gsx_ctx_t *ctx, int slot, float *multicast_drgb, float *const *peer_drgb_host,
                                           int n_peers, void *stream);
+/* Same transfer for a dense [N][3] block that was already extracted locally (gsx_batch_extract_view_rgb_grad): lets the
+ * caller run the push on a side stream so the per-Gaussian backward is not queued behind NVLink back-pressure. */
+int gsx_push_view_rgb_peers(const float *drgb_local, int N, float *multicast_drgb, float *const *peer_drgb_host,
+                            int n_peers, void *stream);
 /* In-switch (NVLS) sum-allreduce of n_floats (multiple of 4, 16-byte aligned) floats of a symmetric buffer through its
  * multicast address: rank r reduces slice r with multimem.ld_reduce and broadcasts it with multimem.st.  The caller
  * barriers across the ranks before and after. */

@@ -38,7 +38,8 @@ def main():
     want = {k: t.clone() for k, t in gd0.grads.items()}
     r0.close()
     report = []
-    for symmetric in (False, True):
+    for symmetric, fused in ((False, "1"), (True, "1"), (True, "0")):
+        os.environ["GSX_DP_FUSED"] = fused
         gd = mk()
         gd.zero_grads()
         r = H.Rasterizer(N, W, Hh, instance_capacity=8 * N)
@@ -54,7 +55,7 @@ def main():
             rel = float((a - b).norm() / (b.norm() + 1e-30))
             worst = max(worst, rel)
             assert rel <= 1e-3, f"transport {vp.ex.transport}: d {k} rel err {rel}"
-        report.append(f"{vp.ex.transport}:{worst:.1e}" + (f"(no symm: {vp.ex.why_not})" if symmetric and vp.ex.transport == "nccl" else ""))
+        report.append(f"{vp.ex.transport}{"" if not symmetric else ("-fused" if vp.fused_extract else "-push")}:{worst:.1e}" + (f"(no symm: {vp.ex.why_not})" if symmetric and vp.ex.transport == "nccl" else ""))
         r.close()
     if rank == 0:
         print("DP_OK world=%d %s" % (world, " ".join(report)), flush=True)
