@@ -95,6 +95,11 @@ struct gsx_ctx {
   // 6 compositing forward; 7,8 compositing backward; 9,10 per-Gaussian backward
   bool timing = false;
   cudaEvent_t ev[11] = {};
+  // host pipeline of gsx_batch_render_host: the gradient images of a batch are uploaded on their own stream while the
+  // per-Gaussian forward runs, rendered images are downloaded on a third stream under the following backward
+  cudaStream_t cs_in = nullptr, cs_out = nullptr;
+  cudaEvent_t ev_in[GSX_MAX_BATCH] = {}, ev_img = nullptr, ev_out = nullptr, ev_go = nullptr;
+  float *grad_stage[GSX_MAX_BATCH] = {};
 };
 
 namespace gsx {
@@ -217,6 +222,15 @@ int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (!c) return GSX_OK;
   for (int k = 0; k < GSX_MAX_BATCH; ++k) free_slot(c->slot[k]);
   cudaFree(c->bin_ws); if (c->key64) cudaFree(c->key64); cudaFree(c->ranges); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
+  for (int k = 0; k < GSX_MAX_BATCH; ++k) {
+    if (c->grad_stage[k]) cudaFree(c->grad_stage[k]);
+    if (c->ev_in[k]) cudaEventDestroy(c->ev_in[k]);
+  }
+  if (c->ev_img) cudaEventDestroy(c->ev_img);
+  if (c->ev_out) cudaEventDestroy(c->ev_out);
+  if (c->ev_go) cudaEventDestroy(c->ev_go);
+  if (c->cs_in) cudaStreamDestroy(c->cs_in);
+  if (c->cs_out) cudaStreamDestroy(c->cs_out);
   cudaFree(c->grad_image); cudaFree(c->d_P); cudaFree(c->d_ccount); cudaFreeHost(c->h_stats);
   delete c;
   return GSX_OK;
@@ -375,24 +389,64 @@ int gsx_sh_grads_from_view_rgb(const float *xyz_w, int N, int l_max, const float
 
 // Host-buffer batch step: per view H2D of the loss-gradient image and D2H of the rendered image (pinned host memory),
 // forward + backward of every view, one pass of parameter gradients.  Synchronises.
+static int ensure_host_pipeline(gsx_ctx_t *c, int n_views) {
+  if (!c->cs_in) {
+    GSX_CUDA(cudaStreamCreateWithFlags(&c->cs_in, cudaStreamNonBlocking));
+    GSX_CUDA(cudaStreamCreateWithFlags(&c->cs_out, cudaStreamNonBlocking));
+    GSX_CUDA(cudaEventCreateWithFlags(&c->ev_img, cudaEventDisableTiming));
+    GSX_CUDA(cudaEventCreateWithFlags(&c->ev_out, cudaEventDisableTiming));
+    GSX_CUDA(cudaEventCreateWithFlags(&c->ev_go, cudaEventDisableTiming));
+  }
+  const size_t bytes = (size_t)c->max_w * c->max_h * 3 * sizeof(float);
+  for (int k = 0; k < n_views; ++k) {
+    if (!c->ev_in[k]) GSX_CUDA(cudaEventCreateWithFlags(&c->ev_in[k], cudaEventDisableTiming));
+    if (!c->grad_stage[k]) GSX_CUDA(cudaMalloc(&c->grad_stage[k], bytes));
+  }
+  return GSX_OK;
+}
+
+// Whole batch from host buffers (pinned for the copies to overlap).  Three streams: uploads of the n gradient images
+// start at once and hide under the per-Gaussian forward, view k's image goes back to the host while its backward runs;
+// the compute stream waits only for the upload it is about to read and for the image buffer it is about to overwrite.
 int gsx_batch_render_host(gsx_ctx_t *c, const gsx_view_t *views, int n_views, const gsx_params_t *p, int N,
                           const float *const *grad_images_host, float *const *images_host, const gsx_grads_t *g, int flags,
                           void *stream) {
   if (!c || !views || !p || !g || !grad_images_host) { set_error("null argument"); return GSX_E_NULL; }
+  if (n_views < 1 || n_views > GSX_MAX_BATCH) { set_error("n_views out of range"); return GSX_E_ARG; }
   cudaStream_t st = (cudaStream_t)stream;
-  int rc = gsx_batch_forward_params(c, views, n_views, p, N, stream);
+  int rc = ensure_host_pipeline(c, n_views);
   if (rc != GSX_OK) return rc;
+  GSX_CUDA(cudaEventRecord(c->ev_go, st));            // the staging buffers may still be read by work queued on st
+  GSX_CUDA(cudaStreamWaitEvent(c->cs_in, c->ev_go, 0));
   for (int k = 0; k < n_views; ++k) {
+    if (views[k].width > c->max_w || views[k].height > c->max_h) { set_error("view larger than the context"); return GSX_E_ARG; }
+    if (!grad_images_host[k]) { set_error("null gradient image"); return GSX_E_NULL; }
     const size_t bytes = (size_t)views[k].width * views[k].height * 3 * sizeof(float);
-    GSX_CUDA(cudaMemcpyAsync(c->grad_image, grad_images_host[k], bytes, cudaMemcpyHostToDevice, st));
-    rc = gsx_batch_forward_view(c, k, stream);
-    if (rc != GSX_OK) return rc;
-    if (images_host && images_host[k]) GSX_CUDA(cudaMemcpyAsync(images_host[k], c->image, bytes, cudaMemcpyDeviceToHost, st));
-    rc = gsx_batch_backward_view(c, k, c->grad_image, stream);
-    if (rc != GSX_OK) return rc;
+    GSX_CUDA(cudaMemcpyAsync(c->grad_stage[k], grad_images_host[k], bytes, cudaMemcpyHostToDevice, c->cs_in));
+    GSX_CUDA(cudaEventRecord(c->ev_in[k], c->cs_in));
   }
-  rc = gsx_batch_backward_params(c, p, N, g, flags, stream);
-  if (rc != GSX_OK) return rc;
+  rc = gsx_batch_forward_params(c, views, n_views, p, N, stream);
+  bool downloading = false;
+  for (int k = 0; k < n_views && rc == GSX_OK; ++k) {
+    const size_t bytes = (size_t)views[k].width * views[k].height * 3 * sizeof(float);
+    if (downloading) GSX_CUDA(cudaStreamWaitEvent(st, c->ev_out, 0));   // c->image is about to be overwritten
+    rc = gsx_batch_forward_view(c, k, stream);
+    if (rc != GSX_OK) break;
+    if (images_host && images_host[k]) {
+      GSX_CUDA(cudaEventRecord(c->ev_img, st));
+      GSX_CUDA(cudaStreamWaitEvent(c->cs_out, c->ev_img, 0));
+      GSX_CUDA(cudaMemcpyAsync(images_host[k], c->image, bytes, cudaMemcpyDeviceToHost, c->cs_out));
+      GSX_CUDA(cudaEventRecord(c->ev_out, c->cs_out));
+      downloading = true;
+    }
+    GSX_CUDA(cudaStreamWaitEvent(st, c->ev_in[k], 0));
+    rc = gsx_batch_backward_view(c, k, c->grad_stage[k], stream);
+  }
+  if (rc == GSX_OK) rc = gsx_batch_backward_params(c, p, N, g, flags, stream);
+  // never return with copies in flight, error or not
+  cudaStreamSynchronize(c->cs_in);
+  cudaStreamSynchronize(c->cs_out);
+  if (rc != GSX_OK) { cudaStreamSynchronize(st); return rc; }
   GSX_CUDA(cudaStreamSynchronize(st));
   return GSX_OK;
 }

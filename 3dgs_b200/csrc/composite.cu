@@ -213,31 +213,30 @@ k_composite_bwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
         const float alpha = fminf(0.99f, q1.w * gg);
         const bool valid = inside && (alpha >= ALPHA_MIN) && (idx < count);
         if (!__any_sync(0xffffffffu, valid)) continue;
+        // Branch-free body: a lane that does not take the entry runs it with alpha = 0 and g = 0, which leaves its
+        // pixel state untouched and contributes exact zeros.  Per lane only the moments of dL/dpower are formed
+        // (gp, gp dx, gp dy, gp dx^2, gp dx dy, gp dy^2); the per-entry linear combinations that turn them into the
+        // uv / conic / opacity gradients (render_backward.cu:154-166) are applied once per entry at the flush.
+        const float4 q2 = s_r2[e];
+        const float al = valid ? alpha : 0.0f;
+        const float gm = valid ? gg : 0.0f;
+        const float om = 1.0f - al;
+        const float inv_om = rcp_fast(om);   // render_backward.cu:132 divides; 1 - alpha >= 0.01
+        T = valid ? T * inv_om : T;
+        const float w = al * T;
+        float ga = 0.0f;
+        ga += (q2.x - ar) * gx; ga += (q2.y - ag) * gy; ga += (q2.z - ab) * gz;
+        ga *= T;
+        ga += (-Tf * inv_om) * bgdot;
+        ar = al * q2.x + om * ar; ag = al * q2.y + om * ag; ab = al * q2.z + om * ab;
+        const float gp = gm * (ga * q1.w);   // d L / d power
+        const float gpx = gp * dx, gpy = gp * dy;
         float v[8];
-        float vo = 0.0f;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) v[k] = 0.0f;
-        if (valid) {
-          const float4 q2 = s_r2[e];
-          const float om = 1.0f - alpha;
-          const float inv_om = rcp_fast(om);   // render_backward.cu:132 divides; 1 - alpha >= 0.01
-          T *= inv_om;
-          const float w = alpha * T;
-          v[0] = w * gx; v[1] = w * gy; v[2] = w * gz;
-          float ga = 0.0f;
-          ga += (q2.x - ar) * gx; ga += (q2.y - ag) * gy; ga += (q2.z - ab) * gz;
-          ga *= T;
-          ga += (-Tf * inv_om) * bgdot;
-          vo = gg * ga * q2.w;                       // g * grad_alpha * opa * (1 - opa)
-          ar = alpha * q2.x + om * ar; ag = alpha * q2.y + om * ag; ab = alpha * q2.z + om * ab;
-          const float gp = gg * (ga * q1.w);         // d L / d power
-          v[3] = (-q1.x * dx - q1.y * dy) * gp * half_w;   // Q5: NDC-scaled
-          v[4] = (-q1.z * dy - q1.y * dx) * gp * half_h;
-          v[5] = gp * (-0.5f * dx * dx);
-          v[6] = gp * (-dx * dy);
-          v[7] = gp * (-0.5f * dy * dy);
-        }
-        // transposing butterfly: 8 values over 32 lanes in 9 shuffles
+        v[0] = w * gx; v[1] = w * gy; v[2] = w * gz;
+        v[3] = gpx; v[4] = gpy; v[5] = gpx * dx; v[6] = gpx * dy; v[7] = gpy * dy;
+        float vo = gp;
+        // transposing butterfly: 9 values over 32 lanes in 12 shuffles (the ninth rides along for three steps and
+        // then shares the last two shuffles with the other eight)
         float a4[4], a2[2], a1;
         {
           const bool up = lane & 16;
@@ -246,6 +245,7 @@ k_composite_bwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
             const float send = up ? v[k] : v[k + 4], keep = up ? v[k + 4] : v[k];
             a4[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
           }
+          vo += __shfl_xor_sync(0xffffffffu, vo, 16);
         }
         {
           const bool up = lane & 8;
@@ -254,31 +254,42 @@ k_composite_bwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
             const float send = up ? a4[k] : a4[k + 2], keep = up ? a4[k + 2] : a4[k];
             a2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
           }
+          vo += __shfl_xor_sync(0xffffffffu, vo, 8);
         }
         {
           const bool up = lane & 4;
           const float send = up ? a2[0] : a2[1], keep = up ? a2[1] : a2[0];
           a1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+          vo += __shfl_xor_sync(0xffffffffu, vo, 4);
         }
-        a1 += __shfl_xor_sync(0xffffffffu, a1, 2);
+        {
+          const bool up = lane & 2;   // lanes with bit 1 set carry the ninth value from here on
+          const float send = up ? a1 : vo, keep = up ? vo : a1;
+          a1 = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+        }
         a1 += __shfl_xor_sync(0xffffffffu, a1, 1);
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) vo += __shfl_xor_sync(0xffffffffu, vo, off);
-        // lane with (lane&3)==0 holds value k = 4*b4 + 2*b3 + b2 ; lane 1 publishes the opacity sum
-        const int k = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
-        if ((lane & 3) == 0) atomicAdd(&s_acc[e * 9 + k], a1);
-        else if (lane == 1) atomicAdd(&s_acc[e * 9 + 8], vo);
+        // lane with (lane&3)==0 holds value k = 4*b4 + 2*b3 + b2 ; lane 2 publishes the ninth
+        const int k = (lane == 2) ? 8 : ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+        if ((lane & 3) == 0 || lane == 2) atomicAdd(&s_acc[e * 9 + k], a1);
       }
     }
     __syncthreads();
     if (tid < nb) {
-      float a[9];
+      float m[9];
       bool any = false;
 #pragma unroll
-      for (int k = 0; k < 9; ++k) { a[k] = s_acc[tid * 9 + k]; any |= (a[k] != 0.0f); }
+      for (int k = 0; k < 9; ++k) { m[k] = s_acc[tid * 9 + k]; any |= (m[k] != 0.0f); }
       // Q7 (render_backward.cu:170): the reference drops the whole entry when every lane's opacity partial is
       // exactly zero -- which is what happens when opa*(1-opa) underflows to 0.
-      if (any && s_r2[tid].w != 0.0f) {
+      const float4 q1 = s_r1[tid];
+      const float w2 = s_r2[tid].w;
+      if (any && w2 != 0.0f) {
+        float a[9];
+        a[0] = m[0]; a[1] = m[1]; a[2] = m[2];
+        a[3] = (-q1.x * m[3] - q1.y * m[4]) * half_w;   // Q5: NDC-scaled
+        a[4] = (-q1.z * m[4] - q1.y * m[3]) * half_h;
+        a[5] = -0.5f * m[5]; a[6] = -m[6]; a[7] = -0.5f * m[7];
+        a[8] = m[8] * (w2 / q1.w);                      // sum of g * grad_alpha * opa * (1 - opa)
         const int g = s_ids[tid];
         if (PACKED) {
           float *o = dst.packed + (size_t)g * 12;
