@@ -41,7 +41,7 @@ BinLayout bin_layout(int N, long long capacity);
 int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
                   const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
                   const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
-                  uint32_t *ckey, uint32_t *cid, const int *ccount);
+                  uint32_t *ckey, uint32_t *cid, const int *ccount, int tight);
 int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, cudaStream_t st);
 int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, const gsx_grads_t &g, int flags,
                      cudaStream_t st);
@@ -166,7 +166,7 @@ static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[2], st));
   int rc = bin_sort_impl((const float *)s.p.r0, 4, s.p.depth, 1, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, c->bin_ws,
                          c->L, c->ranges, &c->sorted_tiles, &c->sorted_vals, st, c->timing ? &c->ev[3] : nullptr, s.p.ckey, s.p.cid,
-                         s.p.ccount);
+                         s.p.ccount, (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0);
   if (rc != GSX_OK) return rc;
   rc = composite_fwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, v.width, v.height, v.background,
                             c->spp, c->wpp, c->image, st);

@@ -61,7 +61,7 @@ __device__ __forceinline__ void stage_rows(float *s_dst, const float *sh, int sh
   }
 }
 
-constexpr int VCW = sizeof(ViewConst) / 4;   // words per view (42: consecutive views fall on distinct banks)
+constexpr int VCW = sizeof(ViewConst) / 4;   // words per view (43: consecutive views fall on distinct banks)
 static_assert(sizeof(ViewConst) % 4 == 0, "ViewConst is word-sized");
 // (view, local Gaussian) slots of a block: BB * nv, sized at launch (a single view needs 1/8 of the 8-view staging,
 // which lifts the backward kernel from 3 to 4+ CTAs per SM)
@@ -170,6 +170,7 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       if (w.x1 > w.x0 && w.y1 > w.y0) {
         so = obb_sat_setup(compute_obb(uv.x, uv.y, rad.x, rad.y, rad.z, rad.w));
         tr = sat_aabb_range(so, w);
+        if (vc.tight) clip_range_to_extent(tr, uv.x, uv.y, ext.x, ext.y);
       }
       const float3 rgb = sh_to_rgb<L>(px, py, pz, vc.campos, b0, L > 0 ? s_sh + g * SHF : nullptr);
       sp.r0[gi] = make_float4(uv.x, uv.y, ext.x, ext.y);

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
                                                  const int *__restrict__ touched, const int *__restrict__ offsets,
                                                  int ntx, int nty, int N_host, const int *__restrict__ n_dev,
                                                  long long capacity, uint32_t *__restrict__ tiles,
-                                                 uint32_t *__restrict__ vals) {
+                                                 uint32_t *__restrict__ vals, int tight) {
   const int j = blockIdx.x * kBlock + threadIdx.x;
   const int lane = threadIdx.x & 31;
   const int N = n_dev ? min(*n_dev, N_host) : N_host;
@@ -107,6 +107,8 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
     const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
     s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
     tr = sat_aabb_range(s, w);
+    // contributing-only lists (view-level path, uv_stride 4: the record is {u, v, extent_x, extent_y})
+    if (tight) clip_range_to_extent(tr, u, v, uv[(size_t)i * uv_stride + 2], uv[(size_t)i * uv_stride + 3]);
   }
   const bool big = live && rect_cells(tr) > COOP_CELLS;
   if (live && !big) {
@@ -302,7 +304,7 @@ BinLayout bin_layout(int N, long long capacity) {
 int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
                   const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
                   const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
-                  uint32_t *ckey, uint32_t *cid, const int *ccount) {
+                  uint32_t *ckey, uint32_t *cid, const int *ccount, int tight) {
   // ev (optional): 3 events recorded after emission, after the tile sort and after the ranges (stage timing)
   // ckey/cid/ccount (optional, view-level path): depth keys + ids of the Gaussians that touch a tile, already compacted by
   // the per-Gaussian kernel (unordered; *ccount entries) -- the depth sort, scan and emission then run over P' not N
@@ -334,7 +336,7 @@ int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_
   if (rc != GSX_OK) return rc;
   if (N > 0) {
     k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, dkeys, perm, touched, offsets, ntx, nty, N, ccount, capacity,
-                                                   ka, va);
+                                                   ka, va, (tight && uv_stride == 4) ? 1 : 0);
     GSX_LAUNCH_CHECK();
   }
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
@@ -444,7 +446,7 @@ int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const floa
   const uint32_t *sk;
   const uint32_t *sv;
   rc = bin_sort_impl(uv, 2, xyz_c + 2, 3, (const float4 *)radius, (const int *)(ws + L.touched), n_tiles_x, n_tiles_y, N,
-                     capacity, ws, L, ranges, &sk, &sv, st, nullptr, nullptr, nullptr, nullptr);
+                     capacity, ws, L, ranges, &sk, &sv, st, nullptr, nullptr, nullptr, nullptr, 0);
   if (rc != GSX_OK) return rc;
   rc = copy_ids_launch(sv, sorted_gaussians, capacity, (const int *)(ws + L.total), st);
   if (rc != GSX_OK) return rc;

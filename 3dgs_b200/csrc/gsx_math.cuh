@@ -287,6 +287,20 @@ __device__ __forceinline__ TileRange sat_aabb_range(const ObbSat &s, const TileW
   r.y1 = (int)fmaxf(fminf(floorf(s.max_y * 0.0625f), fy1), fy0 - 1.0f);
   return r;
 }
+// GSX_LISTS_CONTRIBUTING: keep only the tile columns / rows the half-extents (ex, ey) of {alpha >= 1/255} around (u, v)
+// can reach.  Compositing rejects an entry for a sub-tile [X0, X0+7] when u + ex < X0 or u - ex > X0 + 7
+// (composite.cu); over the sub-tiles of tile column tx that leaves 16 tx <= u + ex and u - ex <= 16 tx + 15, and
+// floor((u - ex)/16) <= tx is a superset of the latter -- so no (tile, entry) with a contributing pixel is dropped.
+// NaN constrains nothing, +inf extents (conic not positive definite) keep everything, -inf extents (opacity below
+// the threshold) leave an empty range.  The count (batch.cu) and the emission (binning.cu) both call this on the same
+// stored floats, so the scanned offsets match the emitted instances.
+__device__ __forceinline__ void clip_range_to_extent(TileRange &r, float u, float v, float ex, float ey) {
+  const float big = 1.0e6f;
+  r.x0 = max(r.x0, (int)fminf(fmaxf(floorf((u - ex) * 0.0625f), -big), big));
+  r.x1 = min(r.x1, (int)fmaxf(fminf(floorf((u + ex) * 0.0625f), big), -big));
+  r.y0 = max(r.y0, (int)fminf(fmaxf(floorf((v - ey) * 0.0625f), -big), big));
+  r.y1 = min(r.y1, (int)fmaxf(fminf(floorf((v + ey) * 0.0625f), big), -big));
+}
 // axes 2 and 3 only (axes 0/1 already decided by sat_aabb_range)
 __device__ __forceinline__ bool sat_tile_rot(const ObbSat &s, int tx, int ty) {
   const float l = (float)tx * 16.0f, r = (float)(tx + 1) * 16.0f, t = (float)ty * 16.0f, b = (float)(ty + 1) * 16.0f;

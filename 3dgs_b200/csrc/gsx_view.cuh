@@ -14,6 +14,7 @@ struct ViewConst {
   float near_thresh;
   int padding;
   float mh_dist;
+  int tight;        // GSX_LISTS_CONTRIBUTING: clip each Gaussian's tile rectangle to its alpha >= 1/255 extent
 };
 
 static inline ViewConst make_view_const(const gsx_view_t &v) {
@@ -25,6 +26,7 @@ static inline ViewConst make_view_const(const gsx_view_t &v) {
   c.width = v.width; c.height = v.height;
   c.ntx = (v.width + 15) / 16; c.nty = (v.height + 15) / 16;
   c.near_thresh = v.near_thresh; c.padding = v.cull_padding; c.mh_dist = v.mh_dist;
+  c.tight = (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0;
   return c;
 }
 

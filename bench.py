@@ -193,7 +193,10 @@ def main():
     mk = lambda cam, flags: Hh.make_view(cam["view"], cam["proj"], cam["campos"], cam["fx"], cam["fy"], W, H,
                                          near_thresh=S.NEAR_THRESH, cull_padding=S.CULL_PADDING, mh_dist=S.MH_DIST,
                                          background=0.0, l_max=l_max, flags=flags)
-    vstructs = [mk(cams[k], 0) for k in my_views]
+    # GSX_LISTS=contributing: per-tile lists clipped to the alpha >= 1/255 footprint (gsx.h GSX_LISTS_CONTRIBUTING);
+    # default = the reference's lists
+    VF = 8 if os.environ.get("GSX_LISTS", "reference") == "contributing" else 0
+    vstructs = [mk(cams[k], VF) for k in my_views]
     nv = len(vstructs)
     r = Hh.Rasterizer(N, W, H, instance_capacity=4 * N)
     r.batch_reserve(nv)
@@ -209,7 +212,7 @@ def main():
 
     # One step = the rank's views of the batch through the batch path (parameters read once per direction, gradients
     # of the rank's views summed in one pass with '=' semantics: no 1.4 GB memset) + the gradient allreduce.
-    all_views = [mk(c, 0) for c in cams]
+    all_views = [mk(c, VF) for c in cams]
     # GSX_DP_TRANSPORT=nccl forces the NCCL transport (default: symmetric memory -- multimem / p2p -- when available)
     vp = gs.dp.ViewParallel(r, gd, all_views, [c["campos"] for c in cams], l_max, world, rank,
                             symmetric=os.environ.get("GSX_DP_TRANSPORT", "auto") != "nccl")
@@ -362,7 +365,8 @@ def main():
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "ms_per_view_per_gpu": ms_total / args.steps / len(my_views),
         "config": {"workload": f"{args.config}: synthetic {N} Gaussians, SH deg {l_max}, {W}x{H}, batch of {N_VIEWS} views "
-                               f"sharded over {world} GPU(s); exchange per step: {xbytes}",
+                               f"sharded over {world} GPU(s); per-tile lists: {'contributing-only (GSX_LISTS_CONTRIBUTING)' if VF else 'reference-identical'}; "
+                               f"exchange per step: {xbytes}",
                    "views_per_step": N_VIEWS, "l2": "inputs larger than L2 (1.4 GB parameters + 1.4 GB gradients per view)",
                    "visible_P": int(P), "touching_P": int(Pt), "instances_K": int(K), "pixel_entries_S": int(Sx), "contributing_Splus": int(Sp)},
         "clocks": clocks,

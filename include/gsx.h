@@ -37,6 +37,12 @@ extern "C" {
 #define GSX_GRAD_OVERWRITE 2  /* gsx_backward: overwrite parameter gradients instead of accumulating */
 #define GSX_GRAD_NO_SH 4      /* gsx_batch_backward_params: leave the band-0 / SH coefficient gradients out (they are
                                  rebuilt from the gathered per-view colour gradients, gsx_sh_grads_from_view_rgb) */
+#define GSX_LISTS_CONTRIBUTING 8 /* gsx_view.flags, view-level path only: per-tile lists keep only the instances whose
+                                 {alpha >= 1/255} footprint reaches the tile (the reference's 3-sigma OBB test keeps ~3x
+                                 more).  Image and gradients are unchanged -- the dropped instances are exactly those
+                                 compositing rejects for every pixel of the tile -- but sorted list, ranges and
+                                 splats_per_pixel are then a filtered version of the reference's.  Default 0 =
+                                 reference-identical lists. */
 #define GSX_MAX_VIEWS_TOTAL 64 /* views of a whole (multi-GPU) batch accepted by gsx_sh_grads_from_view_rgb */
 
 int gsx_version(void);
@@ -135,7 +141,7 @@ typedef struct gsx_view {
   float mh_dist;         /* config mh_dist */
   float background;      /* scalar grey background (Q4) */
   int l_max;             /* 0..3 */
-  int flags;             /* GSX_SH_DSPH_CORRECT | GSX_GRAD_OVERWRITE */
+  int flags;             /* GSX_SH_DSPH_CORRECT | GSX_GRAD_OVERWRITE | GSX_LISTS_CONTRIBUTING */
 } gsx_view_t;
 
 typedef struct gsx_params {   /* GaussianParameters, cuda_data.cuh:11-24 */

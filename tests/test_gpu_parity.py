@@ -583,3 +583,53 @@ def test_full_size_properties_c2(B):
         assert float((a - b).norm()) <= 1e-3 * float(b.norm()) + 1e-12, k
     assert all(bool(torch.isfinite(t).all()) for t in gd.grads.values())
     r.close()
+
+
+@pytest.mark.parametrize("l_max", [3, 0])
+def test_contributing_lists_same_image_and_gradients(B, l_max):
+    """GSX_LISTS_CONTRIBUTING (view flag 8): per-tile lists clipped to each Gaussian's alpha >= 1/255 footprint.  The
+    image must be BIT-identical to the reference-identical lists' (the same entries contribute, in the same order), the
+    gradients equal up to the atomics' summation order, every per-tile list a subsequence of the exact one, and no
+    pixel may have consumed an entry that the exact path did not."""
+    import torch
+    W, H, N = 224, 160, 12000
+    az = [10.0, 130.0, 250.0]
+    cams = [S.orbit_camera(W, H, azimuth_deg=a) for a in az]
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=45)
+    Hh = gs.host
+    gis_d = [torch.as_tensor(S.grad_image(W, H, seed=80 + k) * 1e3).cuda() for k in range(len(az))]
+    bgs = [0.0, 0.4, 1.0]
+    res = {}
+    for tight in (0, 8):
+        gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+        views = [util.gsx_view(c, l_max, bg, tight) for c, bg in zip(cams, bgs)]
+        r = Hh.Rasterizer(N, W, H, instance_capacity=8 * N)
+        r.batch_reserve(len(views))
+        states = []
+        r.batch_step(views, gd, gis_d, flags=2,
+                     on_image=lambda k: states.append({kk: (t.cpu().numpy().copy() if hasattr(t, "cpu") else t)
+                                                       for kk, t in r.state().items()}))
+        torch.cuda.synchronize()
+        res[tight] = (states, {k: t.cpu().numpy().copy() for k, t in gd.grads.items()})
+        r.close()
+    (se, ge), (st, gt) = res[0], res[8]
+    kept = 0
+    for k, (a, b) in enumerate(zip(st, se)):
+        assert 0 < a["K"] < b["K"], (a["K"], b["K"])
+        kept += a["K"]
+        np.testing.assert_array_equal(a["image"], b["image"], err_msg=f"view {k}: image not bit-identical")
+        assert (a["splats_per_pixel"] <= b["splats_per_pixel"]).all()
+        ra, rb = a["ranges"], b["ranges"]
+        la, lb = a["sorted_gaussians"], b["sorted_gaussians"]
+        for t in range(len(ra) - 1):
+            xa, xb = la[ra[t]:ra[t + 1]], lb[rb[t]:rb[t + 1]]
+            pos = {int(v): i for i, v in enumerate(xb)}
+            idx = [pos[int(v)] for v in xa]          # KeyError = an instance the exact list does not have
+            assert all(i < j for i, j in zip(idx, idx[1:])), f"view {k} tile {t}: order changed"
+    nsh = ((l_max + 1) ** 2 - 1) * 3
+    for k in ge:
+        if k == "sh" and nsh == 0:
+            continue
+        a_, b_ = (gt[k][:, :nsh], ge[k][:, :nsh]) if k == "sh" else (gt[k], ge[k])
+        util.assert_grad_close(a_, b_, f"d {k}: contributing-only vs exact lists", outlier=2e-3)
+    print("instances kept:", kept, "of", sum(b["K"] for b in se))
