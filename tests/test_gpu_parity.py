@@ -633,3 +633,52 @@ def test_contributing_lists_same_image_and_gradients(B, l_max):
         a_, b_ = (gt[k][:, :nsh], ge[k][:, :nsh]) if k == "sh" else (gt[k], ge[k])
         util.assert_grad_close(a_, b_, f"d {k}: contributing-only vs exact lists", outlier=2e-3)
     print("instances kept:", kept, "of", sum(b["K"] for b in se))
+
+
+@pytest.mark.parametrize("pinned", [True, False])
+def test_host_buffer_entry_points_match_device_path(B, pinned):
+    """gsx_batch_render_host (the call bench.py's e2e leg times: uploads / downloads pipelined on copy streams) and
+    gsx_render_view_host must return the images and gradients of the device-buffer path, twice in a row (the staging
+    buffers and events are re-used), with pinned and with pageable host memory."""
+    import torch
+    W, H, N, l_max = 224, 160, 12000, 3
+    az = [10.0, 130.0, 250.0, 300.0]
+    cams = [S.orbit_camera(W, H, azimuth_deg=a) for a in az]
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=46)
+    Hh = gs.host
+    gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+    views = [util.gsx_view(c, l_max, bg) for c, bg in zip(cams, [0.0, 0.4, 1.0, 0.2])]
+    mk = (lambda t: t.pin_memory()) if pinned else (lambda t: t)
+    gis_h = [mk(torch.as_tensor(S.grad_image(W, H, seed=90 + k) * 1e3)) for k in range(len(az))]
+    gis_d = [t.cuda() for t in gis_h]
+    r = Hh.Rasterizer(N, W, H, instance_capacity=8 * N)
+    r.batch_reserve(len(views))
+    want_img = []
+    r.batch_step(views, gd, gis_d, flags=2, on_image=lambda k: want_img.append(r.state_image().cpu().numpy().copy()))
+    torch.cuda.synchronize()
+    want = {k: t.cpu().numpy().copy() for k, t in gd.grads.items()}
+    for rep in range(2):
+        imgs_h = [mk(torch.full((H, W, 3), -1.0, dtype=torch.float32)) for _ in views]
+        for t in gd.grads.values():
+            t.fill_(55.0)
+        r.batch_render_host(views, gd, gis_h, imgs_h, flags=2)
+        got = {k: t.cpu().numpy().copy() for k, t in gd.grads.items()}
+        for k, (a, b) in enumerate(zip(imgs_h, want_img)):
+            np.testing.assert_array_equal(a.numpy(), b, err_msg=f"rep {rep} view {k}: host image")
+        for k in want:
+            util.assert_grad_close(got[k], want[k], f"rep {rep} d {k}: host-buffer batch vs device batch", outlier=2e-3)
+    # single-view host entry point: same image, gradients accumulate onto the batch's
+    img1 = mk(torch.empty((H, W, 3), dtype=torch.float32))
+    for t in gd.grads.values():
+        t.zero_()
+    r.render_view_host(views[1], gd, gis_h[1], img1)
+    np.testing.assert_array_equal(img1.numpy(), want_img[1])
+    g1 = {k: t.cpu().numpy().copy() for k, t in gd.grads.items()}
+    for t in gd.grads.values():
+        t.zero_()
+    r.forward(views[1], gd)
+    r.backward(views[1], gd, gis_d[1])
+    torch.cuda.synchronize()
+    for k in g1:
+        util.assert_grad_close(g1[k], gd.grads[k].cpu().numpy(), f"d {k}: render_view_host vs forward+backward", outlier=2e-3)
+    r.close()
