@@ -160,13 +160,29 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
   {
     unsigned excl = 0;
     if (tile != 0) {
+      // windowed: LB predecessors are fetched at once (independent loads in flight) and consumed nearest first up to
+      // the first one that is inclusive or not yet published -- with every tile of a small input resident in one wave
+      // the walk back is long, and one L2 round trip per hop was the latency of the whole pass
+      constexpr int LB = 8;
       long long t = (long long)tile - 1;
       while (true) {
-        const unsigned s = ld_volatile(status + (size_t)t * RADIX + tid);
-        if ((s & FLAG_MASK) == 0) continue;
-        excl += s & VAL_MASK;
-        if ((s & FLAG_MASK) == FLAG_INC) break;
-        --t;
+        unsigned s[LB];
+#pragma unroll
+        for (int w = 0; w < LB; ++w)
+          s[w] = (t - w >= 0) ? ld_volatile(status + (size_t)(t - w) * RADIX + tid) : FLAG_INC;   // before tile 0: nothing
+        int used = 0;
+        bool fin = false;
+#pragma unroll
+        for (int w = 0; w < LB; ++w) {
+          const unsigned f = s[w] & FLAG_MASK;
+          if (!fin && used == w && f != 0) {
+            excl += s[w] & VAL_MASK;
+            used = w + 1;
+            fin = (f == FLAG_INC);
+          }
+        }
+        if (fin) break;
+        t -= used;
       }
       st_volatile(my, FLAG_INC | (excl + total));
     }
