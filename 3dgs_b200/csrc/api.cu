@@ -38,10 +38,14 @@ int check_device_ptr(const void *p, const char *name) {
 
 // from binning.cu / composite.cu / batch.cu
 BinLayout bin_layout(int N, long long capacity);
-int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
-                  const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
-                  const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
-                  uint32_t *ckey, uint32_t *cid, const int *ccount, int tight);
+int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, int N, bool compact, const int *ccount,
+                    PreBin *pb, cudaStream_t st);
+int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, const int *touched, int ntx, int nty, int N,
+                       long long capacity, char *ws, const BinLayout &L, const PreBin &pb, int *ranges,
+                       const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
+                       int tight);
+size_t prebin_sort_ws_bytes(int N);
+size_t prebin_block_sums_count(int N);
 int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, cudaStream_t st);
 int batch_bwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, const gsx_grads_t &g, int flags,
                      cudaStream_t st);
@@ -68,6 +72,10 @@ struct gsx_slot {          // per-view state that must outlive the view inside a
   SlotPtrs p{};
   gsx_view_t view{};
   bool allocated = false;
+  // pre-binning (depth sort + scan) of the view: own buffers so that it can run ahead on the side stream
+  PreBin pb{};
+  cudaEvent_t ev_pre = nullptr;
+  bool pre_async = false;     // issued on the side stream by gsx_batch_forward_params; ev_pre marks its end
 };
 
 struct gsx_ctx {
@@ -97,6 +105,9 @@ struct gsx_ctx {
   cudaEvent_t ev[11] = {};
   // host pipeline of gsx_batch_render_host: the gradient images of a batch are uploaded on their own stream while the
   // per-Gaussian forward runs, rendered images are downloaded on a third stream under the following backward
+  cudaStream_t cs_pre = nullptr;     // pre-binning of the later views of a batch, under the earlier views' compositing
+  cudaEvent_t ev_fwd = nullptr;
+  const int *cur_total = nullptr;    // device K of the last forward (the slot's PreBin::total)
   cudaStream_t cs_in = nullptr, cs_out = nullptr;
   cudaEvent_t ev_in[GSX_MAX_BATCH] = {}, ev_img = nullptr, ev_out = nullptr, ev_go = nullptr;
   float *grad_stage[GSX_MAX_BATCH] = {};
@@ -143,6 +154,16 @@ static int alloc_slot(gsx_ctx *c, int k) {
   GSX_CUDA(cudaMalloc(&s.p.ckey, n * sizeof(uint32_t)));
   GSX_CUDA(cudaMalloc(&s.p.cid, n * sizeof(uint32_t)));
   s.p.ccount = c->d_ccount + k;
+  s.pb.key_a = s.p.ckey; s.pb.val_a = s.p.cid;
+  GSX_CUDA(cudaMalloc(&s.pb.key_b, n * sizeof(uint32_t)));
+  GSX_CUDA(cudaMalloc(&s.pb.val_b, n * sizeof(uint32_t)));
+  GSX_CUDA(cudaMalloc(&s.pb.offsets, n * sizeof(int)));
+  GSX_CUDA(cudaMalloc(&s.pb.block_sums, prebin_block_sums_count(c->max_n) * sizeof(int)));
+  GSX_CUDA(cudaMalloc(&s.pb.total, 4 * sizeof(int)));
+  GSX_CUDA(cudaMemset(s.pb.total, 0, 4 * sizeof(int)));
+  s.pb.sort_ws_bytes = prebin_sort_ws_bytes(c->max_n);
+  GSX_CUDA(cudaMalloc(&s.pb.sort_ws, s.pb.sort_ws_bytes));
+  GSX_CUDA(cudaEventCreateWithFlags(&s.ev_pre, cudaEventDisableTiming));
   GSX_CUDA(cudaMemset(s.p.gacc, 0, n * 12 * sizeof(float)));
   GSX_CUDA(cudaMemset(s.p.mask, 0, n));
   GSX_CUDA(cudaMemset(s.p.touched, 0, n * sizeof(int)));
@@ -154,19 +175,31 @@ static void free_slot(gsx_slot &s) {
   if (!s.allocated) return;
   cudaFree(s.p.r0); cudaFree(s.p.r1); cudaFree(s.p.r2); cudaFree(s.p.radius); cudaFree(s.p.depth); cudaFree(s.p.mask);
   cudaFree(s.p.touched); cudaFree(s.p.gacc); cudaFree(s.p.ckey); cudaFree(s.p.cid);
+  cudaFree(s.pb.key_b); cudaFree(s.pb.val_b); cudaFree(s.pb.offsets); cudaFree(s.pb.block_sums); cudaFree(s.pb.total);
+  cudaFree(s.pb.sort_ws);
+  if (s.ev_pre) cudaEventDestroy(s.ev_pre);
   s = gsx_slot();
 }
 
 // bin + sort + ranges + compositing forward of the view whose per-Gaussian records are in slot k
 static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
-  const gsx_slot &s = c->slot[k];
+  gsx_slot &s = c->slot[k];
   const gsx_view_t &v = s.view;
   const int ntx = (v.width + 15) / 16, nty = (v.height + 15) / 16;
   c->last_n = N; c->last_w = v.width; c->last_h = v.height; c->cur = k;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[2], st));
-  int rc = bin_sort_impl((const float *)s.p.r0, 4, s.p.depth, 1, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, c->bin_ws,
-                         c->L, c->ranges, &c->sorted_tiles, &c->sorted_vals, st, c->timing ? &c->ev[3] : nullptr, s.p.ckey, s.p.cid,
-                         s.p.ccount, (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0);
+  int rc;
+  if (s.pre_async) {
+    GSX_CUDA(cudaStreamWaitEvent(st, s.ev_pre, 0));   // issued by gsx_batch_forward_params on the side stream
+    s.pre_async = false;
+  } else {
+    rc = bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, st);
+    if (rc != GSX_OK) return rc;
+  }
+  c->cur_total = s.pb.total;
+  rc = bin_emit_sort_impl((const float *)s.p.r0, 4, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, c->bin_ws, c->L, s.pb,
+                          c->ranges, &c->sorted_tiles, &c->sorted_vals, st, c->timing ? &c->ev[3] : nullptr,
+                          (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0);
   if (rc != GSX_OK) return rc;
   rc = composite_fwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, v.width, v.height, v.background,
                             c->spp, c->wpp, c->image, st);
@@ -203,6 +236,7 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
   {
     int rc0 = alloc_slot(c, 0);
     if (rc0 != GSX_OK) return rc0;
+    c->cur_total = c->slot[0].pb.total;   // zero until the first forward
   }
   GSX_CUDA(cudaMalloc(&c->ranges, sizeof(int) * (size_t)(T + 1)));
   GSX_CUDA(cudaMalloc(&c->image, px * 3 * sizeof(float)));
@@ -229,6 +263,8 @@ int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (c->ev_img) cudaEventDestroy(c->ev_img);
   if (c->ev_out) cudaEventDestroy(c->ev_out);
   if (c->ev_go) cudaEventDestroy(c->ev_go);
+  if (c->cs_pre) { cudaStreamSynchronize(c->cs_pre); cudaStreamDestroy(c->cs_pre); }
+  if (c->ev_fwd) cudaEventDestroy(c->ev_fwd);
   if (c->cs_in) cudaStreamDestroy(c->cs_in);
   if (c->cs_out) cudaStreamDestroy(c->cs_out);
   cudaFree(c->grad_image); cudaFree(c->d_P); cudaFree(c->d_ccount); cudaFreeHost(c->h_stats);
@@ -315,11 +351,32 @@ int gsx_batch_forward_params(gsx_ctx_t *c, const gsx_view_t *views, int n_views,
   BatchConst bc;
   fill_batch_const(c, n_views, &bc);
   cudaStream_t st = (cudaStream_t)stream;
+  for (int k = 0; k < c->n_slots; ++k)   // pre-binning of a previous batch whose views were never consumed
+    if (c->slot[k].pre_async) { GSX_CUDA(cudaStreamWaitEvent(st, c->slot[k].ev_pre, 0)); c->slot[k].pre_async = false; }
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
   GSX_CUDA(cudaMemsetAsync(c->d_ccount, 0, GSX_MAX_BATCH * sizeof(int), st));
   int rc = batch_fwd_launch(bc, *p, N, views[0].l_max, st);
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[1], st));
-  return rc;
+  if (rc != GSX_OK) return rc;
+  // Pre-binning (depth sort + scan: ten short latency-bound launches per view) depends only on the kernel above: with
+  // more than one view it runs on a side stream, so views 1.. are pre-binned under the compositing of the views before
+  // them.  With stage timing on everything stays on the caller's stream so that the stages remain attributable.
+  if (n_views > 1 && !c->timing) {
+    if (!c->cs_pre) {
+      GSX_CUDA(cudaStreamCreateWithFlags(&c->cs_pre, cudaStreamNonBlocking));
+      GSX_CUDA(cudaEventCreateWithFlags(&c->ev_fwd, cudaEventDisableTiming));
+    }
+    GSX_CUDA(cudaEventRecord(c->ev_fwd, st));
+    GSX_CUDA(cudaStreamWaitEvent(c->cs_pre, c->ev_fwd, 0));
+    for (int k = 0; k < n_views; ++k) {
+      gsx_slot &s = c->slot[k];
+      rc = bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, c->cs_pre);
+      if (rc != GSX_OK) return rc;
+      GSX_CUDA(cudaEventRecord(s.ev_pre, c->cs_pre));
+      s.pre_async = true;
+    }
+  }
+  return GSX_OK;
 }
 
 int gsx_batch_forward_view(gsx_ctx_t *c, int slot, void *stream) {
@@ -539,7 +596,7 @@ int gsx_ctx_stats(gsx_ctx_t *c, gsx_stats_t *out, void *stream) {
     k_count_mask<<<kNumSMs * 4, 256, 0, st>>>(c->slot[c->cur].p.mask, c->last_n, c->d_P);
     GSX_LAUNCH_CHECK();
   }
-  GSX_CUDA(cudaMemcpyAsync(&c->h_stats[0], c->bin_ws + c->L.total, sizeof(int), cudaMemcpyDeviceToHost, st));
+  GSX_CUDA(cudaMemcpyAsync(&c->h_stats[0], (const char *)c->cur_total, sizeof(int), cudaMemcpyDeviceToHost, st));
   GSX_CUDA(cudaMemcpyAsync(&c->h_stats[1], c->d_P, sizeof(int), cudaMemcpyDeviceToHost, st));
   GSX_CUDA(cudaStreamSynchronize(st));
   out->N = c->last_n; out->P = c->h_stats[1]; out->K = c->h_stats[0]; out->capacity = c->capacity;
@@ -559,7 +616,7 @@ int gsx_ctx_state(gsx_ctx_t *c, gsx_state_t *o) {
   o->tiles_touched = sp.touched;
   o->sorted_gaussians = (const int *)c->sorted_vals;
   o->sorted_keys = nullptr;   /* never materialised by the two-level sort: gsx_ctx_build_sorted_keys */
-  o->ranges = c->ranges; o->num_instances = (const int *)(c->bin_ws + c->L.total);
+  o->ranges = c->ranges; o->num_instances = (const int *)((const char *)c->cur_total);
   o->packed_grads = (const float *)sp.gacc;
   return GSX_OK;
 }
@@ -577,7 +634,7 @@ int gsx_ctx_build_sorted_keys(gsx_ctx_t *c, const uint64_t **out) {
   }
   GSX_CUDA(cudaDeviceSynchronize());
   k_compose_keys<<<kNumSMs * 8, 256>>>(c->sorted_tiles, c->sorted_vals, c->slot[c->cur].p.depth,
-                                       (const int *)(c->bin_ws + c->L.total), c->capacity, c->key64);
+                                       (const int *)((const char *)c->cur_total), c->capacity, c->key64);
   GSX_LAUNCH_CHECK();
   GSX_CUDA(cudaDeviceSynchronize());
   *out = c->key64;

@@ -299,57 +299,76 @@ BinLayout bin_layout(int N, long long capacity) {
   return L;
 }
 
-// depth sort -> scan -> emit -> tile sort -> ranges, given touched[] already filled.  Leaves the sorted tile ids / Gaussian
-// ids in (*sorted_tiles, *sorted_vals) inside the workspace; K in total_dev[0].
-int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
-                  const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
-                  const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
-                  uint32_t *ckey, uint32_t *cid, const int *ccount, int tight) {
-  // ev (optional): 3 events recorded after emission, after the tile sort and after the ranges (stage timing)
-  // ckey/cid/ccount (optional, view-level path): depth keys + ids of the Gaussians that touch a tile, already compacted by
-  // the per-Gaussian kernel (unordered; *ccount entries) -- the depth sort, scan and emission then run over P' not N
-  int *offsets = (int *)(ws + L.offsets);
-  int *block_sums = (int *)(ws + L.block_sums), *total = (int *)(ws + L.total);
-  uint32_t *dka = (uint32_t *)(ws + L.dk_a), *dkb = (uint32_t *)(ws + L.dk_b);
-  uint32_t *dva = (uint32_t *)(ws + L.dv_a), *dvb = (uint32_t *)(ws + L.dv_b);
+// ---- phase 1 (pre-binning): depth sort -> tie fix-up -> scan of the tile counts in depth order.
+// compact mode (ckey given): key_a / val_a are the slot's compacted, unordered depth keys + ids (*ccount entries) written
+// by the per-Gaussian kernel, so everything here runs over P' entries; otherwise keys are derived from depth[] over N.
+int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, int N, bool compact, const int *ccount,
+                    PreBin *pb, cudaStream_t st) {
+  int in_b = 0, rc;
+  pb->perm = nullptr; pb->dkeys = nullptr; pb->count = nullptr;
+  if (N > 0) {
+    if (compact) {
+      pb->count = ccount;
+    } else {
+      k_depth_keys<<<ceil_div(N, kBlock), kBlock, 0, st>>>(depth, depth_stride, touched, N, pb->key_a, pb->val_a);
+      GSX_LAUNCH_CHECK();
+    }
+    rc = sort_pairs_u32_impl(pb->key_a, pb->key_b, pb->val_a, pb->val_b, N, pb->count, 32, pb->sort_ws, pb->sort_ws_bytes, st, &in_b);
+    if (rc != GSX_OK) return rc;
+    uint32_t *sk = in_b ? pb->key_b : pb->key_a, *sv = in_b ? pb->val_b : pb->val_a;
+    if (compact) {
+      k_fix_ties<<<ceil_div(N, kBlock), kBlock, 0, st>>>(sk, sv, N, ccount);
+      GSX_LAUNCH_CHECK();
+    }
+    pb->perm = sv; pb->dkeys = sk;
+  }
+  return exclusive_scan_i32(touched, pb->perm, pb->dkeys, N, pb->count, pb->offsets, pb->block_sums, pb->total, st);
+}
+
+// ---- phase 2: emit in depth order -> tile sort -> ranges.  Leaves the sorted tile ids / Gaussian ids in
+// (*sorted_tiles, *sorted_vals) inside the workspace; K is pb.total[0].
+// ev (optional): 3 events recorded after emission, after the tile sort and after the ranges (stage timing)
+int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, const int *touched, int ntx, int nty, int N,
+                       long long capacity, char *ws, const BinLayout &L, const PreBin &pb, int *ranges,
+                       const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
+                       int tight) {
   uint32_t *ka = (uint32_t *)(ws + L.keys_a), *kb = (uint32_t *)(ws + L.keys_b);
   uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
   int in_b = 0, rc;
-  const uint32_t *perm = nullptr, *dkeys = nullptr;
-  if (N > 0 && ckey) {
-    rc = sort_pairs_u32_impl(ckey, dkb, cid, dvb, N, ccount, 32, ws + L.sort_ws, L.sort_ws_bytes, st, &in_b);
-    if (rc != GSX_OK) return rc;
-    uint32_t *sk = in_b ? dkb : ckey, *sv = in_b ? dvb : cid;
-    k_fix_ties<<<ceil_div(N, kBlock), kBlock, 0, st>>>(sk, sv, N, ccount);
-    GSX_LAUNCH_CHECK();
-    perm = sv; dkeys = sk;
-  } else if (N > 0) {
-    ccount = nullptr;
-    k_depth_keys<<<ceil_div(N, kBlock), kBlock, 0, st>>>(depth, depth_stride, touched, N, dka, dva);
-    GSX_LAUNCH_CHECK();
-    rc = sort_pairs_u32_impl(dka, dkb, dva, dvb, N, nullptr, 32, ws + L.sort_ws, L.sort_ws_bytes, st, &in_b);
-    if (rc != GSX_OK) return rc;
-    perm = in_b ? dvb : dva;
-    dkeys = in_b ? dkb : dka;
-  }
-  rc = exclusive_scan_i32(touched, perm, dkeys, N, ccount, offsets, block_sums, total, st);
-  if (rc != GSX_OK) return rc;
   if (N > 0) {
-    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, dkeys, perm, touched, offsets, ntx, nty, N, ccount, capacity,
-                                                   ka, va, (tight && uv_stride == 4) ? 1 : 0);
+    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, pb.dkeys, pb.perm, touched, pb.offsets, ntx, nty, N,
+                                                   pb.count, capacity, ka, va, (tight && uv_stride == 4) ? 1 : 0);
     GSX_LAUNCH_CHECK();
   }
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
-  rc = sort_pairs_u32_impl(ka, kb, va, vb, capacity, total, tile_key_bits(ntx * nty) - 32, ws + L.sort_ws, L.sort_ws_bytes, st,
+  rc = sort_pairs_u32_impl(ka, kb, va, vb, capacity, pb.total, tile_key_bits(ntx * nty) - 32, ws + L.sort_ws, L.sort_ws_bytes, st,
                            &in_b);
   if (rc != GSX_OK) return rc;
   *sorted_tiles = in_b ? kb : ka;
   *sorted_vals = in_b ? vb : va;
   if (ev) GSX_CUDA(cudaEventRecord(ev[1], st));
-  rc = tile_ranges_u32_impl(*sorted_tiles, capacity, total, ntx * nty, ranges, st);
+  rc = tile_ranges_u32_impl(*sorted_tiles, capacity, pb.total, ntx * nty, ranges, st);
   if (ev) GSX_CUDA(cudaEventRecord(ev[2], st));
   return rc;
 }
+
+// both phases on one stream out of one workspace (per-function F7 path)
+int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_stride, const float4 *radius,
+                  const int *touched, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L, int *ranges,
+                  const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st) {
+  PreBin pb;
+  pb.key_a = (uint32_t *)(ws + L.dk_a); pb.key_b = (uint32_t *)(ws + L.dk_b);
+  pb.val_a = (uint32_t *)(ws + L.dv_a); pb.val_b = (uint32_t *)(ws + L.dv_b);
+  pb.offsets = (int *)(ws + L.offsets); pb.block_sums = (int *)(ws + L.block_sums); pb.total = (int *)(ws + L.total);
+  pb.sort_ws = ws + L.sort_ws; pb.sort_ws_bytes = L.sort_ws_bytes;
+  int rc = bin_prebin_impl(depth, depth_stride, touched, N, false, nullptr, &pb, st);
+  if (rc != GSX_OK) return rc;
+  return bin_emit_sort_impl(uv, uv_stride, radius, touched, ntx, nty, N, capacity, ws, L, pb, ranges, sorted_tiles, sorted_vals, st,
+                            nullptr, 0);
+}
+
+size_t prebin_sort_ws_bytes(int N) { return sort_workspace_bytes_impl(N); }
+size_t prebin_block_sums_count(int N) { return scan_block_sums_count(N); }
 
 int count_tiles_launch(const float *uv, int uv_stride, const float4 *radius, const uint8_t *mask, int ntx, int nty, int N, int *touched,
                        unsigned long long *coarse_total, cudaStream_t st) {
@@ -446,7 +465,7 @@ int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const floa
   const uint32_t *sk;
   const uint32_t *sv;
   rc = bin_sort_impl(uv, 2, xyz_c + 2, 3, (const float4 *)radius, (const int *)(ws + L.touched), n_tiles_x, n_tiles_y, N,
-                     capacity, ws, L, ranges, &sk, &sv, st, nullptr, nullptr, nullptr, nullptr, 0);
+                     capacity, ws, L, ranges, &sk, &sv, st);
   if (rc != GSX_OK) return rc;
   rc = copy_ids_launch(sv, sorted_gaussians, capacity, (const int *)(ws + L.total), st);
   if (rc != GSX_OK) return rc;

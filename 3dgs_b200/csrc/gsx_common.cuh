@@ -42,4 +42,17 @@ struct BinLayout {
   size_t touched, offsets, block_sums, total, dk_a, dk_b, dv_a, dv_b, keys_a, keys_b, vals_a, vals_b, sort_ws, sort_ws_bytes, bytes;
 };
 
+// Buffers and products of a view's pre-binning (depth sort of the Gaussians that touch a tile + scan of their tile
+// counts).  It depends only on the per-Gaussian forward, so the context runs it for the later views of a batch on a side
+// stream while earlier views are being composited (api.cu); the per-function F7 path carves one out of its workspace.
+struct PreBin {
+  uint32_t *key_a = nullptr, *val_a = nullptr;   // ping-pong partners of the depth sort (compact mode: a = the slot's lists)
+  uint32_t *key_b = nullptr, *val_b = nullptr;
+  int *offsets = nullptr, *block_sums = nullptr, *total = nullptr;   // total[0] = K after the scan
+  char *sort_ws = nullptr;
+  size_t sort_ws_bytes = 0;
+  const uint32_t *perm = nullptr, *dkeys = nullptr;   // results: ids in depth order and their keys
+  const int *count = nullptr;                          // device count of sorted entries (compact mode) or null
+};
+
 }  // namespace gsx
