@@ -76,6 +76,17 @@ struct gsx_slot {          // per-view state that must outlive the view inside a
   PreBin pb{};
   cudaEvent_t ev_pre = nullptr;
   bool pre_async = false;     // issued on the side stream by gsx_batch_forward_params; ev_pre marks its end
+  cudaEvent_t ev_bin = nullptr;
+  bool bin_async = false;     // emission + tile sort + ranges issued ahead on the binning stream; ev_bin marks their end
+};
+
+// Instance buffers + ranges of one binned view.  Two sets: view k uses set k & 1, so that view k+1 can be binned on the
+// binning stream while view k is composited out of the other set.
+struct BinSet {
+  char *ws = nullptr;
+  int *ranges = nullptr;
+  const uint32_t *sorted_tiles = nullptr, *sorted_vals = nullptr;
+  int owner = -1;             // slot whose sorted list the set holds (-1: none)
 };
 
 struct gsx_ctx {
@@ -106,7 +117,10 @@ struct gsx_ctx {
   // host pipeline of gsx_batch_render_host: the gradient images of a batch are uploaded on their own stream while the
   // per-Gaussian forward runs, rendered images are downloaded on a third stream under the following backward
   cudaStream_t cs_pre = nullptr;     // pre-binning of the later views of a batch, under the earlier views' compositing
-  cudaEvent_t ev_fwd = nullptr;
+  cudaStream_t cs_bin = nullptr;     // emission + tile sort + ranges of view k+1 under the compositing of view k
+  cudaEvent_t ev_fwd = nullptr, ev_free = nullptr;
+  BinSet bset[2];                    // bin_ws / ranges / sorted_* below point into the current view's set
+  int n_px_tiles = 0;
   const int *cur_total = nullptr;    // device K of the last forward (the slot's PreBin::total)
   cudaStream_t cs_in = nullptr, cs_out = nullptr;
   cudaEvent_t ev_in[GSX_MAX_BATCH] = {}, ev_img = nullptr, ev_out = nullptr, ev_go = nullptr;
@@ -131,11 +145,19 @@ __global__ void k_count_mask(const uint8_t *__restrict__ mask, int N, int *__res
 }
 
 static int alloc_bin(gsx_ctx *c, long long capacity) {
-  if (c->bin_ws) { cudaFree(c->bin_ws); c->bin_ws = nullptr; }
+  for (BinSet &b : c->bset) {
+    if (b.ws) { cudaFree(b.ws); b.ws = nullptr; }
+    b.sorted_tiles = b.sorted_vals = nullptr; b.owner = -1;
+  }
   c->sorted_tiles = nullptr; c->sorted_vals = nullptr;
   c->capacity = std::max<long long>(capacity, 1024);
   c->L = bin_layout(c->max_n, c->capacity);
-  GSX_CUDA(cudaMalloc(&c->bin_ws, c->L.bytes));
+  const int sets = c->n_slots > 1 ? 2 : 1;     // the second set exists once a batch of views was reserved
+  for (int i = 0; i < sets; ++i) {
+    GSX_CUDA(cudaMalloc(&c->bset[i].ws, c->L.bytes));
+    if (!c->bset[i].ranges) GSX_CUDA(cudaMalloc(&c->bset[i].ranges, sizeof(int) * (size_t)(c->n_px_tiles + 1)));
+  }
+  c->bin_ws = c->bset[0].ws; c->ranges = c->bset[0].ranges;
   return GSX_OK;
 }
 
@@ -164,6 +186,7 @@ static int alloc_slot(gsx_ctx *c, int k) {
   s.pb.sort_ws_bytes = prebin_sort_ws_bytes(c->max_n);
   GSX_CUDA(cudaMalloc(&s.pb.sort_ws, s.pb.sort_ws_bytes));
   GSX_CUDA(cudaEventCreateWithFlags(&s.ev_pre, cudaEventDisableTiming));
+  GSX_CUDA(cudaEventCreateWithFlags(&s.ev_bin, cudaEventDisableTiming));
   GSX_CUDA(cudaMemset(s.p.gacc, 0, n * 12 * sizeof(float)));
   GSX_CUDA(cudaMemset(s.p.mask, 0, n));
   GSX_CUDA(cudaMemset(s.p.touched, 0, n * sizeof(int)));
@@ -178,29 +201,80 @@ static void free_slot(gsx_slot &s) {
   cudaFree(s.pb.key_b); cudaFree(s.pb.val_b); cudaFree(s.pb.offsets); cudaFree(s.pb.block_sums); cudaFree(s.pb.total);
   cudaFree(s.pb.sort_ws);
   if (s.ev_pre) cudaEventDestroy(s.ev_pre);
+  if (s.ev_bin) cudaEventDestroy(s.ev_bin);
   s = gsx_slot();
+}
+
+// Work issued ahead on the side streams reads the slots' per-Gaussian outputs and writes the instance-buffer sets: before
+// either is overwritten (next per-Gaussian forward, capacity growth) the caller's stream waits for all of it.
+static int drain_async(gsx_ctx *c, cudaStream_t st) {
+  for (int k = 0; k < c->n_slots; ++k) {
+    gsx_slot &s = c->slot[k];
+    if (s.pre_async) { GSX_CUDA(cudaStreamWaitEvent(st, s.ev_pre, 0)); s.pre_async = false; }
+    if (s.bin_async) { GSX_CUDA(cudaStreamWaitEvent(st, s.ev_bin, 0)); s.bin_async = false; }
+  }
+  for (BinSet &b : c->bset) b.owner = -1;
+  return GSX_OK;
+}
+
+// emission + tile sort + ranges of slot k's view into instance-buffer set k & 1, on stream `st`
+static int issue_emit_sort(gsx_ctx *c, int k, int N, cudaStream_t st, cudaEvent_t *ev) {
+  gsx_slot &s = c->slot[k];
+  BinSet &b = c->bset[c->bset[1].ws ? (k & 1) : 0];
+  const gsx_view_t &v = s.view;
+  const int ntx = (v.width + 15) / 16, nty = (v.height + 15) / 16;
+  b.owner = k;
+  return bin_emit_sort_impl((const float *)s.p.r0, 4, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, b.ws, c->L, s.pb, b.ranges,
+                            &b.sorted_tiles, &b.sorted_vals, st, ev, (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0);
+}
+
+// view k+... binned ahead on the binning stream: after its pre-binning and after everything queued so far on `st` (the
+// compositing of the view that used the same instance-buffer set)
+static int issue_ahead(gsx_ctx *c, int k, int N, cudaStream_t st) {
+  gsx_slot &s = c->slot[k];
+  if (!s.pre_async || s.bin_async) return GSX_OK;
+  GSX_CUDA(cudaEventRecord(c->ev_free, st));
+  GSX_CUDA(cudaStreamWaitEvent(c->cs_bin, c->ev_free, 0));
+  GSX_CUDA(cudaStreamWaitEvent(c->cs_bin, s.ev_pre, 0));
+  int rc = issue_emit_sort(c, k, N, c->cs_bin, nullptr);
+  if (rc != GSX_OK) return rc;
+  GSX_CUDA(cudaEventRecord(s.ev_bin, c->cs_bin));
+  s.bin_async = true;
+  return GSX_OK;
 }
 
 // bin + sort + ranges + compositing forward of the view whose per-Gaussian records are in slot k
 static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
   gsx_slot &s = c->slot[k];
   const gsx_view_t &v = s.view;
-  const int ntx = (v.width + 15) / 16, nty = (v.height + 15) / 16;
   c->last_n = N; c->last_w = v.width; c->last_h = v.height; c->cur = k;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[2], st));
+  BinSet &b = c->bset[c->bset[1].ws ? (k & 1) : 0];
   int rc;
-  if (s.pre_async) {
-    GSX_CUDA(cudaStreamWaitEvent(st, s.ev_pre, 0));   // issued by gsx_batch_forward_params on the side stream
-    s.pre_async = false;
+  if (s.bin_async && b.owner == k) {
+    GSX_CUDA(cudaStreamWaitEvent(st, s.ev_bin, 0));    // binned ahead (which waited for the pre-binning)
+    s.bin_async = false; s.pre_async = false;
   } else {
-    rc = bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, st);
+    for (int j = 0; j < c->n_slots; ++j)               // out-of-order call: nothing may still be writing this set
+      if (c->slot[j].bin_async) { GSX_CUDA(cudaStreamWaitEvent(st, c->slot[j].ev_bin, 0)); c->slot[j].bin_async = false; }
+    if (s.pre_async) {
+      GSX_CUDA(cudaStreamWaitEvent(st, s.ev_pre, 0));  // issued by gsx_batch_forward_params on the side stream
+      s.pre_async = false;
+    } else {
+      rc = bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, st);
+      if (rc != GSX_OK) return rc;
+    }
+    rc = issue_emit_sort(c, k, N, st, c->timing ? &c->ev[3] : nullptr);
     if (rc != GSX_OK) return rc;
   }
   c->cur_total = s.pb.total;
-  rc = bin_emit_sort_impl((const float *)s.p.r0, 4, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, c->bin_ws, c->L, s.pb,
-                          c->ranges, &c->sorted_tiles, &c->sorted_vals, st, c->timing ? &c->ev[3] : nullptr,
-                          (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0);
-  if (rc != GSX_OK) return rc;
+  c->bin_ws = b.ws; c->ranges = b.ranges; c->sorted_tiles = b.sorted_tiles; c->sorted_vals = b.sorted_vals;
+  // the next view's instance buffers are the other set, last read by the compositing backward of view k-1 (already
+  // queued on st): its emission and tile sort start now and run under this view's compositing
+  if (c->cs_bin && k + 1 < c->batch_nv) {
+    rc = issue_ahead(c, k + 1, N, st);
+    if (rc != GSX_OK) return rc;
+  }
   rc = composite_fwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, v.width, v.height, v.background,
                             c->spp, c->wpp, c->image, st);
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[6], st));
@@ -238,7 +312,7 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
     if (rc0 != GSX_OK) return rc0;
     c->cur_total = c->slot[0].pb.total;   // zero until the first forward
   }
-  GSX_CUDA(cudaMalloc(&c->ranges, sizeof(int) * (size_t)(T + 1)));
+  c->n_px_tiles = T;
   GSX_CUDA(cudaMalloc(&c->image, px * 3 * sizeof(float)));
   GSX_CUDA(cudaMalloc(&c->wpp, px * sizeof(float)));
   GSX_CUDA(cudaMalloc(&c->spp, px * sizeof(int)));
@@ -255,7 +329,9 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
 int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (!c) return GSX_OK;
   for (int k = 0; k < GSX_MAX_BATCH; ++k) free_slot(c->slot[k]);
-  cudaFree(c->bin_ws); if (c->key64) cudaFree(c->key64); cudaFree(c->ranges); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
+  cudaDeviceSynchronize();
+  for (BinSet &b : c->bset) { if (b.ws) cudaFree(b.ws); if (b.ranges) cudaFree(b.ranges); }
+  if (c->key64) cudaFree(c->key64); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
   for (int k = 0; k < GSX_MAX_BATCH; ++k) {
     if (c->grad_stage[k]) cudaFree(c->grad_stage[k]);
     if (c->ev_in[k]) cudaEventDestroy(c->ev_in[k]);
@@ -264,7 +340,9 @@ int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (c->ev_out) cudaEventDestroy(c->ev_out);
   if (c->ev_go) cudaEventDestroy(c->ev_go);
   if (c->cs_pre) { cudaStreamSynchronize(c->cs_pre); cudaStreamDestroy(c->cs_pre); }
+  if (c->cs_bin) cudaStreamDestroy(c->cs_bin);
   if (c->ev_fwd) cudaEventDestroy(c->ev_fwd);
+  if (c->ev_free) cudaEventDestroy(c->ev_free);
   if (c->cs_in) cudaStreamDestroy(c->cs_in);
   if (c->cs_out) cudaStreamDestroy(c->cs_out);
   cudaFree(c->grad_image); cudaFree(c->d_P); cudaFree(c->d_ccount); cudaFreeHost(c->h_stats);
@@ -277,6 +355,7 @@ int gsx_ctx_reserve(gsx_ctx_t *c, long long instance_capacity) {
   if (instance_capacity <= c->capacity) return GSX_OK;
   if (instance_capacity >= (1LL << 30)) { set_error("instance capacity %lld >= 2^30", instance_capacity); return GSX_E_ARG; }
   GSX_CUDA(cudaDeviceSynchronize());
+  for (int k = 0; k < c->n_slots; ++k) c->slot[k].pre_async = c->slot[k].bin_async = false;
   return alloc_bin(c, instance_capacity);
 }
 
@@ -286,6 +365,8 @@ int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N,
   int rc = check_view(c, v, p, N);
   if (rc != GSX_OK) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  rc = drain_async(c, st);
+  if (rc != GSX_OK) return rc;
   c->slot[0].view = *v;
   c->batch_n = N; c->batch_nv = 1; c->batch_lmax = v->l_max;
   BatchConst bc;
@@ -328,6 +409,10 @@ int gsx_batch_reserve(gsx_ctx_t *c, int n_slots) {
     int rc = alloc_slot(c, k);
     if (rc != GSX_OK) return rc;
   }
+  if (c->n_slots > 1 && !c->bset[1].ws) {        // second instance-buffer set for the binning pipeline
+    GSX_CUDA(cudaMalloc(&c->bset[1].ws, c->L.bytes));
+    GSX_CUDA(cudaMalloc(&c->bset[1].ranges, sizeof(int) * (size_t)(c->n_px_tiles + 1)));
+  }
   return GSX_OK;
 }
 
@@ -351,8 +436,10 @@ int gsx_batch_forward_params(gsx_ctx_t *c, const gsx_view_t *views, int n_views,
   BatchConst bc;
   fill_batch_const(c, n_views, &bc);
   cudaStream_t st = (cudaStream_t)stream;
-  for (int k = 0; k < c->n_slots; ++k)   // pre-binning of a previous batch whose views were never consumed
-    if (c->slot[k].pre_async) { GSX_CUDA(cudaStreamWaitEvent(st, c->slot[k].ev_pre, 0)); c->slot[k].pre_async = false; }
+  {
+    int rcd = drain_async(c, st);          // side-stream work of a previous batch whose views were never consumed
+    if (rcd != GSX_OK) return rcd;
+  }
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
   GSX_CUDA(cudaMemsetAsync(c->d_ccount, 0, GSX_MAX_BATCH * sizeof(int), st));
   int rc = batch_fwd_launch(bc, *p, N, views[0].l_max, st);
@@ -363,8 +450,14 @@ int gsx_batch_forward_params(gsx_ctx_t *c, const gsx_view_t *views, int n_views,
   // them.  With stage timing on everything stays on the caller's stream so that the stages remain attributable.
   if (n_views > 1 && !c->timing) {
     if (!c->cs_pre) {
-      GSX_CUDA(cudaStreamCreateWithFlags(&c->cs_pre, cudaStreamNonBlocking));
+      // high priority: their short kernels take CTA slots as the (thousands of queued) compositing CTAs retire, instead
+      // of waiting behind the whole compositing grid
+      int lo = 0, hi = 0;
+      GSX_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+      GSX_CUDA(cudaStreamCreateWithPriority(&c->cs_pre, cudaStreamNonBlocking, hi));
+      GSX_CUDA(cudaStreamCreateWithPriority(&c->cs_bin, cudaStreamNonBlocking, hi));
       GSX_CUDA(cudaEventCreateWithFlags(&c->ev_fwd, cudaEventDisableTiming));
+      GSX_CUDA(cudaEventCreateWithFlags(&c->ev_free, cudaEventDisableTiming));
     }
     GSX_CUDA(cudaEventRecord(c->ev_fwd, st));
     GSX_CUDA(cudaStreamWaitEvent(c->cs_pre, c->ev_fwd, 0));
@@ -374,6 +467,11 @@ int gsx_batch_forward_params(gsx_ctx_t *c, const gsx_view_t *views, int n_views,
       if (rc != GSX_OK) return rc;
       GSX_CUDA(cudaEventRecord(s.ev_pre, c->cs_pre));
       s.pre_async = true;
+    }
+    // both instance-buffer sets are free here (everything of the previous batch is ahead of this call on st)
+    for (int k = 0; k < 2 && k < n_views && c->bset[1].ws; ++k) {
+      rc = issue_ahead(c, k, N, st);
+      if (rc != GSX_OK) return rc;
     }
   }
   return GSX_OK;
