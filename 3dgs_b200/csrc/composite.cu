@@ -135,6 +135,99 @@ k_composite_fwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
   }
 }
 
+// View-level forward, two pixels per lane (a warp owns an 8x8 block, a 128-thread CTA one tile): the per-entry overhead of
+// the hit loop (next-hit extraction, two shared-memory record loads, dx and its products) is shared by the two pixels.
+// Per-pixel arithmetic identical to k_composite_fwd.
+__global__ void __launch_bounds__(128)
+k_composite_fwd2(const float4 *__restrict__ r0, const float4 *__restrict__ r1, const float4 *__restrict__ r2,
+                 const int *__restrict__ sorted, const int *__restrict__ ranges, int ntx, int W, int H, float bg,
+                 int *__restrict__ splats_per_pixel, float *__restrict__ weight_per_pixel, float *__restrict__ image) {
+  constexpr int CF = 128;
+  __shared__ float4 s_r0[CF], s_r1[CF], s_r2[CF];
+  const int tile = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int X0 = (tile % ntx) * 16 + (warp & 1) * 8, Y0 = (tile / ntx) * 16 + (warp >> 1) * 8;
+  const int px = X0 + (lane & 7);
+  const float fpx = (float)px;
+  const float bx0 = (float)X0, bx1 = (float)(X0 + 7), by0 = (float)Y0, by1 = (float)(Y0 + 7);
+  const int start = ranges[tile];
+  const int total = ranges[tile + 1] - start;
+
+  float fpy[2], T[2], cr[2], cg[2], cb[2];
+  bool done[2], inside[2];
+  int count[2];
+#pragma unroll
+  for (int p = 0; p < 2; ++p) {
+    const int py = Y0 + (lane >> 3) + 4 * p;
+    fpy[p] = (float)py;
+    inside[p] = px < W && py < H;
+    done[p] = !inside[p];
+    T[p] = 1.0f; cr[p] = cg[p] = cb[p] = 0.0f;
+    count[p] = total;
+  }
+  bool warp_done = __ballot_sync(0xffffffffu, !(done[0] && done[1])) == 0;
+
+  for (int base = 0; base < total; base += CF) {
+    if (__syncthreads_and(warp_done)) break;
+    const int nb = min(CF, total - base);
+    if (tid < nb) {
+      const int g = sorted[start + base + tid];
+      s_r0[tid] = __ldg(r0 + g); s_r1[tid] = __ldg(r1 + g); s_r2[tid] = __ldg(r2 + g);
+    }
+    __syncthreads();
+    if (warp_done) continue;
+    for (int c = 0; c < nb; c += 32) {
+      const int j = c + lane;
+      bool hit = false;
+      if (j < nb) {
+        const float4 q = s_r0[j];
+        hit = !(q.x + q.z < bx0 || q.x - q.z > bx1 || q.y + q.w < by0 || q.y - q.w > by1);
+      }
+      unsigned m = __ballot_sync(0xffffffffu, hit);
+      while (m) {
+        const int e = c + __ffs(m) - 1;
+        m &= m - 1;
+        const float4 q0 = s_r0[e], q1 = s_r1[e];
+        const float dx = q0.x - fpx;
+        float alpha[2];
+        bool take = false;
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+          const float dy = q0.y - fpy[p];
+          const float power = fminf(0.0f, -0.5f * (q1.x * dx * dx + q1.z * dy * dy) - q1.y * dx * dy);
+          alpha[p] = fminf(0.99f, q1.w * exp_neg(power));
+          take |= (alpha[p] > ALPHA_MIN && !done[p]);
+        }
+        if (take) {
+          const float4 q2 = s_r2[e];
+#pragma unroll
+          for (int p = 0; p < 2; ++p) {
+            if (alpha[p] > ALPHA_MIN && !done[p]) {
+              const float test_T = T[p] * (1.0f - alpha[p]);
+              const float w = alpha[p] * T[p];
+              cr[p] += q2.x * w; cg[p] += q2.y * w; cb[p] += q2.z * w;
+              T[p] = test_T;
+              if (test_T < 0.0001f) { done[p] = true; count[p] = base + e + 1; }
+            }
+          }
+        }
+      }
+      if (__ballot_sync(0xffffffffu, !(done[0] && done[1])) == 0) { warp_done = true; break; }
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < 2; ++p) {
+    if (inside[p]) {
+      const size_t q = (size_t)(Y0 + (lane >> 3) + 4 * p) * W + px;
+      splats_per_pixel[q] = count[p];
+      weight_per_pixel[q] = T[p];
+      image[3 * q + 0] = cr[p] + T[p] * bg;
+      image[3 * q + 1] = cg[p] + T[p] * bg;
+      image[3 * q + 2] = cb[p] + T[p] * bg;
+    }
+  }
+}
+
 struct GradDst {
   float *packed;                                   // [N][12]: {r,g,b,opa} {u,v,ca,cb} {cc,-,-,-}
   float *grad_rgb, *grad_opacity, *grad_uv, *grad_conic;   // reference layouts
@@ -309,6 +402,177 @@ k_composite_bwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
   }
 }
 
+// View-level backward, two pixels per lane: a warp owns an 8x8 block (lane -> column lane&7, rows lane>>3 and +4), a
+// 128-thread CTA one tile.  The per-pixel arithmetic is k_composite_bwd's; what changes is the cost of the cross-lane
+// reduction (12 shuffles + selects + the shared-memory publish per contributing warp-hit, more than half of that kernel's
+// instructions): the two pixels of a lane are summed in registers first, so it is paid once per 64 pixels.
+template <int PPL>
+__global__ void __launch_bounds__(256 / PPL)
+k_composite_bwd2(const float4 *__restrict__ r0, const float4 *__restrict__ r1, const float4 *__restrict__ r2,
+                 const int *__restrict__ sorted, const int *__restrict__ ranges, int ntx, int W, int H, float bg,
+                 const int *__restrict__ splats_per_pixel, const float *__restrict__ weight_per_pixel,
+                 const float *__restrict__ grad_image, float *__restrict__ packed) {
+  constexpr int CB2 = 256 / PPL;   // threads per CTA == staged entries per batch
+  constexpr int WROWS = 4 * PPL;   // rows of a warp's block
+  __shared__ float4 s_r0[CB2], s_r1[CB2], s_r2[CB2];
+  __shared__ float s_acc[CB2 * 9];
+  __shared__ int s_ids[CB2];
+  __shared__ int s_max;
+  const int tile = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int X0 = (tile % ntx) * 16 + (warp & 1) * 8, Y0 = (tile / ntx) * 16 + (warp >> 1) * WROWS;
+  const int px = X0 + (lane & 7);
+  const float fpx = (float)px;
+  const float bx0 = (float)X0, bx1 = (float)(X0 + 7), by0 = (float)Y0, by1 = (float)(Y0 + WROWS - 1);
+  const int start = ranges[tile];
+  const float half_w = 0.5f * (float)W, half_h = 0.5f * (float)H;
+
+  int count[PPL];
+  float fpy[PPL], T[PPL], Tf[PPL], gx[PPL], gy[PPL], gz[PPL], bgdot[PPL], ar[PPL], ag[PPL], ab[PPL];
+  bool inside[PPL];
+#pragma unroll
+  for (int p = 0; p < PPL; ++p) {
+    const int py = Y0 + (lane >> 3) + 4 * p;
+    fpy[p] = (float)py;
+    inside[p] = px < W && py < H;
+    count[p] = 0; T[p] = Tf[p] = 0.0f; gx[p] = gy[p] = gz[p] = 0.0f;
+    if (inside[p]) {
+      const size_t q = (size_t)py * W + px;
+      count[p] = splats_per_pixel[q];
+      T[p] = Tf[p] = weight_per_pixel[q];
+      gx[p] = grad_image[3 * q]; gy[p] = grad_image[3 * q + 1]; gz[p] = grad_image[3 * q + 2];
+    }
+    float b = 0.0f;   // render_backward.cu:149-152
+    b += bg * gx[p]; b += bg * gy[p]; b += bg * gz[p];
+    bgdot[p] = b;
+    ar[p] = ag[p] = ab[p] = 0.0f;   // colour accumulated behind the current entry
+  }
+  int cmax = count[0];
+#pragma unroll
+  for (int p = 1; p < PPL; ++p) cmax = max(cmax, count[p]);
+  const int warp_max = __reduce_max_sync(0xffffffffu, cmax);
+  if (tid == 0) s_max = 0;
+  __syncthreads();
+  if (lane == 0 && warp_max > 0) atomicMax(&s_max, warp_max);
+  __syncthreads();
+  const int cta_max = s_max;   // render_backward.cu:74 (start index = max count - 1)
+
+  for (int top = cta_max; top > 0; top -= CB2) {
+    const int lo = max(0, top - CB2);
+    const int nb = top - lo;
+    __syncthreads();
+    if (tid < nb) {
+      const int g = sorted[start + lo + tid];
+      s_ids[tid] = g;
+      s_r0[tid] = __ldg(r0 + g); s_r1[tid] = __ldg(r1 + g); s_r2[tid] = __ldg(r2 + g);
+    }
+#pragma unroll
+    for (int k = 0; k < 9; ++k) s_acc[tid + k * CB2] = 0.0f;
+    __syncthreads();
+    const int hi = min(top, warp_max);
+    for (int chi = hi; chi > lo; chi -= 32) {
+      const int j = chi - 1 - lane;   // lane 0 = farthest entry first (back to front)
+      bool hit = false;
+      if (j >= lo) {
+        const float4 q = s_r0[j - lo];
+        hit = !(q.x + q.z < bx0 || q.x - q.z > bx1 || q.y + q.w < by0 || q.y - q.w > by1);
+      }
+      unsigned m = __ballot_sync(0xffffffffu, hit);
+      while (m) {
+        const int idx = chi - 1 - (__ffs(m) - 1);
+        m &= m - 1;
+        const int e = idx - lo;
+        const float4 q0 = s_r0[e], q1 = s_r1[e];
+        const float dx = q0.x - fpx;
+        float dy[PPL], gg[PPL], alpha[PPL];
+        bool valid[PPL], anyv = false;
+#pragma unroll
+        for (int p = 0; p < PPL; ++p) {
+          dy[p] = q0.y - fpy[p];
+          const float power = fminf(0.0f, -0.5f * (q1.x * dx * dx + q1.z * dy[p] * dy[p]) - q1.y * dx * dy[p]);
+          gg[p] = exp_neg(power);
+          alpha[p] = fminf(0.99f, q1.w * gg[p]);
+          valid[p] = inside[p] && (alpha[p] >= ALPHA_MIN) && (idx < count[p]);
+          anyv |= valid[p];
+        }
+        if (!__any_sync(0xffffffffu, anyv)) continue;
+        const float4 q2 = s_r2[e];
+        float v[8], vo = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] = 0.0f;
+#pragma unroll
+        for (int p = 0; p < PPL; ++p) {   // branch-free: a pixel that does not take the entry runs with alpha = 0, g = 0
+          const float al = valid[p] ? alpha[p] : 0.0f;
+          const float gm = valid[p] ? gg[p] : 0.0f;
+          const float om = 1.0f - al;
+          const float inv_om = rcp_fast(om);   // render_backward.cu:132 divides; 1 - alpha >= 0.01
+          T[p] = valid[p] ? T[p] * inv_om : T[p];
+          const float w = al * T[p];
+          float ga = 0.0f;
+          ga += (q2.x - ar[p]) * gx[p]; ga += (q2.y - ag[p]) * gy[p]; ga += (q2.z - ab[p]) * gz[p];
+          ga *= T[p];
+          ga += (-Tf[p] * inv_om) * bgdot[p];
+          ar[p] = al * q2.x + om * ar[p]; ag[p] = al * q2.y + om * ag[p]; ab[p] = al * q2.z + om * ab[p];
+          const float gp = gm * (ga * q1.w);   // d L / d power
+          const float gpx = gp * dx, gpy = gp * dy[p];
+          v[0] += w * gx[p]; v[1] += w * gy[p]; v[2] += w * gz[p];
+          v[3] += gpx; v[4] += gpy; v[5] += gpx * dx; v[6] += gpx * dy[p]; v[7] += gpy * dy[p];
+          vo += gp;
+        }
+        // transposing butterfly: 9 values over 32 lanes in 12 shuffles (as k_composite_bwd)
+        float a4[4], a2[2], a1;
+        {
+          const bool up = lane & 16;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const float send = up ? v[k] : v[k + 4], keep = up ? v[k + 4] : v[k];
+            a4[k] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+          }
+          vo += __shfl_xor_sync(0xffffffffu, vo, 16);
+        }
+        {
+          const bool up = lane & 8;
+#pragma unroll
+          for (int k = 0; k < 2; ++k) {
+            const float send = up ? a4[k] : a4[k + 2], keep = up ? a4[k + 2] : a4[k];
+            a2[k] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+          }
+          vo += __shfl_xor_sync(0xffffffffu, vo, 8);
+        }
+        {
+          const bool up = lane & 4;
+          const float send = up ? a2[0] : a2[1], keep = up ? a2[1] : a2[0];
+          a1 = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+          vo += __shfl_xor_sync(0xffffffffu, vo, 4);
+        }
+        {
+          const bool up = lane & 2;
+          const float send = up ? a1 : vo, keep = up ? vo : a1;
+          a1 = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+        }
+        a1 += __shfl_xor_sync(0xffffffffu, a1, 1);
+        const int k = (lane == 2) ? 8 : ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);
+        if ((lane & 3) == 0 || lane == 2) atomicAdd(&s_acc[e * 9 + k], a1);
+      }
+    }
+    __syncthreads();
+    if (tid < nb) {
+      float m[9];
+      bool any = false;
+#pragma unroll
+      for (int k = 0; k < 9; ++k) { m[k] = s_acc[tid * 9 + k]; any |= (m[k] != 0.0f); }
+      const float4 q1 = s_r1[tid];
+      const float w2 = s_r2[tid].w;
+      if (any && w2 != 0.0f) {   // Q7 (render_backward.cu:170), see k_composite_bwd
+        float *o = packed + (size_t)s_ids[tid] * 12;
+        red_add_v4(o, m[0], m[1], m[2], m[8] * (w2 / q1.w));
+        red_add_v4(o + 4, (-q1.x * m[3] - q1.y * m[4]) * half_w, (-q1.z * m[4] - q1.y * m[3]) * half_h, -0.5f * m[5], -m[6]);
+        atomicAdd(o + 8, -0.5f * m[7]);
+      }
+    }
+  }
+}
+
 // Work counters for the roofline arithmetic (bench.py only): S = sum of splats_per_pixel (pixel-entries the
 // reference evaluates), S+ = those with alpha >= 1/255.  One thread per pixel, no staging: not a hot path.
 __global__ void __launch_bounds__(CB)
@@ -348,9 +612,7 @@ int count_work_launch(const float4 *r0, const float4 *r1, const int *sorted, con
 int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
                          int W, int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st) {
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
-  GaussSrc s{};
-  s.r0 = r0; s.r1 = r1; s.r2 = r2;
-  k_composite_fwd<true><<<ntx * nty, CB, 0, st>>>(s, sorted, ranges, ntx, W, H, bg, spp, wpp, image);
+  k_composite_fwd2<<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, image);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -359,11 +621,7 @@ int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, c
                          int W, int H, float bg, const int *spp, const float *wpp, const float *grad_image,
                          float *packed_grads, cudaStream_t st) {
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
-  GaussSrc s{};
-  s.r0 = r0; s.r1 = r1; s.r2 = r2;
-  GradDst d{};
-  d.packed = packed_grads;
-  k_composite_bwd<true><<<ntx * nty, CB, 0, st>>>(s, sorted, ranges, ntx, W, H, bg, spp, wpp, grad_image, d);
+  k_composite_bwd2<2><<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, grad_image, packed_grads);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
