@@ -682,3 +682,63 @@ def test_host_buffer_entry_points_match_device_path(B, pinned):
     for k in g1:
         util.assert_grad_close(g1[k], gd.grads[k].cpu().numpy(), f"d {k}: render_view_host vs forward+backward", outlier=2e-3)
     r.close()
+
+
+def test_batch_pipeline_call_orders(B):
+    """The context bins views ahead on side streams (pre-binning of all views at gsx_batch_forward_params, emission + tile
+    sort of view k+1 under the compositing of view k, two instance-buffer sets).  Whatever the call order -- in order,
+    out of order, a view repeated, a batch abandoned half-way, a single-view forward in between -- every view's state
+    must equal the in-order one's."""
+    import torch
+    W, H, N, l_max = 224, 160, 12000, 2
+    az = [10.0, 100.0, 190.0, 280.0, 330.0]
+    cams = [S.orbit_camera(W, H, azimuth_deg=a) for a in az]
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=47)
+    Hh = gs.host
+    gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+    views = [util.gsx_view(c, l_max, 0.1 * k) for k, c in enumerate(cams)]
+    gi = torch.as_tensor(S.grad_image(W, H, seed=99) * 1e3).cuda()
+    r = Hh.Rasterizer(N, W, H, instance_capacity=8 * N)
+    r.batch_reserve(len(views))
+    keys = ("K", "ranges", "sorted_gaussians", "sorted_keys", "splats_per_pixel", "image")
+
+    def snap():
+        st = r.state()
+        return {k: (st[k].cpu().numpy().copy() if hasattr(st[k], "cpu") else st[k]) for k in keys}
+
+    def same(a, b, what):
+        assert a["K"] == b["K"], what
+        for k in keys[1:]:
+            np.testing.assert_array_equal(a[k][: a["K"]] if k.startswith("sorted") else a[k],
+                                          b[k][: b["K"]] if k.startswith("sorted") else b[k], err_msg=f"{what}: {k}")
+
+    # in order, forward + backward: the reference states and gradients
+    want = []
+    r.batch_step(views, gd, gi, flags=2, on_image=lambda k: want.append(snap()))
+    torch.cuda.synchronize()
+    want_g = {k: t.cpu().numpy().copy() for k, t in gd.grads.items()}
+    # out of order, forward only
+    r.batch_forward_params(views, gd)
+    for k in (3, 0, 4, 1, 2):
+        r.batch_forward_view(k)
+        same(snap(), want[k], f"out of order, view {k}")
+    # a view repeated, then the rest in order with backward
+    r.batch_forward_params(views, gd)
+    r.batch_forward_view(0)
+    r.batch_forward_view(0)
+    same(snap(), want[0], "repeated view 0")
+    # abandoned half-way (views 1.. binned ahead, never consumed), a single-view forward in between, then a full batch
+    r.batch_forward_params(views, gd)
+    r.batch_forward_view(0)
+    r.forward(views[2], gd)
+    same(snap(), want[2], "single-view forward after an abandoned batch")
+    got = []
+    for t in gd.grads.values():
+        t.fill_(3.0)
+    r.batch_step(views, gd, gi, flags=2, on_image=lambda k: got.append(snap()))
+    torch.cuda.synchronize()
+    for k in range(len(views)):
+        same(got[k], want[k], f"full batch after the detours, view {k}")
+    for k in want_g:
+        util.assert_grad_close(gd.grads[k].cpu().numpy(), want_g[k], f"d {k} after the detours", outlier=2e-3)
+    r.close()
