@@ -17,6 +17,13 @@
 // Bound: FP32/issue (no tensor cores: not a dense contraction).  Algorithmic work per SURVEY 8d.
 #include "gsx_common.cuh"
 
+// minimum resident CTAs per SM of the view-level compositing kernels (register cap); overridable for A/B builds
+#ifndef GSX_CBWD_MINB
+#define GSX_CBWD_MINB 8
+#endif
+#ifndef GSX_CFWD_MINB
+#define GSX_CFWD_MINB 1
+#endif
 namespace gsx {
 
 constexpr float ALPHA_MIN = 0.00392156862f;   // render.cu:74, render_backward.cu:123
@@ -138,7 +145,7 @@ k_composite_fwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
 // View-level forward, two pixels per lane (a warp owns an 8x8 block, a 128-thread CTA one tile): the per-entry overhead of
 // the hit loop (next-hit extraction, two shared-memory record loads, dx and its products) is shared by the two pixels.
 // Per-pixel arithmetic identical to k_composite_fwd.
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, GSX_CFWD_MINB)
 k_composite_fwd2(const float4 *__restrict__ r0, const float4 *__restrict__ r1, const float4 *__restrict__ r2,
                  const int *__restrict__ sorted, const int *__restrict__ ranges, int ntx, int W, int H, float bg,
                  int *__restrict__ splats_per_pixel, float *__restrict__ weight_per_pixel, float *__restrict__ image) {
@@ -407,7 +414,7 @@ k_composite_bwd(GaussSrc src, const int *__restrict__ sorted, const int *__restr
 // reduction (12 shuffles + selects + the shared-memory publish per contributing warp-hit, more than half of that kernel's
 // instructions): the two pixels of a lane are summed in registers first, so it is paid once per 64 pixels.
 template <int PPL>
-__global__ void __launch_bounds__(256 / PPL)
+__global__ void __launch_bounds__(256 / PPL, GSX_CBWD_MINB)
 k_composite_bwd2(const float4 *__restrict__ r0, const float4 *__restrict__ r1, const float4 *__restrict__ r2,
                  const int *__restrict__ sorted, const int *__restrict__ ranges, int ntx, int W, int H, float bg,
                  const int *__restrict__ splats_per_pixel, const float *__restrict__ weight_per_pixel,

@@ -312,7 +312,10 @@ __device__ __forceinline__ bool sat_tile_rot(const ObbSat &s, int tx, int ty) {
 // single lane busy for hundreds of SAT tests while 31 wait): the leader's SAT constants and rectangle are broadcast,
 // the 32 lanes test 32 cells per step (same tx-major order as the serial loop) and fn(c0, hit, ballot) sees each step.
 // Must be called by all 32 lanes with the same `leader`.
-constexpr int COOP_CELLS = 16;   // rectangles with more cells than this are handled cooperatively
+#ifndef GSX_COOP_CELLS
+#define GSX_COOP_CELLS 16
+#endif
+constexpr int COOP_CELLS = GSX_COOP_CELLS;   // rectangles with more cells than this are handled cooperatively
 template <typename F>
 __device__ __forceinline__ void coop_tile_rect(int leader, const ObbSat &so, const TileRange &tr, F &&fn) {
   const unsigned full = 0xffffffffu;

@@ -20,9 +20,15 @@ namespace gsx {
 
 namespace {
 
-constexpr int RS_THREADS = 256;
+#ifndef GSX_RS_THREADS
+#define GSX_RS_THREADS 256
+#endif
+#ifndef GSX_RS_IPT
+#define GSX_RS_IPT 16
+#endif
+constexpr int RS_THREADS = GSX_RS_THREADS;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_IPT = 16;
+constexpr int RS_IPT = GSX_RS_IPT;
 constexpr int RS_TILE = RS_THREADS * RS_IPT;   // 4096 keys per tile
 constexpr int RADIX = 256;
 constexpr int MAX_PASSES = 8;
