@@ -226,13 +226,36 @@ def main():
         if world == 1:
             r.batch_render_host(vstructs, gd, gi_host, img_host, flags=OVER)
             return
-        # host buffers in / out around the same exchange: per view H2D of the loss gradient, D2H of the image
-        gis = [h.to(dev, non_blocking=True) for h in gi_host]
+        # host buffers in / out around the same exchange: per view H2D of the loss gradient, D2H of the image, on two copy
+        # streams (uploads under the per-Gaussian forward, view k's download under its backward) like the library's
+        # own gsx_batch_render_host does at N = 1
+        cur = torch.cuda.current_stream()
+        e2e_go.record(cur)
+        with torch.cuda.stream(up_s):
+            up_s.wait_event(e2e_go)
+            for k_ in range(nv):
+                gis_dev[k_].copy_(gi_host[k_], non_blocking=True)
+                up_ev[k_].record(up_s)
 
         def grab(k_):
-            img_host[k_].copy_(r.state_image(), non_blocking=True)
-        vp.step(gis, on_image=grab)
+            if k_ >= 2:
+                cur.wait_event(down_ev[k_ - 2])                    # the staging image is free again
+            img_stage[k_ & 1].copy_(r.state_image())
+            img_ev[k_].record(cur)
+            with torch.cuda.stream(down_s):
+                down_s.wait_event(img_ev[k_])
+                img_host[k_].copy_(img_stage[k_ & 1], non_blocking=True)
+                down_ev[k_].record(down_s)
+            cur.wait_event(up_ev[k_])                              # this view's loss gradient has arrived
+        vp.step(gis_dev, on_image=grab)
         torch.cuda.synchronize()
+
+    if world > 1:
+        up_s, down_s = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        gis_dev = [torch.empty((H, W, 3), device=dev, dtype=torch.float32) for _ in range(nv)]
+        img_stage = [torch.empty((H, W, 3), device=dev, dtype=torch.float32) for _ in range(2)]
+        mkev = lambda: [torch.cuda.Event() for _ in range(nv)]
+        up_ev, img_ev, down_ev, e2e_go = mkev(), mkev(), mkev(), torch.cuda.Event()
 
     def barrier():
         if world > 1:
