@@ -261,35 +261,44 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
   const int any_t = __syncthreads_or(tch != 0);
   if (!any_t && !out.overwrite) return;
   if (any_t && L > 0) stage_rows<SHF>(s_coef, sh, sh_stride, row0, rows, use_tma, &s_bar);   // overlaps the loads below
-  unsigned act = 0;
-#ifndef GSX_BWD_PREFETCH
-#define GSX_BWD_PREFETCH 1
+#ifndef GSX_BWD_EARLY
+#define GSX_BWD_EARLY 1
 #endif
-  // two views per trip: both views' packed gradients are requested before either is tested (one DRAM round trip per
-  // pair of views instead of one per view -- 47 % of this kernel's stall samples waited on these dependent loads)
-  for (int v0 = 0; v0 < nv; v0 += 2) {
+#ifndef GSX_BWD_PF
+#define GSX_BWD_PF 4
+#endif
+  // parameters of every touched Gaussian are requested now, together with the packed gradients below, instead of one
+  // more dependent round trip after the gradients turned out non-zero (a touched Gaussian whose gradients are all zero
+  // -- occluded in every view -- costs 52 B of reads it did not need)
+  float3 pw = make_float3(0.f, 0.f, 0.f);
+  float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
+  float s0 = 0.f, s1 = 0.f, s2 = 0.f, b0r = 0.f, b0g = 0.f, b0b = 0.f;
+  if (GSX_BWD_EARLY && tch) {
+    pw = make_float3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+    q = reinterpret_cast<const float4 *>(quat)[i];
+    s0 = scale[3 * i]; s1 = scale[3 * i + 1]; s2 = scale[3 * i + 2];
+    b0r = band0[3 * i]; b0g = band0[3 * i + 1]; b0b = band0[3 * i + 2];
+  }
+  unsigned act = 0;
+  // GSX_BWD_PF views per trip: their packed gradients are all requested before any is tested (one DRAM round trip per
+  // group of views instead of one per view -- 47 % of this kernel's stall samples waited on these dependent loads)
+  for (int v0 = 0; v0 < nv; v0 += GSX_BWD_PF) {
     const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    float4 a[2][3] = {{z4, z4, z4}, {z4, z4, z4}};
-    bool tv[2];
+    float4 a[GSX_BWD_PF][3];
+    bool tv[GSX_BWD_PF];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < GSX_BWD_PF; ++u) {
       const int v = v0 + u;
-      tv[u] = GSX_BWD_PREFETCH ? (v < nv && ((tch >> v) & 1u)) : false;
+      tv[u] = v < nv && ((tch >> v) & 1u);
+      a[u][0] = a[u][1] = a[u][2] = z4;
       if (tv[u]) {
         const float4 *ga = bc.s[v].gacc + 3 * (size_t)i;
         a[u][0] = ga[0]; a[u][1] = ga[1]; a[u][2] = ga[2];
       }
     }
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
+    for (int u = 0; u < GSX_BWD_PF; ++u) {
       const int v = v0 + u;
-      if (!GSX_BWD_PREFETCH) {
-        tv[u] = v < nv && ((tch >> v) & 1u);
-        if (tv[u]) {
-          const float4 *ga = bc.s[v].gacc + 3 * (size_t)i;
-          a[u][0] = ga[0]; a[u][1] = ga[1]; a[u][2] = ga[2];
-        }
-      }
       if (!tv[u]) continue;
       const float4 a0 = a[u][0], a1 = a[u][1], a2 = a[u][2];
       const bool nz = (a0.x != 0.f) | (a0.y != 0.f) | (a0.z != 0.f) | (a0.w != 0.f) | (a1.x != 0.f) | (a1.y != 0.f) |
@@ -301,19 +310,19 @@ k_batch_bwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       st[4 * nslot] = a1.x; st[5 * nslot] = a1.y; st[6 * nslot] = a1.z; st[7 * nslot] = a1.w; st[8 * nslot] = a2.x;
     }
   }
-  float3 pw = make_float3(0.f, 0.f, 0.f);
-  float4 q = make_float4(1.f, 0.f, 0.f, 0.f);
-  float s0 = 0.f, s1 = 0.f, s2 = 0.f;
   if (act) {
-    pw = make_float3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
-    q = reinterpret_cast<const float4 *>(quat)[i];
-    s0 = scale[3 * i]; s1 = scale[3 * i + 1]; s2 = scale[3 * i + 2];
+    if (!GSX_BWD_EARLY) {
+      pw = make_float3(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+      q = reinterpret_cast<const float4 *>(quat)[i];
+      s0 = scale[3 * i]; s1 = scale[3 * i + 1]; s2 = scale[3 * i + 2];
+      b0r = band0[3 * i]; b0g = band0[3 * i + 1]; b0b = band0[3 * i + 2];
+    }
     float sig[6];
     sigma_from_qs(q.x, q.y, q.z, q.w, s0, s1, s2, sig);
     s_g[0 * BB + t] = pw.x; s_g[1 * BB + t] = pw.y; s_g[2 * BB + t] = pw.z;
 #pragma unroll
     for (int k = 0; k < 6; ++k) s_g[(3 + k) * BB + t] = sig[k];
-    s_g[9 * BB + t] = band0[3 * i]; s_g[10 * BB + t] = band0[3 * i + 1]; s_g[11 * BB + t] = band0[3 * i + 2];
+    s_g[9 * BB + t] = b0r; s_g[10 * BB + t] = b0g; s_g[11 * BB + t] = b0b;
     append_pairs(act, t, &s_n, s_pair);
   }
   __syncthreads();
