@@ -92,23 +92,27 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
   bool live = j < N && dkeys[j] != 0xffffffffu;
   int i = 0, cnt = 0;
   long long o = 0;
+  float u = 0.f, v = 0.f, ex = 0.f, ey = 0.f;
+  float4 r = make_float4(0.f, 0.f, 0.f, 1.f);
   if (live) {
     i = (int)perm[j];
-    cnt = touched[i];
     o = offsets[j];
+    cnt = touched[i];
+    // the three gathers through the permutation leave together (a key != ~0 means cnt > 0)
+    u = uv[(size_t)i * uv_stride]; v = uv[(size_t)i * uv_stride + 1];
+    if (tight) { ex = uv[(size_t)i * uv_stride + 2]; ey = uv[(size_t)i * uv_stride + 3]; }
+    r = radius[i];
     live = cnt > 0 && o + cnt <= capacity;   // overflow: detected by the host through the total
   }
   if (!__any_sync(0xffffffffu, live)) return;
   ObbSat s{};
   TileRange tr{0, -1, 0, -1};
   if (live) {
-    const float u = uv[(size_t)i * uv_stride], v = uv[(size_t)i * uv_stride + 1];
-    const float4 r = radius[i];
     const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
     s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
     tr = sat_aabb_range(s, w);
     // contributing-only lists (view-level path, uv_stride 4: the record is {u, v, extent_x, extent_y})
-    if (tight) clip_range_to_extent(tr, u, v, uv[(size_t)i * uv_stride + 2], uv[(size_t)i * uv_stride + 3]);
+    if (tight) clip_range_to_extent(tr, u, v, ex, ey);
   }
   const bool big = live && rect_cells(tr) > COOP_CELLS;
   if (live && !big) {
