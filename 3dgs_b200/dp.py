@@ -46,9 +46,18 @@ class GradExchange:
     """Buffers + collectives of one batch step.  drgb[v] is the dense d rgb of global view v ([N][3]); geom holds the
     allreduced arrays as views of one flat buffer (a single collective)."""
 
-    def __init__(self, N, n_views, world, rank, device, group=None, symmetric=False):
+    def __init__(self, N, n_views, world, rank, device, group=None, symmetric=False, interleaved=False):
+        """interleaved: buffer slot of (rank r, local view k) is k*world + r instead of the global view index r*vpr + k, so
+        that the k-th views of all ranks are contiguous and can be all-gathered on their own (all_gather_view) as soon
+        as they exist, under the compute of the following views.  slot_of_view maps global view -> slot."""
         self.N, self.n_views, self.world, self.rank, self.group = N, n_views, world, rank, group
         self.mine = shard_views(n_views, world, rank)
+        self.interleaved = bool(interleaved) and world > 1
+        vpr = n_views // world
+        self.vpr = vpr
+        slot = (lambda r, k: k * world + r) if self.interleaved else (lambda r, k: r * vpr + k)
+        self.slots_mine = [slot(rank, k) for k in range(vpr)]
+        self.slot_of_view = [slot(v // vpr, v % vpr) for v in range(n_views)]
         offs, off = {}, 0
         for nm, w in GEOM:
             offs[nm] = off
@@ -82,7 +91,7 @@ class GradExchange:
 
     def view_targets(self, k):
         """(multicast pointer or 0, peer pointers) of the [N][3] block of this rank's k-th view in every rank's buffer"""
-        byte_off = self.mine[k] * self.N * 3 * 4
+        byte_off = self.slots_mine[k] * self.N * 3 * 4
         if self.transport == "multimem":
             return int(self.hdl.multicast_ptr) + byte_off, []
         return 0, [int(p) + byte_off for p in self.hdl.buffer_ptrs]
@@ -94,7 +103,24 @@ class GradExchange:
 
     def local_drgb(self, k):
         """buffer of this rank's k-th view"""
-        return self.drgb[self.mine[k]]
+        return self.drgb[self.slots_mine[k]]
+
+    def in_slot_order(self, per_view):
+        """a per-global-view list (camera positions) re-ordered to the buffer's slot order"""
+        out = [None] * self.n_views
+        for v, x in enumerate(per_view):
+            out[self.slot_of_view[v]] = x
+        return out
+
+    def all_gather_view(self, k):
+        """all-gather of the ranks' k-th views alone (interleaved layout: one contiguous [world][N][3] block)"""
+        assert self.interleaved
+        blk = self.drgb[k * self.world:(k + 1) * self.world]
+        try:
+            dist.all_gather_into_tensor(blk.view(-1), blk[self.rank].view(-1), group=self.group)
+        except (RuntimeError, NotImplementedError):         # backends without the flat variant
+            parts = [blk[r].view(-1) for r in range(self.world)]
+            dist.all_gather(parts, blk[self.rank].view(-1).clone(), group=self.group)
 
     def link_bytes_per_step(self):
         """payload bytes: (all-gathered, allreduced)"""
@@ -102,6 +128,10 @@ class GradExchange:
 
     def all_gather_drgb(self):
         if self.world == 1:
+            return
+        if self.interleaved:
+            for k in range(self.vpr):
+                self.all_gather_view(k)
             return
         flat = self.drgb.view(self.world, -1)               # blocked sharding: rank r's views are row r
         try:
@@ -140,8 +170,18 @@ class ViewParallel:
         N = gaussians.N
         if gaussians.grads is None:
             gaussians.zero_grads()
+        import os
+        # symmetric transport: fuse the peer stores into the extraction kernel (1) or push from a side stream (0)
+        self.fused_extract = os.environ.get("GSX_DP_FUSED", "1") == "1"
+        # d rgb gather: "nccl" (default) = one NCCL all-gather per local view on the side stream, issued as soon as the
+        # view's backward is done (interleaved buffer layout), under the compute of the following views; "fused" = peer
+        # stores from the extraction kernel.  Measured on B200 (C4, v12 kernels): nccl 771 / 1323 / 1892 views/s at
+        # 2 / 4 / 8 GPUs, fused 743 / 1248 / 1614 -- the stores of the fused kernel back-pressure the compositing.
+        self.nccl_gather = os.environ.get("GSX_DP_GATHER", "nccl") == "nccl"
         if world > 1:
-            self.ex = GradExchange(N, len(views_all), world, rank, dev, group, symmetric=symmetric)
+            self.ex = GradExchange(N, len(views_all), world, rank, dev, group, symmetric=symmetric,
+                                   interleaved=self.nccl_gather)
+            self.campos_buf = self.ex.in_slot_order(self.campos_all)
             for nm, _ in GEOM:                              # the geometry gradients live in the flat allreduce buffer
                 gaussians.grads[nm] = self.ex.geom[nm]
             self.comm = torch.cuda.Stream(device=dev, priority=-1)
@@ -150,14 +190,6 @@ class ViewParallel:
         else:
             self.ex = None
         self.timing = None          # set to {} to collect per-phase CUDA-event times (ms) of the next step()
-        import os
-        # symmetric transport: fuse the peer stores into the extraction kernel (1) or push from a side stream (0)
-        self.fused_extract = os.environ.get("GSX_DP_FUSED", "1") == "1"
-        # GSX_DP_GATHER=nccl: NCCL all-gather on the side stream + in-switch allreduce kernel (hybrid)
-        # (measured on 8 B200: with 8 ranks storing at once the fused stores back-pressure the views phase by 0.75 ms, while
-        # an NCCL all-gather on the side stream hides under the per-Gaussian backward: 1688 vs 1614 views/s; with <= 4
-        # ranks the fused stores overlap the next views' compositing and win)
-        self.nccl_gather = os.environ.get("GSX_DP_GATHER", "nccl" if world >= 8 else "fused") == "nccl"
 
     def _mark(self, name, stream):
         if self.timing is not None:
@@ -190,12 +222,15 @@ class ViewParallel:
             gi = grad_images[k] if isinstance(grad_images, (list, tuple)) else grad_images
             r.batch_backward_view(k, gi)
             r.batch_extract_view_rgb_grad(k, self.ex.local_drgb(k))
+            if self.ex.interleaved:
+                self._gather_view(k, main)
         self.ev_views.record(main)
         self._mark("views", main)
         with torch.cuda.stream(self.comm):                  # all-gather of d rgb overlaps the per-Gaussian backward
             self.comm.wait_event(self.ev_views)
-            self._mark("g0", self.comm)
-            self.ex.all_gather_drgb()
+            if not self.ex.interleaved:
+                self._mark("g0", self.comm)
+                self.ex.all_gather_drgb()
             self._mark("g1", self.comm)
             self.ev_gathered.record(self.comm)
         r.batch_backward_params(g, OVER | NO_SH)            # geometry gradients -> flat buffer
@@ -209,11 +244,20 @@ class ViewParallel:
             self.ev_reduced.record(self.comm)
         main.wait_event(self.ev_gathered)
         self._mark("s0", main)
-        sh_grads_from_view_rgb(g.xyz, self.campos_all, self.ex.drgb, self.l_max, g.grads["sh"], g.grads["band0"],
+        sh_grads_from_view_rgb(g.xyz, self.campos_buf, self.ex.drgb, self.l_max, g.grads["sh"], g.grads["band0"],
                                g.sh_stride, OVER)
         self._mark("s1", main)
         main.wait_event(self.ev_reduced)
         self._mark("end", main)
+
+    def _gather_view(self, k, main):
+        """side stream: all-gather of the ranks' k-th views, after this rank's extraction of view k"""
+        self.ev_views.record(main)
+        with torch.cuda.stream(self.comm):
+            self.comm.wait_event(self.ev_views)
+            if k == 0:
+                self._mark("g0", self.comm)
+            self.ex.all_gather_view(k)
 
     def _step_symmetric(self, grad_images, on_image):
         """Same exchange with the all-gather fused into the extraction kernel (stores into every rank's buffer over
@@ -235,6 +279,7 @@ class ViewParallel:
             arr = (C.c_void_p * max(len(peers), 1))(*peers) if peers else None
             if self.nccl_gather:
                 r.batch_extract_view_rgb_grad(k, ex.local_drgb(k))
+                self._gather_view(k, main)
             elif self.fused_extract:
                 # extraction + all-gather in ONE kernel: rows go from the packed gradients straight to every rank
                 check(lib().gsx_batch_extract_view_rgb_grad_peers(r.h, int(k), C.c_void_p(mc), arr, len(peers), st))
@@ -251,11 +296,7 @@ class ViewParallel:
                                                         len(peers), C.c_void_p(self.comm.cuda_stream)))
         self._mark("views", main)
         if self.nccl_gather:
-            self.ev_views.record(main)
             with torch.cuda.stream(self.comm):
-                self.comm.wait_event(self.ev_views)
-                self._mark("g0", self.comm)
-                ex.all_gather_drgb()
                 self._mark("g1", self.comm)
                 self.ev_gathered.record(self.comm)
         elif self.fused_extract:
@@ -279,7 +320,7 @@ class ViewParallel:
             self._mark("r1", self.comm)
             self.ev_reduced.record(self.comm)
         self._mark("s0", main)
-        sh_grads_from_view_rgb(g.xyz, self.campos_all, ex.drgb, self.l_max, g.grads["sh"], g.grads["band0"],
+        sh_grads_from_view_rgb(g.xyz, self.campos_buf, ex.drgb, self.l_max, g.grads["sh"], g.grads["band0"],
                                g.sh_stride, OVER)
         self._mark("s1", main)
         main.wait_event(self.ev_reduced)

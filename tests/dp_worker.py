@@ -38,8 +38,12 @@ def main():
     want = {k: t.clone() for k, t in gd0.grads.items()}
     r0.close()
     report = []
-    for symmetric, fused in ((False, "1"), (True, "1"), (True, "0")):
+    # (symmetric memory?, d rgb gather, fused extraction?): NCCL only with both buffer layouts, then the hybrid default
+    # (per-view NCCL gathers + in-switch allreduce) and the two peer-store variants
+    for symmetric, gather, fused in ((False, "nccl", "1"), (False, "fused", "1"), (True, "nccl", "1"), (True, "fused", "1"),
+                                     (True, "fused", "0")):
         os.environ["GSX_DP_FUSED"] = fused
+        os.environ["GSX_DP_GATHER"] = gather
         gd = mk()
         gd.zero_grads()
         r = H.Rasterizer(N, W, Hh, instance_capacity=8 * N)
@@ -55,7 +59,8 @@ def main():
             rel = float((a - b).norm() / (b.norm() + 1e-30))
             worst = max(worst, rel)
             assert rel <= 1e-3, f"transport {vp.ex.transport}: d {k} rel err {rel}"
-        report.append(f"{vp.ex.transport}{"" if not symmetric else ("-fused" if vp.fused_extract else "-push")}:{worst:.1e}" + (f"(no symm: {vp.ex.why_not})" if symmetric and vp.ex.transport == "nccl" else ""))
+        how = ("-pergather" if vp.nccl_gather else "") if not symmetric else ("-hybrid" if vp.nccl_gather else ("-fused" if vp.fused_extract else "-push"))
+        report.append(f"{vp.ex.transport}{how}:{worst:.1e}" + (f"(no symm: {vp.ex.why_not})" if symmetric and vp.ex.transport == "nccl" else ""))
         r.close()
     if rank == 0:
         print("DP_OK world=%d %s" % (world, " ".join(report)), flush=True)

@@ -48,14 +48,15 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, out_dir):
+def _worker(rank, world, port, out_dir, interleaved):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from oracle import golden as G
         gs, S, g, cams, gis = _scene()
         dp = gs.dp
-        ex = dp.GradExchange(N, N_VIEWS, world, rank, "cpu")
+        ex = dp.GradExchange(N, N_VIEWS, world, rank, "cpu", interleaved=interleaved)
+        assert ex.slots_mine == ([rank, world + rank] if interleaved else ex.mine)
         assert ex.mine == dp.shard_views(N_VIEWS, world, rank) == list(range(rank * 2, rank * 2 + 2))
         geom = {nm: np.zeros((N, w) if w > 1 else (N,), np.float32) for nm, w in dp.GEOM}
         key = dict(xyz="xyz", scale="scale", quaternion="quat", opacity="opacity")
@@ -72,11 +73,11 @@ def _worker(rank, world, port, out_dir):
         nsh = (L_MAX + 1) ** 2 - 1
         sh_g, b0_g = np.zeros((N, nsh, 3), np.float32), np.zeros((N, 3), np.float32)
         for v in range(N_VIEWS):
-            d = ex.drgb[v].numpy()
+            d = ex.drgb[ex.slot_of_view[v]].numpy()
             a, b, _ = G.sh_backward(g["xyz"], g["band0"], g["sh"][:, :nsh], cams[v]["campos"], d, L_MAX)
             sh_g += a.reshape(N, nsh, 3)
             b0_g += b
-        np.savez(os.path.join(out_dir, f"rank{rank}.npz"), sh=sh_g, band0=b0_g, drgb=ex.drgb.numpy(),
+        np.savez(os.path.join(out_dir, f"rank{rank}.npz"), sh=sh_g, band0=b0_g, drgb=ex.drgb.numpy()[ex.slot_of_view],
                  **{nm: ex.geom[nm].numpy() for nm in geom})
     finally:
         dist.destroy_process_group()
@@ -99,9 +100,11 @@ def test_shard_views():
 
 
 @pytest.mark.timeout(300)
-def test_view_parallel_exchange_world2(tmp_path):
+@pytest.mark.parametrize("interleaved", [False, True])
+def test_view_parallel_exchange_world2(tmp_path, interleaved):
+    """blocked buffer layout (one all-gather after the views) and interleaved (one all-gather per local view)"""
     world = 2
-    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path), interleaved), nprocs=world, join=True)
     gs, S, g, cams, gis = _scene()
     tot, drgb_all = None, []
     for v in range(N_VIEWS):
