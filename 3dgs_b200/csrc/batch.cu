@@ -184,8 +184,10 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     // exact tile count (F7 window + SAT): small rectangles per thread, large ones by the whole warp
     const bool big = active && rect_cells(tr) > COOP_CELLS;
     if (active && !big) {
-      for (int tx = tr.x0; tx <= tr.x1; ++tx)
-        for (int ty = tr.y0; ty <= tr.y1; ++ty) cnt += sat_tile_rot(so, tx, ty) ? 1 : 0;
+      for (int tx = tr.x0; tx <= tr.x1; ++tx) {
+        const SatCol col = sat_col(so, tx);
+        for (int ty = tr.y0; ty <= tr.y1; ++ty) cnt += sat_cell(so, col, ty) ? 1 : 0;
+      }
     }
     unsigned bm = __ballot_sync(0xffffffffu, big);
     while (bm) {

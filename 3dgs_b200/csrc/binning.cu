@@ -46,8 +46,10 @@ __device__ __forceinline__ int count_tiles(float u, float v, float4 r, int ntx, 
   const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
   const TileRange tr = sat_aabb_range(s, w);
   int c = 0;
-  for (int tx = tr.x0; tx <= tr.x1; ++tx)
-    for (int ty = tr.y0; ty <= tr.y1; ++ty) c += sat_tile_rot(s, tx, ty) ? 1 : 0;
+  for (int tx = tr.x0; tx <= tr.x1; ++tx) {
+    const SatCol col = sat_col(s, tx);
+    for (int ty = tr.y0; ty <= tr.y1; ++ty) c += sat_cell(s, col, ty) ? 1 : 0;
+  }
   return c;
 }
 
@@ -116,13 +118,15 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
   }
   const bool big = live && rect_cells(tr) > COOP_CELLS;
   if (live && !big) {
-    for (int tx = tr.x0; tx <= tr.x1; ++tx)
+    for (int tx = tr.x0; tx <= tr.x1; ++tx) {
+      const SatCol col = sat_col(s, tx);
       for (int ty = tr.y0; ty <= tr.y1; ++ty)
-        if (sat_tile_rot(s, tx, ty)) {
+        if (sat_cell(s, col, ty)) {
           tiles[o] = (uint32_t)(ty * ntx + tx);
           vals[o] = (uint32_t)i;
           ++o;
         }
+    }
   }
   unsigned bm = __ballot_sync(0xffffffffu, big);
   while (bm) {

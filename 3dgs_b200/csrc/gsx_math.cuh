@@ -301,12 +301,27 @@ __device__ __forceinline__ void clip_range_to_extent(TileRange &r, float u, floa
   r.y0 = max(r.y0, (int)fminf(fmaxf(floorf((v - ey) * 0.0625f), -big), big));
   r.y1 = min(r.y1, (int)fmaxf(fminf(floorf((v + ey) * 0.0625f), big), -big));
 }
-// axes 2 and 3 only (axes 0/1 already decided by sat_aabb_range)
-__device__ __forceinline__ bool sat_tile_rot(const ObbSat &s, int tx, int ty) {
-  const float l = (float)tx * 16.0f, r = (float)(tx + 1) * 16.0f, t = (float)ty * 16.0f, b = (float)(ty + 1) * 16.0f;
-  if (!sat_axis(s.a2x, s.a2y, s.lo2, s.hi2, l, r, t, b)) return false;
-  return sat_axis(s.a3x, s.a3y, s.lo3, s.hi3, l, r, t, b);
+// Axes 2 and 3 only (axes 0/1 already decided by sat_aabb_range), separable form.  The reference takes the min / max of
+// the four corner projections fl(X + Y), X in {ax l, ax r}, Y in {ay t, ay b} (culling.cu:112-146).  Rounding is
+// monotone, so those extremes are exactly fl(min X + min Y) and fl(max X + max Y): the X part is per tile column, the Y
+// part per tile row, and a tile costs 2 multiplies + 2 min/max + 2 adds per axis instead of 4 + 6 + 4 -- with the same
+// bits as sat_axis (tests: per-tile lists bit-exact against the oracle and against the reference's own kernels).
+struct SatCol { float x2mn, x2mx, x3mn, x3mx; };
+__device__ __forceinline__ SatCol sat_col(const ObbSat &s, int tx) {
+  const float l = (float)tx * 16.0f, r = (float)(tx + 1) * 16.0f;
+  const float a = mul_(s.a2x, l), b = mul_(s.a2x, r), c = mul_(s.a3x, l), d = mul_(s.a3x, r);
+  SatCol o;
+  o.x2mn = fminf(a, b); o.x2mx = fmaxf(a, b); o.x3mn = fminf(c, d); o.x3mx = fmaxf(c, d);
+  return o;
 }
+__device__ __forceinline__ bool sat_cell(const ObbSat &s, const SatCol &c, int ty) {
+  const float t = (float)ty * 16.0f, b = (float)(ty + 1) * 16.0f;
+  const float y2t = mul_(s.a2y, t), y2b = mul_(s.a2y, b);
+  if (add_(c.x2mn, fminf(y2t, y2b)) > s.hi2 || add_(c.x2mx, fmaxf(y2t, y2b)) < s.lo2) return false;
+  const float y3t = mul_(s.a3y, t), y3b = mul_(s.a3y, b);
+  return !(add_(c.x3mn, fminf(y3t, y3b)) > s.hi3 || add_(c.x3mx, fmaxf(y3t, y3b)) < s.lo3);
+}
+__device__ __forceinline__ bool sat_tile_rot(const ObbSat &s, int tx, int ty) { return sat_cell(s, sat_col(s, tx), ty); }
 
 // Warp-cooperative evaluation of ONE lane's tile rectangle (Gaussians covering many tiles would otherwise keep a
 // single lane busy for hundreds of SAT tests while 31 wait): the leader's SAT constants and rectangle are broadcast,
