@@ -29,7 +29,7 @@ SYMBOLS = [
     "gsx_batch_reserve", "gsx_batch_forward_params", "gsx_batch_forward_view", "gsx_batch_backward_view",
     "gsx_batch_backward_params", "gsx_batch_render_host", "gsx_batch_extract_view_rgb_grad",
     "gsx_sh_grads_from_view_rgb", "gsx_ctx_build_sorted_keys", "gsx_batch_extract_view_rgb_grad_peers",
-    "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers",
+    "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers", "gsx_adam_step", "gsx_adam_step_fused",
 ]
 
 
@@ -60,6 +60,14 @@ class GsxState(C.Structure):
                 ("depth", C.c_void_p), ("mask", C.c_void_p), ("tiles_touched", C.c_void_p),
                 ("sorted_gaussians", C.c_void_p), ("sorted_keys", C.c_void_p), ("ranges", C.c_void_p),
                 ("num_instances", C.c_void_p), ("packed_grads", C.c_void_p)]
+
+
+class GsxAdamGroup(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("width", C.c_int), ("lr", C.c_float)]
+
+
+GSX_ADAM_MAX_GROUPS = 8
 
 
 class GsxError(RuntimeError):

@@ -1,4 +1,5 @@
 // compat.cu -- the 15 reference-named C++ entry points (include/gsplat_cuda/cuda_forward.cuh, cuda_backward.cuh)
+// and adam_step (optimizer.cuh)
 // on top of the gsx C ABI, with the reference's error convention: any failure prints and exit(EXIT_FAILURE)
 // (reference cuda/checks.cuh:17-38).
 #include <stdio.h>
@@ -6,6 +7,7 @@
 
 #include "../../include/gsplat_cuda/cuda_backward.cuh"
 #include "../../include/gsplat_cuda/cuda_forward.cuh"
+#include "../../include/gsplat_cuda/optimizer.cuh"
 #include "../../include/gsx.h"
 
 static void gsx_or_die(int rc, const char *fn) {
@@ -109,4 +111,12 @@ void render_image_backward(const float *const uvs, const float *const opacity, c
   DIE_UNLESS(gsx_render_image_backward(uvs, opacity, conic, rgb, background_opacity, sorted_splats, splat_range_by_tile,
                                        num_splats_per_pixel, final_weight_per_pixel, grad_image, image_width,
                                        image_height, 0, grad_rgb, grad_opacity, grad_uv, grad_conic, stream));
+}
+
+// SURVEY 8f rank 2 (reference cuda/optimizer.cu:30-44)
+void adam_step(float *params, float *const param_grads, float *exp_avg, float *exp_avg_sq, const float lr,
+               const float b1, const float b2, const float eps, const float bias1, const float bias2, const int N,
+               const int S, cudaStream_t stream) {
+  DIE_UNLESS(gsx_adam_step(params, param_grads, exp_avg, exp_avg_sq, lr, b1, b2, eps, bias1, bias2, (long long)N * S,
+                           stream));
 }

@@ -187,6 +187,44 @@ def compute_camera_space_points_backward(xyz_w, view, xyz_c_grad, xyz_w_grad=Non
 
 
 # ------------------------------------------------------------------------------------------------ sort primitives
+# ------------------------------------------------------------------------------------------------ optimiser (8f rank 2)
+def adam_step(params, param_grads, exp_avg, exp_avg_sq, lr, b1, b2, eps, bias1, bias2):
+    """adam_step of the reference (include/gsplat_cuda/optimizer.cuh:27, cuda/optimizer.cu:30-44): every float of
+    `params` is updated in place (N*S elements), moments in place."""
+    _chk_f32(params, param_grads, exp_avg, exp_avg_sq)
+    n = params.numel()
+    assert param_grads.numel() == n and exp_avg.numel() == n and exp_avg_sq.numel() == n
+    check(lib().gsx_adam_step(_ptr(params), _ptr(param_grads), _ptr(exp_avg), _ptr(exp_avg_sq), f32(lr), f32(b1), f32(b2),
+                              f32(eps), f32(bias1), f32(bias2), C.c_longlong(n), _stream()))
+    return params
+
+
+def adam_step_fused(groups, mask, b1, b2, eps, bias1, bias2, uv_grad=None, uv_grad_accum=None, grad_accum_dur=None):
+    """TrainerImpl::optimizer_step of the reference (cuda/trainer.cu:1027-1158) in one launch.
+    groups: list of (param [N][w], grad [N][w], exp_avg, exp_avg_sq, lr), gradients indexed by the global Gaussian
+    index; mask: uint8 [N] or None; Gaussians with mask 0 keep parameters and moments.  With uv_grad [N][2] the
+    densification accumulators are advanced for the same Gaussians (trainer.cu:1138-1157)."""
+    assert 0 < len(groups) <= _ffi.GSX_ADAM_MAX_GROUPS
+    n = groups[0][0].shape[0]
+    arr = (_ffi.GsxAdamGroup * len(groups))()
+    for k, (p, g, m, v, lr) in enumerate(groups):
+        _chk_f32(p, g, m, v)
+        assert p.shape[0] == n and g.numel() == p.numel() and m.numel() == p.numel() and v.numel() == p.numel()
+        for t in (p, g, m, v):
+            assert t.is_cuda and t.is_contiguous()
+        arr[k].param, arr[k].grad = p.data_ptr(), g.data_ptr()
+        arr[k].exp_avg, arr[k].exp_avg_sq = m.data_ptr(), v.data_ptr()
+        arr[k].width = p.numel() // n if n else 1
+        arr[k].lr = float(lr)
+    if mask is not None:
+        assert mask.dtype in (torch.uint8, torch.bool) and mask.numel() == n
+    if uv_grad is not None:
+        assert uv_grad.dtype == torch.float32 and uv_grad.numel() == 2 * n
+        assert uv_grad_accum.dtype == torch.float32 and grad_accum_dur.dtype == torch.int32
+    check(lib().gsx_adam_step_fused(arr, len(groups), _ptr(mask), n, f32(b1), f32(b2), f32(eps), f32(bias1), f32(bias2),
+                                    _ptr(uv_grad), _ptr(uv_grad_accum), _ptr(grad_accum_dur), _stream()))
+
+
 def sort_pairs_u64(keys, vals, key_bits=64):
     """keys: int64 CUDA tensor holding uint64 bit patterns, vals: int32.  Returns sorted copies."""
     n = keys.numel()

@@ -89,3 +89,23 @@ def camera_space_points_backward(view, xyz_c_grad, xyz_w_grad=None):
     g = _d(xyz_c_grad)
     return _h(H.compute_camera_space_points_backward(g, _d(view).reshape(16), g,
                                                      _d(xyz_w_grad) if xyz_w_grad is not None else None))
+
+
+# ------------------------------------------------------------------------------------------------ optimiser (8f rank 2)
+def adam_step(param, grad, exp_avg, exp_avg_sq, lr, b1, b2, eps, bias1, bias2):
+    p, m, v = _d(param), _d(exp_avg), _d(exp_avg_sq)
+    H.adam_step(p, _d(grad), m, v, lr, b1, b2, eps, bias1, bias2)
+    return _h(p), _h(m), _h(v)
+
+
+def adam_step_fused(groups, mask, b1, b2, eps, bias1, bias2, uv_grad=None, uv_grad_accum=None, grad_accum_dur=None):
+    """groups: list of (param, grad, exp_avg, exp_avg_sq, lr) numpy arrays [N][w]; returns the list of updated
+    (param, exp_avg, exp_avg_sq) and, with uv_grad, the advanced (uv_grad_accum, grad_accum_dur)."""
+    dev = [(_d(p), _d(g), _d(m), _d(v), lr) for p, g, m, v, lr in groups]
+    mk = None if mask is None else _d(mask, torch.uint8)
+    acc = dur = None
+    if uv_grad is not None:
+        acc, dur = _d(uv_grad_accum), _d(grad_accum_dur, torch.int32)
+    H.adam_step_fused(dev, mk, b1, b2, eps, bias1, bias2, _d(uv_grad) if uv_grad is not None else None, acc, dur)
+    out = [(_h(p), _h(m), _h(v)) for p, _, m, v, _ in dev]
+    return (out, (_h(acc), _h(dur))) if uv_grad is not None else out

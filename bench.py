@@ -371,6 +371,34 @@ def main():
                  "peak_source": peak_src if roof["bound"] == "hbm" else "FP32 FMA peak measured in this run (gsx_measure_fp32_tflops)",
                  "share_of_view": round(stage_ms[top] / sum(stage_ms.values()), 3)})
 
+    # ---- next row, outside the timed region: the optimiser step that consumes these gradients --------
+    # gsx_adam_step_fused: every parameter group + the densification accumulators in one launch over the global-index
+    # gradient buffers (the reference: 16-19 compactions + 5-6 adam_step launches + 16-19 scatters, trainer.cu:1027-1158)
+    next_rows = {}
+    if world == 1:
+        names = ["xyz", "scale", "quaternion", "opacity", "band0"] + (["sh"] if gd.sh_stride else [])
+        lrs = dict(xyz=1.6e-4, scale=5e-3, quaternion=1e-3, opacity=5e-2, band0=2.5e-3, sh=1.25e-4)
+        pcl = {nm: getattr(gd, nm).clone().view(N, -1) for nm in names}
+        groups = [(pcl[nm], gviews[nm].view(N, -1), torch.zeros_like(pcl[nm]), torch.zeros_like(pcl[nm]), lrs[nm]) for nm in names]
+        uvg = torch.randn((N, 2), device=dev) * 1e-4
+        uva, dur = torch.zeros(N, device=dev), torch.zeros(N, device=dev, dtype=torch.int32)
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps_a = 10
+        for it in range(3 + reps_a):
+            if it == 3:
+                a0.record()
+            Hh.adam_step_fused(groups, None, 0.9, 0.999, 1e-8, 1 - 0.9 ** (it + 1), 1 - 0.999 ** (it + 1), uvg, uva, dur)
+        a1.record()
+        torch.cuda.synchronize()
+        adam_ms = a0.elapsed_time(a1) / reps_a
+        adam_bytes = 28 * sum(p_.numel() for p_, *_ in groups) + 24 * N   # p,g,m,v read + p,m,v written; per Gaussian uv_grad 8 + accumulator 4+4 + counter 4+4
+        assert int(dur[0].item()) == 3 + reps_a and bool(torch.isfinite(pcl["xyz"]).all().item())
+        next_rows["optimizer_step"] = {"ms": round(adam_ms, 4), "launches": 1, "bound": "hbm", "bytes": adam_bytes,
+                                       "achieved": round(adam_bytes / adam_ms / 1e6, 1), "peak": round(hbm_peak, 1), "unit": "GB/s",
+                                       "frac": round(adam_bytes / adam_ms / 1e6 / hbm_peak, 4),
+                                       "what": "gsx_adam_step_fused over all 6 parameter groups (59 floats/Gaussian) + densification accumulators, every Gaussian visible"}
+        del pcl, groups, uvg, uva, dur
+
     views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
     if world > 1:
         ga_, ar_ = vp.ex.link_bytes_per_step()
@@ -397,6 +425,7 @@ def main():
                 "h2d_bytes_per_step": N_VIEWS * (W * H * 3 * 4 + 200), "d2h_bytes_per_step": N_VIEWS * W * H * 3 * 4},
         "gpu_launches": (launches_per_view * nv + 2) * args.steps * world,
         "exchange_ms": exch, "exchange_transport": (vp.ex.transport if world > 1 else None), "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": round(fp32_peak, 2),
+        "next_rows": next_rows,
     }
     if world == 1 and not args.no_cpu_baseline:
         from oracle import golden as G

@@ -262,6 +262,31 @@ int gsx_measure_fp32_tflops(float *tflops_host);
 int gsx_render_view_host(gsx_ctx_t *ctx, const gsx_view_t *view_host, const gsx_params_t *params, int N,
                          const float *grad_image_host, float *image_host, const gsx_grads_t *grads, void *stream);
 
+/* ---- Adam on the path's global-index gradients (the step right after the backward) ----
+ * gsx_adam_step replaces adam_step (include/gsplat_cuda/optimizer.cuh:27, cuda/optimizer.cu:30-44) on one array of
+ * n_floats = N*S elements: m = b1 m + (1-b1) g; v = b2 v + (1-b2) g^2; p -= lr (m/bias1) / (sqrt(v/bias2) + eps);
+ * a NaN gradient counts as 0 (optimizer.cu:14-16).
+ * gsx_adam_step_fused replaces TrainerImpl::optimizer_step (cuda/trainer.cu:1027-1158) in ONE launch: every parameter
+ * group [N][width] with its own learning rate, gradients indexed by the GLOBAL Gaussian index (as gsx_backward /
+ * gsx_batch_backward_params write them; the reference compacts to [P] first).  mask [N] (the cull mask, uint8) or
+ * null: a Gaussian with mask 0 keeps parameters and both moments untouched -- the effect of the reference's
+ * compact -> adam_step -> scatter.  uv_grad [N][2] (8-byte aligned) or null: when given, uv_grad_accum[i] +=
+ * |uv_grad[i]| and grad_accum_dur[i] += 1 for the same Gaussians (trainer.cu:1138-1157). */
+#define GSX_ADAM_MAX_GROUPS 8
+typedef struct {
+  float *param;          /* [N][width] */
+  const float *grad;     /* [N][width] */
+  float *exp_avg;        /* [N][width] */
+  float *exp_avg_sq;     /* [N][width] */
+  int width;             /* floats per Gaussian: 3 xyz, 3 scale, 4 quaternion, 1 opacity, 3 band0, 3(n-1) sh */
+  float lr;
+} gsx_adam_group_t;
+int gsx_adam_step(float *params, const float *param_grads, float *exp_avg, float *exp_avg_sq, float lr, float b1,
+                  float b2, float eps, float bias1, float bias2, long long n_floats, void *stream);
+int gsx_adam_step_fused(const gsx_adam_group_t *groups_host, int n_groups, const uint8_t *mask, int N, float b1,
+                        float b2, float eps, float bias1, float bias2, const float *uv_grad, float *uv_grad_accum,
+                        int *grad_accum_dur, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

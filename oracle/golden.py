@@ -295,3 +295,33 @@ def backward(vw, st, grad_image, grads=None, want_intermediates=False):
     if want_intermediates:
         return grads, {k: v[:P] for k, v in inter.items()}
     return grads
+
+
+# ------------------------------------------------------------------------------------------------ optimiser (8f rank 2)
+def adam_step(param, grad, exp_avg, exp_avg_sq, lr, b1, b2, eps, bias1, bias2):
+    """adam_kernel, cuda/optimizer.cu:6-28.  Returns (param, exp_avg, exp_avg_sq) as new arrays."""
+    p, m, v = _f(param).copy(), _f(exp_avg).copy(), _f(exp_avg_sq).copy()
+    g = _f(grad)
+    lib().gold_adam_step(_p(p), _p(g), _p(m), _p(v), C.c_float(lr), C.c_float(b1), C.c_float(b2), C.c_float(eps),
+                         C.c_float(bias1), C.c_float(bias2), C.c_longlong(p.size))
+    return p, m, v
+
+
+def adam_step_masked(param, grad, exp_avg, exp_avg_sq, mask, lr, b1, b2, eps, bias1, bias2):
+    """One parameter group of TrainerImpl::optimizer_step (cuda/trainer.cu:1027-1085), global-index gradients."""
+    p, m, v = _f(param).copy(), _f(exp_avg).copy(), _f(exp_avg_sq).copy()
+    g = _f(grad)
+    n = p.shape[0]
+    width = p.size // n if n else 1
+    mk = None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8)
+    lib().gold_adam_step_masked(_p(p), _p(g), _p(m), _p(v), width, _p(mk), n, C.c_float(lr), C.c_float(b1),
+                                C.c_float(b2), C.c_float(eps), C.c_float(bias1), C.c_float(bias2))
+    return p, m, v
+
+
+def accumulate_uv_grad(uv_grad, mask, uv_grad_accum, grad_accum_dur):
+    """cuda/trainer.cu:1138-1157.  Returns the advanced (uv_grad_accum, grad_accum_dur)."""
+    acc, dur = _f(uv_grad_accum).copy(), _i(grad_accum_dur).copy()
+    mk = None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8)
+    lib().gold_accumulate_uv_grad(_p(_f(uv_grad)), _p(mk), acc.shape[0], _p(acc), _p(dur))
+    return acc, dur

@@ -24,5 +24,12 @@ r.batch_reserve(nv)
 gi = torch.as_tensor(S.grad_image(W, Hh)).cuda()
 for _ in range(nb):
     r.batch_step(views, gd, gi, flags=2)
+# the step after the path: one fused Adam launch over the gradients just produced
+names = ["xyz", "scale", "quaternion", "opacity", "band0", "sh"]
+groups = [(getattr(gd, nm).view(N, -1), gd.grads[nm].view(N, -1), torch.zeros_like(getattr(gd, nm)).view(N, -1),
+           torch.zeros_like(getattr(gd, nm)).view(N, -1), 1e-4) for nm in names]
+vis = (torch.rand(N, device="cuda") < 0.52).to(torch.uint8)   # C4: 52 % of the Gaussians survive a view's cull
+H.adam_step_fused(groups, vis, 0.9, 0.999, 1e-8, 0.1, 0.001, torch.zeros((N, 2), device="cuda"),
+                  torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda", dtype=torch.int32))
 torch.cuda.synchronize()
 print("ok", r.stats())

@@ -2,7 +2,8 @@
 
 Each check_* takes a backend `B` exposing the F1..F15 functions with numpy in / numpy out (oracle/golden.py for
 the CPU oracle, the `3dgs_b200` host module for the CUDA path through the C-ABI), so the same vectors pin
-both.  Citations: /root/reference/tests/cuda_forward_test.cpp (fwd) and cuda_backward_test.cpp (bwd).
+both.  Citations: /root/reference/tests/cuda_forward_test.cpp (fwd), cuda_backward_test.cpp (bwd) and optimizer_test.cpp
+(the Adam step that follows the path).
 """
 import numpy as np
 
@@ -293,7 +294,25 @@ def check_render_backward(B):  # cuda_backward_test.cpp:678-890, tol 1e-3
     np.testing.assert_allclose(g_rgb, _fd(lambda r: L(f64(uv), f64(opacity), f64(con), r), rgb, 1e-6), atol=1e-3)
 
 
+def check_adam_step(B):  # tests/optimizer_test.cpp:18-140 (AdamOptimizerTest.Correctness), tolerance 1e-6
+    N, lr, b1, b2, eps = 1024, np.float32(0.001), np.float32(0.9), np.float32(0.999), np.float32(1e-8)
+    param = np.arange(N, dtype=np.float32)
+    grad = (np.float32(0.1) * np.arange(1, N + 1, dtype=np.float32)).astype(np.float32)
+    zero = np.zeros(N, np.float32)
+    one = np.float32(1.0)
+    p, m, v = B.adam_step(param, grad, zero, zero, lr, b1, b2, eps, one - b1, one - b2)
+    em = (b1 * zero + (one - b1) * grad).astype(np.float32)
+    ev = (b2 * zero + (one - b2) * grad * grad).astype(np.float32)
+    m_hat = (em / (one - b1)).astype(np.float32)
+    v_hat = (ev / (one - b2)).astype(np.float32)
+    ep = (param + (-lr * m_hat / (np.sqrt(v_hat) + eps)).astype(np.float32)).astype(np.float32)
+    # the reference compares with an absolute 1e-6 on parameters up to 1023 (ulp 6e-5): i.e. bit-equal there
+    np.testing.assert_allclose(p, ep, atol=1e-6, rtol=1.2e-7)
+    np.testing.assert_allclose(m, em, atol=1e-6)
+    np.testing.assert_allclose(v, ev, atol=1e-6, rtol=2e-7)
+
+
 ALL = [check_compute_sigma, check_project_to_screen, check_culling, check_camera_space_points, check_compute_conic,
        check_sorted_gaussian_list, check_sh_forward, check_render_image, check_project_to_screen_backward,
        check_camera_space_points_backward, check_jacobian_backward, check_conic_backward, check_sigma_backward,
-       check_sh_backward, check_render_backward]
+       check_sh_backward, check_render_backward, check_adam_step]

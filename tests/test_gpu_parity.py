@@ -742,3 +742,126 @@ def test_batch_pipeline_call_orders(B):
     for k in want_g:
         util.assert_grad_close(gd.grads[k].cpu().numpy(), want_g[k], f"d {k} after the detours", outlier=2e-3)
     r.close()
+
+
+# ------------------------------------------------------------------------------------------ optimiser
+_ADAM = dict(b1=0.9, b2=0.999, eps=1e-8)
+# float tolerance of the Adam step: the device contracts b*m + (1-b)*g into a fused multiply-add, the oracle
+# (-ffp-contract=off) does not: <= 1 ulp on each moment, a few ulp on the step, <= 1 ulp of the parameter
+_ADAM_TOL_MOM = dict(rtol=4e-7, atol=1e-37)
+_ADAM_TOL_PAR = dict(rtol=2.5e-7, atol=1e-7)   # steps are lr * O(0.1) = 1e-5 .. 1e-2 here
+
+
+def _adam_arrays(rng, n, w):
+    """moments consistent with the gradient history (m ~ g, v ~ g^2, as in a running optimiser), so that no sum in the
+    update cancels and the fused-multiply-add difference stays at the ulp level the tolerances above state"""
+    p = rng.normal(0, 1, (n, w)).astype(np.float32)
+    g = (rng.normal(0, 1, (n, w)) * 10.0 ** rng.uniform(-6, 0, (n, 1))).astype(np.float32)
+    m = (g * rng.uniform(0.5, 1.5, (n, w))).astype(np.float32)
+    v = (g.astype(np.float64) ** 2 * rng.uniform(0.5, 1.5, (n, w))).astype(np.float32)
+    return p, g, m, v
+
+
+@pytest.mark.parametrize("n", [1, 3, 1024, 4099])
+def test_adam_step_parity(B, n):
+    """gsx_adam_step against the oracle's restatement of adam_kernel (cuda/optimizer.cu:6-28); NaN gradients count as 0"""
+    rng = np.random.default_rng(100 + n)
+    p, g, m, v = _adam_arrays(rng, n, 1)
+    g[rng.random(g.shape) < 0.05] = np.nan
+    it = 7
+    bias1, bias2 = 1 - _ADAM["b1"] ** it, 1 - _ADAM["b2"] ** it
+    got = B.adam_step(p, g, m, v, 1.6e-4, bias1=bias1, bias2=bias2, **_ADAM)
+    exp = G.adam_step(p, g, m, v, 1.6e-4, bias1=bias1, bias2=bias2, **_ADAM)
+    assert np.isfinite(got[0]).all()
+    np.testing.assert_allclose(got[0], exp[0], **_ADAM_TOL_PAR)
+    np.testing.assert_allclose(got[1], exp[1], **_ADAM_TOL_MOM)
+    np.testing.assert_allclose(got[2], exp[2], **_ADAM_TOL_MOM)
+
+
+def test_adam_step_unaligned_views():
+    """arrays that start 4 bytes into an allocation take the scalar path and give the same bits as the float4 path"""
+    import torch
+    H = gs.host
+    rng = np.random.default_rng(5)
+    n = 10001
+    p, g, m, v = (torch.from_numpy(a.reshape(-1)).cuda() for a in _adam_arrays(rng, n, 1))
+    pa, ma, va = p.clone(), m.clone(), v.clone()
+    H.adam_step(pa, g, ma, va, 1e-3, 0.9, 0.999, 1e-8, 0.1, 0.001)
+    shifted = [torch.zeros(n + 1, device="cuda")[1:] for _ in range(4)]
+    for dst, src in zip(shifted, (p, g, m, v)):
+        dst.copy_(src)
+    assert shifted[0].data_ptr() % 16 == 4
+    H.adam_step(shifted[0], shifted[1], shifted[2], shifted[3], 1e-3, 0.9, 0.999, 1e-8, 0.1, 0.001)
+    assert torch.equal(shifted[0], pa) and torch.equal(shifted[2], ma) and torch.equal(shifted[3], va)
+
+
+@pytest.mark.parametrize("l_max,with_mask", [(0, True), (3, True), (3, False), (1, True)])
+def test_adam_fused_parity(B, l_max, with_mask):
+    """gsx_adam_step_fused (every parameter group + densification accumulators in one launch, global-index gradients,
+    cull mask read in place) against the oracle's compact -> adam_step -> scatter (cuda/trainer.cu:1027-1158)"""
+    rng = np.random.default_rng(40 + l_max)
+    n = 10007
+    widths = [3, 3, 1, 3, 4] + ([3 * ((l_max + 1) ** 2 - 1)] if l_max > 0 else [])
+    lrs = [1.6e-4, 2.5e-3, 5e-2, 5e-3, 1e-3, 1.25e-4][:len(widths)]
+    groups = [(*_adam_arrays(rng, n, w), lr) for w, lr in zip(widths, lrs)]
+    mask = (rng.random(n) < 0.55).astype(np.uint8) if with_mask else None
+    uv_grad = rng.normal(0, 1e-3, (n, 2)).astype(np.float32)
+    acc0 = rng.random(n).astype(np.float32)
+    dur0 = rng.integers(0, 100, n).astype(np.int32)
+    it = 3
+    bias1, bias2 = 1 - _ADAM["b1"] ** it, 1 - _ADAM["b2"] ** it
+    got, (acc, dur) = B.adam_step_fused(groups, mask, bias1=bias1, bias2=bias2, uv_grad=uv_grad, uv_grad_accum=acc0,
+                                        grad_accum_dur=dur0, **_ADAM)
+    keep = np.ones(n, bool) if mask is None else mask.astype(bool)
+    for (p, g, m, v, lr), (gp, gm, gv) in zip(groups, got):
+        ep, em, ev = G.adam_step_masked(p, g, m, v, mask, lr, bias1=bias1, bias2=bias2, **_ADAM)
+        np.testing.assert_allclose(gp, ep, **_ADAM_TOL_PAR)
+        np.testing.assert_allclose(gm, em, **_ADAM_TOL_MOM)
+        np.testing.assert_allclose(gv, ev, **_ADAM_TOL_MOM)
+        # culled Gaussians: parameters and moments bit-identical to the input
+        np.testing.assert_array_equal(gp[~keep], p[~keep])
+        np.testing.assert_array_equal(gm[~keep], m[~keep])
+        np.testing.assert_array_equal(gv[~keep], v[~keep])
+    eacc, edur = G.accumulate_uv_grad(uv_grad, mask, acc0, dur0)
+    np.testing.assert_allclose(acc, eacc, rtol=2e-7, atol=1e-9)
+    np.testing.assert_array_equal(dur, edur)
+
+
+def test_adam_fused_equals_per_array_at_size():
+    """size-independent property at 1 M Gaussians, SH degree 3 (59 floats each): with every Gaussian visible the fused
+    launch gives the same bits as one gsx_adam_step per array (the reference's call pattern, trainer.cu:1052-1124);
+    with a mask, exactly the masked-out rows keep their bits"""
+    import torch
+    H = gs.host
+    n = 1_000_000
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    widths, lrs = [3, 3, 1, 3, 4, 45], [1.6e-4, 2.5e-3, 5e-2, 5e-3, 1e-3, 1.25e-4]
+    mk = lambda w, s: torch.randn((n, w), device="cuda", generator=gen) * s
+    groups = [(mk(w, 1.0), mk(w, 1e-3), mk(w, 1e-3), mk(w, 1e-3) ** 2, lr) for w, lr in zip(widths, lrs)]
+    args = (0.9, 0.999, 1e-8, 1 - 0.9 ** 5, 1 - 0.999 ** 5)
+    fused = [(p.clone(), g, m.clone(), v.clone(), lr) for p, g, m, v, lr in groups]
+    H.adam_step_fused(fused, None, *args)
+    for (p, g, m, v, lr), (fp, _, fm, fv, _) in zip(groups, fused):
+        sp, sm, sv = p.clone(), m.clone(), v.clone()
+        H.adam_step(sp, g, sm, sv, lr, *args)
+        assert torch.equal(sp, fp) and torch.equal(sm, fm) and torch.equal(sv, fv)
+    mask = (torch.rand(n, device="cuda", generator=gen) < 0.5).to(torch.uint8)
+    masked = [(p.clone(), g, m.clone(), v.clone(), lr) for p, g, m, v, lr in groups]
+    H.adam_step_fused(masked, mask, *args)
+    keep = mask.bool()
+    for (p, _, m, v, _), (fp, _, fm, fv, _), (mp, _, mm, mv, _) in zip(groups, fused, masked):
+        assert torch.equal(mp[~keep], p[~keep]) and torch.equal(mm[~keep], m[~keep]) and torch.equal(mv[~keep], v[~keep])
+        assert torch.equal(mp[keep], fp[keep]) and torch.equal(mm[keep], fm[keep]) and torch.equal(mv[keep], fv[keep])
+
+
+def test_adam_rejects_host_pointers():
+    """pointer checks of the reference (ASSERT_DEVICE_POINTER in adam_step, cuda/optimizer.cu:33-36) as a status code"""
+    import ctypes as C
+    from importlib import import_module
+    ffi = import_module("3dgs_b200._ffi")
+    host = np.zeros(16, np.float32)
+    rc = ffi.lib().gsx_adam_step(host.ctypes.data_as(C.c_void_p), host.ctypes.data_as(C.c_void_p),
+                                 host.ctypes.data_as(C.c_void_p), host.ctypes.data_as(C.c_void_p), C.c_float(1e-3),
+                                 C.c_float(0.9), C.c_float(0.999), C.c_float(1e-8), C.c_float(0.1), C.c_float(0.001),
+                                 C.c_longlong(16), None)
+    assert rc in (1, 2)

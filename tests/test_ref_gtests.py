@@ -1,5 +1,5 @@
 """Drop-in proof at the C++ boundary: the REFERENCE's own gtest files (tests/cuda_forward_test.cpp and
-cuda_backward_test.cpp, compiled unchanged from /root/reference against the reference's own headers by
+cuda_backward_test.cpp, plus optimizer_test.cpp for the Adam step after the path, compiled unchanged from /root/reference against the reference's own headers by
 oracle/build_ref_gtests.sh) linked with libgsx.so instead of the reference's gsplat_cuda library.  All hot-path tests
 must pass; the two tests of out-of-scope functions (fused_loss, compute_morton_codes) are filtered out."""
 import os
@@ -11,6 +11,7 @@ import pytest
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 FWD = os.path.join(ROOT, "oracle", "_ref", "ref_gtest_forward")
 BWD = os.path.join(ROOT, "oracle", "_ref", "ref_gtest_backward")
+OPT = os.path.join(ROOT, "oracle", "_ref", "ref_gtest_optimizer")   # tests/optimizer_test.cpp
 FILTER = "--gtest_filter=-*FusedLoss*:*MortonCodes*"
 
 
@@ -22,16 +23,16 @@ def _need(path):
 def test_reference_gtests_link_against_libgsx():
     """CPU check: the binaries resolve every reference-named symbol from libgsx.so (no compute)."""
     _need(FWD)
-    for exe in (FWD, BWD):
+    for exe in (FWD, BWD) + ((OPT,) if os.path.exists(OPT) else ()):
         out = subprocess.run(["ldd", "-r", exe], capture_output=True, text=True)
         assert "libgsx.so" in out.stdout
         assert "undefined symbol" not in out.stdout + out.stderr, out.stdout + out.stderr
         lst = subprocess.run([exe, "--gtest_list_tests"], capture_output=True, text=True)
-        assert lst.returncode == 0 and ("CudaKernelTest" in lst.stdout or "CudaBackwardKernelTest" in lst.stdout)
+        assert lst.returncode == 0 and re.search("CudaKernelTest|CudaBackwardKernelTest|AdamOptimizerTest", lst.stdout)
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("exe,n_tests", [(FWD, 8), (BWD, 7)])
+@pytest.mark.parametrize("exe,n_tests", [(FWD, 8), (BWD, 7), (OPT, 1)])
 def test_reference_gtests_pass_on_libgsx(exe, n_tests):
     _need(exe)
     out = subprocess.run([exe, FILTER], capture_output=True, text=True, timeout=300)
