@@ -39,3 +39,32 @@ def test_sph_basis_pinned_to_sphericart_l3():
     Y, dY = G.sph(xyz.astype(np.float32), 3, grad=True)
     np.testing.assert_allclose(Y, sph, atol=2e-6)
     np.testing.assert_allclose(dY, dsph, atol=2e-5, rtol=1e-5)
+
+
+def test_oracle_adam_masked_is_compact_step_scatter():
+    """oracle self-check for the optimiser row: the masked form equals adam_step on the rows the
+    mask keeps and leaves the others bit-identical (cuda/trainer.cu:1027-1085); accumulators per trainer.cu:1138-1157"""
+    rng = np.random.default_rng(9)
+    n, w = 257, 5
+    p, g, m, v = (rng.normal(0, 1, (n, w)).astype(np.float32) for _ in range(4))
+    v = v * v
+    g[3, 2] = np.nan
+    mask = (rng.random(n) < 0.5).astype(np.uint8)
+    keep = mask.astype(bool)
+    a = (1e-3, 0.9, 0.999, 1e-8, 0.19, 0.002)
+    pm, mm, vm = G.adam_step_masked(p, g, m, v, mask, *a)
+    pk, mk, vk = G.adam_step(p[keep], g[keep], m[keep], v[keep], *a)
+    np.testing.assert_array_equal(pm[keep], pk)
+    np.testing.assert_array_equal(mm[keep], mk)
+    np.testing.assert_array_equal(vm[keep], vk)
+    np.testing.assert_array_equal(pm[~keep], p[~keep])
+    np.testing.assert_array_equal(mm[~keep], m[~keep])
+    np.testing.assert_array_equal(vm[~keep], v[~keep])
+    assert np.isfinite(pm).all()                      # the NaN gradient counted as 0 (cuda/optimizer.cu:14-16)
+    pa, ma, va = G.adam_step_masked(p, g, m, v, None, *a)
+    pf, mf, vf = G.adam_step(p, g, m, v, *a)
+    np.testing.assert_array_equal(pa, pf)
+    uv = rng.normal(0, 1, (n, 2)).astype(np.float32)
+    acc, dur = G.accumulate_uv_grad(uv, mask, np.ones(n, np.float32), np.zeros(n, np.int32))
+    np.testing.assert_array_equal(dur, mask.astype(np.int32))
+    np.testing.assert_allclose(acc, 1 + keep * np.sqrt((uv.astype(np.float64) ** 2).sum(1)), rtol=3e-7)
