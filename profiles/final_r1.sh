@@ -13,3 +13,4 @@ timeout 600 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu_$TAG.log 2>&1
 echo "gpu suite rc=$?"; tail -4 $OUT/pytest_gpu_$TAG.log
 timeout 600 bash profiles/prof.sh $TAG
 echo "prof rc=$?"
+timeout 120 python profiles/adam_bw.py $TAG > $OUT/adam_bw_$TAG.json 2> $OUT/adam_bw_$TAG.err; cat $OUT/adam_bw_$TAG.json
