@@ -30,6 +30,7 @@ SYMBOLS = [
     "gsx_batch_backward_params", "gsx_batch_render_host", "gsx_batch_extract_view_rgb_grad",
     "gsx_sh_grads_from_view_rgb", "gsx_ctx_build_sorted_keys", "gsx_batch_extract_view_rgb_grad_peers",
     "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers", "gsx_adam_step", "gsx_adam_step_fused",
+    "gsx_fused_loss_workspace_bytes", "gsx_fused_loss",
 ]
 
 
@@ -95,6 +96,8 @@ def lib():
         L.gsx_sorted_list_workspace_bytes.restype = C.c_size_t
         L.gsx_sort_workspace_bytes.restype = C.c_size_t
         L.gsx_sort_workspace_bytes.argtypes = [C.c_longlong]
+        L.gsx_fused_loss_workspace_bytes.restype = C.c_size_t
+        L.gsx_fused_loss_workspace_bytes.argtypes = [C.c_int, C.c_int]
         L.gsx_sorted_list_workspace_bytes.argtypes = [C.c_int, C.c_longlong]
         _lib = L
     return _lib

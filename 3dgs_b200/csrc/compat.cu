@@ -1,5 +1,5 @@
 // compat.cu -- the 15 reference-named C++ entry points (include/gsplat_cuda/cuda_forward.cuh, cuda_backward.cuh)
-// and adam_step (optimizer.cuh)
+// and the two steps around the path: adam_step (optimizer.cuh), fused_loss (cuda_forward.cuh:144)
 // on top of the gsx C ABI, with the reference's error convention: any failure prints and exit(EXIT_FAILURE)
 // (reference cuda/checks.cuh:17-38).
 #include <stdio.h>
@@ -119,4 +119,25 @@ void adam_step(float *params, float *const param_grads, float *exp_avg, float *e
                const int S, cudaStream_t stream) {
   DIE_UNLESS(gsx_adam_step(params, param_grads, exp_avg, exp_avg_sq, lr, b1, b2, eps, bias1, bias2, (long long)N * S,
                            stream));
+}
+
+// SURVEY 8f rank 3 (reference cuda/loss.cu:440-471): returns the mean loss, i.e. synchronises like the reference does.
+// The reference allocates its temporaries per call; the shim keeps one grow-only workspace (single trainer thread, 8b).
+float fused_loss(const float *predicted_data, const float *gt_data, int rows, int cols, const float ssim_weight,
+                 float *image_grad, cudaStream_t stream) {
+  static void *ws = nullptr;
+  static size_t ws_bytes = 0;
+  const size_t need = gsx_fused_loss_workspace_bytes(rows, cols);
+  if (need > ws_bytes) {
+    if (ws) cudaFree(ws);
+    if (cudaMalloc(&ws, need) != cudaSuccess) {
+      fprintf(stderr, "Assertion failed in fused_loss: cannot allocate %zu workspace bytes\n", need);
+      exit(EXIT_FAILURE);
+    }
+    ws_bytes = need;
+  }
+  float loss = 0.0f;
+  DIE_UNLESS(gsx_fused_loss(predicted_data, gt_data, rows, cols, ssim_weight, image_grad, ws, ws_bytes, nullptr, &loss,
+                            stream));
+  return loss;
 }

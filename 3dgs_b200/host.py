@@ -225,6 +225,30 @@ def adam_step_fused(groups, mask, b1, b2, eps, bias1, bias2, uv_grad=None, uv_gr
                                     _ptr(uv_grad), _ptr(uv_grad_accum), _ptr(grad_accum_dur), _stream()))
 
 
+# ------------------------------------------------------------------------------------------------ loss (8f rank 3)
+_loss_ws = {}
+
+
+def fused_loss(predicted, gt, ssim_weight, image_grad=None, sync=True):
+    """fused_loss of the reference (include/gsplat_cuda/cuda_forward.cuh:144, cuda/loss.cu:440-471) on [H][W][3] CUDA
+    tensors.  Returns (loss, image_grad); loss is a Python float when sync (the reference's behaviour), else a 1-element
+    device tensor filled in stream order."""
+    _chk_f32(predicted, gt, image_grad)
+    rows, cols = predicted.shape[0], predicted.shape[1]
+    assert predicted.shape == (rows, cols, 3) and gt.shape == predicted.shape
+    image_grad = torch.empty_like(predicted) if image_grad is None else image_grad
+    need = lib().gsx_fused_loss_workspace_bytes(rows, cols)
+    key = (predicted.device.index, torch.cuda.current_stream().cuda_stream)
+    ws = _loss_ws.get(key)
+    if ws is None or ws.numel() < need:
+        ws = _loss_ws[key] = torch.empty(need, device=predicted.device, dtype=torch.uint8)
+    loss_dev = torch.empty(1, device=predicted.device, dtype=torch.float32)
+    loss_host = C.c_float(0)
+    check(lib().gsx_fused_loss(_ptr(predicted), _ptr(gt), rows, cols, f32(ssim_weight), _ptr(image_grad), _ptr(ws),
+                               C.c_size_t(ws.numel()), _ptr(loss_dev), C.byref(loss_host) if sync else None, _stream()))
+    return (float(loss_host.value) if sync else loss_dev), image_grad
+
+
 def sort_pairs_u64(keys, vals, key_bits=64):
     """keys: int64 CUDA tensor holding uint64 bit patterns, vals: int32.  Returns sorted copies."""
     n = keys.numel()

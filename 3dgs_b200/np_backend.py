@@ -109,3 +109,9 @@ def adam_step_fused(groups, mask, b1, b2, eps, bias1, bias2, uv_grad=None, uv_gr
     H.adam_step_fused(dev, mk, b1, b2, eps, bias1, bias2, _d(uv_grad) if uv_grad is not None else None, acc, dur)
     out = [(_h(p), _h(m), _h(v)) for p, _, m, v, _ in dev]
     return (out, (_h(acc), _h(dur))) if uv_grad is not None else out
+
+
+# ------------------------------------------------------------------------------------------------ loss (8f rank 3)
+def fused_loss(pred, gt, ssim_weight):
+    loss, grad = H.fused_loss(_d(pred), _d(gt), ssim_weight)
+    return loss, _h(grad)

@@ -399,6 +399,26 @@ def main():
                                        "what": "gsx_adam_step_fused over all 6 parameter groups (59 floats/Gaussian) + densification accumulators, every Gaussian visible"}
         del pcl, groups, uvg, uva, dur
 
+    # ---- next row, outside the timed region: L1 + SSIM loss of a rendered view -> grad_image ----------
+    if world == 1:
+        rendered = r.state_image().clone()
+        gt_img = (rendered + 0.05 * torch.randn_like(rendered)).clamp_(0, 1)
+        gl = torch.empty_like(rendered)
+        l0_, l1_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        for it in range(13):
+            if it == 3:
+                l0_.record()
+            loss_dev, _ = Hh.fused_loss(rendered, gt_img, 0.2, image_grad=gl, sync=False)
+        l1_.record()
+        torch.cuda.synchronize()
+        loss_ms = l0_.elapsed_time(l1_) / 10
+        loss_bytes = 132 * W * H          # fwd: 24 read + 36 written; bwd: 36 + 24 read + 12 written
+        assert bool(torch.isfinite(gl).all().item()) and 0.0 <= float(loss_dev.item()) < 1.0
+        next_rows["fused_loss"] = {"ms": round(loss_ms, 4), "launches": 2, "bound": "hbm", "bytes": loss_bytes,
+                                   "achieved": round(loss_bytes / loss_ms / 1e6, 1), "peak": round(hbm_peak, 1), "unit": "GB/s",
+                                   "frac": round(loss_bytes / loss_ms / 1e6 / hbm_peak, 4),
+                                   "what": f"gsx_fused_loss (L1 + SSIM, 11x11 window) fwd+bwd on one {W}x{H} view, loss left on the device"}
+
     views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
     if world > 1:
         ga_, ar_ = vp.ex.link_bytes_per_step()

@@ -3,8 +3,8 @@
 // /root/reference/include/gsplat_cuda/cuda_forward.cuh:26-131 exactly so tests/cuda_forward_test.cpp,
 // cuda/raster.cu and cuda/trainer.cu compile and link unchanged.  Error convention as the reference
 // (cuda/checks.cuh): a null / non-device pointer prints to stderr and exits.
-// Not provided (outside the hot path): fused_loss, compute_psnr, accumulate_gradients,
-// compute_morton_codes.
+// Also provided: fused_loss (the step before the backward; reference cuda_forward.cuh:144).
+// Not provided (outside the hot path): compute_psnr, accumulate_gradients, compute_morton_codes.
 #pragma once
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -40,3 +40,6 @@ void render_image(const float *uv, const float *opacity, const float *conic, con
                   const float background_opacity, const int *sorted_splats, const int *splat_range_by_tile,
                   const int image_width, const int image_height, int *splats_per_pixel, float *weight_per_pixel,
                   float *image, cudaStream_t stream = 0);
+// mean L1 + SSIM loss (returned: synchronises) and d loss / d predicted into image_grad
+float fused_loss(const float *predicted_data, const float *gt_data, int rows, int cols, const float ssim_weight,
+                 float *image_grad, cudaStream_t stream = 0);

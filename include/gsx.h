@@ -287,6 +287,17 @@ int gsx_adam_step_fused(const gsx_adam_group_t *groups_host, int n_groups, const
                         float b2, float eps, float bias1, float bias2, const float *uv_grad, float *uv_grad_accum,
                         int *grad_accum_dur, void *stream);
 
+/* ---- L1 + SSIM loss and its image gradient (the step right before gsx_backward) ----
+ * Replaces fused_loss (include/gsplat_cuda/cuda_forward.cuh:144, cuda/loss.cu:440-471).  predicted / gt / image_grad are
+ * [rows][cols][3] interleaved RGB; loss = mean over rows*cols*3 of (1-w)|p-g| + w(1 - ssim), 11x11 Gaussian window;
+ * image_grad = d loss / d predicted (overwritten).  workspace: gsx_fused_loss_workspace_bytes(rows, cols) device bytes
+ * (the reference allocates per call).  loss_dev (device float, may be null) receives the mean loss without any
+ * synchronisation; loss_host (host float, may be null) additionally copies it back and synchronises the stream, which
+ * is what the reference's return value does. */
+size_t gsx_fused_loss_workspace_bytes(int rows, int cols);
+int gsx_fused_loss(const float *predicted, const float *gt, int rows, int cols, float ssim_weight, float *image_grad,
+                   void *workspace, size_t workspace_bytes, float *loss_dev, float *loss_host, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

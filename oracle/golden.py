@@ -325,3 +325,14 @@ def accumulate_uv_grad(uv_grad, mask, uv_grad_accum, grad_accum_dur):
     mk = None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8)
     lib().gold_accumulate_uv_grad(_p(_f(uv_grad)), _p(mk), acc.shape[0], _p(acc), _p(dur))
     return acc, dur
+
+
+# ------------------------------------------------------------------------------------------------ loss (8f rank 3)
+def fused_loss(pred, gt, ssim_weight):
+    """fused_loss, cuda/loss.cu:58-471, on [H][W][3] arrays.  Returns (mean loss, d loss / d pred)."""
+    p, g = _f(pred), _f(gt)
+    H, W = p.shape[0], p.shape[1]
+    grad = np.empty_like(p)
+    lib().gold_fused_loss.restype = C.c_float
+    loss = lib().gold_fused_loss(_p(p), _p(g), H, W, C.c_float(ssim_weight), _p(grad))
+    return float(loss), grad

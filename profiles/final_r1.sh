@@ -5,7 +5,7 @@ set -u
 TAG=${1:-r1v14}
 OUT=gpurun_out
 mkdir -p $OUT
-timeout 300 python -m pytest tests -m gpu -x -q -k "adam or optimizer" > $OUT/pytest_adam_$TAG.log 2>&1
+timeout 300 python -m pytest tests -m gpu -x -q -k "adam or optimizer or fused_loss or gtests" > $OUT/pytest_adam_$TAG.log 2>&1
 echo "adam tests rc=$?"; tail -4 $OUT/pytest_adam_$TAG.log
 timeout 400 python bench.py > $OUT/bench_${TAG}_n1.json 2> $OUT/bench_$TAG.err
 echo "bench rc=$?"; tail -c 600 $OUT/bench_${TAG}_n1.json; tail -3 $OUT/bench_$TAG.err

@@ -9,6 +9,6 @@ python profiles/prof_driver.py 2 2 > $OUT/prof_plain_$TAG.log 2>&1 || { echo "pl
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $OUT/launches_$TAG.csv \
     python profiles/prof_driver.py 2 2 > $OUT/ncu_launch_$TAG.log 2>&1
 ncu --set full --clock-control none --import-source on \
-    -k regex:'k_batch_bwd|k_batch_fwd|k_composite_bwd2|k_composite_fwd2|k_emit|k_onesweep|k_scan_apply|k_histogram|k_depth_keys|k_tile_ranges|k_adam_fused' \
-    -s 28 -c 30 -o $OUT/prof_$TAG -f python profiles/prof_driver.py 2 2 > $OUT/ncu_full_$TAG.log 2>&1
+    -k regex:'k_batch_bwd|k_batch_fwd|k_composite_bwd2|k_composite_fwd2|k_emit|k_onesweep|k_scan_apply|k_histogram|k_depth_keys|k_tile_ranges|k_adam_fused|k_loss_fwd|k_loss_bwd' \
+    -s 28 -c 32 -o $OUT/prof_$TAG -f python profiles/prof_driver.py 2 2 > $OUT/ncu_full_$TAG.log 2>&1
 tail -3 $OUT/ncu_full_$TAG.log

@@ -31,5 +31,8 @@ groups = [(getattr(gd, nm).view(N, -1), gd.grads[nm].view(N, -1), torch.zeros_li
 vis = (torch.rand(N, device="cuda") < 0.52).to(torch.uint8)   # C4: 52 % of the Gaussians survive a view's cull
 H.adam_step_fused(groups, vis, 0.9, 0.999, 1e-8, 0.1, 0.001, torch.zeros((N, 2), device="cuda"),
                   torch.zeros(N, device="cuda"), torch.zeros(N, device="cuda", dtype=torch.int32))
+# the step before the backward: loss + image gradient of the last rendered view
+img = r.state_image().clone()
+H.fused_loss(img, (img + 0.05 * torch.randn_like(img)).clamp_(0, 1), 0.2, sync=False)
 torch.cuda.synchronize()
 print("ok", r.stats())

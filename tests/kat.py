@@ -312,7 +312,30 @@ def check_adam_step(B):  # tests/optimizer_test.cpp:18-140 (AdamOptimizerTest.Co
     np.testing.assert_allclose(v, ev, atol=1e-6, rtol=2e-7)
 
 
+def check_fused_loss(B):  # cuda_forward_test.cpp:783-915 (FusedLossKernel_RGB_Correctness): uniform 16x16 RGB images
+    rows = cols = 16
+    w = np.float32(0.2)
+    vp, vg = np.array([0.5, 0.4, 0.1], np.float32), np.array([0.6, 0.4, 0.9], np.float32)
+    pred = np.broadcast_to(vp, (rows, cols, 3)).copy()
+    gt = np.broadcast_to(vg, (rows, cols, 3)).copy()
+    loss, grad = B.fused_loss(pred, gt, float(w))
+    C1 = np.float32((0.01 * 1.0) ** 2)
+    g11 = np.array([0.00102838, 0.00759876, 0.03600077, 0.10936069, 0.21300553, 0.26601171, 0.21300553, 0.10936069,
+                    0.03600077, 0.00759876, 0.00102838], np.float32)
+    sw2 = float(g11.sum()) ** 2
+    exp_loss, exp_grad = 0.0, np.zeros(3)
+    for c in range(3):
+        mp, mg = float(vp[c]), float(vg[c])
+        num, den = 2 * mp * mg + C1, mp * mp + mg * mg + C1
+        exp_loss += (1 - w) * abs(mp - mg) + w * (1 - num / den)
+        l1_dir = 1.0 if mp > mg else -1.0
+        dssim = ((2 * mg) * den - num * (2 * mp)) / (den * den)
+        exp_grad[c] = ((1 - w) * l1_dir + w * (-dssim * sw2)) / (rows * cols * 3)
+    assert abs(loss - exp_loss / 3) < 1e-4
+    np.testing.assert_allclose(grad[5:rows - 5, 5:cols - 5], np.broadcast_to(exp_grad, (rows - 10, cols - 10, 3)), atol=1e-6)
+
+
 ALL = [check_compute_sigma, check_project_to_screen, check_culling, check_camera_space_points, check_compute_conic,
        check_sorted_gaussian_list, check_sh_forward, check_render_image, check_project_to_screen_backward,
        check_camera_space_points_backward, check_jacobian_backward, check_conic_backward, check_sigma_backward,
-       check_sh_backward, check_render_backward, check_adam_step]
+       check_sh_backward, check_render_backward, check_adam_step, check_fused_loss]

@@ -865,3 +865,67 @@ def test_adam_rejects_host_pointers():
                                  C.c_float(0.9), C.c_float(0.999), C.c_float(1e-8), C.c_float(0.1), C.c_float(0.001),
                                  C.c_longlong(16), None)
     assert rc in (1, 2)
+
+
+# ------------------------------------------------------------------------------------------ loss
+def _loss_images(rng, H, W):
+    yy, xx = np.mgrid[0:H, 0:W]
+    base = 0.5 + 0.3 * np.sin(xx / 7.0)[..., None] * np.cos(yy / 5.0)[..., None] * np.array([1.0, 0.7, -0.5])
+    pred = np.clip(base + rng.normal(0, 0.05, (H, W, 3)), 0, 1).astype(np.float32)
+    gt = np.clip(base + rng.normal(0, 0.05, (H, W, 3)), 0, 1).astype(np.float32)
+    return pred, gt
+
+
+@pytest.mark.parametrize("H,W,w", [(16, 16, 0.2), (1, 1, 0.2), (7, 3, 0.5), (37, 45, 0.2), (80, 100, 0.2), (33, 129, 0.0),
+                                   (131, 67, 1.0)])
+def test_fused_loss_parity(B, H, W, w):
+    """gsx_fused_loss against the oracle's restatement of fused_loss (cuda/loss.cu:58-471): ragged sizes, images smaller
+    than the window, pure L1 and pure SSIM.  Tolerance: loss 2e-6 absolute (float sums in a different order); gradient
+    1e-4 of its largest magnitude (fused multiply-adds on the device, none in the oracle)"""
+    rng = np.random.default_rng(H * 1000 + W)
+    pred, gt = _loss_images(rng, H, W)
+    pred[0, 0] = gt[0, 0]                                       # the p == g subgradient (-1, cuda/loss.cu:421)
+    loss, grad = B.fused_loss(pred, gt, w)
+    eloss, egrad = G.fused_loss(pred, gt, w)
+    assert abs(loss - eloss) < 2e-6, (loss, eloss)
+    np.testing.assert_allclose(grad, egrad, rtol=0, atol=1e-4 * float(np.abs(egrad).max()))
+
+
+def test_fused_loss_full_size_properties():
+    """size-independent properties at 1920x1080: identical images give loss 0 (ssim = 1 everywhere) and the pure-L1
+    subgradient; the device-resident loss equals the returned one; gradient of w-blend is linear in the SSIM part"""
+    import torch
+    Hh = gs.host
+    H, W = 1080, 1920
+    gen = torch.Generator(device="cuda").manual_seed(7)
+    img = torch.rand((H, W, 3), device="cuda", generator=gen)
+    loss, grad = Hh.fused_loss(img, img.clone(), 0.2)
+    assert abs(loss) < 1e-6
+    other = (img + 0.1 * torch.rand((H, W, 3), device="cuda", generator=gen)).clamp(0, 1)
+    l_sync, g_sync = Hh.fused_loss(img, other, 0.2)
+    l_dev, g_dev = Hh.fused_loss(img, other, 0.2, sync=False)
+    torch.cuda.synchronize()
+    assert abs(float(l_dev.item()) - l_sync) < 1e-6 and torch.allclose(g_dev, g_sync, rtol=0, atol=1e-12)
+    l0, g0 = Hh.fused_loss(img, other, 0.0)
+    l1, g1 = Hh.fused_loss(img, other, 1.0)
+    n = H * W * 3
+    torch.testing.assert_close(g0 * n, torch.where(img > other, 1.0, -1.0), rtol=0, atol=1e-6)   # pure L1: +-1 / n
+    assert abs(l0 - float((img - other).abs().mean().item())) < 1e-6
+    assert abs(l_sync - (0.8 * l0 + 0.2 * l1)) < 2e-6
+    torch.testing.assert_close(g_sync, 0.8 * g0 + 0.2 * g1, rtol=0, atol=2e-6 * float(g_sync.abs().max().item()))
+
+
+def test_fused_loss_rejects_small_workspace_and_host_pointers():
+    import ctypes as C
+    import torch
+    from importlib import import_module
+    ffi = import_module("3dgs_b200._ffi")
+    a = torch.zeros((16, 16, 3), device="cuda")
+    ws = torch.zeros(64, device="cuda", dtype=torch.uint8)
+    p = lambda t: C.c_void_p(t.data_ptr())
+    rc = ffi.lib().gsx_fused_loss(p(a), p(a), 16, 16, C.c_float(0.2), p(a), p(ws), C.c_size_t(64), None, None, None)
+    assert rc == 5                                              # GSX_E_WORKSPACE
+    host = np.zeros((16, 16, 3), np.float32)
+    rc = ffi.lib().gsx_fused_loss(host.ctypes.data_as(C.c_void_p), p(a), 16, 16, C.c_float(0.2), p(a), p(ws),
+                                  C.c_size_t(64), None, None, None)
+    assert rc in (1, 2)

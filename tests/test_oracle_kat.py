@@ -68,3 +68,40 @@ def test_oracle_adam_masked_is_compact_step_scatter():
     acc, dur = G.accumulate_uv_grad(uv, mask, np.ones(n, np.float32), np.zeros(n, np.int32))
     np.testing.assert_array_equal(dur, mask.astype(np.int32))
     np.testing.assert_allclose(acc, 1 + keep * np.sqrt((uv.astype(np.float64) ** 2).sum(1)), rtol=3e-7)
+
+
+def _ssim_l1_loss64(pred, gt, w):
+    """float64 numpy statement of the loss (replicate-padded 11x11 Gaussian window), independent of the oracle's code"""
+    from scipy.ndimage import correlate1d
+    g = np.array([0.001028380123898387, 0.0075987582094967365, 0.036000773310661316, 0.10936068743467331,
+                  0.21300552785396576, 0.26601171493530273, 0.21300552785396576, 0.10936068743467331,
+                  0.036000773310661316, 0.0075987582094967365, 0.001028380123898387])
+    blur = lambda a: correlate1d(correlate1d(a, g, axis=0, mode="nearest"), g, axis=1, mode="nearest")
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    mu1, mu2 = blur(pred), blur(gt)
+    s1, s2, s12 = blur(pred * pred) - mu1 * mu1, blur(gt * gt) - mu2 * mu2, blur(pred * gt) - mu1 * mu2
+    ssim = ((2 * mu1 * mu2 + C1) * (2 * s12 + C2)) / ((mu1 * mu1 + mu2 * mu2 + C1) * (s1 + s2 + C2))
+    return float(((1 - w) * np.abs(pred - gt) + w * (1 - ssim)).mean())
+
+
+def test_oracle_fused_loss_matches_float64_statement_and_finite_differences():
+    """oracle pin for the loss row beyond the reference's uniform-image test: loss value against a
+    float64 numpy/scipy statement, gradient against central differences of it at pixels >= 10 px from the border
+    (nearer, the reference's zero-padded back-convolution is not the adjoint of its replicate-padded forward)"""
+    rng = np.random.default_rng(3)
+    H, W, w = 37, 45, 0.2
+    yy, xx = np.mgrid[0:H, 0:W]
+    base = 0.5 + 0.3 * np.sin(xx / 7.0)[..., None] * np.cos(yy / 5.0)[..., None] * np.array([1.0, 0.7, -0.5])
+    pred = np.clip(base + rng.normal(0, 0.05, (H, W, 3)), 0, 1).astype(np.float32)
+    gt = np.clip(base + rng.normal(0, 0.05, (H, W, 3)), 0, 1).astype(np.float32)
+    loss, grad = G.fused_loss(pred, gt, w)
+    p64, g64 = pred.astype(np.float64), gt.astype(np.float64)
+    assert abs(loss - _ssim_l1_loss64(p64, g64, w)) < 2e-6
+    for _ in range(12):
+        y, x, c = int(rng.integers(10, H - 10)), int(rng.integers(10, W - 10)), int(rng.integers(0, 3))
+        d = np.zeros_like(p64)
+        d[y, x, c] = 1e-5
+        if abs(p64[y, x, c] - g64[y, x, c]) < 2e-5:
+            continue                                  # |p - g| kink inside the stencil
+        fd = (_ssim_l1_loss64(p64 + d, g64, w) - _ssim_l1_loss64(p64 - d, g64, w)) / 2e-5
+        assert abs(grad[y, x, c] - fd) < 2e-3 * abs(fd) + 1e-8, (y, x, c, grad[y, x, c], fd)
