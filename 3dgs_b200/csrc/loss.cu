@@ -30,6 +30,18 @@ constexpr int kSX = kTX + 2 * kHalo;              // 42
 constexpr int kSY = kTY + 2 * kHalo;              // 26
 constexpr int kSP = kSX + 1;                      // padded row pitch of the staged tile
 constexpr int kThreads = kBX * kBY;
+// GSX_LOSS_REG=1 (build variant): sliding windows in registers -- a thread produces 4 adjacent columns of the horizontal
+// pass from 14 staged values and 2 adjacent rows of the vertical pass from 12, instead of 11 shared-memory loads per
+// output.  Tried because the capture shows 63 % / 55 % of the shared-memory wavefront peak
+// (profiles/r1_v16_ncu_full_summary.txt); measured on the same box it changes nothing (0.260 vs 0.261 ms at 1920x1080,
+// profiles/r1_loss_ab_variants.jsonl, both parity-green): the kernels are bound by instruction issue as a whole (74 % SM
+// throughput: index arithmetic of the staging loops, 7 IEEE divisions per pixel and channel), not by that pipe.  Default
+// stays 0.
+#ifndef GSX_LOSS_REG
+#define GSX_LOSS_REG 0
+#endif
+constexpr int kHP = kTX + 1;                      // row pitch of the horizontal-pass buffer (conflict-free 4-column stores)
+[[maybe_unused]] constexpr int kCG = kTX / 4;     // 4-column groups per tile row (GSX_LOSS_REG)
 constexpr float kC1 = (0.01f * 1.0f) * (0.01f * 1.0f);   // cuda/loss.cu:19-25
 constexpr float kC2 = (0.03f * 1.0f) * (0.03f * 1.0f);
 
@@ -49,7 +61,7 @@ __global__ void __launch_bounds__(kThreads) k_loss_fwd(int H, int W, float ssim_
                                                        const float *__restrict__ gt, float *__restrict__ maps,
                                                        float *__restrict__ loss_sum) {
   __shared__ float sP[3][kSY][kSP], sG[3][kSY][kSP];   // planar staged tile + halo: prediction, ground truth
-  __shared__ float sH[5][kSY][kTX];                    // horizontal pass of one channel: E[x], E[x^2], E[y], E[y^2], E[xy]
+  __shared__ float sH[5][kSY][kHP];                    // horizontal pass of one channel: E[x], E[x^2], E[y], E[y^2], E[xy]
   __shared__ float sRed[kThreads / 32];
   const int tid = threadIdx.y * kBX + threadIdx.x;
   const int x0 = blockIdx.x * kTX, y0 = blockIdx.y * kTY;
@@ -68,6 +80,25 @@ __global__ void __launch_bounds__(kThreads) k_loss_fwd(int H, int W, float ssim_
 
   float loss = 0.0f;
   for (int c = 0; c < 3; ++c) {
+#if GSX_LOSS_REG
+    for (int e = tid; e < kSY * kCG; e += kThreads) {
+      const int row = e / kCG, col0 = (e - row * kCG) * 4;
+      float pv[4 + 2 * kHalo], gv[4 + 2 * kHalo];
+#pragma unroll
+      for (int k = 0; k < 4 + 2 * kHalo; ++k) {
+        pv[k] = sP[c][row][col0 + k];
+        gv[k] = sG[c][row][col0 + k];
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        sH[0][row][col0 + j] = tap11([&](int d) { return pv[j + kHalo + d]; });
+        sH[1][row][col0 + j] = tap11([&](int d) { return pv[j + kHalo + d] * pv[j + kHalo + d]; });
+        sH[2][row][col0 + j] = tap11([&](int d) { return gv[j + kHalo + d]; });
+        sH[3][row][col0 + j] = tap11([&](int d) { return gv[j + kHalo + d] * gv[j + kHalo + d]; });
+        sH[4][row][col0 + j] = tap11([&](int d) { return pv[j + kHalo + d] * gv[j + kHalo + d]; });
+      }
+    }
+#else
     for (int e = tid; e < kSY * kTX; e += kThreads) {
       const int row = e / kTX, col = e - row * kTX;
       const float *p = &sP[c][row][col + kHalo], *g = &sG[c][row][col + kHalo];
@@ -77,15 +108,36 @@ __global__ void __launch_bounds__(kThreads) k_loss_fwd(int H, int W, float ssim_
       sH[3][row][col] = tap11([&](int d) { return g[d] * g[d]; });
       sH[4][row][col] = tap11([&](int d) { return p[d] * g[d]; });
     }
+#endif
     __syncthreads();
+#if GSX_LOSS_REG
+    float o2[2][5];
+#pragma unroll
+    for (int s = 0; s < 5; ++s) {
+      float v[2 + 2 * kHalo];
+#pragma unroll
+      for (int k = 0; k < 2 + 2 * kHalo; ++k) v[k] = sH[s][2 * threadIdx.y + k][threadIdx.x];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) o2[h][s] = tap11([&](int d) { return v[h + kHalo + d]; });
+    }
+#endif
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
+#if GSX_LOSS_REG
+      const int ly = 2 * threadIdx.y + half, lx = threadIdx.x;
+#else
       const int ly = threadIdx.y + half * kBY, lx = threadIdx.x;
+#endif
       const int y = y0 + ly, x = x0 + lx;
       if (y < H && x < W) {
         float o[5];
+#if GSX_LOSS_REG
+#pragma unroll
+        for (int s = 0; s < 5; ++s) o[s] = o2[half][s];
+#else
 #pragma unroll
         for (int s = 0; s < 5; ++s) o[s] = tap11([&](int d) { return sH[s][ly + kHalo + d][lx]; });
+#endif
         // SSIM of the window centred on the pixel and its partial derivatives (cuda/loss.cu:214-252)
         const float mu1 = o[0], mu2 = o[2];
         const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2;
@@ -126,7 +178,7 @@ __global__ void __launch_bounds__(kThreads) k_loss_bwd(int H, int W, float ssim_
                                                        float *__restrict__ image_grad, const float *__restrict__ loss_sum,
                                                        float *__restrict__ loss_mean) {
   __shared__ float sD[3][kSY][kSP];   // the three derivative maps of one channel, zero outside the image
-  __shared__ float sH[3][kSY][kTX];
+  __shared__ float sH[3][kSY][kHP];
   const int tid = threadIdx.y * kBX + threadIdx.x;
   const int x0 = blockIdx.x * kTX, y0 = blockIdx.y * kTY;
   const size_t plane = (size_t)H * W;
@@ -142,6 +194,17 @@ __global__ void __launch_bounds__(kThreads) k_loss_bwd(int H, int W, float ssim_
       sD[m][row][px] = in ? maps[(size_t)(3 * m + c) * plane + (size_t)gy * W + gx] : 0.0f;
     }
     __syncthreads();
+#if GSX_LOSS_REG
+    for (int e = tid; e < 3 * kSY * kCG; e += kThreads) {
+      const int m = e / (kSY * kCG), k2 = e - m * (kSY * kCG);
+      const int row = k2 / kCG, col0 = (k2 - row * kCG) * 4;
+      float v[4 + 2 * kHalo];
+#pragma unroll
+      for (int k = 0; k < 4 + 2 * kHalo; ++k) v[k] = sD[m][row][col0 + k];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) sH[m][row][col0 + j] = tap11([&](int d) { return v[j + kHalo + d]; });
+    }
+#else
     for (int e = tid; e < kSY * kTX; e += kThreads) {
       const int row = e / kTX, col = e - row * kTX;
 #pragma unroll
@@ -150,15 +213,36 @@ __global__ void __launch_bounds__(kThreads) k_loss_bwd(int H, int W, float ssim_
         sH[m][row][col] = tap11([&](int d) { return s[d]; });
       }
     }
+#endif
     __syncthreads();
+#if GSX_LOSS_REG
+    float sum2[2][3];
+#pragma unroll
+    for (int m = 0; m < 3; ++m) {
+      float v[2 + 2 * kHalo];
+#pragma unroll
+      for (int k = 0; k < 2 + 2 * kHalo; ++k) v[k] = sH[m][2 * threadIdx.y + k][threadIdx.x];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) sum2[h][m] = tap11([&](int d) { return v[h + kHalo + d]; });
+    }
+#endif
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
+#if GSX_LOSS_REG
+      const int ly = 2 * threadIdx.y + half, lx = threadIdx.x;
+#else
       const int ly = threadIdx.y + half * kBY, lx = threadIdx.x;
+#endif
       const int y = y0 + ly, x = x0 + lx;
       if (y < H && x < W) {
         float sum[3];
+#if GSX_LOSS_REG
+#pragma unroll
+        for (int m = 0; m < 3; ++m) sum[m] = sum2[half][m];
+#else
 #pragma unroll
         for (int m = 0; m < 3; ++m) sum[m] = tap11([&](int d) { return sH[m][ly + kHalo + d][lx]; });
+#endif
         const size_t at = ((size_t)y * W + x) * 3 + c;
         const float p1 = pred[at], p2 = gt[at];
         const float ssim_part = sum[0] + (2.f * p1) * sum[1] + p2 * sum[2];          // cuda/loss.cu:418
