@@ -31,6 +31,7 @@ SYMBOLS = [
     "gsx_sh_grads_from_view_rgb", "gsx_ctx_build_sorted_keys", "gsx_batch_extract_view_rgb_grad_peers",
     "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers", "gsx_adam_step", "gsx_adam_step_fused",
     "gsx_fused_loss_workspace_bytes", "gsx_fused_loss",
+    "gsx_compute_morton_codes", "gsx_morton_order_workspace_bytes", "gsx_morton_order", "gsx_gather_rows",
 ]
 
 
@@ -96,6 +97,8 @@ def lib():
         L.gsx_sorted_list_workspace_bytes.restype = C.c_size_t
         L.gsx_sort_workspace_bytes.restype = C.c_size_t
         L.gsx_sort_workspace_bytes.argtypes = [C.c_longlong]
+        L.gsx_morton_order_workspace_bytes.restype = C.c_size_t
+        L.gsx_morton_order_workspace_bytes.argtypes = [C.c_int]
         L.gsx_fused_loss_workspace_bytes.restype = C.c_size_t
         L.gsx_fused_loss_workspace_bytes.argtypes = [C.c_int, C.c_int]
         L.gsx_sorted_list_workspace_bytes.argtypes = [C.c_int, C.c_longlong]

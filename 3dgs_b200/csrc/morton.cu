@@ -1,0 +1,113 @@
+// morton.cu -- SURVEY 8f rank 4 (first half): Morton re-layout of the Gaussian arrays, the on-device order the splatting
+// path reads its parameters in.
+//
+// Reference: compute_morton_codes, cuda/culling.cu:14-68,345-359 (63-bit codes: 21 bits per axis, quantised against a
+// caller-provided bounding box, z|y|x interleaved) and TrainerImpl::sort_gaussians, cuda/trainer.cu:871-924
+// (thrust::sequence + thrust::sort_by_key, then one gather per parameter / optimiser array).  Here the codes and the
+// identity permutation come out of one kernel, the sort is the library's own onesweep radix sort (stable: equal codes
+// keep index order, where thrust's order is unspecified), and a row gather serves every array width.
+#include "gsx_common.cuh"
+
+namespace gsx {
+namespace {
+
+constexpr uint32_t kBitsPerCoord = 21;                      // culling.cu:15-16
+constexpr uint32_t kMaxCoord = (1u << kBitsPerCoord) - 1;   // 2^21 - 1
+
+// two zero bits between consecutive bits of the low 21 (culling.cu:18-40)
+__device__ __forceinline__ uint64_t spread3(uint64_t n) {
+  n &= kMaxCoord;
+  n = (n | (n << 32)) & 0x1F00000000FFFFull;
+  n = (n | (n << 16)) & 0x1F0000FF0000FFull;
+  n = (n | (n << 8)) & 0x100F00F00F00F00Full;
+  n = (n | (n << 4)) & 0x10C30C30C30C30C3ull;
+  n = (n | (n << 2)) & 0x1249249249249249ull;
+  return n;
+}
+
+__global__ void __launch_bounds__(256) k_morton_codes(int N, const float *__restrict__ xyz, float x_max, float y_max,
+                                                      float z_max, float x_min, float y_min, float z_min,
+                                                      uint64_t *__restrict__ codes, uint32_t *__restrict__ iota) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= N) return;
+  const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  // quantisation exactly as culling.cu:55-57: (v - min) * (2097151 / (max - min)), truncated; float -> uint64
+  // conversion saturates (negative and NaN give 0)
+  const uint64_t xq = __float2ull_rz(__fmul_rn(__fsub_rn(x, x_min), __fdiv_rn((float)kMaxCoord, __fsub_rn(x_max, x_min))));
+  const uint64_t yq = __float2ull_rz(__fmul_rn(__fsub_rn(y, y_min), __fdiv_rn((float)kMaxCoord, __fsub_rn(y_max, y_min))));
+  const uint64_t zq = __float2ull_rz(__fmul_rn(__fsub_rn(z, z_min), __fdiv_rn((float)kMaxCoord, __fsub_rn(z_max, z_min))));
+  codes[i] = (spread3(zq) << 2) | (spread3(yq) << 1) | spread3(xq);
+  if (iota) iota[i] = (uint32_t)i;
+}
+
+// dst[i][:] = src[order[i]][:], one thread per float; rows are `width` floats
+__global__ void __launch_bounds__(256) k_gather_rows(const float *__restrict__ src, const int *__restrict__ order,
+                                                     long long total, int width, float *__restrict__ dst) {
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
+    const long long i = e / width;
+    const int k = (int)(e - i * width);
+    dst[e] = src[(long long)order[i] * width + k];
+  }
+}
+
+}  // namespace
+}  // namespace gsx
+
+using namespace gsx;
+
+extern "C" {
+
+int gsx_compute_morton_codes(int N, const float *xyz, float x_max, float y_max, float z_max, float x_min, float y_min,
+                             float z_min, uint64_t *codes, void *stream) {
+  GSX_REQUIRE_DEV(xyz); GSX_REQUIRE_DEV(codes);
+  if (N <= 0) return GSX_OK;
+  k_morton_codes<<<ceil_div(N, 256), 256, 0, (cudaStream_t)stream>>>(N, xyz, x_max, y_max, z_max, x_min, y_min, z_min,
+                                                                    codes, nullptr);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+size_t gsx_morton_order_workspace_bytes(int N) {
+  const size_t n = (size_t)(N > 0 ? N : 1);
+  return align_up(n * 8, 256) * 2 + align_up(n * 4, 256) + align_up(gsx_sort_workspace_bytes((long long)n), 256);
+}
+
+int gsx_morton_order(int N, const float *xyz, float x_max, float y_max, float z_max, float x_min, float y_min,
+                     float z_min, int *order, uint64_t *sorted_codes, void *workspace, size_t workspace_bytes,
+                     void *stream) {
+  GSX_REQUIRE_DEV(xyz); GSX_REQUIRE_DEV(order); GSX_REQUIRE_DEV(workspace);
+  if (sorted_codes) GSX_REQUIRE_DEV(sorted_codes);
+  if (N <= 0) return GSX_OK;
+  if (workspace_bytes < gsx_morton_order_workspace_bytes(N)) {
+    set_error("workspace %zu < %zu bytes", workspace_bytes, gsx_morton_order_workspace_bytes(N));
+    return GSX_E_WORKSPACE;
+  }
+  char *w = reinterpret_cast<char *>(workspace);
+  uint64_t *keys_a = reinterpret_cast<uint64_t *>(w); w += align_up((size_t)N * 8, 256);
+  uint64_t *keys_b = reinterpret_cast<uint64_t *>(w); w += align_up((size_t)N * 8, 256);
+  uint32_t *vals_a = reinterpret_cast<uint32_t *>(w); w += align_up((size_t)N * 4, 256);
+  const size_t sort_bytes = gsx_sort_workspace_bytes(N);
+  cudaStream_t st = (cudaStream_t)stream;
+  k_morton_codes<<<ceil_div(N, 256), 256, 0, st>>>(N, xyz, x_max, y_max, z_max, x_min, y_min, z_min, keys_a, vals_a);
+  GSX_LAUNCH_CHECK();
+  int rc = gsx_sort_pairs_u64(keys_a, keys_b, vals_a, reinterpret_cast<uint32_t *>(order), N, nullptr, 3 * kBitsPerCoord, w,
+                              sort_bytes, stream);
+  if (rc != GSX_OK) return rc;
+  if (sorted_codes) GSX_CUDA(cudaMemcpyAsync(sorted_codes, keys_b, (size_t)N * 8, cudaMemcpyDeviceToDevice, st));
+  return GSX_OK;
+}
+
+int gsx_gather_rows(const float *src, const int *order, int N, int width, float *dst, void *stream) {
+  GSX_REQUIRE_DEV(src); GSX_REQUIRE_DEV(order); GSX_REQUIRE_DEV(dst);
+  if (width <= 0) { set_error("width %d", width); return GSX_E_ARG; }
+  if (src == dst) { set_error("gather_rows is out of place"); return GSX_E_ARG; }
+  if (N <= 0) return GSX_OK;
+  const long long total = (long long)N * width;
+  long long blocks = (total + 255) / 256;
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  k_gather_rows<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, order, total, width, dst);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+}  // extern "C"

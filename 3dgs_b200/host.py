@@ -249,6 +249,48 @@ def fused_loss(predicted, gt, ssim_weight, image_grad=None, sync=True):
     return (float(loss_host.value) if sync else loss_dev), image_grad
 
 
+# ------------------------------------------------------------------------------------------------ Morton re-layout (8f rank 4)
+def _bbox(xyz, bbox):
+    if bbox is None:                                   # the reference reduces it with thrust (cuda/trainer.cu:874-884)
+        mn, mx = xyz.amin(0).tolist(), xyz.amax(0).tolist()
+        bbox = (mx[0], mx[1], mx[2], mn[0], mn[1], mn[2])
+    return [f32(b) for b in bbox]
+
+
+def compute_morton_codes(xyz, bbox=None):
+    """compute_morton_codes of the reference (cuda/culling.cu:345-359); bbox = (x_max, y_max, z_max, x_min, y_min, z_min)
+    or None for the tight box.  Returns int64 codes (uint64 bit patterns, 63 bits used)."""
+    _chk_f32(xyz)
+    n = xyz.shape[0]
+    codes = torch.empty(n, device=xyz.device, dtype=torch.int64)
+    check(lib().gsx_compute_morton_codes(n, _ptr(xyz), *_bbox(xyz, bbox), _ptr(codes), _stream()))
+    return codes
+
+
+def morton_order(xyz, bbox=None, want_codes=False):
+    """The permutation TrainerImpl::sort_gaussians applies (cuda/trainer.cu:886-893): order[i] = Gaussian that comes i-th in
+    Morton order, ties in index order."""
+    _chk_f32(xyz)
+    n = xyz.shape[0]
+    order = torch.empty(n, device=xyz.device, dtype=torch.int32)
+    codes = torch.empty(n, device=xyz.device, dtype=torch.int64) if want_codes else None
+    wsb = lib().gsx_morton_order_workspace_bytes(n)
+    ws = torch.empty(wsb, device=xyz.device, dtype=torch.uint8)
+    check(lib().gsx_morton_order(n, _ptr(xyz), *_bbox(xyz, bbox), _ptr(order), _ptr(codes), _ptr(ws), C.c_size_t(wsb),
+                                 _stream()))
+    return (order, codes) if want_codes else order
+
+
+def gather_rows(src, order):
+    """gather_with_stride of the reference (cuda/trainer.cu:897-923), out of place: dst[i] = src[order[i]]"""
+    _chk_f32(src)
+    n = order.numel()
+    assert order.dtype == torch.int32 and src.shape[0] == n
+    dst = torch.empty_like(src)
+    check(lib().gsx_gather_rows(_ptr(src), _ptr(order), n, src.numel() // max(n, 1), _ptr(dst), _stream()))
+    return dst
+
+
 def sort_pairs_u64(keys, vals, key_bits=64):
     """keys: int64 CUDA tensor holding uint64 bit patterns, vals: int32.  Returns sorted copies."""
     n = keys.numel()

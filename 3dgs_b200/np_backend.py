@@ -115,3 +115,12 @@ def adam_step_fused(groups, mask, b1, b2, eps, bias1, bias2, uv_grad=None, uv_gr
 def fused_loss(pred, gt, ssim_weight):
     loss, grad = H.fused_loss(_d(pred), _d(gt), ssim_weight)
     return loss, _h(grad)
+
+
+# ------------------------------------------------------------------------------------------------ Morton re-layout (8f rank 4)
+def morton_codes(xyz, bbox):
+    return _h(H.compute_morton_codes(_d(xyz), bbox)).view(np.uint64)
+
+
+def morton_order(xyz, bbox):
+    return _h(H.morton_order(_d(xyz), bbox))

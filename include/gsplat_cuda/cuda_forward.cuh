@@ -4,11 +4,13 @@
 // cuda/raster.cu and cuda/trainer.cu compile and link unchanged.  Error convention as the reference
 // (cuda/checks.cuh): a null / non-device pointer prints to stderr and exits.
 // Also provided: fused_loss (the step before the backward; reference cuda_forward.cuh:144).
-// Not provided (outside the hot path): compute_psnr, accumulate_gradients, compute_morton_codes.
+// and compute_morton_codes (reference cuda_forward.cuh:186).
+// Not provided (outside the hot path): compute_psnr, accumulate_gradients (never defined by the reference).
 #pragma once
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <cstddef>
+#include <cstdint>
 
 inline constexpr int TILE_SIZE_FWD = 16;
 
@@ -43,3 +45,7 @@ void render_image(const float *uv, const float *opacity, const float *conic, con
 // mean L1 + SSIM loss (returned: synchronises) and d loss / d predicted into image_grad
 float fused_loss(const float *predicted_data, const float *gt_data, int rows, int cols, const float ssim_weight,
                  float *image_grad, cudaStream_t stream = 0);
+// 63-bit Morton codes (21 bits per axis) of xyz[N][3] inside the given bounding box
+void compute_morton_codes(const int N, const float *d_xyz, const float x_max, const float y_max, const float z_max,
+                          const float x_min, const float y_min, const float z_min, uint64_t *codes,
+                          cudaStream_t stream = 0);

@@ -21,8 +21,7 @@ LFLAGS="-gencode arch=compute_100a,code=sm_100a -ccbin /usr/bin/g++ --cudart sha
 $NVCC $CFLAGS -x cu -c $REF/tests/cuda_forward_test.cpp -o "$OUT/fwd_test.o"
 $NVCC $CFLAGS -x cu -c $REF/tests/cuda_backward_test.cpp -o "$OUT/bwd_test.o"
 $NVCC $CFLAGS -x cu -c $REF/tests/optimizer_test.cpp -o "$OUT/opt_test.o"
-$NVCC $CFLAGS -c "$HERE/ref_gtest_stubs.cu" -o "$OUT/stubs.o"
-$NVCC "$OUT/fwd_test.o" "$OUT/stubs.o" "$OUT/gtest-all.o" "$OUT/gtest_main.o" $LFLAGS -o "$OUT/ref_gtest_forward"
+$NVCC "$OUT/fwd_test.o" "$OUT/gtest-all.o" "$OUT/gtest_main.o" $LFLAGS -o "$OUT/ref_gtest_forward"
 $NVCC "$OUT/bwd_test.o" "$OUT/gtest-all.o" $LFLAGS -o "$OUT/ref_gtest_backward"
 $NVCC "$OUT/opt_test.o" "$OUT/gtest-all.o" $LFLAGS -o "$OUT/ref_gtest_optimizer"
 echo "[build_ref_gtests] built $OUT/ref_gtest_forward $OUT/ref_gtest_backward $OUT/ref_gtest_optimizer"

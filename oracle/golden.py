@@ -336,3 +336,17 @@ def fused_loss(pred, gt, ssim_weight):
     lib().gold_fused_loss.restype = C.c_float
     loss = lib().gold_fused_loss(_p(p), _p(g), H, W, C.c_float(ssim_weight), _p(grad))
     return float(loss), grad
+
+
+# ------------------------------------------------------------------------------------------------ Morton re-layout (8f rank 4)
+def morton_codes(xyz, bbox):
+    """morton_codes_kernel, cuda/culling.cu:42-68; bbox = (x_max, y_max, z_max, x_min, y_min, z_min).  uint64 codes."""
+    p = _f(xyz)
+    codes = np.empty(p.shape[0], np.uint64)
+    lib().gold_morton_codes(p.shape[0], _p(p), *[C.c_float(b) for b in bbox], _p(codes))
+    return codes
+
+
+def morton_order(xyz, bbox):
+    """sequence + sort_by_key of TrainerImpl::sort_gaussians (cuda/trainer.cu:886-893), ties in index order"""
+    return np.argsort(morton_codes(xyz, bbox), kind="stable").astype(np.int32)

@@ -335,7 +335,26 @@ def check_fused_loss(B):  # cuda_forward_test.cpp:783-915 (FusedLossKernel_RGB_C
     np.testing.assert_allclose(grad[5:rows - 5, 5:cols - 5], np.broadcast_to(exp_grad, (rows - 10, cols - 10, 3)), atol=1e-6)
 
 
+def check_morton_codes(B):  # cuda_forward_test.cpp:917-1018 (ComputeMortonCodes): exact
+    bbox = (10.0, 5.0, 20.0, -10.0, -5.0, 0.0)          # x_max, y_max, z_max, x_min, y_min, z_min
+    xyz = np.array([[-10, -5, 0], [10, 5, 20], [0, 0, 10], [5, 2, 5], [-5, -2, 15]], np.float32)
+    codes = np.asarray(B.morton_codes(xyz, bbox), np.uint64)
+    M = np.float32(2097151)
+    mx, mn = np.array(bbox[:3], np.float32), np.array(bbox[3:], np.float32)
+    norm = np.clip(((xyz - mn) / (mx - mn)).astype(np.float32), 0, 1)
+    q = (norm * M).astype(np.float32).astype(np.uint64)
+
+    def spread(n):
+        r = 0
+        for b in range(21):
+            r |= ((int(n) >> b) & 1) << (3 * b)
+        return r
+    exp = np.array([(spread(z) << 2) | (spread(y) << 1) | spread(x) for x, y, z in q], np.uint64)
+    np.testing.assert_array_equal(codes, exp)
+    assert codes[0] == 0 and codes[1] == (1 << 63) - 1
+
+
 ALL = [check_compute_sigma, check_project_to_screen, check_culling, check_camera_space_points, check_compute_conic,
        check_sorted_gaussian_list, check_sh_forward, check_render_image, check_project_to_screen_backward,
        check_camera_space_points_backward, check_jacobian_backward, check_conic_backward, check_sigma_backward,
-       check_sh_backward, check_render_backward, check_adam_step, check_fused_loss]
+       check_sh_backward, check_render_backward, check_adam_step, check_fused_loss, check_morton_codes]
