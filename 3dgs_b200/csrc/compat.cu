@@ -145,5 +145,5 @@ float fused_loss(const float *predicted_data, const float *gt_data, int rows, in
 // SURVEY 8f rank 4 (reference cuda/culling.cu:345-359)
 void compute_morton_codes(const int N, const float *d_xyz, const float x_max, const float y_max, const float z_max,
                           const float x_min, const float y_min, const float z_min, uint64_t *codes, cudaStream_t stream) {
-  DIE_UNLESS(gsx_compute_morton_codes(N, d_xyz, x_max, y_max, z_max, x_min, y_min, z_min, codes, stream));
+  DIE_UNLESS(gsx_compute_morton_codes(N, d_xyz, x_max, y_max, z_max, x_min, y_min, z_min, 0, codes, stream));
 }

@@ -14,17 +14,22 @@ namespace {
 constexpr uint32_t kBitsPerCoord = 21;                      // culling.cu:15-16
 constexpr uint32_t kMaxCoord = (1u << kBitsPerCoord) - 1;   // 2^21 - 1
 
-// two zero bits between consecutive bits of the low 21 (culling.cu:18-40)
+// Bit spreading.  TRUE = false reproduces the reference's spread_bits mask sequence (culling.cu:18-40) bit for bit: its
+// third and fourth masks are not the ones of a 3-way interleave, so most coordinate bits are dropped (only bits 0, 2, 3,
+// 9, 10 and 12 of a coordinate reach the code) -- SURVEY quirk, kept as the default because the reference's own test and trainer see
+// exactly these codes.  TRUE = true is the real interleave (bit b -> bit 3b), opt-in through GSX_MORTON_TRUE_INTERLEAVE.
+template <bool TRUE>
 __device__ __forceinline__ uint64_t spread3(uint64_t n) {
   n &= kMaxCoord;
-  n = (n | (n << 32)) & 0x1F00000000FFFFull;
+  n = (n | (n << 32)) & (TRUE ? 0x1F00000000FFFFull : 0x1F000000FFFFull);
   n = (n | (n << 16)) & 0x1F0000FF0000FFull;
-  n = (n | (n << 8)) & 0x100F00F00F00F00Full;
-  n = (n | (n << 4)) & 0x10C30C30C30C30C3ull;
+  n = (n | (n << 8)) & (TRUE ? 0x100F00F00F00F00Full : 0x100F807C0F807C0Full);
+  n = (n | (n << 4)) & (TRUE ? 0x10C30C30C30C30C3ull : 0x1084210842108421ull);
   n = (n | (n << 2)) & 0x1249249249249249ull;
   return n;
 }
 
+template <bool TRUE>
 __global__ void __launch_bounds__(256) k_morton_codes(int N, const float *__restrict__ xyz, float x_max, float y_max,
                                                       float z_max, float x_min, float y_min, float z_min,
                                                       uint64_t *__restrict__ codes, uint32_t *__restrict__ iota) {
@@ -36,7 +41,7 @@ __global__ void __launch_bounds__(256) k_morton_codes(int N, const float *__rest
   const uint64_t xq = __float2ull_rz(__fmul_rn(__fsub_rn(x, x_min), __fdiv_rn((float)kMaxCoord, __fsub_rn(x_max, x_min))));
   const uint64_t yq = __float2ull_rz(__fmul_rn(__fsub_rn(y, y_min), __fdiv_rn((float)kMaxCoord, __fsub_rn(y_max, y_min))));
   const uint64_t zq = __float2ull_rz(__fmul_rn(__fsub_rn(z, z_min), __fdiv_rn((float)kMaxCoord, __fsub_rn(z_max, z_min))));
-  codes[i] = (spread3(zq) << 2) | (spread3(yq) << 1) | spread3(xq);
+  codes[i] = (spread3<TRUE>(zq) << 2) | (spread3<TRUE>(yq) << 1) | spread3<TRUE>(xq);
   if (iota) iota[i] = (uint32_t)i;
 }
 
@@ -58,11 +63,15 @@ using namespace gsx;
 extern "C" {
 
 int gsx_compute_morton_codes(int N, const float *xyz, float x_max, float y_max, float z_max, float x_min, float y_min,
-                             float z_min, uint64_t *codes, void *stream) {
+                             float z_min, int flags, uint64_t *codes, void *stream) {
   GSX_REQUIRE_DEV(xyz); GSX_REQUIRE_DEV(codes);
   if (N <= 0) return GSX_OK;
-  k_morton_codes<<<ceil_div(N, 256), 256, 0, (cudaStream_t)stream>>>(N, xyz, x_max, y_max, z_max, x_min, y_min, z_min,
-                                                                    codes, nullptr);
+  if (flags & GSX_MORTON_TRUE_INTERLEAVE)
+    k_morton_codes<true><<<ceil_div(N, 256), 256, 0, (cudaStream_t)stream>>>(N, xyz, x_max, y_max, z_max, x_min, y_min,
+                                                                            z_min, codes, nullptr);
+  else
+    k_morton_codes<false><<<ceil_div(N, 256), 256, 0, (cudaStream_t)stream>>>(N, xyz, x_max, y_max, z_max, x_min, y_min,
+                                                                             z_min, codes, nullptr);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -73,8 +82,8 @@ size_t gsx_morton_order_workspace_bytes(int N) {
 }
 
 int gsx_morton_order(int N, const float *xyz, float x_max, float y_max, float z_max, float x_min, float y_min,
-                     float z_min, int *order, uint64_t *sorted_codes, void *workspace, size_t workspace_bytes,
-                     void *stream) {
+                     float z_min, int flags, int *order, uint64_t *sorted_codes, void *workspace,
+                     size_t workspace_bytes, void *stream) {
   GSX_REQUIRE_DEV(xyz); GSX_REQUIRE_DEV(order); GSX_REQUIRE_DEV(workspace);
   if (sorted_codes) GSX_REQUIRE_DEV(sorted_codes);
   if (N <= 0) return GSX_OK;
@@ -88,7 +97,10 @@ int gsx_morton_order(int N, const float *xyz, float x_max, float y_max, float z_
   uint32_t *vals_a = reinterpret_cast<uint32_t *>(w); w += align_up((size_t)N * 4, 256);
   const size_t sort_bytes = gsx_sort_workspace_bytes(N);
   cudaStream_t st = (cudaStream_t)stream;
-  k_morton_codes<<<ceil_div(N, 256), 256, 0, st>>>(N, xyz, x_max, y_max, z_max, x_min, y_min, z_min, keys_a, vals_a);
+  if (flags & GSX_MORTON_TRUE_INTERLEAVE)
+    k_morton_codes<true><<<ceil_div(N, 256), 256, 0, st>>>(N, xyz, x_max, y_max, z_max, x_min, y_min, z_min, keys_a, vals_a);
+  else
+    k_morton_codes<false><<<ceil_div(N, 256), 256, 0, st>>>(N, xyz, x_max, y_max, z_max, x_min, y_min, z_min, keys_a, vals_a);
   GSX_LAUNCH_CHECK();
   int rc = gsx_sort_pairs_u64(keys_a, keys_b, vals_a, reinterpret_cast<uint32_t *>(order), N, nullptr, 3 * kBitsPerCoord, w,
                               sort_bytes, stream);

@@ -257,17 +257,18 @@ def _bbox(xyz, bbox):
     return [f32(b) for b in bbox]
 
 
-def compute_morton_codes(xyz, bbox=None):
+def compute_morton_codes(xyz, bbox=None, flags=0):
     """compute_morton_codes of the reference (cuda/culling.cu:345-359); bbox = (x_max, y_max, z_max, x_min, y_min, z_min)
-    or None for the tight box.  Returns int64 codes (uint64 bit patterns, 63 bits used)."""
+    or None for the tight box; flags = 0 reproduces the reference's bit spread, GSX_MORTON_TRUE_INTERLEAVE (1) is the real
+    interleave.  Returns int64 codes (uint64 bit patterns, 63 bits used)."""
     _chk_f32(xyz)
     n = xyz.shape[0]
     codes = torch.empty(n, device=xyz.device, dtype=torch.int64)
-    check(lib().gsx_compute_morton_codes(n, _ptr(xyz), *_bbox(xyz, bbox), _ptr(codes), _stream()))
+    check(lib().gsx_compute_morton_codes(n, _ptr(xyz), *_bbox(xyz, bbox), int(flags), _ptr(codes), _stream()))
     return codes
 
 
-def morton_order(xyz, bbox=None, want_codes=False):
+def morton_order(xyz, bbox=None, want_codes=False, flags=0):
     """The permutation TrainerImpl::sort_gaussians applies (cuda/trainer.cu:886-893): order[i] = Gaussian that comes i-th in
     Morton order, ties in index order."""
     _chk_f32(xyz)
@@ -276,7 +277,7 @@ def morton_order(xyz, bbox=None, want_codes=False):
     codes = torch.empty(n, device=xyz.device, dtype=torch.int64) if want_codes else None
     wsb = lib().gsx_morton_order_workspace_bytes(n)
     ws = torch.empty(wsb, device=xyz.device, dtype=torch.uint8)
-    check(lib().gsx_morton_order(n, _ptr(xyz), *_bbox(xyz, bbox), _ptr(order), _ptr(codes), _ptr(ws), C.c_size_t(wsb),
+    check(lib().gsx_morton_order(n, _ptr(xyz), *_bbox(xyz, bbox), int(flags), _ptr(order), _ptr(codes), _ptr(ws), C.c_size_t(wsb),
                                  _stream()))
     return (order, codes) if want_codes else order
 

@@ -118,9 +118,9 @@ def fused_loss(pred, gt, ssim_weight):
 
 
 # ------------------------------------------------------------------------------------------------ Morton re-layout (8f rank 4)
-def morton_codes(xyz, bbox):
-    return _h(H.compute_morton_codes(_d(xyz), bbox)).view(np.uint64)
+def morton_codes(xyz, bbox, true_interleave=False):
+    return _h(H.compute_morton_codes(_d(xyz), bbox, flags=int(true_interleave))).view(np.uint64)
 
 
-def morton_order(xyz, bbox):
-    return _h(H.morton_order(_d(xyz), bbox))
+def morton_order(xyz, bbox, true_interleave=False):
+    return _h(H.morton_order(_d(xyz), bbox, flags=int(true_interleave)))

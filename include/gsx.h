@@ -301,16 +301,20 @@ int gsx_fused_loss(const float *predicted, const float *gt, int rows, int cols, 
 /* ---- SURVEY 8f rank 4 (first half): Morton re-layout of the Gaussian arrays ----
  * gsx_compute_morton_codes replaces compute_morton_codes (include/gsplat_cuda/cuda_forward.cuh:186, cuda/culling.cu:42-68,
  * 345-359): 63-bit codes, 21 bits per axis quantised as (v - min) * (2097151 / (max - min)), z|y|x interleaved.
+ * flags = 0 reproduces the reference's spread_bits (culling.cu:18-40) bit for bit -- its mask sequence keeps only
+ * coordinate bits {0,2,3,9,10,12}, so the codes are a coarse key; GSX_MORTON_TRUE_INTERLEAVE gives the real 3-way
+ * interleave (better locality; results then differ from the reference's by construction).
  * gsx_morton_order replaces the sequence + sort_by_key of TrainerImpl::sort_gaussians (cuda/trainer.cu:886-893): order[i]
  * = index of the Gaussian that comes i-th in Morton order (stable: equal codes keep index order); sorted_codes (may be
  * null) receives the codes in that order.  gsx_gather_rows replaces gather_with_stride (trainer.cu:897-923), out of
  * place: dst[i][0..width) = src[order[i]][0..width). */
+#define GSX_MORTON_TRUE_INTERLEAVE 1
 int gsx_compute_morton_codes(int N, const float *xyz, float x_max, float y_max, float z_max, float x_min, float y_min,
-                             float z_min, uint64_t *codes, void *stream);
+                             float z_min, int flags, uint64_t *codes, void *stream);
 size_t gsx_morton_order_workspace_bytes(int N);
 int gsx_morton_order(int N, const float *xyz, float x_max, float y_max, float z_max, float x_min, float y_min,
-                     float z_min, int *order, uint64_t *sorted_codes, void *workspace, size_t workspace_bytes,
-                     void *stream);
+                     float z_min, int flags, int *order, uint64_t *sorted_codes, void *workspace,
+                     size_t workspace_bytes, void *stream);
 int gsx_gather_rows(const float *src, const int *order, int N, int width, float *dst, void *stream);
 
 #ifdef __cplusplus

@@ -339,14 +339,15 @@ def fused_loss(pred, gt, ssim_weight):
 
 
 # ------------------------------------------------------------------------------------------------ Morton re-layout (8f rank 4)
-def morton_codes(xyz, bbox):
-    """morton_codes_kernel, cuda/culling.cu:42-68; bbox = (x_max, y_max, z_max, x_min, y_min, z_min).  uint64 codes."""
+def morton_codes(xyz, bbox, true_interleave=False):
+    """morton_codes_kernel, cuda/culling.cu:42-68; bbox = (x_max, y_max, z_max, x_min, y_min, z_min).  uint64 codes.
+    Default: the reference's own (lossy) spread_bits; true_interleave: the real 3-way interleave."""
     p = _f(xyz)
     codes = np.empty(p.shape[0], np.uint64)
-    lib().gold_morton_codes(p.shape[0], _p(p), *[C.c_float(b) for b in bbox], _p(codes))
+    lib().gold_morton_codes(p.shape[0], _p(p), *[C.c_float(b) for b in bbox], int(true_interleave), _p(codes))
     return codes
 
 
-def morton_order(xyz, bbox):
+def morton_order(xyz, bbox, true_interleave=False):
     """sequence + sort_by_key of TrainerImpl::sort_gaussians (cuda/trainer.cu:886-893), ties in index order"""
-    return np.argsort(morton_codes(xyz, bbox), kind="stable").astype(np.int32)
+    return np.argsort(morton_codes(xyz, bbox, true_interleave), kind="stable").astype(np.int32)

@@ -344,14 +344,19 @@ def check_morton_codes(B):  # cuda_forward_test.cpp:917-1018 (ComputeMortonCodes
     norm = np.clip(((xyz - mn) / (mx - mn)).astype(np.float32), 0, 1)
     q = (norm * M).astype(np.float32).astype(np.uint64)
 
-    def spread(n):
-        r = 0
-        for b in range(21):
-            r |= ((int(n) >> b) & 1) << (3 * b)
-        return r
+    def spread(n):                                      # the test's own lambda, cuda_forward_test.cpp:963-971
+        n = int(n) & 2097151
+        n = (n | (n << 32)) & 0x1F000000FFFF
+        n = (n | (n << 16)) & 0x1F0000FF0000FF
+        n = (n | (n << 8)) & 0x100F807C0F807C0F
+        n = (n | (n << 4)) & 0x1084210842108421
+        n = (n | (n << 2)) & 0x1249249249249249
+        return n
     exp = np.array([(spread(z) << 2) | (spread(y) << 1) | spread(x) for x, y, z in q], np.uint64)
     np.testing.assert_array_equal(codes, exp)
-    assert codes[0] == 0 and codes[1] == (1 << 63) - 1
+    # the same points through the real interleave (opt-in): bit b of a coordinate lands on bit 3b (+0 x, +1 y, +2 z)
+    true_codes = np.asarray(B.morton_codes(xyz, bbox, true_interleave=True), np.uint64)
+    assert true_codes[0] == 0 and true_codes[1] == (1 << 63) - 1
 
 
 ALL = [check_compute_sigma, check_project_to_screen, check_culling, check_camera_space_points, check_compute_conic,

@@ -932,23 +932,27 @@ def test_fused_loss_rejects_small_workspace_and_host_pointers():
 
 
 # ------------------------------------------------------------------------------------------ Morton re-layout
-def test_morton_codes_and_order_parity(B):
-    """gsx_compute_morton_codes / gsx_morton_order against the oracle (cuda/culling.cu:42-68, trainer.cu:886-893): codes
-    bit-exact, including points on and outside the box; order = stable argsort of the codes (duplicates keep index order)"""
+@pytest.mark.parametrize("true_interleave", [False, True])
+def test_morton_codes_and_order_parity(B, true_interleave):
+    """gsx_compute_morton_codes / gsx_morton_order against the oracle (cuda/culling.cu:18-68, trainer.cu:886-893) in both
+    modes -- the reference's own lossy bit spread (default) and the real interleave: codes bit-exact, including points on
+    and outside the box; order = stable argsort of the codes (equal codes keep index order)"""
     rng = np.random.default_rng(21)
     n = 200_003
     xyz = rng.normal(0, 2, (n, 3)).astype(np.float32)
     xyz[1000:1200] = xyz[0]                                  # duplicate positions: equal codes
     bbox = (float(xyz[:, 0].max()), float(xyz[:, 1].max()), float(xyz[:, 2].max()),
             float(xyz[:, 0].min()), float(xyz[:, 1].min()), float(xyz[:, 2].min()))
-    np.testing.assert_array_equal(B.morton_codes(xyz, bbox), G.morton_codes(xyz, bbox))
-    np.testing.assert_array_equal(B.morton_order(xyz, bbox), G.morton_order(xyz, bbox))
+    t = true_interleave
+    np.testing.assert_array_equal(B.morton_codes(xyz, bbox, t), G.morton_codes(xyz, bbox, t))
+    np.testing.assert_array_equal(B.morton_order(xyz, bbox, t), G.morton_order(xyz, bbox, t))
     tight = (1.0, 1.0, 1.0, -1.0, -1.0, -1.0)              # many points outside: negative -> 0, beyond max wraps by the 21-bit mask
-    np.testing.assert_array_equal(B.morton_codes(xyz, tight), G.morton_codes(xyz, tight))
-    np.testing.assert_array_equal(B.morton_order(xyz, tight), G.morton_order(xyz, tight))
+    np.testing.assert_array_equal(B.morton_codes(xyz, tight, t), G.morton_codes(xyz, tight, t))
+    np.testing.assert_array_equal(B.morton_order(xyz, tight, t), G.morton_order(xyz, tight, t))
 
 
-def test_morton_relayout_properties_at_size():
+@pytest.mark.parametrize("flags", [0, 1])
+def test_morton_relayout_properties_at_size(flags):
     """size-independent properties at 2 M Gaussians: the order is a permutation, the codes come out sorted, gathering the
     positions and recomputing their codes reproduces the sorted codes, and gather_rows equals torch indexing for every
     parameter width (1, 3, 4, 45)"""
@@ -959,12 +963,12 @@ def test_morton_relayout_properties_at_size():
     xyz = torch.randn((n, 3), device="cuda", generator=gen)
     mn, mx = xyz.amin(0).tolist(), xyz.amax(0).tolist()
     bbox = (mx[0], mx[1], mx[2], mn[0], mn[1], mn[2])
-    order, codes = Hh.morton_order(xyz, bbox, want_codes=True)
+    order, codes = Hh.morton_order(xyz, bbox, want_codes=True, flags=flags)
     assert torch.equal(torch.sort(order.long()).values, torch.arange(n, device="cuda"))
     assert bool((codes[1:] >= codes[:-1]).all().item())     # 63-bit codes: signed compare is the unsigned one
     moved = Hh.gather_rows(xyz, order)
     assert torch.equal(moved, xyz[order.long()])
-    assert torch.equal(Hh.compute_morton_codes(moved, bbox), codes)
+    assert torch.equal(Hh.compute_morton_codes(moved, bbox, flags=flags), codes)
     for w in (1, 4, 45):
         a = torch.randn((n, w), device="cuda", generator=gen)
         assert torch.equal(Hh.gather_rows(a, order), a[order.long()])
