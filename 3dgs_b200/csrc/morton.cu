@@ -15,7 +15,7 @@ constexpr uint32_t kBitsPerCoord = 21;                      // culling.cu:15-16
 constexpr uint32_t kMaxCoord = (1u << kBitsPerCoord) - 1;   // 2^21 - 1
 
 // Bit spreading.  TRUE = false reproduces the reference's spread_bits mask sequence (culling.cu:18-40) bit for bit: its
-// third and fourth masks are not the ones of a 3-way interleave, so most coordinate bits are dropped (only bits 0, 2, 3,
+// first, third and fourth masks are not the ones of a 3-way interleave, so most coordinate bits are dropped (only bits 0, 2, 3,
 // 9, 10 and 12 of a coordinate reach the code) -- SURVEY quirk, kept as the default because the reference's own test and trainer see
 // exactly these codes.  TRUE = true is the real interleave (bit b -> bit 3b), opt-in through GSX_MORTON_TRUE_INTERLEAVE.
 template <bool TRUE>
