@@ -35,7 +35,8 @@ __global__ void __launch_bounds__(256) k_morton_codes(int N, const float *__rest
                                                       uint64_t *__restrict__ codes, uint32_t *__restrict__ iota) {
   const int i = blockIdx.x * 256 + threadIdx.x;
   if (i >= N) return;
-  const float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+  const size_t b = (size_t)3 * i;
+  const float x = xyz[b], y = xyz[b + 1], z = xyz[b + 2];
   // quantisation exactly as culling.cu:55-57: (v - min) * (2097151 / (max - min)), truncated; float -> uint64
   // conversion saturates (negative and NaN give 0)
   const uint64_t xq = __float2ull_rz(__fmul_rn(__fsub_rn(x, x_min), __fdiv_rn((float)kMaxCoord, __fsub_rn(x_max, x_min))));
