@@ -23,9 +23,9 @@ SYMBOLS = [
     "gsx_sorted_list_workspace_bytes", "gsx_get_sorted_gaussian_list", "gsx_render_image",
     "gsx_render_image_backward", "gsx_precompute_spherical_harmonics_backward", "gsx_compute_conic_backward",
     "gsx_compute_projection_jacobian_backward", "gsx_compute_sigma_backward", "gsx_project_to_screen_backward",
-    "gsx_compute_camera_space_points_backward", "gsx_sort_workspace_bytes", "gsx_sort_pairs_u64", "gsx_tile_ranges",
-    "gsx_ctx_create", "gsx_ctx_destroy", "gsx_forward", "gsx_backward", "gsx_ctx_stats", "gsx_ctx_reserve",
-    "gsx_ctx_state", "gsx_render_view_host", "gsx_ctx_enable_timing", "gsx_ctx_timing", "gsx_ctx_count_work", "gsx_measure_fp32_tflops",
+    "gsx_compute_camera_space_points_backward", "gsx_sort_workspace_bytes", "gsx_sort_pairs_u64", "gsx_sort_pairs_u32", "gsx_tile_ranges",
+    "gsx_ctx_create", "gsx_ctx_destroy", "gsx_forward", "gsx_backward", "gsx_ctx_stats", "gsx_ctx_reserve", "gsx_ctx_overflow",
+    "gsx_ctx_state", "gsx_render_view_host", "gsx_ctx_enable_timing", "gsx_ctx_timing", "gsx_ctx_count_work", "gsx_ctx_count_hits", "gsx_measure_fp32_tflops",
     "gsx_batch_reserve", "gsx_batch_forward_params", "gsx_batch_forward_view", "gsx_batch_backward_view",
     "gsx_batch_backward_params", "gsx_batch_render_host", "gsx_batch_extract_view_rgb_grad",
     "gsx_sh_grads_from_view_rgb", "gsx_ctx_build_sorted_keys", "gsx_batch_extract_view_rgb_grad_peers",

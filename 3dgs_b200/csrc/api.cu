@@ -5,6 +5,7 @@
 // count K stays on the device and every kernel downstream of the scan reads it from there.
 #include <algorithm>
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include "gsx_common.cuh"
 #include "gsx_math.cuh"
@@ -39,7 +40,7 @@ int check_device_ptr(const void *p, const char *name) {
 // from binning.cu / composite.cu / batch.cu
 BinLayout bin_layout(int N, long long capacity);
 int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, int N, bool compact, const int *ccount,
-                    PreBin *pb, cudaStream_t st);
+                    PreBin *pb, cudaStream_t st, long long capacity);
 int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, const int *touched, int ntx, int nty, int N,
                        long long capacity, char *ws, const BinLayout &L, const PreBin &pb, int *ranges,
                        const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
@@ -63,6 +64,9 @@ int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, c
                          float *packed_grads, cudaStream_t st);
 int count_work_launch(const float4 *r0, const float4 *r1, const int *sorted, const int *ranges, int W, int H,
                       const int *spp, unsigned long long *out_dev, cudaStream_t st);
+int composite_hits_launch(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges, int W,
+                          int H, const int *spp, const float *wpp, const float *grad_image, unsigned long long *out_dev,
+                          cudaStream_t st);
 
 }  // namespace gsx
 
@@ -107,8 +111,10 @@ struct gsx_ctx {
   const uint32_t *sorted_vals = nullptr;
   int last_n = 0, last_w = 0, last_h = 0;
   int batch_n = 0, batch_nv = 0, batch_lmax = 0;
-  int *h_stats = nullptr;           // pinned: [0] = K, [1] = P
+  int *h_stats = nullptr;           // pinned: [0] = K, [1] = P, [4 + k] = K of slot k
+  int *h_over = nullptr;            // pinned + mapped: largest K that exceeded the capacity since the last reserve (0: none)
   int *d_P = nullptr;
+  unsigned long long *d_work = nullptr;   // gsx_ctx_count_work's two counters
   int *d_ccount = nullptr;          // [GSX_MAX_BATCH] compacted-Gaussian counters of the slots
   // optional stage timing (gsx_ctx_enable_timing): 0,1 per-Gaussian forward; 2 view start, 3 emit, 4 sort, 5 ranges,
   // 6 compositing forward; 7,8 compositing backward; 9,10 per-Gaussian backward
@@ -150,20 +156,30 @@ static int alloc_bin(gsx_ctx *c, long long capacity) {
     b.sorted_tiles = b.sorted_vals = nullptr; b.owner = -1;
   }
   c->sorted_tiles = nullptr; c->sorted_vals = nullptr;
+  if (capacity >= (1LL << 30)) { set_error("instance capacity %lld >= 2^30", capacity); return GSX_E_ARG; }
   c->capacity = std::max<long long>(capacity, 1024);
   c->L = bin_layout(c->max_n, c->capacity);
   const int sets = c->n_slots > 1 ? 2 : 1;     // the second set exists once a batch of views was reserved
   for (int i = 0; i < sets; ++i) {
     GSX_CUDA(cudaMalloc(&c->bset[i].ws, c->L.bytes));
+    // tests poison the instance buffers (GSX_DEBUG_POISON=1) to prove that an overflowed view never reads them
+    if (getenv("GSX_DEBUG_POISON")) GSX_CUDA(cudaMemset(c->bset[i].ws, 0xFF, c->L.bytes));
     if (!c->bset[i].ranges) GSX_CUDA(cudaMalloc(&c->bset[i].ranges, sizeof(int) * (size_t)(c->n_px_tiles + 1)));
   }
   c->bin_ws = c->bset[0].ws; c->ranges = c->bset[0].ranges;
   return GSX_OK;
 }
 
+static void release_slot(gsx_slot &s);
+static int alloc_slot_buffers(gsx_ctx *c, int k);
 static int alloc_slot(gsx_ctx *c, int k) {
+  if (c->slot[k].allocated) return GSX_OK;
+  const int rc = alloc_slot_buffers(c, k);
+  if (rc != GSX_OK) release_slot(c->slot[k]);   // a failed cudaMalloc must not leak the buffers obtained before it
+  return rc;
+}
+static int alloc_slot_buffers(gsx_ctx *c, int k) {
   gsx_slot &s = c->slot[k];
-  if (s.allocated) return GSX_OK;
   const size_t n = (size_t)c->max_n;
   GSX_CUDA(cudaMalloc(&s.p.r0, n * sizeof(float4)));
   GSX_CUDA(cudaMalloc(&s.p.r1, n * sizeof(float4)));
@@ -177,6 +193,7 @@ static int alloc_slot(gsx_ctx *c, int k) {
   GSX_CUDA(cudaMalloc(&s.p.cid, n * sizeof(uint32_t)));
   s.p.ccount = c->d_ccount + k;
   s.pb.key_a = s.p.ckey; s.pb.val_a = s.p.cid;
+  s.pb.over_flag = c->h_over;
   GSX_CUDA(cudaMalloc(&s.pb.key_b, n * sizeof(uint32_t)));
   GSX_CUDA(cudaMalloc(&s.pb.val_b, n * sizeof(uint32_t)));
   GSX_CUDA(cudaMalloc(&s.pb.offsets, n * sizeof(int)));
@@ -194,8 +211,7 @@ static int alloc_slot(gsx_ctx *c, int k) {
   if (k + 1 > c->n_slots) c->n_slots = k + 1;
   return GSX_OK;
 }
-static void free_slot(gsx_slot &s) {
-  if (!s.allocated) return;
+static void release_slot(gsx_slot &s) {   // cudaFree(nullptr) is a no-op
   cudaFree(s.p.r0); cudaFree(s.p.r1); cudaFree(s.p.r2); cudaFree(s.p.radius); cudaFree(s.p.depth); cudaFree(s.p.mask);
   cudaFree(s.p.touched); cudaFree(s.p.gacc); cudaFree(s.p.ckey); cudaFree(s.p.cid);
   cudaFree(s.pb.key_b); cudaFree(s.pb.val_b); cudaFree(s.pb.offsets); cudaFree(s.pb.block_sums); cudaFree(s.pb.total);
@@ -203,6 +219,9 @@ static void free_slot(gsx_slot &s) {
   if (s.ev_pre) cudaEventDestroy(s.ev_pre);
   if (s.ev_bin) cudaEventDestroy(s.ev_bin);
   s = gsx_slot();
+}
+static void free_slot(gsx_slot &s) {
+  if (s.allocated) release_slot(s);
 }
 
 // Work issued ahead on the side streams reads the slots' per-Gaussian outputs and writes the instance-buffer sets: before
@@ -261,7 +280,7 @@ static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
       GSX_CUDA(cudaStreamWaitEvent(st, s.ev_pre, 0));  // issued by gsx_batch_forward_params on the side stream
       s.pre_async = false;
     } else {
-      rc = bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, st);
+      rc = bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, st, c->capacity);
       if (rc != GSX_OK) return rc;
     }
     rc = issue_emit_sort(c, k, N, st, c->timing ? &c->ev[3] : nullptr);
@@ -290,6 +309,12 @@ static int check_view(gsx_ctx *c, const gsx_view_t *v, const gsx_params_t *p, in
   if (v->l_max < 0 || v->l_max > 3) { set_error("l_max %d out of range 0..3", v->l_max); return GSX_E_ARG; }
   const int shf = ((v->l_max + 1) * (v->l_max + 1) - 1) * 3;
   if (v->l_max > 0 && p->sh_stride < shf) { set_error("sh_stride %d < %d", p->sh_stride, shf); return GSX_E_ARG; }
+  if (((uintptr_t)p->quaternion) & 15) { set_error("params.quaternion must be 16-byte aligned (float4 loads)"); return GSX_E_ARG; }
+  return GSX_OK;
+}
+static int check_grads(const gsx_grads_t *g) {
+  if (((uintptr_t)g->quaternion) & 15) { set_error("grads.quaternion must be 16-byte aligned (float4 stores)"); return GSX_E_ARG; }
+  if (((uintptr_t)g->uv) & 7) { set_error("grads.uv must be 8-byte aligned"); return GSX_E_ARG; }
   return GSX_OK;
 }
 }  // namespace gsx
@@ -305,8 +330,12 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
   c->max_n = max_gaussians; c->max_w = max_width; c->max_h = max_height;
   const size_t px = (size_t)max_width * max_height;
   const int T = ((max_width + 15) / 16) * ((max_height + 15) / 16);
+  if (instance_capacity >= (1LL << 30)) { set_error("instance capacity %lld >= 2^30", instance_capacity); delete c; return GSX_E_ARG; }
   GSX_CUDA(cudaMalloc(&c->d_ccount, GSX_MAX_BATCH * sizeof(int)));
   GSX_CUDA(cudaMemset(c->d_ccount, 0, GSX_MAX_BATCH * sizeof(int)));
+  GSX_CUDA(cudaHostAlloc(&c->h_over, 4 * sizeof(int), cudaHostAllocMapped));
+  c->h_over[0] = 0;
+  GSX_CUDA(cudaMalloc(&c->d_work, 2 * sizeof(unsigned long long)));
   {
     int rc0 = alloc_slot(c, 0);
     if (rc0 != GSX_OK) return rc0;
@@ -318,8 +347,8 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
   GSX_CUDA(cudaMalloc(&c->spp, px * sizeof(int)));
   GSX_CUDA(cudaMalloc(&c->grad_image, px * 3 * sizeof(float)));
   GSX_CUDA(cudaMalloc(&c->d_P, sizeof(int)));
-  GSX_CUDA(cudaMallocHost(&c->h_stats, 4 * sizeof(int)));
-  if (instance_capacity <= 0) instance_capacity = 8LL * max_gaussians;
+  GSX_CUDA(cudaMallocHost(&c->h_stats, (4 + GSX_MAX_BATCH) * sizeof(int)));
+  if (instance_capacity <= 0) instance_capacity = std::min<long long>(8LL * max_gaussians, (1LL << 30) - 1);
   int rc = alloc_bin(c, instance_capacity);
   if (rc != GSX_OK) return rc;
   *out = c;
@@ -346,6 +375,7 @@ int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (c->cs_in) cudaStreamDestroy(c->cs_in);
   if (c->cs_out) cudaStreamDestroy(c->cs_out);
   cudaFree(c->grad_image); cudaFree(c->d_P); cudaFree(c->d_ccount); cudaFreeHost(c->h_stats);
+  cudaFree(c->d_work); cudaFreeHost(c->h_over);
   delete c;
   return GSX_OK;
 }
@@ -356,6 +386,7 @@ int gsx_ctx_reserve(gsx_ctx_t *c, long long instance_capacity) {
   if (instance_capacity >= (1LL << 30)) { set_error("instance capacity %lld >= 2^30", instance_capacity); return GSX_E_ARG; }
   GSX_CUDA(cudaDeviceSynchronize());
   for (int k = 0; k < c->n_slots; ++k) c->slot[k].pre_async = c->slot[k].bin_async = false;
+  c->h_over[0] = 0;
   return alloc_bin(c, instance_capacity);
 }
 
@@ -388,8 +419,10 @@ int gsx_backward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N
   }
   cudaStream_t st = (cudaStream_t)stream;
   const gsx_slot &s = c->slot[0];
+  int rc = check_grads(g);
+  if (rc != GSX_OK) return rc;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[7], st));
-  int rc = composite_bwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
+  rc = composite_bwd_packed(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, v->width, v->height,
                                 v->background, c->spp, c->wpp, grad_image, (float *)s.p.gacc, st);
   if (rc != GSX_OK) return rc;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[8], st));
@@ -463,7 +496,7 @@ int gsx_batch_forward_params(gsx_ctx_t *c, const gsx_view_t *views, int n_views,
     GSX_CUDA(cudaStreamWaitEvent(c->cs_pre, c->ev_fwd, 0));
     for (int k = 0; k < n_views; ++k) {
       gsx_slot &s = c->slot[k];
-      rc = bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, c->cs_pre);
+      rc = bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, c->cs_pre, c->capacity);
       if (rc != GSX_OK) return rc;
       GSX_CUDA(cudaEventRecord(s.ev_pre, c->cs_pre));
       s.pre_async = true;
@@ -498,6 +531,11 @@ int gsx_batch_backward_view(gsx_ctx_t *c, int slot, const float *grad_image, voi
 int gsx_batch_backward_params(gsx_ctx_t *c, const gsx_params_t *p, int N, const gsx_grads_t *g, int flags, void *stream) {
   if (!c || !p || !g) { set_error("null argument"); return GSX_E_NULL; }
   if (N != c->batch_n || c->batch_nv < 1) { set_error("gsx_batch_backward_params does not match the current batch"); return GSX_E_ARG; }
+  if (((uintptr_t)p->quaternion) & 15) { set_error("params.quaternion must be 16-byte aligned (float4 loads)"); return GSX_E_ARG; }
+  {
+    int rcg = check_grads(g);
+    if (rcg != GSX_OK) return rcg;
+  }
   BatchConst bc;
   fill_batch_const(c, c->batch_nv, &bc);
   cudaStream_t st = (cudaStream_t)stream;
@@ -610,16 +648,30 @@ int gsx_batch_render_host(gsx_ctx_t *c, const gsx_view_t *views, int n_views, co
 int gsx_ctx_count_work(gsx_ctx_t *c, unsigned long long *out_host, void *stream) {
   if (!c || !out_host) return GSX_E_NULL;
   cudaStream_t st = (cudaStream_t)stream;
-  unsigned long long *d = nullptr;
-  GSX_CUDA(cudaMalloc(&d, 2 * sizeof(unsigned long long)));
+  unsigned long long *d = c->d_work;
   GSX_CUDA(cudaMemsetAsync(d, 0, 2 * sizeof(unsigned long long), st));
   int rc = count_work_launch(c->slot[c->cur].p.r0, c->slot[c->cur].p.r1, (const int *)c->sorted_vals, c->ranges, c->last_w, c->last_h, c->spp, d, st);
   if (rc == GSX_OK) {
     GSX_CUDA(cudaMemcpyAsync(out_host, d, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
     GSX_CUDA(cudaStreamSynchronize(st));
   }
-  cudaFree(d);
   return rc;
+}
+
+// out_host[2] = {warp-hits, contributing warp-hits} of the compositing backward over the last forward's lists: the
+// number of (8x8 pixel block, entry) pairs that survive the extent-box cull, and of those with a contributing pixel --
+// the units the compositing kernels' instruction counts scale with.  Diagnostics; synchronises.
+int gsx_ctx_count_hits(gsx_ctx_t *c, const float *grad_image, unsigned long long *out_host, void *stream) {
+  if (!c || !out_host || !grad_image) return GSX_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  const gsx_slot &s = c->slot[c->cur];
+  GSX_CUDA(cudaMemsetAsync(c->d_work, 0, 2 * sizeof(unsigned long long), st));
+  int rc = composite_hits_launch(s.p.r0, s.p.r1, s.p.r2, (const int *)c->sorted_vals, c->ranges, c->last_w, c->last_h, c->spp,
+                                 c->wpp, grad_image, c->d_work, st);
+  if (rc != GSX_OK) return rc;
+  GSX_CUDA(cudaMemcpyAsync(out_host, c->d_work, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+  GSX_CUDA(cudaStreamSynchronize(st));
+  return GSX_OK;
 }
 
 int gsx_ctx_enable_timing(gsx_ctx_t *c, int on) {
@@ -696,10 +748,35 @@ int gsx_ctx_stats(gsx_ctx_t *c, gsx_stats_t *out, void *stream) {
   }
   GSX_CUDA(cudaMemcpyAsync(&c->h_stats[0], (const char *)c->cur_total, sizeof(int), cudaMemcpyDeviceToHost, st));
   GSX_CUDA(cudaMemcpyAsync(&c->h_stats[1], c->d_P, sizeof(int), cudaMemcpyDeviceToHost, st));
+  // every view of the current batch is checked, not only the last one forwarded: an overflowed view composites nothing
+  // (binning.cu k_scan_block_sums), so its image and gradients are missing until the caller reserves and re-runs
+  const int nv = std::max(1, std::min(c->batch_nv, c->n_slots));
+  for (int k = 0; k < nv; ++k) {
+    c->h_stats[4 + k] = 0;
+    if (c->slot[k].allocated && c->slot[k].pb.total)
+      GSX_CUDA(cudaMemcpyAsync(&c->h_stats[4 + k], c->slot[k].pb.total, sizeof(int), cudaMemcpyDeviceToHost, st));
+  }
   GSX_CUDA(cudaStreamSynchronize(st));
   out->N = c->last_n; out->P = c->h_stats[1]; out->K = c->h_stats[0]; out->capacity = c->capacity;
-  if (out->K > c->capacity) {
-    set_error("instance capacity exceeded: K=%lld > %lld (gsx_ctx_reserve and re-run)", out->K, c->capacity);
+  long long worst = out->K;
+  for (int k = 0; k < nv; ++k) worst = std::max<long long>(worst, c->h_stats[4 + k]);
+  if (worst > c->capacity) {
+    if (out->K <= c->capacity) out->K = worst;   // report what has to be reserved
+    set_error("instance capacity exceeded: K=%lld > %lld (gsx_ctx_reserve and re-run)", worst, c->capacity);
+    return GSX_E_CAPACITY;
+  }
+  return GSX_OK;
+}
+
+// No synchronisation: reads the pinned flag the scan kernels raise.  GSX_E_CAPACITY (and the K to reserve for) if any view
+// forwarded since the last gsx_ctx_reserve exceeded the instance capacity; such a view rendered background only and
+// contributed no gradients.  Definitive once the stream that ran the views is synchronised; a training loop polls it once per step.
+int gsx_ctx_overflow(gsx_ctx_t *c, long long *required_capacity_host) {
+  if (!c) return GSX_E_NULL;
+  const int k = *(volatile int *)c->h_over;
+  if (required_capacity_host) *required_capacity_host = k;
+  if (k > 0) {
+    set_error("instance capacity exceeded: K=%d > %lld (gsx_ctx_reserve and re-run)", k, c->capacity);
     return GSX_E_CAPACITY;
   }
   return GSX_OK;
@@ -732,7 +809,7 @@ int gsx_ctx_build_sorted_keys(gsx_ctx_t *c, const uint64_t **out) {
   }
   GSX_CUDA(cudaDeviceSynchronize());
   k_compose_keys<<<kNumSMs * 8, 256>>>(c->sorted_tiles, c->sorted_vals, c->slot[c->cur].p.depth,
-                                       (const int *)((const char *)c->cur_total), c->capacity, c->key64);
+                                       c->cur_total + 1, c->capacity, c->key64);
   GSX_LAUNCH_CHECK();
   GSX_CUDA(cudaDeviceSynchronize());
   *out = c->key64;
@@ -743,9 +820,11 @@ int gsx_render_view_host(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *
                          const float *grad_image_host, float *image_host, const gsx_grads_t *g, void *stream) {
   if (!c || !v || !p) { set_error("null argument"); return GSX_E_NULL; }
   cudaStream_t st = (cudaStream_t)stream;
+  int rc = check_view(c, v, p, N);   // before any copy: an oversize view must not overrun the staging buffer
+  if (rc != GSX_OK) return rc;
   const size_t bytes = (size_t)v->width * v->height * 3 * sizeof(float);
   if (grad_image_host) GSX_CUDA(cudaMemcpyAsync(c->grad_image, grad_image_host, bytes, cudaMemcpyHostToDevice, st));
-  int rc = gsx_forward(c, v, p, N, stream);
+  rc = gsx_forward(c, v, p, N, stream);
   if (rc != GSX_OK) return rc;
   if (image_host) GSX_CUDA(cudaMemcpyAsync(image_host, c->image, bytes, cudaMemcpyDeviceToHost, st));
   if (grad_image_host && g) {

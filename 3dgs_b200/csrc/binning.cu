@@ -13,6 +13,8 @@
 // ever materialised, and emission order is Gaussian-major so equal (tile, depth) keys come out in ascending
 // Gaussian id after the stable sort.
 #include <algorithm>
+#include <climits>
+#include <mutex>
 
 #include "gsx_common.cuh"
 #include "gsx_math.cuh"
@@ -86,10 +88,13 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
                                                  const uint32_t *__restrict__ perm,
                                                  const int *__restrict__ touched, const int *__restrict__ offsets,
                                                  int ntx, int nty, int N_host, const int *__restrict__ n_dev,
-                                                 long long capacity, uint32_t *__restrict__ tiles,
-                                                 uint32_t *__restrict__ vals, int tight) {
+                                                 const int *__restrict__ total, long long capacity,
+                                                 uint32_t *__restrict__ tiles, uint32_t *__restrict__ vals, int tight) {
   const int j = blockIdx.x * kBlock + threadIdx.x;
   const int lane = threadIdx.x & 31;
+  // total[1] = live instance count: 0 when the view has no instances OR when K exceeds the capacity (the scan flags the
+  // overflow; nothing is emitted, sorted or composited for such a view, so no stale id is ever dereferenced)
+  if (total[1] == 0) return;
   const int N = n_dev ? min(*n_dev, N_host) : N_host;
   bool live = j < N && dkeys[j] != 0xffffffffu;
   int i = 0, cnt = 0;
@@ -202,9 +207,12 @@ __global__ void __launch_bounds__(kBlock) k_scan_reduce(const int *__restrict__ 
   if (threadIdx.x == 0) block_sums[blockIdx.x] = t;
 }
 
-__global__ void __launch_bounds__(1024) k_scan_block_sums(int *__restrict__ block_sums, int nb, int *__restrict__ total) {
+// total[0] = K (saturated at INT_MAX), total[1] = live count = K if K <= capacity else 0; an overflow is also recorded in
+// *over_flag (pinned host memory mapped into the device, polled by gsx_ctx_overflow without any synchronisation)
+__global__ void __launch_bounds__(1024) k_scan_block_sums(int *__restrict__ block_sums, int nb, int *__restrict__ total,
+                                                          long long capacity, int *over_flag) {
   __shared__ int s[1024];
-  __shared__ int carry;
+  __shared__ long long carry;
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
   for (int b0 = 0; b0 < nb; b0 += 1024) {
@@ -218,12 +226,18 @@ __global__ void __launch_bounds__(1024) k_scan_block_sums(int *__restrict__ bloc
       s[threadIdx.x] += t;
       __syncthreads();
     }
-    if (i < nb) block_sums[i] = carry + s[threadIdx.x] - v;
+    if (i < nb) block_sums[i] = (int)min(carry + s[threadIdx.x] - v, (long long)INT_MAX);
     __syncthreads();
     if (threadIdx.x == 1023) carry += s[1023];
     __syncthreads();
   }
-  if (threadIdx.x == 0) *total = carry;
+  if (threadIdx.x == 0) {
+    const int K = (int)min(carry, (long long)INT_MAX);
+    const bool over = capacity > 0 && carry > capacity;
+    total[0] = K;
+    total[1] = over ? 0 : K;
+    if (over && over_flag && K > *(volatile int *)over_flag) *(volatile int *)over_flag = K;
+  }
 }
 
 __global__ void __launch_bounds__(kBlock) k_scan_apply(const int *__restrict__ in, const uint32_t *__restrict__ perm,
@@ -272,11 +286,11 @@ int tile_key_bits(int n_tiles) {
 }
 
 int exclusive_scan_i32(const int *in, const uint32_t *perm, const uint32_t *dkeys, int N, const int *n_dev, int *out,
-                       int *block_sums, int *total_dev, cudaStream_t st) {
+                       int *block_sums, int *total_dev, cudaStream_t st, long long capacity, int *over_flag) {
   const int nb = std::max(1, ceil_div(N, SCAN_TILE));
   k_scan_reduce<<<nb, kBlock, 0, st>>>(in, perm, dkeys, N, n_dev, block_sums);
   GSX_LAUNCH_CHECK();
-  k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nb, total_dev);
+  k_scan_block_sums<<<1, 1024, 0, st>>>(block_sums, nb, total_dev, capacity, over_flag);
   GSX_LAUNCH_CHECK();
   k_scan_apply<<<nb, kBlock, 0, st>>>(in, perm, dkeys, N, n_dev, block_sums, out);
   GSX_LAUNCH_CHECK();
@@ -311,7 +325,7 @@ BinLayout bin_layout(int N, long long capacity) {
 // compact mode (ckey given): key_a / val_a are the slot's compacted, unordered depth keys + ids (*ccount entries) written
 // by the per-Gaussian kernel, so everything here runs over P' entries; otherwise keys are derived from depth[] over N.
 int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, int N, bool compact, const int *ccount,
-                    PreBin *pb, cudaStream_t st) {
+                    PreBin *pb, cudaStream_t st, long long capacity) {
   int in_b = 0, rc;
   pb->perm = nullptr; pb->dkeys = nullptr; pb->count = nullptr;
   if (N > 0) {
@@ -330,7 +344,8 @@ int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, in
     }
     pb->perm = sv; pb->dkeys = sk;
   }
-  return exclusive_scan_i32(touched, pb->perm, pb->dkeys, N, pb->count, pb->offsets, pb->block_sums, pb->total, st);
+  return exclusive_scan_i32(touched, pb->perm, pb->dkeys, N, pb->count, pb->offsets, pb->block_sums, pb->total, st, capacity,
+                            pb->over_flag);
 }
 
 // ---- phase 2: emit in depth order -> tile sort -> ranges.  Leaves the sorted tile ids / Gaussian ids in
@@ -345,17 +360,17 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
   int in_b = 0, rc;
   if (N > 0) {
     k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, pb.dkeys, pb.perm, touched, pb.offsets, ntx, nty, N,
-                                                   pb.count, capacity, ka, va, (tight && uv_stride == 4) ? 1 : 0);
+                                                   pb.count, pb.total, capacity, ka, va, (tight && uv_stride == 4) ? 1 : 0);
     GSX_LAUNCH_CHECK();
   }
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
-  rc = sort_pairs_u32_impl(ka, kb, va, vb, capacity, pb.total, tile_key_bits(ntx * nty) - 32, ws + L.sort_ws, L.sort_ws_bytes, st,
+  rc = sort_pairs_u32_impl(ka, kb, va, vb, capacity, pb.total + 1, tile_key_bits(ntx * nty) - 32, ws + L.sort_ws, L.sort_ws_bytes, st,
                            &in_b);
   if (rc != GSX_OK) return rc;
   *sorted_tiles = in_b ? kb : ka;
   *sorted_vals = in_b ? vb : va;
   if (ev) GSX_CUDA(cudaEventRecord(ev[1], st));
-  rc = tile_ranges_u32_impl(*sorted_tiles, capacity, pb.total, ntx * nty, ranges, st);
+  rc = tile_ranges_u32_impl(*sorted_tiles, capacity, pb.total + 1, ntx * nty, ranges, st);
   if (ev) GSX_CUDA(cudaEventRecord(ev[2], st));
   return rc;
 }
@@ -369,7 +384,7 @@ int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_
   pb.val_a = (uint32_t *)(ws + L.dv_a); pb.val_b = (uint32_t *)(ws + L.dv_b);
   pb.offsets = (int *)(ws + L.offsets); pb.block_sums = (int *)(ws + L.block_sums); pb.total = (int *)(ws + L.total);
   pb.sort_ws = ws + L.sort_ws; pb.sort_ws_bytes = L.sort_ws_bytes;
-  int rc = bin_prebin_impl(depth, depth_stride, touched, N, false, nullptr, &pb, st);
+  int rc = bin_prebin_impl(depth, depth_stride, touched, N, false, nullptr, &pb, st, capacity);
   if (rc != GSX_OK) return rc;
   return bin_emit_sort_impl(uv, uv_stride, radius, touched, ntx, nty, N, capacity, ws, L, pb, ranges, sorted_tiles, sorted_vals, st,
                             nullptr, 0);
@@ -395,18 +410,27 @@ int copy_ids_launch(const uint32_t *in, int *out, long long n, const int *n_dev,
 }
 
 // small cached internal workspace for callers that pass none (the reference API has no workspace argument)
-static char *g_ws = nullptr;
-static size_t g_ws_bytes = 0;
-int internal_workspace(size_t bytes, char **out) {
-  if (bytes > g_ws_bytes) {
-    if (g_ws) cudaFree(g_ws);
-    g_ws = nullptr; g_ws_bytes = 0;
-    GSX_CUDA(cudaMalloc(&g_ws, bytes));
-    g_ws_bytes = bytes;
+// One per device, grown under a mutex.  A grown buffer replaces the old one only after the device is idle (kernels of an
+// earlier call may still be queued on it).  Callers that share a device between host threads must pass their own
+// workspace (gsx.h): the cached one is handed out without a lease.
+static std::mutex g_ws_mu;
+static char *g_ws[2][64] = {};
+static size_t g_ws_bytes[2][64] = {};
+int internal_workspace_slot(int which, size_t bytes, char **out) {   // which: 0 = sorted list (F7), 1 = fused_loss shim
+  int dev = 0;
+  GSX_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || which < 0 || which > 1) { set_error("device index %d out of range", dev); return GSX_E_ARG; }
+  std::lock_guard<std::mutex> lk(g_ws_mu);
+  if (bytes > g_ws_bytes[which][dev]) {
+    if (g_ws[which][dev]) { GSX_CUDA(cudaDeviceSynchronize()); cudaFree(g_ws[which][dev]); }
+    g_ws[which][dev] = nullptr; g_ws_bytes[which][dev] = 0;
+    GSX_CUDA(cudaMalloc(&g_ws[which][dev], bytes));
+    g_ws_bytes[which][dev] = bytes;
   }
-  *out = g_ws;
+  *out = g_ws[which][dev];
   return GSX_OK;
 }
+int internal_workspace(size_t bytes, char **out) { return internal_workspace_slot(0, bytes, out); }
 
 }  // namespace gsx
 
@@ -417,6 +441,7 @@ extern "C" {
 int gsx_sorted_list_size(const float *uv, const float *radius, int n_tiles_x, int n_tiles_y, int N,
                          long long *coarse_pairs_host, long long *num_instances_host, void *stream) {
   GSX_REQUIRE_DEV(uv); GSX_REQUIRE_DEV(radius);
+  GSX_REQUIRE_ALIGNED(radius, 16);
   cudaStream_t st = (cudaStream_t)stream;
   if (coarse_pairs_host) *coarse_pairs_host = 0;
   if (num_instances_host) *num_instances_host = 0;
@@ -430,7 +455,7 @@ int gsx_sorted_list_size(const float *uv, const float *radius, int n_tiles_x, in
   rc = count_tiles_launch(uv, 2, (const float4 *)radius, nullptr, n_tiles_x, n_tiles_y, N, (int *)(ws + L.touched), coarse, st);
   if (rc != GSX_OK) return rc;
   rc = exclusive_scan_i32((int *)(ws + L.touched), nullptr, nullptr, N, nullptr, (int *)(ws + L.offsets), (int *)(ws + L.block_sums),
-                          (int *)(ws + L.total), st);
+                          (int *)(ws + L.total), st, 0, nullptr);
   if (rc != GSX_OK) return rc;
   unsigned long long hc = 0;
   int hk = 0;
@@ -450,6 +475,7 @@ int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const floa
                                  int n_tiles_y, int N, long long capacity, int *sorted_gaussians, int *ranges,
                                  int *num_instances_dev, void *workspace, size_t workspace_bytes, void *stream) {
   GSX_REQUIRE_DEV(uv); GSX_REQUIRE_DEV(xyz_c); GSX_REQUIRE_DEV(radius); GSX_REQUIRE_DEV(ranges);
+  GSX_REQUIRE_ALIGNED(radius, 16);
   cudaStream_t st = (cudaStream_t)stream;
   const int T = n_tiles_x * n_tiles_y;
   if (N <= 0 || capacity <= 0) {
@@ -475,7 +501,7 @@ int gsx_get_sorted_gaussian_list(const float *uv, const float *xyz_c, const floa
   rc = bin_sort_impl(uv, 2, xyz_c + 2, 3, (const float4 *)radius, (const int *)(ws + L.touched), n_tiles_x, n_tiles_y, N,
                      capacity, ws, L, ranges, &sk, &sv, st);
   if (rc != GSX_OK) return rc;
-  rc = copy_ids_launch(sv, sorted_gaussians, capacity, (const int *)(ws + L.total), st);
+  rc = copy_ids_launch(sv, sorted_gaussians, capacity, (const int *)(ws + L.total) + 1, st);
   if (rc != GSX_OK) return rc;
   if (num_instances_dev)
     GSX_CUDA(cudaMemcpyAsync(num_instances_dev, ws + L.total, sizeof(int), cudaMemcpyDeviceToDevice, st));

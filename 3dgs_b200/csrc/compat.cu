@@ -10,6 +10,8 @@
 #include "../../include/gsplat_cuda/optimizer.cuh"
 #include "../../include/gsx.h"
 
+namespace gsx { int internal_workspace_slot(int which, size_t bytes, char **out); }   // binning.cu
+
 static void gsx_or_die(int rc, const char *fn) {
   if (rc != GSX_OK) {
     fprintf(stderr, "Assertion failed in %s: %s (gsx status %d)\n", fn, gsx_last_error(), rc);
@@ -122,22 +124,17 @@ void adam_step(float *params, float *const param_grads, float *exp_avg, float *e
 }
 
 // SURVEY 8f rank 3 (reference cuda/loss.cu:440-471): returns the mean loss, i.e. synchronises like the reference does.
-// The reference allocates its temporaries per call; the shim keeps one grow-only workspace (single trainer thread, 8b).
+// The reference allocates its temporaries per call; the shim keeps one grow-only workspace per device.
 float fused_loss(const float *predicted_data, const float *gt_data, int rows, int cols, const float ssim_weight,
                  float *image_grad, cudaStream_t stream) {
-  static void *ws = nullptr;
-  static size_t ws_bytes = 0;
   const size_t need = gsx_fused_loss_workspace_bytes(rows, cols);
-  if (need > ws_bytes) {
-    if (ws) cudaFree(ws);
-    if (cudaMalloc(&ws, need) != cudaSuccess) {
-      fprintf(stderr, "Assertion failed in fused_loss: cannot allocate %zu workspace bytes\n", need);
-      exit(EXIT_FAILURE);
-    }
-    ws_bytes = need;
+  char *ws = nullptr;   // per-device, mutex-guarded, grow-only (binning.cu internal_workspace_slot)
+  if (gsx::internal_workspace_slot(1, need, &ws) != GSX_OK) {
+    fprintf(stderr, "Assertion failed in fused_loss: cannot allocate %zu workspace bytes\n", need);
+    exit(EXIT_FAILURE);
   }
   float loss = 0.0f;
-  DIE_UNLESS(gsx_fused_loss(predicted_data, gt_data, rows, cols, ssim_weight, image_grad, ws, ws_bytes, nullptr, &loss,
+  DIE_UNLESS(gsx_fused_loss(predicted_data, gt_data, rows, cols, ssim_weight, image_grad, ws, need, nullptr, &loss,
                             stream));
   return loss;
 }

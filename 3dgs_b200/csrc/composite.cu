@@ -15,6 +15,8 @@
 //     reductions per (tile, Gaussian): two red.global.add.v4.f32 + one scalar red into a packed [N][12] buffer
 //     (view-level path) or 9 scalar atomics into the reference's separate arrays (per-function path).
 // Bound: FP32/issue (no tensor cores: not a dense contraction).  Algorithmic work per SURVEY 8d.
+#include <stdlib.h>
+
 #include "gsx_common.cuh"
 
 // minimum resident CTAs per SM of the view-level compositing kernels (register cap); overridable for A/B builds
@@ -616,8 +618,21 @@ int count_work_launch(const float4 *r0, const float4 *r1, const int *sorted, con
   return GSX_OK;
 }
 
+// composite3.cu: the round-2 kernels (packed fp32x2 arithmetic, cp.async ring, direct per-warp reductions).  Default;
+// GSX_COMPOSITE=v2 in the environment selects the round-1 kernels of this file for A/B measurements.
+int composite_fwd3_launch(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges, int W,
+                          int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st);
+int composite_bwd3_launch(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges, int W,
+                          int H, float bg, const int *spp, const float *wpp, const float *grad_image, float *packed_grads,
+                          cudaStream_t st);
+static bool use_v2() {
+  static const int v = [] { const char *e = getenv("GSX_COMPOSITE"); return (e && e[0] == 'v' && e[1] == '2') ? 1 : 0; }();
+  return v != 0;
+}
+
 int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
                          int W, int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st) {
+  if (!use_v2()) return composite_fwd3_launch(r0, r1, r2, sorted, ranges, W, H, bg, spp, wpp, image, st);
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
   k_composite_fwd2<<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, image);
   GSX_LAUNCH_CHECK();
@@ -627,6 +642,7 @@ int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, c
 int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
                          int W, int H, float bg, const int *spp, const float *wpp, const float *grad_image,
                          float *packed_grads, cudaStream_t st) {
+  if (!use_v2()) return composite_bwd3_launch(r0, r1, r2, sorted, ranges, W, H, bg, spp, wpp, grad_image, packed_grads, st);
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
   k_composite_bwd2<2><<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, grad_image, packed_grads);
   GSX_LAUNCH_CHECK();

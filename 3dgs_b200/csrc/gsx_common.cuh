@@ -21,6 +21,16 @@ int check_device_ptr(const void *p, const char *name);
     if (_e != GSX_OK) return _e;                             \
   } while (0)
 
+// vector accesses on caller-owned arrays need the natural alignment of the vector type (a cudaMalloc'd array has it; a
+// slice of a flat buffer at an odd offset does not): rejected with GSX_E_ARG instead of a misaligned-address fault
+#define GSX_REQUIRE_ALIGNED(p, bytes)                                                   \
+  do {                                                                                  \
+    if (((uintptr_t)(p)) & ((bytes)-1)) {                                               \
+      ::gsx::set_error("pointer %s must be %d-byte aligned", #p, (int)(bytes));         \
+      return GSX_E_ARG;                                                                 \
+    }                                                                                   \
+  } while (0)
+
 #define GSX_CUDA(call)                                                                            \
   do {                                                                                            \
     cudaError_t _e = (call);                                                                      \
@@ -37,6 +47,9 @@ static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; 
 
 constexpr int kNumSMs = 148;  // B200
 
+// grow-only cached device workspace, one per (slot, device), mutex-guarded (binning.cu)
+int internal_workspace_slot(int which, size_t bytes, char **out);
+
 // workspace carve-up of the binning stage (binning.cu), shared with the context in api.cu
 struct BinLayout {
   size_t touched, offsets, block_sums, total, dk_a, dk_b, dv_a, dv_b, keys_a, keys_b, vals_a, vals_b, sort_ws, sort_ws_bytes, bytes;
@@ -48,7 +61,9 @@ struct BinLayout {
 struct PreBin {
   uint32_t *key_a = nullptr, *val_a = nullptr;   // ping-pong partners of the depth sort (compact mode: a = the slot's lists)
   uint32_t *key_b = nullptr, *val_b = nullptr;
-  int *offsets = nullptr, *block_sums = nullptr, *total = nullptr;   // total[0] = K after the scan
+  int *offsets = nullptr, *block_sums = nullptr;
+  int *total = nullptr;      // after the scan: total[0] = K, total[1] = live count (K, or 0 when K exceeds the capacity)
+  int *over_flag = nullptr;  // optional mapped host int: receives K when the capacity is exceeded
   char *sort_ws = nullptr;
   size_t sort_ws_bytes = 0;
   const uint32_t *perm = nullptr, *dkeys = nullptr;   // results: ids in depth order and their keys

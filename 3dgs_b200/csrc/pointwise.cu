@@ -192,6 +192,7 @@ int gsx_compute_camera_space_points(const float *xyz_w, const float *view, int N
 int gsx_project_to_screen(const float *xyz_c, const float *proj, int N, int width, int height, float *uv,
                           void *stream) {
   GSX_REQUIRE_DEV(xyz_c); GSX_REQUIRE_DEV(proj); GSX_REQUIRE_DEV(uv);
+  GSX_REQUIRE_ALIGNED(uv, 8);
   if (N <= 0) return GSX_OK;
   k_project<<<grid_for(N), kBlock, 0, (cudaStream_t)stream>>>(xyz_c, proj, N, width, height, uv);
   GSX_LAUNCH_CHECK();
@@ -209,6 +210,7 @@ int gsx_cull_gaussians(const float *uv, const float *xyz_c, int N, float near_th
 
 int gsx_compute_sigma(const float *quaternion, const float *scale, int N, float *sigma, void *stream) {
   GSX_REQUIRE_DEV(quaternion); GSX_REQUIRE_DEV(scale); GSX_REQUIRE_DEV(sigma);
+  GSX_REQUIRE_ALIGNED(quaternion, 16);
   if (N <= 0) return GSX_OK;
   k_sigma<<<grid_for(N), kBlock, 0, (cudaStream_t)stream>>>(quaternion, scale, N, sigma);
   GSX_LAUNCH_CHECK();
@@ -220,6 +222,7 @@ int gsx_compute_conic(const float *xyz_c, const float *view, const float *sigma,
                       void *stream) {
   GSX_REQUIRE_DEV(xyz_c); GSX_REQUIRE_DEV(view); GSX_REQUIRE_DEV(sigma); GSX_REQUIRE_DEV(J); GSX_REQUIRE_DEV(conic);
   GSX_REQUIRE_DEV(radius);
+  GSX_REQUIRE_ALIGNED(radius, 16);
   if (N <= 0) return GSX_OK;
   k_conic<<<grid_for(N), kBlock, 0, (cudaStream_t)stream>>>(xyz_c, view, sigma, focal_x, focal_y, tan_fovx, tan_fovy,
                                                             mh_dist, N, J, conic, reinterpret_cast<float4 *>(radius));
@@ -292,6 +295,7 @@ int gsx_compute_sigma_backward(const float *quaternion, const float *scale, cons
                                float *quat_grad, float *scale_grad, void *stream) {
   GSX_REQUIRE_DEV(quaternion); GSX_REQUIRE_DEV(scale); GSX_REQUIRE_DEV(sigma_grad); GSX_REQUIRE_DEV(quat_grad);
   GSX_REQUIRE_DEV(scale_grad);
+  GSX_REQUIRE_ALIGNED(quaternion, 16); GSX_REQUIRE_ALIGNED(quat_grad, 16);
   if (N <= 0) return GSX_OK;
   k_sigma_bwd<<<grid_for(N), kBlock, 0, (cudaStream_t)stream>>>(quaternion, scale, sigma_grad, N, quat_grad, scale_grad);
   GSX_LAUNCH_CHECK();

@@ -372,6 +372,21 @@ int gsx_sort_pairs_u64(uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in,
   return GSX_OK;
 }
 
+int gsx_sort_pairs_u32(uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in, uint32_t *vals_out, long long n,
+                       const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, void *stream) {
+  GSX_REQUIRE_DEV(keys_in); GSX_REQUIRE_DEV(keys_out); GSX_REQUIRE_DEV(vals_in); GSX_REQUIRE_DEV(vals_out);
+  GSX_REQUIRE_DEV(workspace);
+  int in_b = 0;
+  int rc = sort_pairs_u32_impl(keys_in, keys_out, vals_in, vals_out, n, n_dev, key_bits, workspace, workspace_bytes,
+                               (cudaStream_t)stream, &in_b);
+  if (rc != GSX_OK) return rc;
+  if (!in_b && n > 0) {   // even number of passes: result is in keys_in -> copy to the documented output
+    GSX_CUDA(cudaMemcpyAsync(keys_out, keys_in, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    GSX_CUDA(cudaMemcpyAsync(vals_out, vals_in, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  }
+  return GSX_OK;
+}
+
 int gsx_tile_ranges(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
                     void *stream) {
   GSX_REQUIRE_DEV(ranges);

@@ -210,6 +210,9 @@ class ViewParallel:
         if self.world == 1:
             r.batch_step(self.views, g, grad_images, flags=OVER, on_image=on_image)
             return
+        need = r.overflow()                                 # flag raised by an earlier step, read without a sync
+        if need:
+            raise _ffi.GsxError(_ffi.GSX_E_CAPACITY, f"instance capacity exceeded in a previous step: K={need}; reserve() and re-run it")
         if self.ex.transport != "nccl":
             return self._step_symmetric(grad_images, on_image)
         main = torch.cuda.current_stream()

@@ -415,6 +415,15 @@ class Rasterizer:
     def reserve(self, capacity):
         check(lib().gsx_ctx_reserve(self.h, C.c_longlong(int(capacity))))
 
+    def overflow(self):
+        """0, or the instance count K that exceeded the capacity since the last reserve().  No synchronisation (a pinned
+        flag raised by the device): a training loop polls it once per step and reserves + re-runs when it fires."""
+        need = C.c_longlong(0)
+        rc = lib().gsx_ctx_overflow(self.h, C.byref(need))
+        if rc not in (_ffi.GSX_OK, _ffi.GSX_E_CAPACITY):
+            check(rc)
+        return int(need.value)
+
     def forward_checked(self, view, g):
         """forward + one sync to grow the instance capacity if it overflowed (first view of a scene)."""
         self.forward(view, g)
@@ -466,6 +475,10 @@ class Rasterizer:
     def batch_step(self, views, g, grad_images, flags=_ffi.GSX_GRAD_OVERWRITE, on_image=None):
         """fwd+bwd of every view of the batch, gradients summed over the views.  grad_images: one device tensor per view
         (or a single one used for all); on_image(slot) is called after each forward (the rendered image is in state())."""
+        need = self.overflow()                          # raised by an EARLIER step (no sync): that step lost views
+        if need:
+            raise _ffi.GsxError(_ffi.GSX_E_CAPACITY, f"instance capacity exceeded in a previous step: K={need}; "
+                                                     "reserve() and re-run it")
         self.batch_forward_params(views, g)
         for k in range(len(views)):
             self.batch_forward_view(k)
@@ -502,6 +515,12 @@ class Rasterizer:
         """(S, S+) of the last forward: evaluated pixel-entries and those with alpha >= 1/255."""
         out = (C.c_ulonglong * 2)()
         check(lib().gsx_ctx_count_work(self.h, out, _stream()))
+        return int(out[0]), int(out[1])
+
+    def count_hits(self, grad_image):
+        """(warp-hits, contributing warp-hits) of the compositing backward over the last forward's lists"""
+        out = (C.c_ulonglong * 2)()
+        check(lib().gsx_ctx_count_hits(self.h, _ptr(grad_image), out, _stream()))
         return int(out[0]), int(out[1])
 
     def state_image(self):

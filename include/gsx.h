@@ -8,6 +8,11 @@
  * GSX_E_* code (the reference prints to stderr and exit(1)s instead, cuda/checks.cuh:17-38; the C++ compat
  * shim include/gsplat_cuda/ restores that behaviour on top of these).
  *
+ * Alignment: the quaternion arrays (parameters and gradients) and radius[N][4] are accessed as float4 and must be 16-byte
+ * aligned, uv / uv gradients 8-byte aligned (GSX_E_ARG otherwise); everything else only needs float alignment.
+ * Threads: a gsx_ctx is used by one host thread at a time; entry points that fall back to the library's internal cached
+ * workspace (workspace == NULL) share one grow-only buffer per device under a mutex.
+ *
  * Array layouts are the reference's: xyz[N][3], uv[N][2], quat[N][4] (w,x,y,z), scale[N][3] (log),
  * opacity[N] (logit), band0[N][3], sh[N][n-1][3], sigma[N][6], J[N][6], conic[N][3], radius[N][4]
  * (r_major,r_minor,sin,cos), view/proj row-major 4x4, image[H][W][3], weight[H][W], splats_per_pixel[H][W].
@@ -122,6 +127,10 @@ size_t gsx_sort_workspace_bytes(long long n);
  * (keys_in/vals_in are clobbered).  n_dev, when non-null, is a device int holding the live count (<= n). */
 int gsx_sort_pairs_u64(uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in, uint32_t *vals_out, long long n,
                        const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, void *stream);
+/* Same for 32-bit keys: the two sorts of the view-level path (32 depth bits per Gaussian, then ceil(log2 T) tile bits per
+ * instance) are this one. */
+int gsx_sort_pairs_u32(uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in, uint32_t *vals_out, long long n,
+                       const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, void *stream);
 /* ranges[t] = first i with (keys[i] >> 32) >= t, ranges[n_tiles] = n.  n_dev as above. */
 int gsx_tile_ranges(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
                     void *stream);
@@ -170,9 +179,15 @@ int gsx_forward(gsx_ctx_t *ctx, const gsx_view_t *view_host, const gsx_params_t 
 /* Backward for the view last rendered by gsx_forward on this ctx.  grad_image[H][W][3] device. */
 int gsx_backward(gsx_ctx_t *ctx, const gsx_view_t *view_host, const gsx_params_t *params, int N,
                  const float *grad_image, const gsx_grads_t *grads, void *stream);
-/* Synchronises and reports P, K; returns GSX_E_CAPACITY if the last forward overflowed. */
+/* Synchronises and reports P, K of the last forward; returns GSX_E_CAPACITY (with K = the capacity to reserve) if ANY view
+ * of the current batch overflowed.  A view whose K exceeds the capacity emits, sorts and composites nothing: its image
+ * is the background and it contributes no gradients until the caller reserves and re-runs (no stale data is read). */
 int gsx_ctx_stats(gsx_ctx_t *ctx, gsx_stats_t *out_host, void *stream);
-int gsx_ctx_reserve(gsx_ctx_t *ctx, long long instance_capacity);
+int gsx_ctx_reserve(gsx_ctx_t *ctx, long long instance_capacity);   /* capacity < 2^30; clears the overflow flag */
+/* Overflow poll WITHOUT synchronisation (a pinned flag the device raises): GSX_E_CAPACITY and the K to reserve if any
+ * view forwarded on this context since the last gsx_ctx_reserve exceeded the instance capacity, else GSX_OK.  Definitive
+ * after the stream that ran the views was synchronised; a training loop calls it once per step. */
+int gsx_ctx_overflow(gsx_ctx_t *ctx, long long *required_capacity_host);
 /* Device views of the last forward's saved state (ForwardPassData, cuda_data.cuh:70-86), global-index. */
 typedef struct gsx_state {
   const float *image, *weight_per_pixel; const int *splats_per_pixel;   /* [H][W][3], [H][W], [H][W] */
@@ -253,6 +268,9 @@ int gsx_ctx_timing(gsx_ctx_t *ctx, float *ms_out);
 /* out_host[2] = {S, S+}: evaluated pixel-entries (sum of splats_per_pixel) and those with alpha >= 1/255 in the
  * last forward -- the units of the compositing roofline.  Synchronises. */
 int gsx_ctx_count_work(gsx_ctx_t *ctx, unsigned long long *out_host, void *stream);
+/* out_host[2] = {warp-hits, contributing warp-hits} of the compositing backward over the last forward's lists (the
+ * (8x8 pixel block, entry) pairs that survive the extent-box cull / that have a contributing pixel).  Synchronises. */
+int gsx_ctx_count_hits(gsx_ctx_t *ctx, const float *grad_image, unsigned long long *out_host, void *stream);
 /* Measured FP32 FMA peak of the current device in TFLOP/s (roofline denominator of the compositing kernels). */
 int gsx_measure_fp32_tflops(float *tflops_host);
 

@@ -15,11 +15,64 @@ def available():
     return os.path.exists(LIB_PATH)
 
 
+def _ensure_unversioned_libcuda():
+    """sphericart's CUDA backend dlopen()s "libcuda.so" (submodules/sphericart/sphericart/include/dynamic_cuda.hpp:228);
+    a driver-only box may ship libcuda.so.1 alone.  oracle/_ref/shlib is on libref3dgs.so's RUNPATH: put a symlink to the
+    driver library this process already mapped (torch loads it) there."""
+    try:
+        C.CDLL("libcuda.so")
+        return
+    except OSError:
+        pass
+    target = None
+    try:
+        with open("/proc/self/maps") as f:
+            for ln in f:
+                if "libcuda.so" in ln:
+                    target = ln.split()[-1]
+                    break
+    except OSError:
+        pass
+    if target is None:
+        for cand in ("/usr/lib/x86_64-linux-gnu/libcuda.so.1", "/usr/lib64/libcuda.so.1", "/usr/local/cuda/compat/libcuda.so.1"):
+            if os.path.exists(cand):
+                target = cand
+                break
+    if target:
+        d = os.path.join(_HERE, "_ref", "shlib")
+        os.makedirs(d, exist_ok=True)
+        link = os.path.join(d, "libcuda.so")
+        if not os.path.exists(link):
+            try:
+                os.symlink(target, link)
+            except OSError:
+                pass
+
+
 def lib():
     global _lib
     if _lib is None:
+        _ensure_unversioned_libcuda()
         _lib = C.CDLL(LIB_PATH)
     return _lib
+
+
+_has_sh = None
+
+
+def has_sh():
+    """True when the reference's SH functions (sphericart CUDA backend: NVRTC JIT at first call) work on this box"""
+    global _has_sh
+    if _has_sh is None:
+        _has_sh = False
+        if available() and hasattr(lib(), "ref_precompute_spherical_harmonics") and torch.cuda.is_available():
+            try:
+                x = torch.tensor([[0.0, 0.0, 1.0]], device="cuda")
+                out = sh_forward(x, None, torch.zeros((1, 3), device="cuda"), (0.0, 0.0, 0.0), 0)
+                _has_sh = bool(abs(float(out[0, 0].item()) - 0.5) < 1e-6)
+            except Exception:
+                _has_sh = False
+    return _has_sh
 
 
 def _p(t):
@@ -121,4 +174,101 @@ def project_to_screen_backward(xyz_c, proj, g_uv, w, h, out=None):
 def camera_space_points_backward(xyz_w, view, g_xyz_c, out=None):
     out = _new(g_xyz_c.shape, g_xyz_c.device) if out is None else out
     lib().ref_compute_camera_space_points_backward(_p(xyz_w), _p(view), _p(g_xyz_c), g_xyz_c.shape[0], _p(out))
+    return out
+
+
+def sh_forward(xyz_w, sh, band0, campos, l_max):
+    """precompute_spherical_harmonics (cuda/spherical_harmonics.cu:62-94)"""
+    n, dev = xyz_w.shape[0], xyz_w.device
+    out = _new((n, 3), dev)
+    rc = lib().ref_precompute_spherical_harmonics(_p(xyz_w), _p(sh if l_max > 0 else None), _p(band0), _f(campos[0]), _f(campos[1]),
+                                                  _f(campos[2]), int(l_max), n, _p(out))
+    torch.cuda.synchronize()
+    if rc != 0:
+        raise RuntimeError("reference precompute_spherical_harmonics failed (sphericart / NVRTC)")
+    return out
+
+
+def sh_backward(xyz_w, band0, sh, campos, g_rgb, l_max, g_xyz=None):
+    """precompute_spherical_harmonics_backward (cuda/spherical_harmonics_backward.cu:168-209): sh / band-0 gradients
+    written, xyz gradient accumulated"""
+    n, dev = xyz_w.shape[0], xyz_w.device
+    nc = (l_max + 1) ** 2
+    g_sh, g_b0 = _new((n, max(nc - 1, 1), 3), dev), _new((n, 3), dev)
+    g_xyz = _new((n, 3), dev) if g_xyz is None else g_xyz
+    rc = lib().ref_precompute_spherical_harmonics_backward(_p(xyz_w), _p(band0), _p(sh if l_max > 0 else None), _f(campos[0]),
+                                                           _f(campos[1]), _f(campos[2]), _p(g_rgb), int(l_max), n,
+                                                           _p(g_sh if l_max > 0 else None), _p(g_b0), _p(g_xyz))
+    torch.cuda.synchronize()
+    if rc != 0:
+        raise RuntimeError("reference precompute_spherical_harmonics_backward failed (sphericart / NVRTC)")
+    return g_sh[:, : nc - 1], g_b0, g_xyz
+
+
+def replay_view(g, cam, W, H, l_max, near, pad, mh, grad_image, reps=2):
+    """Same-box baseline B1: rasterize_image (cuda/raster.cu:26-135) + backward_pass (cuda/trainer.cu:941-1012) replayed
+    call for call on one view through the reference's own kernels, CUDA-event timed per call.  g: dict of device tensors
+    (xyz, scale, quaternion, opacity, band0, sh[N][n-1][3] or None).  In the reference's favour: its 16 thrust copy_if
+    compactions are done by torch boolean indexing and reported separately.  SH degree l_max when has_sh(), else band 0
+    computed with torch (the report says which).  Returns a dict (stage_ms, ms_per_view, P, C, K, sh_degree)."""
+    xyz, scale, quat, opa, b0, sh = g["xyz"], g["scale"], g["quaternion"], g["opacity"].reshape(-1), g["band0"], g.get("sh")
+    d = lambda a: torch.as_tensor(a, dtype=torch.float32).reshape(-1).cuda()
+    view, proj = d(cam["view"]), d(cam["proj"])
+    ntx, nty = (W + 15) // 16, (H + 15) // 16
+    tx, ty = W / (2 * cam["fx"]), H / (2 * cam["fy"])
+    use_sh = has_sh()
+    deg = l_max if use_sh else 0
+    nsh = (deg + 1) ** 2 - 1
+
+    def timed(acc, name, fn):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn()
+        e1.record()
+        torch.cuda.synchronize()
+        acc[name] = acc.get(name, 0.0) + e0.elapsed_time(e1)
+        return out
+
+    def one_view(acc):
+        xyz_c = timed(acc, "F1 camera_space_points", lambda: camera_space_points(xyz, view))
+        uv = timed(acc, "F2 project_to_screen", lambda: project_to_screen(xyz_c, proj, W, H))
+        mask = timed(acc, "F3 cull", lambda: cull(uv, xyz_c, near, pad, W, H))
+
+        def compact():
+            m = mask.bool()
+            out = [t[m].contiguous() for t in (xyz_c, uv, scale, quat, opa, b0, xyz)]
+            out.append(sh[m][:, :nsh].contiguous() if (sh is not None and nsh) else None)
+            return out
+        xyz_cc, uvc, sc, qc, oc, b0c, xyzw, shc = timed(acc, "compaction (torch indexing; reference: 8 thrust copy_if)", compact)
+        if use_sh:
+            rgb = timed(acc, "F6 spherical harmonics", lambda: sh_forward(xyzw, shc, b0c, cam["campos"], deg))
+        else:
+            rgb = (0.5 + 0.28209479 * b0c).contiguous()
+        sig = timed(acc, "F4 sigma", lambda: sigma(qc, sc))
+        J, con, rad = timed(acc, "F5 conic", lambda: conic(xyz_cc, view, sig, cam["fx"], cam["fy"], tx, ty, mh))
+        lst = timed(acc, "F7 sorted list (both phases)", lambda: sorted_list(uvc, xyz_cc, rad, ntx, nty))
+        img, wpp, spp = timed(acc, "F8 render", lambda: render(uvc, oc, con, rgb, 0.0, lst["sorted"], lst["ranges"], W, H))
+        gr = timed(acc, "F9 render_backward", lambda: render_backward(uvc, oc, con, rgb, 0.0, lst["sorted"], lst["ranges"], spp, wpp, grad_image, W, H))
+        gxw = None
+        if use_sh:
+            gxw = timed(acc, "F10 spherical harmonics backward", lambda: sh_backward(xyzw, b0c, shc, cam["campos"], gr[0], deg))[2]
+        gJ, gS = timed(acc, "F11 conic_backward", lambda: conic_backward(J, sig, view, con, gr[3]))
+        gx = timed(acc, "F12 jacobian_backward", lambda: jacobian_backward(xyz_cc, cam["fx"], cam["fy"], tx, ty, gJ))
+        timed(acc, "F13 sigma_backward", lambda: sigma_backward(qc, sc, gS))
+        gx = timed(acc, "F14 project_backward", lambda: project_to_screen_backward(xyz_cc, proj, gr[2], W, H, gx))
+        timed(acc, "F15 camera_backward", lambda: camera_space_points_backward(xyzw, view, gx, gxw))
+        return int(mask.sum().item()), lst["C"], lst["K"]
+
+    out = {"kind": "reference CUDA kernels (oracle/_ref/libref3dgs.so, sm_100), rasterize_image + backward_pass call sequence",
+           "sh_degree": deg, "sh": "sphericart CUDA backend (NVRTC)" if use_sh else "band 0 via torch (sphericart backend not loadable)"}
+    try:
+        one_view({})                                               # warm-up (NVRTC JIT, allocator)
+        acc = {}
+        for _ in range(reps):
+            P, Cc, K = one_view(acc)
+        st = {k: round(v / reps, 4) for k, v in acc.items()}
+        out.update(P=P, coarse_pairs_C=Cc, instances_K=K, stage_ms=st, ms_per_view=round(sum(st.values()), 3),
+                   ms_per_view_kernels_only=round(sum(v for k, v in st.items() if not k.startswith("compaction")), 3))
+    except Exception as e:                                         # e.g. out of memory in the coarse pair list (SURVEY H4)
+        out["error"] = repr(e)[:300]
     return out

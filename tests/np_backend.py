@@ -1,10 +1,12 @@
-"""numpy in / numpy out adapter over host.py with the same function names as oracle/golden.py, so the
+"""Test plumbing (not part of the product package): numpy in / numpy out adapter over host.py with the same function names as oracle/golden.py, so the
 known-answer tests in tests/kat.py run unchanged against the CUDA path (through the C ABI)."""
 import numpy as np
 import torch
 
-from . import host as H
-from ._ffi import GSX_SH_DSPH_CORRECT
+import importlib
+
+H = importlib.import_module("3dgs_b200.host")
+GSX_SH_DSPH_CORRECT = importlib.import_module("3dgs_b200._ffi").GSX_SH_DSPH_CORRECT
 
 
 def _d(a, dtype=torch.float32):

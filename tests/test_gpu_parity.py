@@ -15,7 +15,8 @@ pytestmark = pytest.mark.gpu
 def B():
     import torch
     assert torch.cuda.is_available(), "GPU tests need a CUDA device"
-    return gs.np_backend
+    import np_backend
+    return np_backend
 
 
 @pytest.mark.parametrize("check", kat.ALL, ids=[c.__name__ for c in kat.ALL])
@@ -401,11 +402,11 @@ def test_batch_path_matches_per_view_and_oracle(B, l_max, sh_alloc, flags, overw
         tot = G.backward(gv, o, gi, grads=tot)
     for ko, kg in (("xyz", "xyz"), ("scale", "scale"), ("quat", "quaternion"), ("opacity", "opacity"), ("band0", "band0")):
         a, b = got[kg].reshape(-1), tot[ko].reshape(-1)
-        assert np.linalg.norm(a - b) <= 5e-3 * np.linalg.norm(b) + 1e-12, kg
+        assert np.linalg.norm(a - b) <= util.GRAD_RTOL * np.linalg.norm(b) + 1e-12, (kg, np.linalg.norm(a - b) / np.linalg.norm(b))
     if l_max > 0:
         nsh = ((l_max + 1) ** 2 - 1) * 3
         a = got["sh"][:, :nsh].reshape(-1); b = tot["sh"].reshape(N, -1)[:, :nsh].reshape(-1)
-        assert np.linalg.norm(a - b) <= 5e-3 * np.linalg.norm(b) + 1e-12
+        assert np.linalg.norm(a - b) <= util.GRAD_RTOL * np.linalg.norm(b) + 1e-12, np.linalg.norm(a - b) / np.linalg.norm(b)
     r.close()
 
 
@@ -585,6 +586,42 @@ def test_full_size_properties_c2(B):
     r.close()
 
 
+@pytest.mark.parametrize("cfg,backward", [("C2", True), ("C3", True), ("C5", False)])
+def test_config_full_size_vs_oracle(B, cfg, backward):
+    """BASELINE configs 2, 3 and 5 at FULL size against the CPU oracle (one view; C5 forward only, as the config says):
+    P equal, K within a few 1-ulp radius ties, ranges + sorted ids BIT-EXACT against the oracle's binning fed with the
+    GPU's own per-Gaussian values, image / final T within 1e-4 with every out-of-tolerance pixel an explained threshold
+    flip, splats_per_pixel likewise, all six parameter-gradient arrays within 1e-3 norm-wise (oracle/parity.py).
+    C4 gets the same report inside bench.py's cpu_baseline leg (`parity_c4`) and tests/test_ref_cuda.py."""
+    import torch
+    from oracle import parity
+    G.lib().gold_set_threads(os.cpu_count() or 1)
+    N, W, H, l_max = S.CONFIGS[cfg]
+    cam = S.orbit_camera(W, H, 0.0)
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=0x3D65 + int(cfg[1:]))
+    Hh = gs.host
+    gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+    r = Hh.Rasterizer(N, W, H, instance_capacity=4 * N)
+    v = util.gsx_view(cam, l_max, 0.0)
+    r.forward_checked(v, gd)
+    torch.cuda.synchronize()
+    st = {k: (t.cpu().numpy() if hasattr(t, "cpu") else t) for k, t in r.state().items() if k != "sorted_keys"}
+    gi = S.grad_image(W, H) * 1e3
+    got = None
+    if backward:
+        gd.zero_grads()
+        r.backward(v, gd, torch.as_tensor(gi).cuda())
+        torch.cuda.synchronize()
+        got = {k: t.cpu().numpy() for k, t in gd.grads.items()}
+    gv = util.make_views(cam, l_max, 0.0)
+    o = G.forward(gv, g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+    og = G.backward(gv, o, gi) if backward else None
+    rep = parity.full_view_report(st, got, o, og, N, W, H, 0.0)
+    print(cfg, "parity:", rep)
+    parity.assert_report(rep)
+    r.close()
+
+
 @pytest.mark.parametrize("l_max", [3, 0])
 def test_contributing_lists_same_image_and_gradients(B, l_max):
     """GSX_LISTS_CONTRIBUTING (view flag 8): per-tile lists clipped to each Gaussian's alpha >= 1/255 footprint.  The
@@ -742,6 +779,78 @@ def test_batch_pipeline_call_orders(B):
     for k in want_g:
         util.assert_grad_close(gd.grads[k].cpu().numpy(), want_g[k], f"d {k} after the detours", outlier=2e-3)
     r.close()
+
+
+def test_capacity_overflow_is_safe_and_reported_for_every_view(B, monkeypatch):
+    """a view whose K exceeds the instance capacity must (a) never touch the unwritten instance buffers --
+    they are poisoned with 0xFF here -- (b) render background only and contribute no gradients, (c) be reported by
+    gsx_ctx_stats for ANY view of the batch (not only the last one forwarded) and by the no-sync poll gsx_ctx_overflow;
+    after reserve() the same batch must equal a never-overflowed run."""
+    import torch
+    monkeypatch.setenv("GSX_DEBUG_POISON", "1")
+    W, H, N, l_max = 224, 160, 12000, 1
+    cams = [S.orbit_camera(W, H, azimuth_deg=a) for a in (20.0, 140.0, 260.0)]
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=48)
+    Hh = gs.host
+    gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+    views = [util.gsx_view(c, l_max, 0.25) for c in cams]
+    gi = torch.as_tensor(S.grad_image(W, H, seed=98) * 1e3).cuda()
+    big = Hh.Rasterizer(N, W, H, instance_capacity=8 * N)
+    big.batch_reserve(3)
+    Ks = []
+    big.batch_step(views, gd, gi, flags=2, on_image=lambda k: Ks.append(big.state()["K"]))
+    torch.cuda.synchronize()
+    want = {k: t.cpu().numpy().copy() for k, t in gd.grads.items()}
+    want_img = big.state()["image"].cpu().numpy().copy()
+    big.close()
+    assert min(Ks) > 2000
+    # capacity between the smallest and the largest K would be ideal; make only view 1 overflow by sizing for the others
+    order = np.argsort(Ks)
+    cap = (Ks[order[1]] + Ks[order[2]]) // 2 if Ks[order[1]] != Ks[order[2]] else Ks[order[2]] - 1
+    r = Hh.Rasterizer(N, W, H, instance_capacity=cap)
+    r.batch_reserve(3)
+    assert r.overflow() == 0
+    imgs = []
+    for t in gd.grads.values():
+        t.fill_(9.0)
+    r.batch_step(views, gd, gi, flags=2, on_image=lambda k: imgs.append(r.state()["image"].cpu().numpy().copy()))
+    torch.cuda.synchronize()                                # no illegal address although the buffers hold 0xFF
+    over = int(order[2])
+    assert (imgs[over] == np.float32(0.25)).all()           # the overflowed view composited nothing
+    assert r.overflow() == Ks[over]                         # no-sync poll carries the K to reserve for
+    st = r.stats(raise_on_overflow=False)
+    assert st["overflow"] and st["K"] == Ks[over]           # reported although the LAST view fitted (when over != 2)
+    assert all(bool(torch.isfinite(t).all()) for t in gd.grads.values())
+    with pytest.raises(gs._ffi.GsxError):                   # the next step refuses to run on a lossy context
+        r.batch_step(views, gd, gi, flags=2)
+    r.reserve(st["K"] + 16)
+    assert r.overflow() == 0
+    r.batch_step(views, gd, gi, flags=2)
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(r.state()["image"].cpu().numpy(), want_img)
+    for k in want:
+        util.assert_grad_close(gd.grads[k].cpu().numpy(), want[k], f"d {k} after reserve")
+    r.close()
+    # same protection on the per-function F7 entry point: capacity below K -> K reported, list empty, ranges zero
+    cam, gg = _scene(N=3000, W=160, H=120, l_max=0)
+    xyz_c = G.camera_space_points(gg["xyz"], cam["view"])
+    uv = G.project_to_screen(xyz_c, cam["proj"], 160, 120)
+    sig = G.sigma(gg["quaternion"], gg["scale"])
+    _, _, rad = G.conic(xyz_c, cam["view"], sig, cam["fx"], cam["fy"], 160 / (2 * cam["fx"]), 120 / (2 * cam["fy"]), S.MH_DIST)
+    full = B.sorted_list(uv, xyz_c, rad, 10, 8)
+    assert full["K"] > 64
+    d = lambda a, dt=torch.float32: torch.as_tensor(np.ascontiguousarray(a), dtype=dt).cuda()
+    srt = torch.full((64,), -1, dtype=torch.int32, device="cuda")
+    ranges = torch.full((81,), -1, dtype=torch.int32, device="cuda")
+    kdev = torch.zeros(1, dtype=torch.int32, device="cuda")
+    import ctypes as C
+    L = gs._ffi.lib()
+    a_uv, a_xyz, a_rad = d(uv), d(xyz_c), d(rad)
+    gs._ffi.check(L.gsx_get_sorted_gaussian_list(C.c_void_p(a_uv.data_ptr()), C.c_void_p(a_xyz.data_ptr()), C.c_void_p(a_rad.data_ptr()),
+                                                 10, 8, 3000, C.c_longlong(64), C.c_void_p(srt.data_ptr()), C.c_void_p(ranges.data_ptr()),
+                                                 C.c_void_p(kdev.data_ptr()), C.c_void_p(0), C.c_size_t(0), C.c_void_p(0)))
+    torch.cuda.synchronize()
+    assert int(kdev.item()) == full["K"] and not ranges.any().item() and (srt == -1).all().item()
 
 
 # ------------------------------------------------------------------------------------------ optimiser (SURVEY 8f rank 2)

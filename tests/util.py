@@ -29,8 +29,16 @@ def assert_image_close(a, b, what="image"):
     return f
 
 
+FLIP_GRAD_BOUND = 2.0 * 0.99 / 255.0   # see assert_grad_close
+
+
 def assert_grad_close(a, b, what="grad", rtol=GRAD_RTOL, outlier=OUTLIER_FRAC):
-    """norm-wise relative error <= rtol, and per element |a-b| <= rtol*|b| + floor with floor = rtol*1e-2*max|b|"""
+    """The spec: norm-wise relative error <= rtol (1e-3).  Per element, |a-b| <= rtol*|b| + floor with floor =
+    rtol*1e-2*max|b|; elements outside are not granted a blanket budget: they must be rare (<= `outlier`, counted) AND small
+    -- a flipped alpha >= 1/255 / idx < count decision of ONE pixel (ex2.approx on the device vs expf in the oracle) removes
+    or adds one pixel-entry whose alpha is 1/255, which perturbs that pixel's share of every gradient it feeds by at most
+    ~alpha; so an outlier's absolute error is bounded by FLIP_GRAD_BOUND (2 x 0.99/255) of the array's largest magnitude.
+    Anything larger is a defect, however rare."""
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     assert a.shape == b.shape, (what, a.shape, b.shape)
     if b.size == 0:
@@ -42,9 +50,16 @@ def assert_grad_close(a, b, what="grad", rtol=GRAD_RTOL, outlier=OUTLIER_FRAC):
         assert rel <= rtol, f"{what}: norm-wise relative error {rel:.3e} > {rtol}"
     else:
         assert np.abs(a).max() <= 1e-12, f"{what}: expected zeros"
-    floor = rtol * 1e-2 * np.abs(b).max()
-    f = close_frac(a, b, rtol, floor)
+    mx = np.abs(b).max()
+    floor = rtol * 1e-2 * mx
+    err = np.abs(a - b)
+    bad = ~(err <= floor + rtol * np.abs(b))
+    f = float(bad.mean())
     assert f <= max(outlier, 2.0 / b.size), f"{what}: {f:.2e} of elements outside rtol {rtol}"
+    if bad.any():
+        worst = float(err[bad].max())
+        assert worst <= FLIP_GRAD_BOUND * mx, (f"{what}: {int(bad.sum())} outliers, worst |a-b| = {worst:.3e} = "
+                                               f"{worst / mx:.3e} of max|b| > the one-pixel flip bound {FLIP_GRAD_BOUND:.3e}")
     return f
 
 
