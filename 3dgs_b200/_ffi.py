@@ -31,7 +31,8 @@ SYMBOLS = [
     "gsx_sh_grads_from_view_rgb", "gsx_ctx_build_sorted_keys", "gsx_batch_extract_view_rgb_grad_peers",
     "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers", "gsx_adam_step", "gsx_adam_step_fused",
     "gsx_fused_loss_workspace_bytes", "gsx_fused_loss",
-    "gsx_compute_morton_codes", "gsx_morton_order_workspace_bytes", "gsx_morton_order", "gsx_gather_rows",
+    "gsx_compute_morton_codes", "gsx_morton_order_workspace_bytes", "gsx_morton_order", "gsx_gather_rows", "gsx_gather_rows_multi",
+    "gsx_clone_gaussians", "gsx_split_gaussians", "gsx_densify_workspace_bytes", "gsx_densify_plan", "gsx_densify_apply",
 ]
 
 
@@ -72,6 +73,21 @@ class GsxAdamGroup(C.Structure):
 GSX_ADAM_MAX_GROUPS = 8
 
 
+class GsxDensityConfig(C.Structure):
+    _fields_ = [("uv_grad_threshold", C.c_float), ("delete_opacity_threshold", C.c_float), ("scene_extent", C.c_float),
+                ("split_scale_factor", C.c_float), ("max_gaussians", C.c_int)]
+
+
+class GsxDensityCounts(C.Structure):
+    _fields_ = [("n_in", C.c_int), ("n_prune", C.c_int), ("n_clone", C.c_int), ("n_split", C.c_int), ("n_out", C.c_int)]
+
+
+class GsxGaussianSet(C.Structure):
+    _fields_ = [("xyz", C.c_void_p), ("scale", C.c_void_p), ("quaternion", C.c_void_p), ("opacity", C.c_void_p),
+                ("band0", C.c_void_p), ("sh", C.c_void_p), ("sh_stride", C.c_int), ("sh_width", C.c_int),
+                ("exp_avg", C.c_void_p * 6), ("exp_avg_sq", C.c_void_p * 6)]
+
+
 class GsxError(RuntimeError):
     def __init__(self, code, msg):
         super().__init__(f"gsx status {code}: {msg}")
@@ -102,6 +118,8 @@ def lib():
         L.gsx_fused_loss_workspace_bytes.restype = C.c_size_t
         L.gsx_fused_loss_workspace_bytes.argtypes = [C.c_int, C.c_int]
         L.gsx_sorted_list_workspace_bytes.argtypes = [C.c_int, C.c_longlong]
+        L.gsx_densify_workspace_bytes.restype = C.c_size_t
+        L.gsx_densify_workspace_bytes.argtypes = [C.c_int]
         _lib = L
     return _lib
 

@@ -4,9 +4,11 @@
 // (reference cuda/checks.cuh:17-38).
 #include <stdio.h>
 #include <stdlib.h>
+#include <time.h>
 
 #include "../../include/gsplat_cuda/cuda_backward.cuh"
 #include "../../include/gsplat_cuda/cuda_forward.cuh"
+#include "../../include/gsplat_cuda/adaptive_density.cuh"
 #include "../../include/gsplat_cuda/optimizer.cuh"
 #include "../../include/gsx.h"
 
@@ -143,4 +145,25 @@ float fused_loss(const float *predicted_data, const float *gt_data, int rows, in
 void compute_morton_codes(const int N, const float *d_xyz, const float x_max, const float y_max, const float z_max,
                           const float x_min, const float y_min, const float z_min, uint64_t *codes, cudaStream_t stream) {
   DIE_UNLESS(gsx_compute_morton_codes(N, d_xyz, x_max, y_max, z_max, x_min, y_min, z_min, 0, codes, stream));
+}
+
+// SURVEY 8f rank 4, second half (reference cuda/adaptive_density.cu:155-206).  The reference seeds its curand states with
+// time(NULL) (:200); the shim does the same for the counter-based generator (a call counter is mixed in so that two calls
+// within one second do not repeat the stream).
+void clone_gaussians(const int N, const int num_sh_coef, const bool *mask, const int *write_ids, const float *xyz_in,
+                     const float *rgb_in, const float *op_in, const float *scale_in, const float *quat_in,
+                     const float *sh_in, float *xyz_out, float *rgb_out, float *op_out, float *scale_out,
+                     float *quat_out, float *sh_out, cudaStream_t stream) {
+  DIE_UNLESS(gsx_clone_gaussians(N, num_sh_coef, reinterpret_cast<const uint8_t *>(mask), write_ids, xyz_in, rgb_in, op_in,
+                                 scale_in, quat_in, sh_in, xyz_out, rgb_out, op_out, scale_out, quat_out, sh_out, stream));
+}
+void split_gaussians(const int N, const float scale_factor, const int num_sh_coef, const bool *mask,
+                     const int *write_ids, const float *xyz_in, const float *rgb_in, const float *op_in,
+                     const float *scale_in, const float *quat_in, const float *sh_in, float *xyz_out, float *rgb_out,
+                     float *op_out, float *scale_out, float *quat_out, float *sh_out, cudaStream_t stream) {
+  static unsigned long long calls = 0;
+  const unsigned long long seed = ((unsigned long long)time(NULL) << 20) ^ (++calls);
+  DIE_UNLESS(gsx_split_gaussians(N, scale_factor, num_sh_coef, reinterpret_cast<const uint8_t *>(mask), write_ids, xyz_in,
+                                 rgb_in, op_in, scale_in, quat_in, sh_in, xyz_out, rgb_out, op_out, scale_out, quat_out,
+                                 sh_out, seed, stream));
 }

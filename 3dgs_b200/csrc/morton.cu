@@ -6,6 +6,8 @@
 // (thrust::sequence + thrust::sort_by_key, then one gather per parameter / optimiser array).  Here the codes and the
 // identity permutation come out of one kernel, the sort is the library's own onesweep radix sort (stable: equal codes
 // keep index order, where thrust's order is unspecified), and a row gather serves every array width.
+#include <algorithm>
+
 #include "gsx_common.cuh"
 
 namespace gsx {
@@ -49,6 +51,22 @@ __global__ void __launch_bounds__(256) k_morton_codes(int N, const float *__rest
 // dst[i][:] = src[order[i]][:], one thread per float; rows are `width` floats
 __global__ void __launch_bounds__(256) k_gather_rows(const float *__restrict__ src, const int *__restrict__ order,
                                                      long long total, int width, float *__restrict__ dst) {
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
+    const long long i = e / width;
+    const int k = (int)(e - i * width);
+    dst[e] = src[(long long)order[i] * width + k];
+  }
+}
+
+// every array of a Gaussian set in ONE launch (blockIdx.y = array): the reference's sort_gaussians issues 17 gathers
+// (cuda/trainer.cu:897-923), each re-reading the permutation
+struct GatherArgs { const float *src[24]; float *dst[24]; int width[24]; int n; };
+__global__ void __launch_bounds__(256) k_gather_rows_multi(const __grid_constant__ GatherArgs A, const int *__restrict__ order,
+                                                           long long N) {
+  const float *__restrict__ src = A.src[blockIdx.y];
+  float *__restrict__ dst = A.dst[blockIdx.y];
+  const int width = A.width[blockIdx.y];
+  const long long total = N * width;
   for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < total; e += (long long)gridDim.x * 256) {
     const long long i = e / width;
     const int k = (int)(e - i * width);
@@ -119,6 +137,30 @@ int gsx_gather_rows(const float *src, const int *order, int N, int width, float 
   long long blocks = (total + 255) / 256;
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
   k_gather_rows<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(src, order, total, width, dst);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
+int gsx_gather_rows_multi(const float *const *src_host, float *const *dst_host, const int *width_host, int n_arrays,
+                          const int *order, int N, void *stream) {
+  if (!src_host || !dst_host || !width_host) { set_error("null array table"); return GSX_E_NULL; }
+  if (n_arrays < 1 || n_arrays > 24) { set_error("n_arrays %d out of range 1..24", n_arrays); return GSX_E_ARG; }
+  GSX_REQUIRE_DEV(order);
+  if (N <= 0) return GSX_OK;
+  GatherArgs A;
+  A.n = n_arrays;
+  long long widest = 1;
+  for (int a = 0; a < n_arrays; ++a) {
+    if (!src_host[a] || !dst_host[a] || src_host[a] == dst_host[a] || width_host[a] <= 0) {
+      set_error("array %d: null, aliased or width <= 0 (the gather is out of place)", a);
+      return GSX_E_ARG;
+    }
+    A.src[a] = src_host[a]; A.dst[a] = dst_host[a]; A.width[a] = width_host[a];
+    widest = std::max<long long>(widest, width_host[a]);
+  }
+  long long blocks = ((long long)N * widest + 255) / 256;
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  k_gather_rows_multi<<<dim3((unsigned)blocks, (unsigned)n_arrays), 256, 0, (cudaStream_t)stream>>>(A, order, (long long)N);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }

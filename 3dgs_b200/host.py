@@ -292,6 +292,96 @@ def gather_rows(src, order):
     return dst
 
 
+# ------------------------------------------------------------------------------------------------ densification (8f rank 4)
+def clone_gaussians(mask, write_ids, arrays, n_out):
+    """clone_gaussians of the reference (include/gsplat_cuda/adaptive_density.cuh:28): arrays = dict with xyz, rgb (band 0),
+    opacity, scale, quaternion, sh ([N][k][3] or None); returns the same dict with n_out rows (selected parents copied to
+    row write_ids[i], other rows zero)."""
+    n = mask.numel()
+    sh = arrays.get("sh")
+    ncoef = 0 if sh is None else sh.numel() // (3 * n)
+    out = {k: torch.zeros((n_out,) + tuple(v.shape[1:]), device=v.device, dtype=torch.float32) for k, v in arrays.items() if v is not None}
+    g = lambda d, k: _ptr(d.get(k))
+    check(lib().gsx_clone_gaussians(n, ncoef, _ptr(mask), _ptr(write_ids), g(arrays, "xyz"), g(arrays, "rgb"), g(arrays, "opacity"),
+                                    g(arrays, "scale"), g(arrays, "quaternion"), g(arrays, "sh"), g(out, "xyz"), g(out, "rgb"),
+                                    g(out, "opacity"), g(out, "scale"), g(out, "quaternion"), g(out, "sh"), _stream()))
+    return out
+
+
+def split_gaussians(mask, write_ids, arrays, n_out, scale_factor, seed):
+    """split_gaussians of the reference (adaptive_density.cuh:54) with an explicit seed; n_out rows = 2 per selected parent"""
+    n = mask.numel()
+    sh = arrays.get("sh")
+    ncoef = 0 if sh is None else sh.numel() // (3 * n)
+    out = {k: torch.zeros((n_out,) + tuple(v.shape[1:]), device=v.device, dtype=torch.float32) for k, v in arrays.items() if v is not None}
+    g = lambda d, k: _ptr(d.get(k))
+    check(lib().gsx_split_gaussians(n, f32(scale_factor), ncoef, _ptr(mask), _ptr(write_ids), g(arrays, "xyz"), g(arrays, "rgb"),
+                                    g(arrays, "opacity"), g(arrays, "scale"), g(arrays, "quaternion"), g(arrays, "sh"),
+                                    g(out, "xyz"), g(out, "rgb"), g(out, "opacity"), g(out, "scale"), g(out, "quaternion"),
+                                    g(out, "sh"), C.c_ulonglong(int(seed)), _stream()))
+    return out
+
+
+DENSIFY_NAMES = ("xyz", "scale", "quaternion", "opacity", "band0", "sh")
+
+
+def _gaussian_set(params, moments, sh_width):
+    s = _ffi.GsxGaussianSet()
+    for k, nm in enumerate(DENSIFY_NAMES):
+        t = params.get(nm)
+        setattr(s, nm, t.data_ptr() if t is not None else None)
+        mv = (moments or {}).get(nm)
+        s.exp_avg[k] = mv[0].data_ptr() if mv is not None else None
+        s.exp_avg_sq[k] = mv[1].data_ptr() if mv is not None else None
+    sh = params.get("sh")
+    s.sh_stride = 0 if sh is None else sh.numel() // max(sh.shape[0], 1)
+    s.sh_width = int(sh_width)
+    return s
+
+
+def densify(params, moments, uv_grad_accum, grad_accum_dur, uv_grad_threshold, delete_opacity_threshold, scene_extent,
+            split_scale_factor=1.6, max_gaussians=0, seed=0, l_max=3):
+    """TrainerImpl::adaptive_density_step of the reference (cuda/trainer.cu:416-775) on device tensors.
+    params: dict xyz [N][3], scale, quaternion, opacity [N], band0, sh [N][stride] (or None); moments: dict name -> (m, v)
+    or None.  Returns (new params, new moments, counts dict); None, None, counts when the step would exceed max_gaussians
+    (the reference skips it)."""
+    n = params["xyz"].shape[0]
+    dev = params["xyz"].device
+    cfg = _ffi.GsxDensityConfig(float(uv_grad_threshold), float(delete_opacity_threshold), float(scene_extent),
+                                float(split_scale_factor), int(max_gaussians))
+    wsb = lib().gsx_densify_workspace_bytes(n)
+    ws = torch.empty(wsb, device=dev, dtype=torch.uint8)
+    cnt = _ffi.GsxDensityCounts()
+    check(lib().gsx_densify_plan(C.byref(cfg), n, _ptr(params["opacity"]), _ptr(params["scale"]), _ptr(uv_grad_accum),
+                                 _ptr(grad_accum_dur), _ptr(ws), C.c_size_t(wsb), C.byref(cnt), _stream()))
+    counts = dict(n_in=cnt.n_in, n_prune=cnt.n_prune, n_clone=cnt.n_clone, n_split=cnt.n_split, n_out=cnt.n_out)
+    if max_gaussians and cnt.n_out > max_gaussians:
+        return None, None, counts
+    new = lambda t: torch.empty((cnt.n_out,) + tuple(t.shape[1:]), device=dev, dtype=torch.float32)
+    out_p = {k: (new(v) if v is not None else None) for k, v in params.items()}
+    out_m = None if moments is None else {k: (new(m), new(v)) for k, (m, v) in moments.items()}
+    shw = 3 * ((l_max + 1) ** 2 - 1) if params.get("sh") is not None else 0
+    sin, sout = _gaussian_set(params, moments, shw), _gaussian_set(out_p, out_m, shw)
+    check(lib().gsx_densify_apply(C.byref(cfg), C.byref(cnt), C.byref(sin), C.byref(sout), _ptr(ws), C.c_size_t(wsb),
+                                  C.c_ulonglong(int(seed)), _stream()))
+    return out_p, out_m, counts
+
+
+def gather_rows_multi(srcs, order):
+    """every array of a Gaussian set re-ordered in one launch (the 17 gather_with_stride calls of trainer.cu:897-923)"""
+    n = order.numel()
+    dsts = [torch.empty_like(t) for t in srcs]
+    k = len(srcs)
+    sp = (C.c_void_p * k)(*[t.data_ptr() for t in srcs])
+    dp_ = (C.c_void_p * k)(*[t.data_ptr() for t in dsts])
+    w = (C.c_int * k)(*[t.numel() // max(n, 1) for t in srcs])
+    for t in srcs:
+        _chk_f32(t)
+        assert t.is_cuda and t.is_contiguous() and t.shape[0] == n
+    check(lib().gsx_gather_rows_multi(sp, dp_, w, k, _ptr(order), n, _stream()))
+    return dsts
+
+
 def sort_pairs_u64(keys, vals, key_bits=64):
     """keys: int64 CUDA tensor holding uint64 bit patterns, vals: int32.  Returns sorted copies."""
     n = keys.numel()

@@ -438,6 +438,66 @@ def main():
                                    "frac": round(loss_bytes / loss_ms / 1e6 / hbm_peak, 4),
                                    "what": f"gsx_fused_loss (L1 + SSIM, 11x11 window) fwd+bwd on one {W}x{H} view, loss left on the device"}
 
+    # ---- next row, outside the timed region: Morton re-layout and one adaptive-density step at N ----
+    if world == 1:
+        try:
+            names = ["xyz", "scale", "quaternion", "opacity", "band0"] + (["sh"] if gd.sh_stride else [])
+            arrs = [getattr(gd, nm).view(N, -1) for nm in names]
+            ev = lambda: torch.cuda.Event(enable_timing=True)
+            m0, m1, m2 = ev(), ev(), ev()
+            bbox = None
+            for it in range(3):
+                if it == 1:
+                    m0.record()
+                order = Hh.morton_order(gd.xyz, bbox=(3.0, 3.0, 3.0, -3.0, -3.0, -3.0), flags=1)
+                if it == 1:
+                    m1.record()
+                moved = Hh.gather_rows_multi(arrs + arrs + arrs, order)     # parameters + both Adam moments: 3 x 59 floats
+                if it == 1:
+                    m2.record()
+                del moved
+            torch.cuda.synchronize()
+            ms_order, ms_gather = m0.elapsed_time(m1), m1.elapsed_time(m2)
+            gbytes = N * (3 * 2 * 4 * sum(a.shape[1] for a in arrs) + 4 * len(arrs) * 3)
+            obytes = N * (12 + 12 + 9 * 24)          # codes + ids written, 63 bits = 8 onesweep passes x 24 B + histogram read
+            next_rows["morton_relayout"] = {
+                "ms": round(ms_order + ms_gather, 4), "order_ms": round(ms_order, 4), "gather_ms": round(ms_gather, 4), "bound": "hbm",
+                "gather_bytes": gbytes, "gather_GBps": round(gbytes / ms_gather / 1e6, 1), "gather_frac": round(gbytes / ms_gather / 1e6 / hbm_peak, 4),
+                "order_bytes": obytes, "order_GBps": round(obytes / ms_order / 1e6, 1), "launches": "codes 1 + sort 11 + gather 1",
+                "what": "gsx_morton_order (63-bit codes, 8-pass onesweep) + gsx_gather_rows_multi over 18 arrays (59 floats x 3 per Gaussian) in one launch; reference: thrust sort_by_key + 17 gathers (trainer.cu:871-924)"}
+            del order
+            # one adaptive-density step: ~5 % pruned, ~5 % cloned, ~5 % split
+            rngd = torch.Generator(device=dev); rngd.manual_seed(7)
+            u = torch.rand(N, device=dev, generator=rngd)
+            dur = torch.full((N,), 4, device=dev, dtype=torch.int32)
+            acc = torch.where(u < 0.10, 8.0, 0.4).to(torch.float32)        # mean |uv grad| 2.0 above / 0.1 below the 0.5 threshold
+            opac = torch.where((u > 0.10) & (u < 0.15), -9.0, 1.0).to(torch.float32)
+            extent = float(torch.exp(gd.scale).amax().item()) * 100.0 / 1.5   # clone threshold splits the high-gradient 10 % roughly in half
+            med = float(torch.exp(gd.scale).amax(1).median().item())
+            extent = med * 100.0
+            pd_ = dict(xyz=gd.xyz, scale=gd.scale, quaternion=gd.quaternion, opacity=opac, band0=gd.band0, sh=(gd.sh if gd.sh_stride else None))
+            momd = {k_: (torch.zeros_like(v_), torch.zeros_like(v_)) for k_, v_ in pd_.items() if v_ is not None}
+            d0, d1 = ev(), ev()
+            cnt = None
+            for it in range(3):
+                if it == 1:
+                    d0.record()
+                outp, outm, cnt = Hh.densify(pd_, momd, acc, dur, 0.5, 0.005, extent, 1.6, max_gaussians=0, seed=it, l_max=l_max)
+                if it == 1:
+                    d1.record()
+                del outp, outm
+            torch.cuda.synchronize()
+            dms = d0.elapsed_time(d1)
+            fl = sum(a.shape[1] for a in arrs)
+            dbytes = 4 * fl * 3 * (N - cnt["n_prune"] + cnt["n_out"]) + N * (4 + 12 + 8 + 1 + 1 + 8 + 18 * 9)   # rows read + written (params + 2 moments), statistics, plan arrays
+            next_rows["densify_step"] = {
+                "ms": round(dms, 4), "bound": "hbm", "bytes": int(dbytes), "GBps": round(dbytes / dms / 1e6, 1), "frac": round(dbytes / dms / 1e6 / hbm_peak, 4),
+                "counts": cnt, "launches": 5,
+                "what": "gsx_densify_plan + gsx_densify_apply (decide, 3-kernel scan, one move of 18 arrays, split geometry; includes the 12-byte host read of the counts); reference: adaptive_density_step, trainer.cu:518-775"}
+            del momd, pd_
+        except Exception as e:
+            next_rows["density_rows_error"] = repr(e)[:300]
+
     views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
     if world > 1:
         ga_, ar_ = vp.ex.link_bytes_per_step()

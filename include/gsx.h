@@ -334,6 +334,58 @@ int gsx_morton_order(int N, const float *xyz, float x_max, float y_max, float z_
                      float z_min, int flags, int *order, uint64_t *sorted_codes, void *workspace,
                      size_t workspace_bytes, void *stream);
 int gsx_gather_rows(const float *src, const int *order, int N, int width, float *dst, void *stream);
+/* The same gather for up to 24 arrays (parameters and optimiser moments) in one launch; the three tables are host arrays. */
+int gsx_gather_rows_multi(const float *const *src_host, float *const *dst_host, const int *width_host, int n_arrays,
+                          const int *order, int N, void *stream);
+
+/* ---- SURVEY 8f rank 4 (second half): adaptive density control -- clone / split / prune ----
+ * gsx_clone_gaussians / gsx_split_gaussians replace clone_gaussians / split_gaussians
+ * (include/gsplat_cuda/adaptive_density.cuh:28,54, cuda/adaptive_density.cu:13-206) with the same argument meaning: mask
+ * [N] selects the parents, write_ids [N] is the exclusive scan of the mask, the outputs are separate buffers holding one
+ * (clone) or two (split) rows per selected parent at row write_ids[i] (* 2 + j).  A clone is an exact copy; a split child
+ * keeps colour / opacity / rotation, gets scale log(exp(s) / scale_factor) and centre xyz + R(q) (n * exp(s)), n ~ N(0, I).
+ * The normals come from Philox4x32-10 keyed by `seed` with counter (parent index, child): reproducible, independent of the
+ * launch shape, no state array (the reference re-seeds a curand state per thread with time(NULL) at every call). */
+int gsx_clone_gaussians(int N, int num_sh_coef, const uint8_t *mask, const int *write_ids, const float *xyz_in,
+                        const float *rgb_in, const float *op_in, const float *scale_in, const float *quat_in,
+                        const float *sh_in, float *xyz_out, float *rgb_out, float *op_out, float *scale_out,
+                        float *quat_out, float *sh_out, void *stream);
+int gsx_split_gaussians(int N, float scale_factor, int num_sh_coef, const uint8_t *mask, const int *write_ids,
+                        const float *xyz_in, const float *rgb_in, const float *op_in, const float *scale_in,
+                        const float *quat_in, const float *sh_in, float *xyz_out, float *rgb_out, float *op_out,
+                        float *scale_out, float *quat_out, float *sh_out, unsigned long long seed, void *stream);
+/* The whole step, TrainerImpl::adaptive_density_step (cuda/trainer.cu:416-775), in five launches and one 12-byte host
+ * read.  gsx_densify_plan decides per Gaussian (same predicates: prune if the opacity logit is below
+ * logit(delete_opacity_threshold) or the largest scale exceeds 0.1 * scene_extent unless it is about to be cloned / split;
+ * clone if the mean |uv gradient| exceeds uv_grad_threshold and the largest scale is <= 0.01 * scene_extent, split if it
+ * is larger), scans the decisions into destination rows inside `workspace`, and returns the counts (synchronises).
+ * gsx_densify_apply moves every array of the set -- parameters and, when given, both Adam moments of each -- from `in`
+ * to `out` (distinct buffers, sized for counts.n_out rows): survivors first in their old order (clone parents included),
+ * then the clones, then the split children; appended Gaussians get zero moments.  GSX_E_CAPACITY (nothing written) when
+ * n_out exceeds max_gaussians -- the reference skips the step with a warning (trainer.cu:579-585). */
+typedef struct gsx_density_config {
+  float uv_grad_threshold;          /* config uv_grad_threshold */
+  float delete_opacity_threshold;   /* config delete_opacity_threshold, a probability in (0, 1) */
+  float scene_extent;               /* computeMaxDiagonal of the camera positions */
+  float split_scale_factor;         /* config split_scale_factor (1.6) */
+  int max_gaussians;                /* capacity of the output arrays (0: unchecked) */
+} gsx_density_config_t;
+typedef struct gsx_density_counts {
+  int n_in, n_prune, n_clone, n_split, n_out;   /* n_out = n_in - n_prune - n_split + n_clone + 2 n_split */
+} gsx_density_counts_t;
+typedef struct gsx_gaussian_set {   /* CudaDataManager's parameter + optimiser arrays (cuda_data.cuh:11-24, 55-68) */
+  float *xyz, *scale, *quaternion, *opacity, *band0, *sh;
+  int sh_stride;                    /* floats per row of sh (and of its moments) */
+  int sh_width;                     /* floats of a row in use: 3 * ((l_max + 1)^2 - 1); 0 = no sh array */
+  float *exp_avg[6], *exp_avg_sq[6];   /* Adam moments in the order xyz, scale, quaternion, opacity, band0, sh; NULL = absent */
+} gsx_gaussian_set_t;
+size_t gsx_densify_workspace_bytes(int N);
+int gsx_densify_plan(const gsx_density_config_t *cfg, int N, const float *opacity, const float *scale,
+                     const float *uv_grad_accum, const int *grad_accum_dur, void *workspace, size_t workspace_bytes,
+                     gsx_density_counts_t *counts_host, void *stream);
+int gsx_densify_apply(const gsx_density_config_t *cfg, const gsx_density_counts_t *counts, const gsx_gaussian_set_t *in,
+                      const gsx_gaussian_set_t *out, const void *workspace, size_t workspace_bytes, unsigned long long seed,
+                      void *stream);
 
 #ifdef __cplusplus
 }

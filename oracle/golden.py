@@ -351,3 +351,57 @@ def morton_codes(xyz, bbox, true_interleave=False):
 def morton_order(xyz, bbox, true_interleave=False):
     """sequence + sort_by_key of TrainerImpl::sort_gaussians (cuda/trainer.cu:886-893), ties in index order"""
     return np.argsort(morton_codes(xyz, bbox, true_interleave), kind="stable").astype(np.int32)
+
+
+# ------------------------------------------------------------------------------------------------ densification (8f rank 4)
+def philox4x32_10(ctr, key):
+    """one Philox4x32-10 block (counter [4], key [2], uint32) -- pinned by the published known-answer vectors"""
+    c, k, out = (C.c_uint32 * 4)(*ctr), (C.c_uint32 * 2)(*key), (C.c_uint32 * 4)()
+    lib().gold_philox4x32_10_block(c, k, out)
+    return [int(x) for x in out]
+
+
+def density_decide(opacity, scale, uv_grad_accum, grad_accum_dur, uv_grad_threshold, delete_opacity_threshold, scene_extent):
+    """decision functors of TrainerImpl::adaptive_density_step (cuda/trainer.cu:416-504): 0 keep, 1 prune, 2 clone, 3 split"""
+    op, sc, acc, dur = _f(opacity), _f(scale), _f(uv_grad_accum), _i(grad_accum_dur)
+    act = np.empty(op.shape[0], np.uint8)
+    lib().gold_density_decide(op.shape[0], _p(op), _p(sc), _p(acc), _p(dur), C.c_float(uv_grad_threshold),
+                              C.c_float(delete_opacity_threshold), C.c_float(scene_extent), _p(act))
+    return act
+
+
+def split_children(seed, i, xyz, scale, quat, scale_factor):
+    """split_gaussians_kernel (cuda/adaptive_density.cu:69-153) for parent i with the Philox samples: (xyz [2][3], scale [3])"""
+    x, s, q = _f(xyz), _f(scale), _f(quat)
+    xo, so = np.empty((2, 3), np.float32), np.empty(3, np.float32)
+    lib().gold_split_children(C.c_ulonglong(seed), C.c_uint32(i), _p(x), _p(s), _p(q), C.c_float(scale_factor), _p(xo), _p(so))
+    return xo, so
+
+
+def densify(params, moments, action, seed, scale_factor):
+    """The compaction + append of adaptive_density_step (cuda/trainer.cu:655-775) given the per-Gaussian actions.
+    params: dict name -> [N][w] array (xyz, scale, quaternion, opacity, band0, sh); moments: dict name -> (m, v) or None.
+    Survivors (keep + clone parents) first in order, then the clones, then two children per split parent; appended
+    Gaussians get zero moments (trainer.cu:694-746)."""
+    action = np.asarray(action)
+    keep = np.nonzero((action == 0) | (action == 2))[0]
+    clone = np.nonzero(action == 2)[0]
+    split = np.nonzero(action == 3)[0]
+    out_p, out_m = {}, {}
+    kids_xyz = np.zeros((split.size, 2, 3), np.float32)
+    kids_scale = np.zeros((split.size, 3), np.float32)
+    for r, i in enumerate(split):
+        kids_xyz[r], kids_scale[r] = split_children(seed, int(i), params["xyz"][i], params["scale"][i], params["quaternion"][i], scale_factor)
+    for nm, a in params.items():
+        a2 = np.asarray(a, np.float32).reshape(action.size, -1)
+        rep = np.repeat(a2[split], 2, axis=0)
+        if nm == "xyz":
+            rep = kids_xyz.reshape(-1, 3)
+        elif nm == "scale":
+            rep = np.repeat(kids_scale, 2, axis=0)
+        out_p[nm] = np.concatenate([a2[keep], a2[clone], rep], axis=0)
+        if moments is not None and nm in moments:
+            out_m[nm] = tuple(np.concatenate([np.asarray(m, np.float32).reshape(action.size, -1)[keep],
+                                              np.zeros((clone.size + 2 * split.size, a2.shape[1]), np.float32)], axis=0)
+                              for m in moments[nm])
+    return out_p, out_m

@@ -39,7 +39,7 @@ def test_library_exports_the_reference_named_cpp_functions():
         src = re.sub(r"//.*", "", open(h).read())
         declared |= set(re.findall(r"^(?:void|float)\s+([a-z_0-9]+)\s*\(", src, flags=re.M))
     assert {"render_image", "render_image_backward", "get_sorted_gaussian_list", "adam_step", "fused_loss",
-            "compute_morton_codes"} <= declared and len(declared) == 18
+            "compute_morton_codes", "clone_gaussians", "split_gaussians"} <= declared and len(declared) == 20
     out = subprocess.run(["nm", "-DC", "--defined-only", ffi.LIB_PATH], capture_output=True, text=True, check=True).stdout
     exported = set(re.findall(r" T ([a-z_0-9]+)\(", out))
     assert declared <= exported, f"declared but not defined: {sorted(declared - exported)}"

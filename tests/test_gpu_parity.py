@@ -1060,6 +1060,20 @@ def test_morton_codes_and_order_parity(B, true_interleave):
     np.testing.assert_array_equal(B.morton_order(xyz, tight, t), G.morton_order(xyz, tight, t))
 
 
+def test_gather_rows_multi_equals_per_array_gathers():
+    """one launch for every array of a Gaussian set = the per-array gathers (and torch indexing)"""
+    import torch
+    Hh = gs.host
+    n = 100_003
+    g = torch.Generator(device="cuda"); g.manual_seed(3)
+    order = torch.randperm(n, device="cuda", generator=g).to(torch.int32)
+    srcs = [torch.randn((n, w), device="cuda", generator=g) for w in (3, 3, 4, 1, 3, 45)]
+    srcs.append(torch.randn(n, device="cuda", generator=g))
+    outs = Hh.gather_rows_multi(srcs, order)
+    for a, o in zip(srcs, outs):
+        assert torch.equal(o, a[order.long()]) and torch.equal(o, Hh.gather_rows(a, order))
+
+
 @pytest.mark.parametrize("flags", [0, 1])
 def test_morton_relayout_properties_at_size(flags):
     """size-independent properties at 2 M Gaussians: the order is a permutation, the codes come out sorted, gathering the
@@ -1081,3 +1095,124 @@ def test_morton_relayout_properties_at_size(flags):
     for w in (1, 4, 45):
         a = torch.randn((n, w), device="cuda", generator=gen)
         assert torch.equal(Hh.gather_rows(a, order), a[order.long()])
+
+
+# ------------------------------------------------------------------------------------------ densification
+def _density_scene(rng, N, ext=10.0, l_max=1):
+    """parameters + statistics whose decisions sit away from every threshold (largest scale in {0.3, 0.7, 1.3, 3} x the
+    clone / max-scale thresholds), so expf rounding on the device cannot flip one"""
+    logit = lambda p: np.log(p / (1 - p))
+    fac = rng.choice([0.3, 0.7, 1.3, 3.0], N)
+    big = rng.random(N) < 0.5
+    smax = np.where(big, ext * 0.1 * fac * 0.9, ext * 0.01 * fac)
+    scale = np.log(smax[:, None] * np.stack([np.ones(N), rng.uniform(0.2, 0.9, N), rng.uniform(0.05, 0.5, N)], 1)).astype(np.float32)
+    scale = np.take_along_axis(scale, rng.permuted(np.tile(np.arange(3), (N, 1)), axis=1), axis=1)
+    op = logit(np.where(rng.random(N) < 0.15, 0.001, rng.uniform(0.02, 0.98, N))).astype(np.float32)
+    dur = rng.integers(0, 6, N).astype(np.int32)
+    acc = (np.where(rng.random(N) < 0.5, 0.1, 2.0) * np.maximum(dur, 1)).astype(np.float32)
+    q = rng.standard_normal((N, 4)).astype(np.float32)
+    nsh = (l_max + 1) ** 2 - 1
+    p = dict(xyz=rng.uniform(-3, 3, (N, 3)).astype(np.float32), scale=scale, quaternion=q, opacity=op,
+             band0=rng.uniform(-1, 1, (N, 3)).astype(np.float32), sh=rng.normal(0, 0.2, (N, nsh * 3)).astype(np.float32))
+    return p, acc, dur
+
+
+def test_clone_and_split_entry_points_vs_oracle(B):
+    """gsx_clone_gaussians / gsx_split_gaussians (the reference's two functions, adaptive_density.cuh:28,54): a clone is an
+    exact copy at row write_ids[i]; split children copy colour / opacity / rotation / SH exactly, carry the scale
+    log(exp(s) / f), and their centres equal the oracle's (same Philox samples; Box-Muller through libm vs device math:
+    1e-5 of the parent's extent) -- and are reproducible from the seed."""
+    import torch
+    rng = np.random.default_rng(12)
+    N = 5003
+    p, _, _ = _density_scene(rng, N)
+    mask = (rng.random(N) < 0.3)
+    wid = (np.cumsum(mask) - mask).astype(np.int32)
+    n_sel = int(mask.sum())
+    d = lambda a, dt=torch.float32: torch.as_tensor(np.ascontiguousarray(a), dtype=dt).cuda()
+    Hh = gs.host
+    arrays = dict(xyz=d(p["xyz"]), rgb=d(p["band0"]), opacity=d(p["opacity"]), scale=d(p["scale"]), quaternion=d(p["quaternion"]),
+                  sh=d(p["sh"]).view(N, -1, 3))
+    src = dict(xyz=p["xyz"], rgb=p["band0"], opacity=p["opacity"], scale=p["scale"], quaternion=p["quaternion"], sh=p["sh"])
+    out = Hh.clone_gaussians(d(mask, torch.uint8), d(wid, torch.int32), arrays, n_sel)
+    torch.cuda.synchronize()
+    for k, v in out.items():
+        np.testing.assert_array_equal(v.cpu().numpy().reshape(n_sel, -1), src[k].reshape(N, -1)[mask], err_msg=f"clone {k}")
+    for seed in (99, 100):
+        out = Hh.split_gaussians(d(mask, torch.uint8), d(wid, torch.int32), arrays, 2 * n_sel, 1.6, seed)
+        torch.cuda.synchronize()
+        o = {k: v.cpu().numpy().reshape(2 * n_sel, -1) for k, v in out.items()}
+        for k in ("rgb", "opacity", "quaternion", "sh"):
+            np.testing.assert_array_equal(o[k], np.repeat(src[k].reshape(N, -1)[mask], 2, axis=0), err_msg=f"split {k}")
+        sel = np.nonzero(mask)[0]
+        np.testing.assert_allclose(o["scale"], np.repeat(np.log(np.exp(p["scale"][sel].astype(np.float64)) / 1.6), 2, axis=0), atol=2e-6)
+        for r in rng.choice(n_sel, 300, replace=False):
+            i = int(sel[r])
+            kids, sc = G.split_children(seed, i, p["xyz"][i], p["scale"][i], p["quaternion"][i], 1.6)
+            ext = float(np.exp(p["scale"][i]).max())
+            np.testing.assert_allclose(o["xyz"][2 * r:2 * r + 2], kids, atol=1e-5 * (ext * 6 + np.abs(p["xyz"][i]).max()))
+        if seed == 99:
+            first = o["xyz"].copy()
+            again = Hh.split_gaussians(d(mask, torch.uint8), d(wid, torch.int32), arrays, 2 * n_sel, 1.6, 99)["xyz"].cpu().numpy()
+            np.testing.assert_array_equal(again, first)                          # same seed, same samples
+        else:
+            assert not np.array_equal(o["xyz"], first)                           # another seed, another stream
+    # distribution of the samples on the device: one anisotropic, rotated parent replicated 100k times
+    M = 100_000
+    one = {k: v[:1].expand(M, *v.shape[1:]).contiguous() for k, v in arrays.items()}
+    allm, ids = torch.ones(M, dtype=torch.uint8, device="cuda"), torch.arange(M, dtype=torch.int32, device="cuda")
+    pts = Hh.split_gaussians(allm, ids, one, 2 * M, 1.6, 5)["xyz"].cpu().numpy().astype(np.float64)
+    q = p["quaternion"][0].astype(np.float64); q /= np.linalg.norm(q)
+    w, x, y, z = q
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                  [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                  [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+    cov = R @ np.diag(np.exp(2 * p["scale"][0].astype(np.float64))) @ R.T
+    sd = np.sqrt(np.abs(cov).max())
+    np.testing.assert_allclose(pts.mean(0), p["xyz"][0], atol=5 * sd / np.sqrt(2 * M))
+    np.testing.assert_allclose(np.cov(pts.T), cov, atol=0.02 * np.abs(cov).max())
+
+
+@pytest.mark.parametrize("N,l_max,with_moments", [(50_003, 1, True), (4096, 3, False), (7, 0, True)])
+def test_densify_step_vs_oracle(B, N, l_max, with_moments):
+    """gsx_densify_plan + gsx_densify_apply = TrainerImpl::adaptive_density_step (cuda/trainer.cu:416-775): decisions and
+    counts equal the oracle's, survivors / clones / split children land in the reference's order with every copied value
+    bit-identical, children scales / centres as above, appended Gaussians get zero Adam moments; over max_gaussians the
+    step is skipped."""
+    import torch
+    rng = np.random.default_rng(N)
+    p, acc, dur = _density_scene(rng, N, l_max=l_max)
+    if l_max == 0:
+        p["sh"] = None
+    act = G.density_decide(p["opacity"], p["scale"], acc, dur, 0.5, 0.005, 10.0)
+    assert N < 100 or all((act == a).sum() > N // 50 for a in range(4))             # every branch is exercised
+    d = lambda a, dt=torch.float32: torch.as_tensor(np.ascontiguousarray(a), dtype=dt).cuda()
+    dp = {k: (d(v) if v is not None else None) for k, v in p.items()}
+    mom_h = {k: (rng.normal(0, 1, v.shape).astype(np.float32), rng.random(v.shape).astype(np.float32)) for k, v in p.items() if v is not None} if with_moments else None
+    mom_d = None if mom_h is None else {k: (d(m), d(v)) for k, (m, v) in mom_h.items()}
+    Hh = gs.host
+    out_p, out_m, cnt = Hh.densify(dp, mom_d, d(acc), d(dur, torch.int32), 0.5, 0.005, 10.0, 1.6, max_gaussians=0, seed=77, l_max=l_max)
+    torch.cuda.synchronize()
+    assert cnt == dict(n_in=N, n_prune=int((act == 1).sum()), n_clone=int((act == 2).sum()), n_split=int((act == 3).sum()),
+                       n_out=int(((act == 0) | (act == 2)).sum() + (act == 2).sum() + 2 * (act == 3).sum()))
+    ph = {k: (v.reshape(N, -1) if v is not None else None) for k, v in p.items()}
+    ep, em = G.densify({k: v for k, v in ph.items() if v is not None}, None if mom_h is None else {k: (m.reshape(N, -1), v.reshape(N, -1)) for k, (m, v) in mom_h.items()}, act, 77, 1.6)
+    n_front = int(((act == 0) | (act == 2)).sum()) + int((act == 2).sum())
+    for k, e in ep.items():
+        g = out_p[k].cpu().numpy().reshape(cnt["n_out"], -1)
+        np.testing.assert_array_equal(g[:n_front], e[:n_front], err_msg=f"{k}: survivors + clones")
+        if k == "xyz":
+            ext = np.repeat(np.exp(ph["scale"][act == 3]).max(1), 2)[:, None]
+            assert (np.abs(g[n_front:] - e[n_front:]) <= 1e-5 * (6 * ext + 3.0)).all(), "split centres"
+        elif k == "scale":
+            np.testing.assert_allclose(g[n_front:], e[n_front:], atol=2e-6, err_msg="split scales")
+        else:
+            np.testing.assert_array_equal(g[n_front:], e[n_front:], err_msg=f"{k}: split children")
+    if with_moments:
+        for k, (m, v) in em.items():
+            np.testing.assert_array_equal(out_m[k][0].cpu().numpy().reshape(cnt["n_out"], -1), m, err_msg=f"exp_avg {k}")
+            np.testing.assert_array_equal(out_m[k][1].cpu().numpy().reshape(cnt["n_out"], -1), v, err_msg=f"exp_avg_sq {k}")
+    # capacity: the reference skips the step when it would exceed max_gaussians (trainer.cu:579-585)
+    if cnt["n_out"] > 1:
+        none_p, none_m, cnt2 = Hh.densify(dp, mom_d, d(acc), d(dur, torch.int32), 0.5, 0.005, 10.0, 1.6, max_gaussians=cnt["n_out"] - 1, seed=77, l_max=l_max)
+        assert none_p is None and cnt2 == cnt

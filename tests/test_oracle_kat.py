@@ -105,3 +105,68 @@ def test_oracle_fused_loss_matches_float64_statement_and_finite_differences():
             continue                                  # |p - g| kink inside the stencil
         fd = (_ssim_l1_loss64(p64 + d, g64, w) - _ssim_l1_loss64(p64 - d, g64, w)) / 2e-5
         assert abs(grad[y, x, c] - fd) < 2e-3 * abs(fd) + 1e-8, (y, x, c, grad[y, x, c], fd)
+
+
+# ------------------------------------------------------------------------------------------------ densification (8f rank 4)
+def test_oracle_philox_known_answers():
+    """The counter-based generator behind the split samples is Philox4x32-10 (Salmon, Moraes, Dror, Shaw, SC'11): pinned
+    by the three known-answer vectors published with the Random123 library (kat_vectors: philox4x32 10)."""
+    assert G.philox4x32_10([0, 0, 0, 0], [0, 0]) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert G.philox4x32_10([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert G.philox4x32_10([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+
+
+def test_oracle_split_children_reference_known_answers():
+    """what the reference's own tests pin for split / clone (tests/adaptive_density_test.cpp:235-299): the children's
+    log-scale is log(exp(s) / 1.6) on every axis for both children, everything else is copied; positions are random
+    there (curand seeded with time(NULL)) and not asserted.  Here they must be distributed as N(xyz, R S^2 R^T)."""
+    xyz, s = np.array([1.0, 2.0, 3.0], np.float32), np.log(np.array([2.0, 2.0, 2.0], np.float32))
+    q = np.array([1.0, 0.0, 0.0, 0.0], np.float32)
+    kids, sc = G.split_children(7, 0, xyz, s, q, 1.6)
+    np.testing.assert_allclose(sc, np.log(2.0 / 1.6), atol=1e-6)                  # adaptive_density_test.cpp:281-290
+    assert kids.shape == (2, 3) and np.isfinite(kids).all() and not np.array_equal(kids[0], kids[1])
+    # distribution: anisotropic, rotated parent; 20000 parents' worth of children
+    s2 = np.log(np.array([0.5, 0.1, 0.02], np.float32))
+    q2 = np.array([0.9, 0.1, -0.3, 0.2], np.float32)                               # non-unit on purpose (normalised inside)
+    pts = np.concatenate([G.split_children(123, i, xyz, s2, q2, 1.6)[0] for i in range(20000)])
+    w, x, y, z = q2 / np.linalg.norm(q2)
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+                  [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                  [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+    cov = R @ np.diag(np.exp(2 * s2.astype(np.float64))) @ R.T
+    np.testing.assert_allclose(pts.mean(0), xyz, atol=4 * 0.5 / np.sqrt(len(pts)))
+    np.testing.assert_allclose(np.cov(pts.T), cov, atol=0.04 * np.abs(cov).max())
+
+
+def test_oracle_density_decisions():
+    """IdentifyPrune / IdentifyClone / IdentifySplit of cuda/trainer.cu:438-504 on hand-made rows (extent 10: max scale 1.0,
+    clone threshold 0.1; uv gradient threshold 0.5; opacity threshold 0.005)."""
+    ext, gthr, othr = 10.0, 0.5, 0.005
+    logit = lambda p: np.log(p / (1 - p))
+    rows = [  # opacity p, largest scale, mean grad (accum / dur), dur -> expected action
+        (0.001, 0.05, 0.9, 4, 1),    # transparent -> prune, whatever the gradient
+        (0.5, 0.05, 0.9, 4, 2),      # small + high gradient -> clone
+        (0.5, 0.5, 0.9, 4, 3),       # large + high gradient -> split
+        (0.5, 1.5, 0.9, 4, 3),       # above max scale but 1.5 / 1.6 <= 1.0 and about to be split -> split, not pruned
+        (0.5, 1.7, 0.9, 4, 1),       # 1.7 / 1.6 > 1.0 -> pruned although the gradient is high
+        (0.5, 1.2, 0.1, 4, 1),       # too large, low gradient -> prune
+        (0.5, 0.5, 0.1, 4, 0),       # nothing to do
+        (0.5, 0.05, 9.9, 0, 0),      # never visible (duration 0): mean gradient 0 -> keep
+    ]
+    op = np.array([logit(r[0]) for r in rows], np.float32)
+    sc = np.log(np.array([[r[1], r[1] * 0.5, r[1] * 0.1] for r in rows], np.float32))
+    acc = np.array([r[2] * max(r[3], 1) for r in rows], np.float32)
+    dur = np.array([r[3] for r in rows], np.int32)
+    act = G.density_decide(op, sc, acc, dur, gthr, othr, ext)
+    np.testing.assert_array_equal(act, [r[4] for r in rows])
+    # the compaction order of trainer.cu:655-775: survivors (clone parents included) in order, clones, split children
+    params = dict(xyz=np.arange(24, dtype=np.float32).reshape(8, 3), scale=sc, quaternion=np.tile([1, 0, 0, 0], (8, 1)).astype(np.float32),
+                  opacity=op.reshape(8, 1), band0=np.zeros((8, 3), np.float32))
+    mom = {k: (np.ones_like(v), 2 * np.ones_like(v)) for k, v in params.items()}
+    out_p, out_m = G.densify(params, mom, act, seed=5, scale_factor=1.6)
+    assert out_p["xyz"].shape[0] == 3 + 1 + 2 * 2                                  # keep {1, 6, 7}, clone {1}, split {2, 3}
+    np.testing.assert_array_equal(out_p["opacity"][:4, 0], op[[1, 6, 7, 1]])
+    np.testing.assert_array_equal(out_p["xyz"][:4], params["xyz"][[1, 6, 7, 1]])
+    np.testing.assert_allclose(out_p["scale"][4:6], np.tile(np.log(np.exp(sc[2]) / 1.6), (2, 1)), atol=1e-6)
+    assert (out_m["xyz"][0][:3] == 1).all() and (out_m["xyz"][1][:3] == 2).all() and not out_m["xyz"][0][3:].any()

@@ -12,6 +12,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 FWD = os.path.join(ROOT, "oracle", "_ref", "ref_gtest_forward")
 BWD = os.path.join(ROOT, "oracle", "_ref", "ref_gtest_backward")
 OPT = os.path.join(ROOT, "oracle", "_ref", "ref_gtest_optimizer")   # tests/optimizer_test.cpp
+DENS = os.path.join(ROOT, "oracle", "_ref", "ref_gtest_density")    # tests/adaptive_density_test.cpp
 FILTER = "--gtest_filter=*"
 
 
@@ -23,16 +24,16 @@ def _need(path):
 def test_reference_gtests_link_against_libgsx():
     """CPU check: the binaries resolve every reference-named symbol from libgsx.so (no compute)."""
     _need(FWD)
-    for exe in (FWD, BWD) + ((OPT,) if os.path.exists(OPT) else ()):
+    for exe in (FWD, BWD) + tuple(x for x in (OPT, DENS) if os.path.exists(x)):
         out = subprocess.run(["ldd", "-r", exe], capture_output=True, text=True)
         assert "libgsx.so" in out.stdout
         assert "undefined symbol" not in out.stdout + out.stderr, out.stdout + out.stderr
         lst = subprocess.run([exe, "--gtest_list_tests"], capture_output=True, text=True)
-        assert lst.returncode == 0 and re.search("CudaKernelTest|CudaBackwardKernelTest|AdamOptimizerTest", lst.stdout)
+        assert lst.returncode == 0 and re.search("CudaKernelTest|CudaBackwardKernelTest|AdamOptimizerTest|AdaptiveDensityTest", lst.stdout)
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("exe,n_tests", [(FWD, 10), (BWD, 7), (OPT, 1)])
+@pytest.mark.parametrize("exe,n_tests", [(FWD, 10), (BWD, 7), (OPT, 1), (DENS, 2)])
 def test_reference_gtests_pass_on_libgsx(exe, n_tests):
     _need(exe)
     out = subprocess.run([exe, FILTER], capture_output=True, text=True, timeout=300)
