@@ -32,6 +32,8 @@ SYMBOLS = [
     "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers", "gsx_adam_step", "gsx_adam_step_fused",
     "gsx_fused_loss_workspace_bytes", "gsx_fused_loss",
     "gsx_compute_morton_codes", "gsx_morton_order_workspace_bytes", "gsx_morton_order", "gsx_gather_rows", "gsx_gather_rows_multi",
+    "gsx_dp_unique_id", "gsx_dp_init", "gsx_dp_destroy", "gsx_dp_grads", "gsx_dp_step", "gsx_dp_render_host", "gsx_dp_allreduce",
+    "gsx_dp_enable_timing", "gsx_dp_timing",
     "gsx_clone_gaussians", "gsx_split_gaussians", "gsx_densify_workspace_bytes", "gsx_densify_plan", "gsx_densify_apply",
 ]
 
@@ -71,6 +73,14 @@ class GsxAdamGroup(C.Structure):
 
 
 GSX_ADAM_MAX_GROUPS = 8
+
+
+class GsxAdamEpilogue(C.Structure):
+    _fields_ = [("params", GsxGrads), ("exp_avg", C.c_void_p * 6), ("exp_avg_sq", C.c_void_p * 6), ("lr", C.c_float * 6),
+                ("b1", C.c_float), ("b2", C.c_float), ("eps", C.c_float), ("bias1", C.c_float), ("bias2", C.c_float)]
+
+
+GSX_DP_ID_BYTES = 128
 
 
 class GsxDensityConfig(C.Structure):

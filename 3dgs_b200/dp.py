@@ -156,6 +156,97 @@ def sh_grads_from_view_rgb(xyz, campos_all, drgb, l_max, sh_grad, band0_grad, sh
         C.c_void_p(band0_grad.data_ptr()), int(flags), st))
 
 
+class DpNative:
+    """The multi-GPU step behind the C ABI (gsx_dp_*, csrc/dp.cu): NCCL communicator, exchange buffers, streams and the
+    whole step live in libgsx.so; this class only hands over pointers.  The 128-byte NCCL id travels from rank 0 to the
+    others through torch.distributed (any backend) -- plumbing, as for an MPI or socket bootstrap in a C++ caller."""
+
+    def __init__(self, rasterizer, gaussians, views_all, l_max, world, rank, group=None):
+        import ctypes as C_
+        self.r, self.g, self.world, self.rank = rasterizer, gaussians, world, rank
+        self.views = (_ffi.GsxView * len(views_all))(*views_all)
+        self.nv_local = len(views_all) // world
+        dev = gaussians.xyz.device
+        idb = torch.zeros(_ffi.GSX_DP_ID_BYTES, dtype=torch.uint8)
+        if rank == 0:
+            buf = (C_.c_ubyte * _ffi.GSX_DP_ID_BYTES)()
+            check(lib().gsx_dp_unique_id(buf))
+            idb = torch.tensor(list(buf), dtype=torch.uint8)
+        if world > 1:
+            t = idb.to(dev) if dist.get_backend(group) == "nccl" else idb
+            dist.broadcast(t, src=0, group=group)
+            idb = t.cpu()
+        raw = (C_.c_ubyte * _ffi.GSX_DP_ID_BYTES)(*idb.tolist())
+        self.h = C_.c_void_p()
+        check(lib().gsx_dp_init(C_.byref(self.h), rasterizer.h, raw, int(rank), int(world), int(gaussians.N), len(views_all),
+                                int(l_max), int(gaussians.sh_stride)))
+        g = _ffi.GsxGrads()
+        check(lib().gsx_dp_grads(self.h, C_.byref(g)))
+        N = gaussians.N
+        from .host import _from_ptr
+        mk = lambda ptr, shape: _from_ptr(ptr, shape, torch.float32)
+        self.grads = dict(xyz=mk(g.xyz, (N, 3)), scale=mk(g.scale, (N, 3)), quaternion=mk(g.quaternion, (N, 4)),
+                          opacity=mk(g.opacity, (N,)), band0=mk(g.band0, (N, 3)),
+                          sh=mk(g.sh, (N, max(gaussians.sh_stride, 1))) if gaussians.sh_stride else torch.zeros((N, 1), device=dev))
+        gaussians.grads = self.grads                       # zero-copy views of the buffers the step writes
+
+    def close(self):
+        if self.h:
+            lib().gsx_dp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def step(self, grad_images, adam=None):
+        """grad_images: device tensors of this rank's views (one, or a list)"""
+        gi = grad_images if isinstance(grad_images, (list, tuple)) else [grad_images] * self.nv_local
+        arr = (C.c_void_p * self.nv_local)(*[t.data_ptr() for t in gi])
+        p = self.g.params()
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        check(lib().gsx_dp_step(self.h, self.views, C.byref(p), arr, C.byref(adam) if adam is not None else None, st))
+
+    def render_host(self, grad_images_host, images_host, adam=None):
+        """pinned host loss-gradient images in, pinned host rendered images out (synchronises)"""
+        gi = (C.c_void_p * self.nv_local)(*[t.data_ptr() for t in grad_images_host])
+        io = (C.c_void_p * self.nv_local)(*[t.data_ptr() for t in images_host])
+        p = self.g.params()
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        check(lib().gsx_dp_render_host(self.h, self.views, C.byref(p), gi, io, C.byref(adam) if adam is not None else None, st))
+
+    def allreduce(self, buf):
+        st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+        check(lib().gsx_dp_allreduce(self.h, C.c_void_p(buf.data_ptr()), C.c_size_t(buf.numel()), st))
+
+    def enable_timing(self, on=True):
+        check(lib().gsx_dp_enable_timing(self.h, int(bool(on))))
+
+    def phase_ms(self):
+        ms = (C.c_float * 6)()
+        check(lib().gsx_dp_timing(self.h, ms))
+        return dict(zip(("views", "gather", "params_bwd", "reduce", "sh_rebuild", "total"), [float(x) for x in ms]))
+
+    def link_bytes_per_step(self):
+        N = self.g.N
+        return len(self.views) * N * 3 * 4, 11 * N * 4
+
+    def adam_epilogue(self, params, moments, lrs, b1, b2, eps, bias1, bias2):
+        """gsx_adam_epilogue_t for step(): params / moments dicts keyed xyz, scale, quaternion, opacity, band0, sh"""
+        a = _ffi.GsxAdamEpilogue()
+        for k, nm in enumerate(("xyz", "scale", "quaternion", "opacity", "band0", "sh")):
+            t = params.get(nm)
+            setattr(a.params, nm, t.data_ptr() if t is not None else None)
+            mv = moments.get(nm)
+            a.exp_avg[k] = mv[0].data_ptr() if mv is not None else None
+            a.exp_avg_sq[k] = mv[1].data_ptr() if mv is not None else None
+            a.lr[k] = float(lrs.get(nm, 0.0))
+        a.b1, a.b2, a.eps, a.bias1, a.bias2 = float(b1), float(b2), float(eps), float(bias1), float(bias2)
+        return a
+
+
 class ViewParallel:
     """One batch step on this rank's GPU: forward + backward of the rank's views, then the exchange above.
     `views_all` / `campos_all` describe ALL views of the batch (every rank needs every camera position)."""

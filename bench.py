@@ -227,17 +227,30 @@ def main():
     # of the rank's views summed in one pass with '=' semantics: no 1.4 GB memset) + the gradient allreduce.
     all_views = [mk(c, VF) for c in cams]
     # GSX_DP_TRANSPORT=nccl forces the NCCL transport (default: symmetric memory -- multimem / p2p -- when available)
-    vp = gs.dp.ViewParallel(r, gd, all_views, [c["campos"] for c in cams], l_max, world, rank,
-                            symmetric=os.environ.get("GSX_DP_TRANSPORT", "auto") != "nccl")
+    # N > 1: the step lives behind the C ABI (gsx_dp_step / gsx_dp_render_host, csrc/dp.cu: NCCL called from C++);
+    # GSX_DP_IMPL=python selects the Python-orchestrated transports of dp.ViewParallel (multimem / p2p kernels) for A/B
+    native = world > 1 and os.environ.get("GSX_DP_IMPL", "native") != "python"
+    nat = vp = None
+    if native:
+        nat = gs.dp.DpNative(r, gd, all_views, l_max, world, rank)
+    else:
+        vp = gs.dp.ViewParallel(r, gd, all_views, [c["campos"] for c in cams], l_max, world, rank,
+                                symmetric=os.environ.get("GSX_DP_TRANSPORT", "auto") != "nccl")
 
     def step():
-        vp.step(gi_dev)
+        if native:
+            nat.step(gi_dev)
+        else:
+            vp.step(gi_dev)
 
     img_dev = torch.empty((H, W, 3), device=dev, dtype=torch.float32)
 
     def step_e2e():
         if world == 1:
             r.batch_render_host(vstructs, gd, gi_host, img_host, flags=OVER)
+            return
+        if native:
+            nat.render_host(gi_host, img_host)                     # the library pipelines the copies (gsx_dp_render_host)
             return
         # host buffers in / out around the same exchange: per view H2D of the loss gradient, D2H of the image, on two copy
         # streams (uploads under the per-Gaussian forward, view k's download under its backward) like the library's
@@ -308,7 +321,13 @@ def main():
     dt_e2e = float(dt_e2e.item())
 
     exch = None
-    if world > 1:                                                  # per-phase times of one more step (outside the timed region)
+    if world > 1 and native:                                       # per-phase times of one more step (outside the timed region)
+        nat.enable_timing(True)
+        step()
+        barrier()
+        exch = {k_: round(v_, 3) for k_, v_ in nat.phase_ms().items()}
+        nat.enable_timing(False)
+    elif world > 1:
         vp.timing = {}
         step()
         barrier()
@@ -500,9 +519,10 @@ def main():
 
     views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
     if world > 1:
-        ga_, ar_ = vp.ex.link_bytes_per_step()
-        how = {"nccl": "NCCL all-gather", "multimem": "in-kernel multicast stores (multimem.st)", "p2p": "in-kernel P2P stores"}[vp.ex.transport]
-        how2 = "in-switch multimem allreduce kernel" if vp.ex.transport == "multimem" else "NCCL allreduce"
+        transport = "nccl from C++ (gsx_dp_step)" if native else vp.ex.transport
+        ga_, ar_ = nat.link_bytes_per_step() if native else vp.ex.link_bytes_per_step()
+        how = "NCCL all-gather" if native else {"nccl": "NCCL all-gather", "multimem": "in-kernel multicast stores (multimem.st)", "p2p": "in-kernel P2P stores"}[vp.ex.transport]
+        how2 = "in-switch multimem allreduce kernel" if (not native and vp.ex.transport == "multimem") else "NCCL allreduce"
         xbytes = (f"{how} of {ga_ / 1e6:.0f} MB per-view d rgb + {how2} of {ar_ / 1e6:.0f} MB geometry "
                   f"gradients (SH gradients rebuilt locally; plain allreduce would be {flat.numel() * 4 / 1e6:.0f} MB)")
     else:
@@ -523,7 +543,7 @@ def main():
         "e2e": {"value": N_VIEWS * args.steps / dt_e2e, "unit": UNIT,
                 "h2d_bytes_per_step": N_VIEWS * (W * H * 3 * 4 + 200), "d2h_bytes_per_step": N_VIEWS * W * H * 3 * 4},
         "gpu_launches": (launches_per_view * nv + 2) * args.steps * world,
-        "exchange_ms": exch, "exchange_transport": (vp.ex.transport if world > 1 else None), "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": round(fp32_peak, 2),
+        "exchange_ms": exch, "exchange_transport": (transport if world > 1 else None), "roofline": roof, "stages": stages, "fp32_peak_tflops_measured": round(fp32_peak, 2),
         "next_rows": next_rows,
     }
     if world == 1 and not args.no_cpu_baseline:

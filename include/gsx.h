@@ -338,6 +338,48 @@ int gsx_gather_rows(const float *src, const int *order, int N, int width, float 
 int gsx_gather_rows_multi(const float *const *src_host, float *const *dst_host, const int *width_host, int n_arrays,
                           const int *order, int N, void *stream);
 
+/* ---- the view-parallel multi-GPU step, NCCL called from C++ -------------------------------------------
+ * One process (or host thread) per GPU, parameters replicated, the n_views_total views of a batch sharded in blocks over
+ * the ranks (rank r owns views [r * n/world, (r+1) * n/world)), gradients summed over all views.  The caller this serves is
+ * the reference's training loop (cuda/trainer.cu:1350-1360: rasterize_image, backward_pass, optimizer_step), widened to a
+ * batch; the reference itself is single-GPU.
+ *   gsx_dp_unique_id(id)      rank 0: a 128-byte ncclUniqueId the caller hands to every rank (MPI, a file, a socket, ...)
+ *   gsx_dp_init(...)          NCCL communicator over `world` ranks (one GPU each, current device), exchange buffers
+ *   gsx_dp_step(...)          forward + backward of this rank's views through ctx's batch path, then the exchange: each
+ *                             local view's dense d rgb is all-gathered as soon as its compositing backward is done (under
+ *                             the next views), the 44 B/Gaussian geometry gradients are allreduced under the local rebuild
+ *                             of the band-0 + SH gradients from all views' d rgb; with `adam` the optimiser step runs as
+ *                             the epilogue on every rank.  Asynchronous on `stream`.  views_all_host: ALL views of the
+ *                             batch in global order; grad_images_dev: this rank's views only.
+ *   gsx_dp_render_host(...)   the same from pinned host buffers: loss-gradient images up, rendered images down, both
+ *                             pipelined on copy streams under the compute.  Synchronises.
+ *   gsx_dp_grads(dp, &g)      where the batch-summed gradients are (device memory owned by dp; valid after a step)
+ *   gsx_dp_allreduce(...)     plain sum-allreduce of a caller buffer (the un-optimised baseline: 236 B/Gaussian at once)
+ * NCCL is bound at run time (dlopen of libnccl.so.2, GSX_NCCL_LIB overrides): libgsx.so has no link-time dependency on it. */
+#define GSX_DP_ID_BYTES 128
+typedef struct gsx_dp gsx_dp_t;
+typedef struct gsx_adam_epilogue {
+  gsx_grads_t params;                   /* the parameter arrays to update in place (uv unused) */
+  float *exp_avg[6], *exp_avg_sq[6];    /* Adam moments: xyz, scale, quaternion, opacity, band0, sh */
+  float lr[6];
+  float b1, b2, eps, bias1, bias2;      /* as gsx_adam_step_fused */
+} gsx_adam_epilogue_t;
+int gsx_dp_unique_id(void *id128_out);
+int gsx_dp_init(gsx_dp_t **dp, gsx_ctx_t *ctx, const void *id128, int rank, int world, int N, int n_views_total, int l_max,
+                int sh_stride);
+int gsx_dp_destroy(gsx_dp_t *dp);
+int gsx_dp_grads(gsx_dp_t *dp, gsx_grads_t *out_host);
+int gsx_dp_step(gsx_dp_t *dp, const gsx_view_t *views_all_host, const gsx_params_t *params, const float *const *grad_images_dev,
+                const gsx_adam_epilogue_t *adam, void *stream);
+int gsx_dp_render_host(gsx_dp_t *dp, const gsx_view_t *views_all_host, const gsx_params_t *params,
+                       const float *const *grad_images_host, float *const *images_host, const gsx_adam_epilogue_t *adam,
+                       void *stream);
+int gsx_dp_allreduce(gsx_dp_t *dp, float *buf, size_t n_floats, void *stream);
+int gsx_dp_enable_timing(gsx_dp_t *dp, int on);
+/* ms_out[6] = views phase, gather tail after the last view, per-Gaussian backward, allreduce, SH rebuild (+ waits,
+ * + Adam), whole step of the last timed step (synchronises; -1 where a phase does not exist, e.g. world == 1) */
+int gsx_dp_timing(gsx_dp_t *dp, float *ms_out);
+
 /* ---- SURVEY 8f rank 4 (second half): adaptive density control -- clone / split / prune ----
  * gsx_clone_gaussians / gsx_split_gaussians replace clone_gaussians / split_gaussians
  * (include/gsplat_cuda/adaptive_density.cuh:28,54, cuda/adaptive_density.cu:13-206) with the same argument meaning: mask

@@ -38,6 +38,31 @@ def main():
     want = {k: t.clone() for k, t in gd0.grads.items()}
     r0.close()
     report = []
+    # the step behind the C ABI (gsx_dp_step / gsx_dp_render_host: NCCL called from C++), device and host-buffer entry points
+    gd = mk()
+    r = H.Rasterizer(N, W, Hh, instance_capacity=8 * N)
+    nat = dp.DpNative(r, gd, views, l_max, world, rank)
+    mine = dp.shard_views(NV, world, rank)
+    for mode in ("step", "render_host"):
+        if mode == "step":
+            for _ in range(2):
+                nat.step([gis[k] for k in mine])
+        else:
+            gih = [gis[k].cpu().pin_memory() for k in mine]
+            imh = [torch.zeros((Hh, W, 3)).pin_memory() for _ in mine]
+            nat.render_host(gih, imh)
+            assert all(float(t.abs().sum()) > 0 for t in imh)
+        torch.cuda.synchronize()
+        dist.barrier()
+        worst = 0.0
+        for k, w in want.items():
+            a, b = nat.grads[k].float().reshape(-1), w.reshape(-1)
+            rel = float((a - b).norm() / (b.norm() + 1e-30))
+            worst = max(worst, rel)
+            assert rel <= 1e-3, f"gsx_dp_{mode}: d {k} rel err {rel}"
+        report.append(f"capi-{mode}:{worst:.1e}")
+    nat.close()
+    r.close()
     # (symmetric memory?, d rgb gather, fused extraction?): NCCL only with both buffer layouts, then the hybrid default
     # (per-view NCCL gathers + in-switch allreduce) and the two peer-store variants
     for symmetric, gather, fused in ((False, "nccl", "1"), (False, "fused", "1"), (True, "nccl", "1"), (True, "fused", "1"),
