@@ -14,25 +14,38 @@
 // (n_dev) so the view-level path never syncs with the host.
 // The kernels are templated on the key type: the view-level path sorts 32-bit keys twice (depth per Gaussian, then
 // tile id per instance, binning.cu) instead of one 64-bit tile|depth key per instance.
+#include <stdlib.h>
+
+#include <algorithm>
+
 #include "gsx_common.cuh"
 
 namespace gsx {
 
 namespace {
 
-#ifndef GSX_RS_THREADS
-#define GSX_RS_THREADS 256
-#endif
-#ifndef GSX_RS_IPT
-#define GSX_RS_IPT 16
-#endif
-constexpr int RS_THREADS = GSX_RS_THREADS;
-constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_IPT = GSX_RS_IPT;
-constexpr int RS_TILE = RS_THREADS * RS_IPT;   // 4096 keys per tile
 constexpr int RADIX = 256;
 constexpr int MAX_PASSES = 8;
 constexpr uint32_t FLAG_AGG = 1u << 30, FLAG_INC = 2u << 30, FLAG_MASK = 3u << 30, VAL_MASK = ~FLAG_MASK;
+
+// Tile shapes of the onesweep kernel (threads x keys per thread).  The per-tile fixed costs -- zeroing and scanning 256
+// digit counters per warp, the look-back over 256 status words -- are amortised over the tile, so larger tiles raise the
+// bandwidth per pass until registers / shared memory cut the occupancy (CUB's sm_100 tuning for 4-byte keys + 4-byte values
+// uses 384-512 threads x ~20 keys, tuning_radix_sort.cuh:92-160).  GSX_RS_CFG=0..3 selects one at run time for A/B runs.
+struct RsCfg { int threads, ipt; };
+constexpr RsCfg kRsCfg[4] = {{256, 16}, {512, 16}, {384, 20}, {512, 12}};
+#ifndef GSX_RS_DEFAULT_CFG
+#define GSX_RS_DEFAULT_CFG 0
+#endif
+static int rs_cfg() {
+  static const int c = [] {
+    const char *e = getenv("GSX_RS_CFG");
+    const int v = e ? atoi(e) : GSX_RS_DEFAULT_CFG;
+    return (v >= 0 && v < 4) ? v : GSX_RS_DEFAULT_CFG;
+  }();
+  return c;
+}
+static int rs_tile() { return kRsCfg[rs_cfg()].threads * kRsCfg[rs_cfg()].ipt; }
 
 __device__ __forceinline__ long long live_count(const int *n_dev, long long n) {
   if (n_dev) { const long long v = *n_dev; return v < n ? v : n; }
@@ -85,53 +98,56 @@ __device__ __forceinline__ void st_volatile(unsigned *p, unsigned v) {
   asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-template <typename KeyT>
-__global__ void __launch_bounds__(RS_THREADS)
+template <typename KeyT, int THREADS, int IPT>
+__global__ void __launch_bounds__(THREADS, (THREADS <= 256 ? (sizeof(KeyT) == 8 ? 3 : 4) : (sizeof(KeyT) == 8 ? 1 : 2)))
 k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
            uint32_t *__restrict__ vals_out, long long n_host, const int *__restrict__ n_dev, int shift, int bits,
            const unsigned int *__restrict__ digit_base /*[256] exclusive*/, unsigned int *__restrict__ status,
            unsigned int *__restrict__ ticket) {
-  __shared__ __align__(16) KeyT s_keys[RS_TILE];            // reused for the values
-  __shared__ unsigned int s_warp[RS_WARPS][RADIX + 1];      // per-warp digit counts -> exclusive offsets
+  constexpr int WARPS = THREADS / 32, TILE = THREADS * IPT;
+  static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit for the digit-parallel steps");
+  extern __shared__ __align__(16) unsigned char s_dyn[];
+  KeyT *s_keys = reinterpret_cast<KeyT *>(s_dyn);           // [TILE], reused for the values
+  __shared__ unsigned int s_warp[WARPS][RADIX + 1];         // per-warp digit counts -> exclusive offsets
   __shared__ unsigned int s_excl[RADIX + 1];                // block-exclusive offset of each digit
   __shared__ int s_gbase[RADIX];                            // global base minus local offset
-  __shared__ unsigned int s_scan[RS_WARPS];
+  __shared__ unsigned int s_scan[RADIX / 32];
   __shared__ unsigned int s_tile;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-  for (int i = tid; i < RS_WARPS * (RADIX + 1); i += RS_THREADS) (&s_warp[0][0])[i] = 0;
-  s_excl[tid] = 0;
+  for (int i = tid; i < WARPS * (RADIX + 1); i += THREADS) (&s_warp[0][0])[i] = 0;
+  if (tid < RADIX) s_excl[tid] = 0;
   __syncthreads();
   const unsigned tile = s_tile;
   const long long n = live_count(n_dev, n_host);
-  const long long base = (long long)tile * RS_TILE;
+  const long long base = (long long)tile * TILE;
   if (base >= n) return;
-  const int valid = (int)min((long long)RS_TILE, n - base);
+  const int valid = (int)min((long long)TILE, n - base);
   const unsigned mask = (1u << bits) - 1u;
 
-  KeyT key[RS_IPT];
-  unsigned pos[RS_IPT];
+  KeyT key[IPT];
+  unsigned pos[IPT];
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) {
-    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+  for (int i = 0; i < IPT; ++i) {
+    const int li = warp * (IPT * 32) + i * 32 + lane;
     key[i] = li < valid ? keys_in[base + li] : ~(KeyT)0;
   }
   // 1. tile histogram first (shared-memory integer atomics) so the tile's aggregate is published BEFORE the ranking:
   //    successors' look-back then never waits on this tile's ranking
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) {
-    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+  for (int i = 0; i < IPT; ++i) {
+    const int li = warp * (IPT * 32) + i * 32 + lane;
     if (li < valid) atomicAdd(&s_excl[(unsigned)(key[i] >> shift) & mask], 1u);
   }
   __syncthreads();
-  const unsigned total = s_excl[tid];   // for digit == tid
+  const unsigned total = tid < RADIX ? s_excl[tid] : 0u;   // for digit == tid
   unsigned *my = status + (size_t)tile * RADIX + tid;
-  st_volatile(my, (tile == 0 ? FLAG_INC : FLAG_AGG) | total);
+  if (tid < RADIX) st_volatile(my, (tile == 0 ? FLAG_INC : FLAG_AGG) | total);
   // 2. stable rank inside the warp: items in order i, lanes in order; peers found with one ballot per digit bit
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) {
-    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+  for (int i = 0; i < IPT; ++i) {
+    const int li = warp * (IPT * 32) + i * 32 + lane;
     const unsigned d = li < valid ? ((unsigned)(key[i] >> shift) & mask) : (unsigned)RADIX;
     // peers = lanes holding the same digit: one vote per digit bit (+ one for the padding digit RADIX, bit 8).
     // Measured against match.any on B200: tile sort 0.427 -> 0.399 ms per view.
@@ -155,27 +171,27 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
   }
   __syncthreads();
   // per digit: exclusive scan over warps
-  {
+  if (tid < RADIX) {
     unsigned run = 0;
 #pragma unroll
-    for (int w = 0; w < RS_WARPS; ++w) { const unsigned t = s_warp[w][tid]; s_warp[w][tid] = run; run += t; }
+    for (int w = 0; w < WARPS; ++w) { const unsigned t = s_warp[w][tid]; s_warp[w][tid] = run; run += t; }
   }
-  // block-exclusive scan of totals over the 256 digits
-  {
-    unsigned incl = total;
+  // block-exclusive scan of totals over the 256 digits (the first 8 warps)
+  unsigned incl = total;
+  if (tid < RADIX) {
 #pragma unroll
     for (int off = 1; off < 32; off <<= 1) {
       const unsigned t = __shfl_up_sync(0xffffffffu, incl, off);
       if (lane >= off) incl += t;
     }
     if (lane == 31) s_scan[warp] = incl;
-    __syncthreads();
+  }
+  __syncthreads();
+  if (tid < RADIX) {
     unsigned wbase = 0;
     for (int w = 0; w < warp; ++w) wbase += s_scan[w];
     s_excl[tid] = wbase + incl - total;
-  }
-  // 3. decoupled look-back for digit == tid (predecessors published their aggregates before ranking)
-  {
+    // 3. decoupled look-back for digit == tid (predecessors published their aggregates before ranking)
     unsigned excl = 0;
     if (tile != 0) {
       // windowed: LB predecessors are fetched at once (independent loads in flight) and consumed nearest first up to
@@ -184,17 +200,17 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
       constexpr int LB = 8;
       long long t = (long long)tile - 1;
       while (true) {
-        unsigned s[LB];
+        unsigned sw[LB];
 #pragma unroll
         for (int w = 0; w < LB; ++w)
-          s[w] = (t - w >= 0) ? ld_volatile(status + (size_t)(t - w) * RADIX + tid) : FLAG_INC;   // before tile 0: nothing
+          sw[w] = (t - w >= 0) ? ld_volatile(status + (size_t)(t - w) * RADIX + tid) : FLAG_INC;   // before tile 0: nothing
         int used = 0;
         bool fin = false;
 #pragma unroll
         for (int w = 0; w < LB; ++w) {
-          const unsigned f = s[w] & FLAG_MASK;
+          const unsigned f = sw[w] & FLAG_MASK;
           if (!fin && used == w && f != 0) {
-            excl += s[w] & VAL_MASK;
+            excl += sw[w] & VAL_MASK;
             used = w + 1;
             fin = (f == FLAG_INC);
           }
@@ -209,8 +225,8 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
   __syncthreads();
   // 4. local reorder through shared memory, then coalesced scatter
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) {
-    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+  for (int i = 0; i < IPT; ++i) {
+    const int li = warp * (IPT * 32) + i * 32 + lane;
     if (li < valid) {   // padding items (digit RADIX) are never written
       const unsigned d = (unsigned)(key[i] >> shift) & mask;
       pos[i] += s_excl[d] + s_warp[warp][d];
@@ -218,10 +234,10 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
     }
   }
   __syncthreads();
-  int gidx[RS_IPT];
+  int gidx[IPT];
 #pragma unroll
-  for (int k = 0; k < RS_IPT; ++k) {
-    const int slot = tid + k * RS_THREADS;
+  for (int k = 0; k < IPT; ++k) {
+    const int slot = tid + k * THREADS;
     gidx[k] = -1;
     if (slot < valid) {
       const KeyT kk = s_keys[slot];
@@ -231,17 +247,17 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
     }
   }
   __syncthreads();
-  // values are loaded only now (16 fewer live registers through the ranking)
+  // values are loaded only now (IPT fewer live registers through the ranking)
   uint32_t *s_vals = reinterpret_cast<uint32_t *>(s_keys);
 #pragma unroll
-  for (int i = 0; i < RS_IPT; ++i) {
-    const int li = warp * (RS_IPT * 32) + i * 32 + lane;
+  for (int i = 0; i < IPT; ++i) {
+    const int li = warp * (IPT * 32) + i * 32 + lane;
     if (li < valid) s_vals[pos[i]] = vals_in[base + li];
   }
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < RS_IPT; ++k)
-    if (gidx[k] >= 0) vals_out[gidx[k]] = s_vals[tid + k * RS_THREADS];
+  for (int k = 0; k < IPT; ++k)
+    if (gidx[k] >= 0) vals_out[gidx[k]] = s_vals[tid + k * THREADS];
 }
 
 // ranges[t] = first i whose tile >= t ; ranges[n_tiles] = n   (reference cuda/culling.cu:302-343; exact integer
@@ -273,7 +289,9 @@ struct SortLayout {
 };
 SortLayout sort_layout(long long n) {
   SortLayout L;
-  L.tiles = (int)((n + RS_TILE - 1) / RS_TILE);
+  // sized for the smallest tile shape, so that one workspace serves whichever shape is selected
+  constexpr int min_tile = 4096;
+  L.tiles = (int)((n + min_tile - 1) / min_tile);
   if (L.tiles < 1) L.tiles = 1;
   size_t off = 0;
   L.hist_off = off; off += align_up(sizeof(unsigned) * MAX_PASSES * RADIX, 256);
@@ -283,13 +301,30 @@ SortLayout sort_layout(long long n) {
   return L;
 }
 
+template <typename KeyT, int THREADS, int IPT>
+static int launch_onesweep(int tiles, const KeyT *kin, KeyT *kout, const uint32_t *vin, uint32_t *vout, long long n,
+                           const int *n_dev, int shift, int bits, const unsigned *base, unsigned *status, unsigned *ticket,
+                           cudaStream_t st) {
+  const size_t dyn = sizeof(KeyT) * (size_t)THREADS * IPT;
+  static bool attr_set = false;   // per instantiation
+  if (!attr_set) {
+    GSX_CUDA(cudaFuncSetAttribute(k_onesweep<KeyT, THREADS, IPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    attr_set = true;
+  }
+  k_onesweep<KeyT, THREADS, IPT><<<tiles, THREADS, dyn, st>>>(kin, kout, vin, vout, n, n_dev, shift, bits, base, status, ticket);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
+}
+
 }  // namespace
 
 // Internal entry (no pointer attribute checks) used by the binning path.  Result lands in keys_b/vals_b when
 // the number of passes is odd, else back in keys_a/vals_a; *result_in_b tells which.
+// flags bit 0 (SORT_HIST_READY): the caller zeroed the workspace with sort_prepare_impl() and accumulated the per-pass digit
+// histograms into sort_hist_impl() itself (the emission kernel does, binning.cu): no memset, no histogram pass here.
 template <typename KeyT>
 static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n, const int *n_dev,
-                        int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st, int *result_in_b) {
+                        int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags) {
   if (key_bits < 1 || key_bits > (int)sizeof(KeyT) * 8) { set_error("key_bits %d out of range", key_bits); return GSX_E_ARG; }
   const int passes = (key_bits + 7) / 8;
   *result_in_b = passes & 1;
@@ -300,34 +335,57 @@ static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *
   unsigned *hist = (unsigned *)(ws + L.hist_off);
   unsigned *ticket = (unsigned *)(ws + L.ticket_off);
   unsigned *status = (unsigned *)(ws + L.status_off);
-  GSX_CUDA(cudaMemsetAsync(ws, 0, L.status_off + sizeof(unsigned) * (size_t)passes * L.tiles * RADIX, st));
-  const int hblocks = (int)std::min<long long>(kNumSMs * 8, (n + 255) / 256);
-  k_histogram<KeyT><<<hblocks, 256, 0, st>>>(keys_a, n, n_dev, passes, key_bits, hist);
-  GSX_LAUNCH_CHECK();
+  const int cfg = rs_cfg();
+  const int tile = kRsCfg[cfg].threads * kRsCfg[cfg].ipt;
+  const int tiles = (int)((n + tile - 1) / tile);
+  if (!(flags & 1)) {
+    GSX_CUDA(cudaMemsetAsync(ws, 0, L.status_off + sizeof(unsigned) * (size_t)passes * tiles * RADIX, st));
+    const int hblocks = (int)std::min<long long>(kNumSMs * 8, (n + 255) / 256);
+    k_histogram<KeyT><<<hblocks, 256, 0, st>>>(keys_a, n, n_dev, passes, key_bits, hist);
+    GSX_LAUNCH_CHECK();
+  }
   k_scan_histogram<<<passes, RADIX, 0, st>>>(hist);
   GSX_LAUNCH_CHECK();
   KeyT *kin = keys_a, *kout = keys_b;
   uint32_t *vin = vals_a, *vout = vals_b;
   for (int p = 0; p < passes; ++p) {
     const int bits = std::min(8, key_bits - 8 * p);
-    k_onesweep<KeyT><<<L.tiles, RS_THREADS, 0, st>>>(kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX,
-                                                     status + (size_t)p * L.tiles * RADIX, ticket + p);
-    GSX_LAUNCH_CHECK();
+    unsigned *stp = status + (size_t)p * tiles * RADIX;
+    int rc;
+    switch (cfg) {
+      case 1: rc = launch_onesweep<KeyT, 512, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st); break;
+      case 2: rc = launch_onesweep<KeyT, 384, 20>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st); break;
+      case 3: rc = launch_onesweep<KeyT, 512, 12>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st); break;
+      default: rc = launch_onesweep<KeyT, 256, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st); break;
+    }
+    if (rc != GSX_OK) return rc;
     std::swap(kin, kout);
     std::swap(vin, vout);
   }
   return GSX_OK;
 }
 
+// zeroes histogram, tickets and status words of a sort of up to n keys on key_bits bits (for SORT_HIST_READY callers)
+int sort_prepare_impl(long long n, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st) {
+  if (n <= 0) return GSX_OK;
+  const SortLayout L = sort_layout(n);
+  if (workspace_bytes < L.total) { set_error("sort workspace %zu < %zu", workspace_bytes, L.total); return GSX_E_WORKSPACE; }
+  const int passes = (key_bits + 7) / 8;
+  const int tiles = (int)((n + rs_tile() - 1) / rs_tile());
+  GSX_CUDA(cudaMemsetAsync(workspace, 0, L.status_off + sizeof(unsigned) * (size_t)passes * tiles * RADIX, st));
+  return GSX_OK;
+}
+unsigned *sort_hist_impl(void *workspace) { return (unsigned *)workspace; }   // [passes][256], pass p = key bits [8p, 8p + 8)
+
 int sort_pairs_impl(uint64_t *keys_a, uint64_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
                     const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
                     int *result_in_b) {
-  return sort_pairs_t<uint64_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b);
+  return sort_pairs_t<uint64_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b, 0);
 }
 int sort_pairs_u32_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
                         const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
-                        int *result_in_b) {
-  return sort_pairs_t<uint32_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b);
+                        int *result_in_b, int flags) {
+  return sort_pairs_t<uint32_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b, flags);
 }
 
 static int ranges_grid(long long n, int n_tiles) {
@@ -378,7 +436,7 @@ int gsx_sort_pairs_u32(uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in,
   GSX_REQUIRE_DEV(workspace);
   int in_b = 0;
   int rc = sort_pairs_u32_impl(keys_in, keys_out, vals_in, vals_out, n, n_dev, key_bits, workspace, workspace_bytes,
-                               (cudaStream_t)stream, &in_b);
+                               (cudaStream_t)stream, &in_b, 0);
   if (rc != GSX_OK) return rc;
   if (!in_b && n > 0) {   // even number of passes: result is in keys_in -> copy to the documented output
     GSX_CUDA(cudaMemcpyAsync(keys_out, keys_in, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
