@@ -281,6 +281,7 @@ static int issue_ahead(gsx_ctx *c, int k, int N, cudaStream_t st) {
 
 // bin + sort + ranges + compositing forward of the view whose per-Gaussian records are in slot k
 static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
+  NvtxRange nvtx_("gsx:view_forward(bin+sort+composite)");
   gsx_slot &s = c->slot[k];
   const gsx_view_t &v = s.view;
   c->last_n = N; c->last_w = v.width; c->last_h = v.height; c->cur = k;
@@ -415,6 +416,7 @@ int gsx_ctx_reserve(gsx_ctx_t *c, long long instance_capacity) {
 
 // Single view = a batch of one: the same pair-compacted per-Gaussian kernels (batch.cu) run with one slot.
 int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N, void *stream) {
+  NvtxRange nvtx_("gsx_forward");
   if (!c || !v || !p) { set_error("null ctx/view/params"); return GSX_E_NULL; }
   int rc = check_view(c, v, p, N);
   if (rc != GSX_OK) return rc;
@@ -435,6 +437,7 @@ int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N,
 
 int gsx_backward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N, const float *grad_image,
                  const gsx_grads_t *g, void *stream) {
+  NvtxRange nvtx_("gsx_backward");
   if (!c || !v || !p || !g || !grad_image) { set_error("null argument"); return GSX_E_NULL; }
   if (c->cur != 0 || c->batch_nv != 1 || N != c->last_n || v->width != c->last_w || v->height != c->last_h) {
     set_error("gsx_backward does not match the last gsx_forward on this context");
@@ -481,6 +484,7 @@ static int fill_batch_const(gsx_ctx *c, int nv, BatchConst *bc) {
 
 int gsx_batch_forward_params(gsx_ctx_t *c, const gsx_view_t *views, int n_views, const gsx_params_t *p, int N,
                              void *stream) {
+  NvtxRange nvtx_("gsx_batch_forward_params(per-Gaussian fwd)");
   if (!c || !views || !p) { set_error("null ctx/views/params"); return GSX_E_NULL; }
   if (n_views < 1 || n_views > c->n_slots) { set_error("n_views %d exceeds the reserved slots (%d)", n_views, c->n_slots); return GSX_E_ARG; }
   for (int k = 0; k < n_views; ++k) {
@@ -541,6 +545,7 @@ int gsx_batch_forward_view(gsx_ctx_t *c, int slot, void *stream) {
 }
 
 int gsx_batch_backward_view(gsx_ctx_t *c, int slot, const float *grad_image, void *stream) {
+  NvtxRange nvtx_("gsx_batch_backward_view(composite bwd)");
   if (!c || !grad_image) { set_error("null argument"); return GSX_E_NULL; }
   if (slot != c->cur || slot >= c->batch_nv) { set_error("gsx_batch_backward_view(%d) must follow gsx_batch_forward_view(%d)", slot, slot); return GSX_E_ARG; }
   cudaStream_t st = (cudaStream_t)stream;
@@ -553,6 +558,7 @@ int gsx_batch_backward_view(gsx_ctx_t *c, int slot, const float *grad_image, voi
 }
 
 int gsx_batch_backward_params(gsx_ctx_t *c, const gsx_params_t *p, int N, const gsx_grads_t *g, int flags, void *stream) {
+  NvtxRange nvtx_("gsx_batch_backward_params(per-Gaussian bwd)");
   if (!c || !p || !g) { set_error("null argument"); return GSX_E_NULL; }
   if (N != c->batch_n || c->batch_nv < 1) { set_error("gsx_batch_backward_params does not match the current batch"); return GSX_E_ARG; }
   if (((uintptr_t)p->quaternion) & 15) { set_error("params.quaternion must be 16-byte aligned (float4 loads)"); return GSX_E_ARG; }
@@ -628,6 +634,7 @@ static int ensure_host_pipeline(gsx_ctx_t *c, int n_views) {
 int gsx_batch_render_host(gsx_ctx_t *c, const gsx_view_t *views, int n_views, const gsx_params_t *p, int N,
                           const float *const *grad_images_host, float *const *images_host, const gsx_grads_t *g, int flags,
                           void *stream) {
+  NvtxRange nvtx_("gsx_batch_render_host");
   if (!c || !views || !p || !g || !grad_images_host) { set_error("null argument"); return GSX_E_NULL; }
   if (n_views < 1 || n_views > GSX_MAX_BATCH) { set_error("n_views out of range"); return GSX_E_ARG; }
   cudaStream_t st = (cudaStream_t)stream;

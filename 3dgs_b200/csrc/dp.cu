@@ -228,6 +228,7 @@ int gsx_dp_allreduce(gsx_dp_t *d, float *buf, size_t n_floats, void *stream) {
 static int dp_step_impl(gsx_dp_t *d, const gsx_view_t *views_all, const gsx_params_t *p, const float *const *grad_images_dev,
                         const float *const *grad_images_host, float *const *images_host, const gsx_adam_epilogue_t *adam,
                         cudaStream_t st) {
+  NvtxRange nvtx_("gsx_dp_step");
   gsx_ctx_t *c = d->ctx;
   const int N = d->N, nv = d->vpr, W = d->world;
   const bool host = grad_images_host != nullptr;

@@ -5,6 +5,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <nvtx3/nvToolsExt.h>   // header-only: ranges cost a no-op call unless a profiler injected the NVTX library
+
 #include "../../include/gsx.h"
 
 namespace gsx {
@@ -44,6 +46,12 @@ int check_device_ptr(const void *p, const char *name);
 
 static inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// NVTX range over the host-side enqueue of a stage (tracing); shows up in Nsight Systems / ncu --nvtx
+struct NvtxRange {
+  explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
 
 constexpr int kNumSMs = 148;  // B200
 
