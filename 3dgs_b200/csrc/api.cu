@@ -45,11 +45,6 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
                        long long capacity, char *ws, const BinLayout &L, const PreBin &pb, int *ranges,
                        const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
                        int tight);
-int bin_prebin_sort_only(const int *touched, int N, const int *ccount, PreBin *pb, cudaStream_t st);
-size_t scan_emit_status_bytes(int N);
-int bin_scan_emit_sort_impl(const float4 *crec, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L,
-                            const PreBin &pb, void *se_status, int *ranges, const uint32_t **sorted_tiles,
-                            const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev, int tight);
 size_t prebin_sort_ws_bytes(int N);
 size_t prebin_block_sums_count(int N);
 int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, cudaStream_t st);
@@ -94,7 +89,6 @@ struct gsx_slot {          // per-view state that must outlive the view inside a
 struct BinSet {
   char *ws = nullptr;
   int *ranges = nullptr;
-  void *se_status = nullptr;  // look-back status words + ticket of the fused scan + emission kernel
   const uint32_t *sorted_tiles = nullptr, *sorted_vals = nullptr;
   int owner = -1;             // slot whose sorted list the set holds (-1: none)
 };
@@ -140,11 +134,6 @@ struct gsx_ctx {
 };
 
 namespace gsx {
-// GSX_BIN=v1 selects the round-1 binning (separate scan kernels + k_emit with three gathers + histogram pass) for A/B runs
-static bool bin_v1() {
-  static const int v = [] { const char *e = getenv("GSX_BIN"); return (e && e[0] == 'v' && e[1] == '1') ? 1 : 0; }();
-  return v != 0;
-}
 static int prebin(gsx_ctx *c, gsx_slot &s, int N, cudaStream_t st);
 // the 64-bit keys the two-level sort never materialises, for inspection: tile << 32 | order-preserving depth bits
 __global__ void k_compose_keys(const uint32_t *__restrict__ tiles, const uint32_t *__restrict__ ids,
@@ -177,7 +166,6 @@ static int alloc_bin(gsx_ctx *c, long long capacity) {
     // tests poison the instance buffers (GSX_DEBUG_POISON=1) to prove that an overflowed view never reads them
     if (getenv("GSX_DEBUG_POISON")) GSX_CUDA(cudaMemset(c->bset[i].ws, 0xFF, c->L.bytes));
     if (!c->bset[i].ranges) GSX_CUDA(cudaMalloc(&c->bset[i].ranges, sizeof(int) * (size_t)(c->n_px_tiles + 1)));
-    if (!c->bset[i].se_status) GSX_CUDA(cudaMalloc(&c->bset[i].se_status, scan_emit_status_bytes(c->max_n)));
   }
   c->bin_ws = c->bset[0].ws; c->ranges = c->bset[0].ranges;
   return GSX_OK;
@@ -204,7 +192,6 @@ static int alloc_slot_buffers(gsx_ctx *c, int k) {
   GSX_CUDA(cudaMalloc(&s.p.gacc, n * 12 * sizeof(float)));
   GSX_CUDA(cudaMalloc(&s.p.ckey, n * sizeof(uint32_t)));
   GSX_CUDA(cudaMalloc(&s.p.cid, n * sizeof(uint32_t)));
-  GSX_CUDA(cudaMalloc(&s.p.crec, n * 4 * sizeof(float4)));
   s.p.ccount = c->d_ccount + k;
   s.pb.key_a = s.p.ckey; s.pb.val_a = s.p.cid;
   s.pb.over_flag = c->h_over;
@@ -227,7 +214,7 @@ static int alloc_slot_buffers(gsx_ctx *c, int k) {
 }
 static void release_slot(gsx_slot &s) {   // cudaFree(nullptr) is a no-op
   cudaFree(s.p.r0); cudaFree(s.p.r1); cudaFree(s.p.r2); cudaFree(s.p.radius); cudaFree(s.p.depth); cudaFree(s.p.mask);
-  cudaFree(s.p.touched); cudaFree(s.p.gacc); cudaFree(s.p.ckey); cudaFree(s.p.cid); cudaFree(s.p.crec);
+  cudaFree(s.p.touched); cudaFree(s.p.gacc); cudaFree(s.p.ckey); cudaFree(s.p.cid);
   cudaFree(s.pb.key_b); cudaFree(s.pb.val_b); cudaFree(s.pb.offsets); cudaFree(s.pb.block_sums); cudaFree(s.pb.total);
   cudaFree(s.pb.sort_ws);
   if (s.ev_pre) cudaEventDestroy(s.ev_pre);
@@ -257,9 +244,6 @@ static int issue_emit_sort(gsx_ctx *c, int k, int N, cudaStream_t st, cudaEvent_
   const gsx_view_t &v = s.view;
   const int ntx = (v.width + 15) / 16, nty = (v.height + 15) / 16;
   b.owner = k;
-  if (!bin_v1())
-    return bin_scan_emit_sort_impl(s.p.crec, ntx, nty, N, c->capacity, b.ws, c->L, s.pb, b.se_status, b.ranges, &b.sorted_tiles,
-                                   &b.sorted_vals, st, ev, (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0);
   return bin_emit_sort_impl((const float *)s.p.r0, 4, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, b.ws, c->L, s.pb, b.ranges,
                             &b.sorted_tiles, &b.sorted_vals, st, ev, (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0);
 }
@@ -318,10 +302,9 @@ static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
   return rc;
 }
 
-// depth sort (+ tie fix-up) of the slot's compacted list; v1 also scans the tile counts here
+// depth sort (+ tie fix-up) of the slot's compacted list and the scan of the tile counts in depth order
 static int prebin(gsx_ctx *c, gsx_slot &s, int N, cudaStream_t st) {
-  if (bin_v1()) return bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, st, c->capacity);
-  return bin_prebin_sort_only(s.p.touched, N, s.p.ccount, &s.pb, st);
+  return bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, st, c->capacity);
 }
 
 static int check_view(gsx_ctx *c, const gsx_view_t *v, const gsx_params_t *p, int N) {
@@ -383,7 +366,7 @@ int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (!c) return GSX_OK;
   for (int k = 0; k < GSX_MAX_BATCH; ++k) free_slot(c->slot[k]);
   cudaDeviceSynchronize();
-  for (BinSet &b : c->bset) { if (b.ws) cudaFree(b.ws); if (b.ranges) cudaFree(b.ranges); if (b.se_status) cudaFree(b.se_status); }
+  for (BinSet &b : c->bset) { if (b.ws) cudaFree(b.ws); if (b.ranges) cudaFree(b.ranges); }
   if (c->key64) cudaFree(c->key64); cudaFree(c->image); cudaFree(c->wpp); cudaFree(c->spp);
   for (int k = 0; k < GSX_MAX_BATCH; ++k) {
     if (c->grad_stage[k]) cudaFree(c->grad_stage[k]);
@@ -471,7 +454,6 @@ int gsx_batch_reserve(gsx_ctx_t *c, int n_slots) {
   if (c->n_slots > 1 && !c->bset[1].ws) {        // second instance-buffer set for the binning pipeline
     GSX_CUDA(cudaMalloc(&c->bset[1].ws, c->L.bytes));
     GSX_CUDA(cudaMalloc(&c->bset[1].ranges, sizeof(int) * (size_t)(c->n_px_tiles + 1)));
-    GSX_CUDA(cudaMalloc(&c->bset[1].se_status, scan_emit_status_bytes(c->max_n)));
   }
   return GSX_OK;
 }

@@ -152,7 +152,6 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     TileRange tr{0, -1, 0, -1};
     int cnt = 0;
     float zc = 0.0f;
-    float4 recA = make_float4(0.f, 0.f, 0.f, 0.f), recB = make_float4(0.f, 0.f, 0.f, 1.f);
     if (active) {
       const float px = s_g[0 * BB + g], py = s_g[1 * BB + g], pz = s_g[2 * BB + g];
       float sig[6];
@@ -174,7 +173,6 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
         if (vc.tight) clip_range_to_extent(tr, uv.x, uv.y, ext.x, ext.y);
       }
       const float3 rgb = sh_to_rgb<L>(px, py, pz, vc.campos, b0, L > 0 ? s_sh + g * SHF : nullptr);
-      recA = make_float4(uv.x, uv.y, ext.x, ext.y); recB = rad;
       sp.r0[gi] = make_float4(uv.x, uv.y, ext.x, ext.y);
       sp.r1[gi] = make_float4(con[0], con[1], con[2], opa);
       sp.r2[gi] = make_float4(rgb.x, rgb.y, rgb.z, opa * (1.0f - opa));
@@ -212,8 +210,6 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       const int pos = basep + __popc(peers & ((1u << lane) - 1u));
       sp.ckey[pos] = min(float_sort_bits(zc), 0xfffffffeu);
       sp.cid[pos] = (uint32_t)gi;
-      float4 *cr = sp.crec + 4 * (size_t)gi;   // what the emission kernel needs of this Gaussian, in one 64-byte line
-      cr[0] = recA; cr[1] = recB; cr[2] = make_float4(__int_as_float(cnt), 0.f, 0.f, 0.f);
     }
   }
 }

@@ -91,12 +91,36 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
                                                  const int *__restrict__ touched, const int *__restrict__ offsets,
                                                  int ntx, int nty, int N_host, const int *__restrict__ n_dev,
                                                  const int *__restrict__ total, long long capacity,
-                                                 uint32_t *__restrict__ tiles, uint32_t *__restrict__ vals, int tight) {
+                                                 uint32_t *__restrict__ tiles, uint32_t *__restrict__ vals, int tight,
+                                                 unsigned *__restrict__ hist, int bits0, int bits1) {
+  // hist (optional): the per-pass digit histograms of the tile sort that follows ([pass][256], pass p = tile-id bits
+  // [8p, 8p + 8)), accumulated here so that the sort does not re-read the 4 K bytes of keys.  The low digit of the tile ids
+  // of a warp's instances is spread over the bins (shared-memory atomics); the HIGH digit is the same for almost every
+  // instance of a Gaussian (it changes every 256 / n_tiles_x tile rows), so it is run-length counted in registers.
+  __shared__ unsigned s_hist[2 * 256];
+  if (hist) { s_hist[threadIdx.x] = 0; s_hist[threadIdx.x + 256] = 0; __syncthreads(); }
+  const unsigned m0 = (1u << bits0) - 1u;
+  unsigned run_bin = 0xffffffffu, run_cnt = 0;
+  auto count_tile = [&](uint32_t t) {
+    atomicAdd(&s_hist[t & m0], 1u);
+    if (bits1 > 0) {
+      const unsigned hb = t >> 8;
+      if (hb != run_bin) { if (run_cnt) atomicAdd(&s_hist[256 + run_bin], run_cnt); run_bin = hb; run_cnt = 0; }
+      ++run_cnt;
+    }
+  };
+  auto flush_hist = [&]() {
+    if (!hist) return;
+    if (run_cnt) atomicAdd(&s_hist[256 + run_bin], run_cnt);
+    __syncthreads();
+    if (s_hist[threadIdx.x]) atomicAdd(&hist[threadIdx.x], s_hist[threadIdx.x]);
+    if (bits1 > 0 && s_hist[256 + threadIdx.x]) atomicAdd(&hist[256 + threadIdx.x], s_hist[256 + threadIdx.x]);
+  };
   const int j = blockIdx.x * kBlock + threadIdx.x;
   const int lane = threadIdx.x & 31;
   // total[1] = live instance count: 0 when the view has no instances OR when K exceeds the capacity (the scan flags the
   // overflow; nothing is emitted, sorted or composited for such a view, so no stale id is ever dereferenced)
-  if (total[1] == 0) return;
+  if (total[1] == 0) return;   // block-uniform
   const int N = n_dev ? min(*n_dev, N_host) : N_host;
   bool live = j < N && dkeys[j] != 0xffffffffu;
   int i = 0, cnt = 0;
@@ -113,149 +137,15 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
     r = radius[i];
     live = cnt > 0 && o + cnt <= capacity;   // overflow: detected by the host through the total
   }
-  if (!__any_sync(0xffffffffu, live)) return;
-  ObbSat s{};
-  TileRange tr{0, -1, 0, -1};
-  if (live) {
-    const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
-    s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
-    tr = sat_aabb_range(s, w);
-    // contributing-only lists (view-level path, uv_stride 4: the record is {u, v, extent_x, extent_y})
-    if (tight) clip_range_to_extent(tr, u, v, ex, ey);
-  }
-  const bool big = live && rect_cells(tr) > COOP_CELLS;
-  if (live && !big) {
-    for (int tx = tr.x0; tx <= tr.x1; ++tx) {
-      const SatCol col = sat_col(s, tx);
-      for (int ty = tr.y0; ty <= tr.y1; ++ty)
-        if (sat_cell(s, col, ty)) {
-          tiles[o] = (uint32_t)(ty * ntx + tx);
-          vals[o] = (uint32_t)i;
-          ++o;
-        }
-    }
-  }
-  unsigned bm = __ballot_sync(0xffffffffu, big);
-  while (bm) {
-    const int leader = __ffs(bm) - 1;
-    bm &= bm - 1;
-    long long ol = __shfl_sync(0xffffffffu, o, leader);
-    const uint32_t il = (uint32_t)__shfl_sync(0xffffffffu, i, leader);
-    coop_tile_rect(leader, s, tr, [&](bool hit, unsigned ballot, int tx, int ty) {
-      if (hit) {
-        const long long pos = ol + __popc(ballot & ((1u << lane) - 1u));
-        tiles[pos] = (uint32_t)(ty * ntx + tx);
-        vals[pos] = il;
-      }
-      ol += __popc(ballot);
-    });
-  }
-}
-
-// ---- fused scan + emission (view-level path, round 2) -------------------------------------------------------------------
-// One kernel replaces k_scan_reduce + k_scan_block_sums + k_scan_apply + k_emit + the tile sort's k_histogram: thread j takes
-// the j-th Gaussian in depth order, fetches its 64-byte binning record (ONE gather: centre, extent, radii, rotation, tile
-// count -- the three separate gathers of k_emit and the two of the scan kernels moved 3x the algorithmic bytes, ncu r1),
-// the exclusive scan of the counts runs inside the kernel (block scan + decoupled look-back over 64-bit status words,
-// tiles ordered by an atomic ticket so a tile only waits on tiles already resident), instances are emitted in depth order,
-// and the digit histograms of the emitted tile ids are accumulated on the way for the radix sort that follows.
-constexpr unsigned long long SE_AGG = 1ull << 62, SE_INC = 2ull << 62, SE_VAL = (1ull << 62) - 1;
-__device__ __forceinline__ unsigned long long ld_volatile64(const unsigned long long *p) {
-  unsigned long long v;
-  asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p));
-  return v;
-}
-__device__ __forceinline__ void st_volatile64(unsigned long long *p, unsigned long long v) {
-  asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-
-__global__ void __launch_bounds__(kBlock) k_scan_emit(const float4 *__restrict__ crec, const uint32_t *__restrict__ perm,
-                                                      int ntx, int nty, int N_host, const int *__restrict__ n_dev,
-                                                      long long capacity, uint32_t *__restrict__ tiles,
-                                                      uint32_t *__restrict__ vals, int tight,
-                                                      unsigned long long *__restrict__ status, unsigned *__restrict__ ticket,
-                                                      int *__restrict__ total, int *over_flag, unsigned *__restrict__ hist,
-                                                      int bits0, int bits1) {
-  __shared__ unsigned s_tile;
-  __shared__ long long s_prefix;
-  __shared__ int s_warp[kBlock / 32];
-  __shared__ unsigned s_hist[2 * 256];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-  s_hist[tid] = 0; s_hist[tid + 256] = 0;
-  __syncthreads();
-  const unsigned tile = s_tile;
-  const int n = n_dev ? min(*n_dev, N_host) : N_host;
-  const int ntiles = max(1, (n + kBlock - 1) / kBlock);
-  if ((int)tile >= ntiles) return;
-  const int j = (int)tile * kBlock + tid;
-  bool live = j < n;
-  int i = 0, cnt = 0;
-  float4 A = make_float4(0.f, 0.f, 0.f, 0.f), B = make_float4(0.f, 0.f, 0.f, 1.f);
-  if (live) {
-    i = (int)perm[j];
-    const float4 *r = crec + 4 * (size_t)i;
-    A = __ldg(r); B = __ldg(r + 1);
-    cnt = __float_as_int(__ldg(r + 2).x);
-  }
-  // block-exclusive scan of the counts
-  int incl = cnt;
-#pragma unroll
-  for (int off = 1; off < 32; off <<= 1) {
-    const int t = __shfl_up_sync(0xffffffffu, incl, off);
-    if (lane >= off) incl += t;
-  }
-  if (lane == 31) s_warp[warp] = incl;
-  __syncthreads();
-  int wbase = 0, tile_sum = 0;
-#pragma unroll
-  for (int w = 0; w < kBlock / 32; ++w) { const int t = s_warp[w]; if (w < warp) wbase += t; tile_sum += t; }
-  // decoupled look-back (warp 0): 32 predecessors per round trip
-  if (warp == 0) {
-    long long excl = 0;
-    if (tile > 0) {
-      if (lane == 0) st_volatile64(status + tile, SE_AGG | (unsigned long long)tile_sum);
-      long long t = (long long)tile - 1;
-      while (true) {
-        const long long idx = t - lane;
-        const unsigned long long wd = idx >= 0 ? ld_volatile64(status + idx) : SE_INC;
-        const unsigned flag = (unsigned)(wd >> 62);
-        const unsigned inc = __ballot_sync(0xffffffffu, flag == 2u), none = __ballot_sync(0xffffffffu, flag == 0u);
-        const int first_inc = inc ? __ffs(inc) - 1 : 32;
-        const unsigned need = first_inc < 31 ? ((2u << first_inc) - 1u) : 0xffffffffu;   // lanes 0 .. first_inc
-        if (none & need) continue;                                                       // a nearer predecessor has not published yet
-        long long v = (lane <= first_inc) ? (long long)(wd & SE_VAL) : 0;
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
-        excl += v;
-        if (first_inc < 32) break;
-        t -= 32;
-      }
-    }
-    if (lane == 0) {
-      st_volatile64(status + tile, SE_INC | (unsigned long long)(excl + tile_sum));
-      s_prefix = excl;
-      if ((int)tile == ntiles - 1) {   // the last tile knows K
-        const long long K = excl + tile_sum;
-        const bool over = capacity > 0 && K > capacity;
-        total[0] = (int)min(K, (long long)INT_MAX);
-        total[1] = over ? 0 : (int)K;   // live count: an overflowed view sorts and composites nothing
-        if (over && over_flag && (int)min(K, (long long)INT_MAX) > *(volatile int *)over_flag) *(volatile int *)over_flag = (int)min(K, (long long)INT_MAX);
-      }
-    }
-  }
-  __syncthreads();
-  long long o = s_prefix + wbase + incl - cnt;
-  live = live && cnt > 0 && o + cnt <= capacity;
-  const unsigned m0 = (1u << bits0) - 1u, m1 = bits1 > 0 ? (1u << bits1) - 1u : 0u;
   if (__any_sync(0xffffffffu, live)) {
     ObbSat s{};
     TileRange tr{0, -1, 0, -1};
     if (live) {
-      const TileWindow w = candidate_window(A.x, A.y, B.x, ntx, nty);
-      s = obb_sat_setup(compute_obb(A.x, A.y, B.x, B.y, B.z, B.w));
+      const TileWindow w = candidate_window(u, v, r.x, ntx, nty);
+      s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
       tr = sat_aabb_range(s, w);
-      if (tight) clip_range_to_extent(tr, A.x, A.y, A.z, A.w);
+      // contributing-only lists (view-level path, uv_stride 4: the record is {u, v, extent_x, extent_y})
+      if (tight) clip_range_to_extent(tr, u, v, ex, ey);
     }
     const bool big = live && rect_cells(tr) > COOP_CELLS;
     if (live && !big) {
@@ -267,7 +157,7 @@ __global__ void __launch_bounds__(kBlock) k_scan_emit(const float4 *__restrict__
             tiles[o] = t;
             vals[o] = (uint32_t)i;
             ++o;
-            if (hist) { atomicAdd(&s_hist[t & m0], 1u); if (bits1 > 0) atomicAdd(&s_hist[256 + ((t >> 8) & m1)], 1u); }
+            if (hist) count_tile(t);
           }
       }
     }
@@ -283,17 +173,13 @@ __global__ void __launch_bounds__(kBlock) k_scan_emit(const float4 *__restrict__
           const uint32_t t = (uint32_t)(ty * ntx + tx);
           tiles[pos] = t;
           vals[pos] = il;
-          if (hist) { atomicAdd(&s_hist[t & m0], 1u); if (bits1 > 0) atomicAdd(&s_hist[256 + ((t >> 8) & m1)], 1u); }
+          if (hist) count_tile(t);
         }
         ol += __popc(ballot);
       });
     }
   }
-  if (hist) {
-    __syncthreads();
-    if (s_hist[tid]) atomicAdd(&hist[tid], s_hist[tid]);
-    if (bits1 > 0 && s_hist[256 + tid]) atomicAdd(&hist[256 + tid], s_hist[256 + tid]);
-  }
+  flush_hist();
 }
 
 // Compacted depth keys arrive in nondeterministic order (atomic append, batch.cu), so Gaussians with EQUAL depth bits
@@ -504,63 +390,19 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
   uint32_t *ka = (uint32_t *)(ws + L.keys_a), *kb = (uint32_t *)(ws + L.keys_b);
   uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
   int in_b = 0, rc;
-  if (N > 0) {
-    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, pb.dkeys, pb.perm, touched, pb.offsets, ntx, nty, N,
-                                                   pb.count, pb.total, capacity, ka, va, (tight && uv_stride == 4) ? 1 : 0);
-    GSX_LAUNCH_CHECK();
-  }
-  if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
-  rc = sort_pairs_u32_impl(ka, kb, va, vb, capacity, pb.total + 1, tile_key_bits(ntx * nty) - 32, ws + L.sort_ws, L.sort_ws_bytes, st,
-                           &in_b, 0);
-  if (rc != GSX_OK) return rc;
-  *sorted_tiles = in_b ? kb : ka;
-  *sorted_vals = in_b ? vb : va;
-  if (ev) GSX_CUDA(cudaEventRecord(ev[1], st));
-  rc = tile_ranges_u32_impl(*sorted_tiles, capacity, pb.total + 1, ntx * nty, ranges, st);
-  if (ev) GSX_CUDA(cudaEventRecord(ev[2], st));
-  return rc;
-}
-
-// ---- view-level path, round 2: depth sort + tie fix-up only (no scan), then the fused scan + emission, tile sort with the
-// histograms the emission accumulated, ranges.  se_status: (N / 256 + 2) 64-bit words + a ticket, zeroed here.
-int bin_prebin_sort_only(const int *touched, int N, const int *ccount, PreBin *pb, cudaStream_t st) {
-  int in_b = 0;
-  pb->perm = nullptr; pb->dkeys = nullptr; pb->count = ccount;
-  if (N <= 0) return GSX_OK;
-  (void)touched;
-  int rc = sort_pairs_u32_impl(pb->key_a, pb->key_b, pb->val_a, pb->val_b, N, pb->count, 32, pb->sort_ws, pb->sort_ws_bytes, st, &in_b, 0);
-  if (rc != GSX_OK) return rc;
-  uint32_t *sk = in_b ? pb->key_b : pb->key_a, *sv = in_b ? pb->val_b : pb->val_a;
-  k_fix_ties<<<ceil_div(N, kBlock), kBlock, 0, st>>>(sk, sv, N, ccount);
-  GSX_LAUNCH_CHECK();
-  pb->perm = sv; pb->dkeys = sk;
-  return GSX_OK;
-}
-size_t scan_emit_status_bytes(int N) { return align_up(sizeof(unsigned long long) * ((size_t)ceil_div(std::max(N, 1), kBlock) + 2), 256) + 256; }
-
-int bin_scan_emit_sort_impl(const float4 *crec, int ntx, int nty, int N, long long capacity, char *ws, const BinLayout &L,
-                            const PreBin &pb, void *se_status, int *ranges, const uint32_t **sorted_tiles,
-                            const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev, int tight) {
-  uint32_t *ka = (uint32_t *)(ws + L.keys_a), *kb = (uint32_t *)(ws + L.keys_b);
-  uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
-  int in_b = 0, rc;
   const int key_bits = tile_key_bits(ntx * nty) - 32;
-  const bool fuse_hist = key_bits <= 16;
+  const bool fuse_hist = key_bits <= 16 && !getenv("GSX_NO_FUSED_HIST");
   if (N > 0) {
-    const size_t sb = scan_emit_status_bytes(N);
-    GSX_CUDA(cudaMemsetAsync(se_status, 0, sb, st));
-    unsigned long long *status = (unsigned long long *)se_status;
-    unsigned *ticket = (unsigned *)((char *)se_status + sb - 256);
+    // the tile sort's digit histograms are accumulated by the emission kernel (tile ids of up to 16 bits: 65536 tiles)
     if (fuse_hist) {
       rc = sort_prepare_impl(capacity, key_bits, ws + L.sort_ws, L.sort_ws_bytes, st);
       if (rc != GSX_OK) return rc;
     }
-    k_scan_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(crec, pb.perm, ntx, nty, N, pb.count, capacity, ka, va, tight, status, ticket,
-                                                       pb.total, pb.over_flag, fuse_hist ? sort_hist_impl(ws + L.sort_ws) : nullptr,
-                                                       std::min(key_bits, 8), std::max(key_bits - 8, 0));
+    k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, pb.dkeys, pb.perm, touched, pb.offsets, ntx, nty, N,
+                                                   pb.count, pb.total, capacity, ka, va, (tight && uv_stride == 4) ? 1 : 0,
+                                                   fuse_hist ? sort_hist_impl(ws + L.sort_ws) : nullptr, std::min(key_bits, 8),
+                                                   std::max(key_bits - 8, 0));
     GSX_LAUNCH_CHECK();
-  } else {
-    GSX_CUDA(cudaMemsetAsync(pb.total, 0, 2 * sizeof(int), st));
   }
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
   rc = sort_pairs_u32_impl(ka, kb, va, vb, capacity, pb.total + 1, key_bits, ws + L.sort_ws, L.sort_ws_bytes, st, &in_b,

@@ -40,8 +40,6 @@ struct SlotPtrs {
   int *touched;
   float4 *gacc;   // [N][3] float4
   uint32_t *ckey, *cid;   // [N] depth bits / ids of the Gaussians touching a tile, compacted (unordered)
-  float4 *crec;           // [N][4] binning record of a Gaussian with instances, one 64-byte line: {u, v, ex, ey} {r_major,
-                          // r_minor, sin, cos} {count (int bits), -, -, -} {-}: ONE gather per Gaussian in the emission kernel
   int *ccount;            // device int: how many
 };
 

@@ -34,18 +34,19 @@ constexpr uint32_t FLAG_AGG = 1u << 30, FLAG_INC = 2u << 30, FLAG_MASK = 3u << 3
 // uses 384-512 threads x ~20 keys, tuning_radix_sort.cuh:92-160).  GSX_RS_CFG=0..3 selects one at run time for A/B runs.
 struct RsCfg { int threads, ipt; };
 constexpr RsCfg kRsCfg[4] = {{256, 16}, {512, 16}, {384, 20}, {512, 12}};
-#ifndef GSX_RS_DEFAULT_CFG
-#define GSX_RS_DEFAULT_CFG 0
-#endif
-static int rs_cfg() {
-  static const int c = [] {
+// Measured on B200 against CUB Policy1000 on the C4 keys (profiles/r2b_*sort_vs_cub*): 4-byte keys, 20.9 M pairs: 512 x 16
+// is the fastest shape; 2.7 M pairs (one wave of tiles, latency-bound): 512 x 12; 8-byte keys: 256 x 16.
+static int rs_cfg(int key_bytes, long long n) {
+  static const int forced = [] {
     const char *e = getenv("GSX_RS_CFG");
-    const int v = e ? atoi(e) : GSX_RS_DEFAULT_CFG;
-    return (v >= 0 && v < 4) ? v : GSX_RS_DEFAULT_CFG;
+    const int v = e ? atoi(e) : -1;
+    return (v >= 0 && v < 4) ? v : -1;
   }();
-  return c;
+  if (forced >= 0) return forced;
+  if (key_bytes == 8) return 0;
+  return n > 6000000 ? 1 : 3;
 }
-static int rs_tile() { return kRsCfg[rs_cfg()].threads * kRsCfg[rs_cfg()].ipt; }
+static int rs_tile(int key_bytes, long long n) { const int c = rs_cfg(key_bytes, n); return kRsCfg[c].threads * kRsCfg[c].ipt; }
 
 __device__ __forceinline__ long long live_count(const int *n_dev, long long n) {
   if (n_dev) { const long long v = *n_dev; return v < n ? v : n; }
@@ -324,10 +325,14 @@ static int launch_onesweep(int tiles, const KeyT *kin, KeyT *kout, const uint32_
 // histograms into sort_hist_impl() itself (the emission kernel does, binning.cu): no memset, no histogram pass here.
 template <typename KeyT>
 static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n, const int *n_dev,
-                        int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags) {
+                        int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags,
+                        KeyT *first_k = nullptr, uint32_t *first_v = nullptr) {
   if (key_bits < 1 || key_bits > (int)sizeof(KeyT) * 8) { set_error("key_bits %d out of range", key_bits); return GSX_E_ARG; }
   const int passes = (key_bits + 7) / 8;
-  *result_in_b = passes & 1;
+  // With an even number of passes the ping-pong a -> b -> a ends in a.  first_k / first_v (a third buffer): the first pass
+  // writes there instead, and the remaining odd number of passes ends in b (what CUB's temp storage does for SortPairs).
+  const bool via_third = first_k && first_v && !(passes & 1);
+  *result_in_b = via_third ? 1 : (passes & 1);
   if (n <= 0) return GSX_OK;
   const SortLayout L = sort_layout(n);
   if (workspace_bytes < L.total) { set_error("sort workspace %zu < %zu", workspace_bytes, L.total); return GSX_E_WORKSPACE; }
@@ -335,7 +340,7 @@ static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *
   unsigned *hist = (unsigned *)(ws + L.hist_off);
   unsigned *ticket = (unsigned *)(ws + L.ticket_off);
   unsigned *status = (unsigned *)(ws + L.status_off);
-  const int cfg = rs_cfg();
+  const int cfg = rs_cfg((int)sizeof(KeyT), n);
   const int tile = kRsCfg[cfg].threads * kRsCfg[cfg].ipt;
   const int tiles = (int)((n + tile - 1) / tile);
   if (!(flags & 1)) {
@@ -346,8 +351,8 @@ static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *
   }
   k_scan_histogram<<<passes, RADIX, 0, st>>>(hist);
   GSX_LAUNCH_CHECK();
-  KeyT *kin = keys_a, *kout = keys_b;
-  uint32_t *vin = vals_a, *vout = vals_b;
+  KeyT *kin = keys_a, *kout = via_third ? first_k : keys_b;
+  uint32_t *vin = vals_a, *vout = via_third ? first_v : vals_b;
   for (int p = 0; p < passes; ++p) {
     const int bits = std::min(8, key_bits - 8 * p);
     unsigned *stp = status + (size_t)p * tiles * RADIX;
@@ -359,8 +364,9 @@ static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *
       default: rc = launch_onesweep<KeyT, 256, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st); break;
     }
     if (rc != GSX_OK) return rc;
-    std::swap(kin, kout);
-    std::swap(vin, vout);
+    if (via_third && p == 0) { kin = first_k; vin = first_v; kout = keys_b; vout = vals_b; }
+    else if (via_third && p == 1) { kin = keys_b; vin = vals_b; kout = keys_a; vout = vals_a; }
+    else { std::swap(kin, kout); std::swap(vin, vout); }
   }
   return GSX_OK;
 }
@@ -371,7 +377,7 @@ int sort_prepare_impl(long long n, int key_bits, void *workspace, size_t workspa
   const SortLayout L = sort_layout(n);
   if (workspace_bytes < L.total) { set_error("sort workspace %zu < %zu", workspace_bytes, L.total); return GSX_E_WORKSPACE; }
   const int passes = (key_bits + 7) / 8;
-  const int tiles = (int)((n + rs_tile() - 1) / rs_tile());
+  const int tiles = (int)((n + rs_tile(4, n) - 1) / rs_tile(4, n));   // SORT_HIST_READY callers sort 4-byte keys
   GSX_CUDA(cudaMemsetAsync(workspace, 0, L.status_off + sizeof(unsigned) * (size_t)passes * tiles * RADIX, st));
   return GSX_OK;
 }
@@ -411,38 +417,47 @@ size_t sort_workspace_bytes_impl(long long n) { return sort_layout(n).total; }
 
 using namespace gsx;
 
+template <typename KeyT>
+static int sort_pairs_public(KeyT *keys_in, KeyT *keys_out, uint32_t *vals_in, uint32_t *vals_out, long long n, const int *n_dev,
+                             int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st) {
+  int in_b = 0;
+  const size_t base = align_up(sort_workspace_bytes_impl(n), 256);
+  const size_t kb = align_up((size_t)std::max<long long>(n, 1) * sizeof(KeyT), 256), vb = align_up((size_t)std::max<long long>(n, 1) * 4, 256);
+  KeyT *tk = nullptr;
+  uint32_t *tv = nullptr;
+  if (workspace_bytes >= base + kb + vb) { tk = (KeyT *)((char *)workspace + base); tv = (uint32_t *)((char *)workspace + base + kb); }
+  int rc = sort_pairs_t<KeyT>(keys_in, keys_out, vals_in, vals_out, n, n_dev, key_bits, workspace, workspace_bytes, st, &in_b, 0, tk, tv);
+  if (rc != GSX_OK) return rc;
+  if (!in_b && n > 0) {   // even number of passes and no room for the third buffer: copy to the documented output
+    GSX_CUDA(cudaMemcpyAsync(keys_out, keys_in, sizeof(KeyT) * n, cudaMemcpyDeviceToDevice, st));
+    GSX_CUDA(cudaMemcpyAsync(vals_out, vals_in, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, st));
+  }
+  return GSX_OK;
+}
+
 extern "C" {
 
-size_t gsx_sort_workspace_bytes(long long n) { return sort_workspace_bytes_impl(n); }
+// internal state + room for a third (key, value) buffer of n 8-byte keys: with it an even number of passes needs no final
+// copy into keys_out (smaller workspaces still work: the result is then copied)
+size_t gsx_sort_workspace_bytes(long long n) {
+  return align_up(sort_workspace_bytes_impl(n), 256) + align_up((size_t)std::max<long long>(n, 1) * 8, 256) +
+         align_up((size_t)std::max<long long>(n, 1) * 4, 256);
+}
 
 int gsx_sort_pairs_u64(uint64_t *keys_in, uint64_t *keys_out, uint32_t *vals_in, uint32_t *vals_out, long long n,
                        const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, void *stream) {
   GSX_REQUIRE_DEV(keys_in); GSX_REQUIRE_DEV(keys_out); GSX_REQUIRE_DEV(vals_in); GSX_REQUIRE_DEV(vals_out);
   GSX_REQUIRE_DEV(workspace);
-  int in_b = 0;
-  int rc = sort_pairs_impl(keys_in, keys_out, vals_in, vals_out, n, n_dev, key_bits, workspace, workspace_bytes,
-                           (cudaStream_t)stream, &in_b);
-  if (rc != GSX_OK) return rc;
-  if (!in_b && n > 0) {   // even number of passes: result is in keys_in -> copy to the documented output
-    GSX_CUDA(cudaMemcpyAsync(keys_out, keys_in, sizeof(uint64_t) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
-    GSX_CUDA(cudaMemcpyAsync(vals_out, vals_in, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
-  }
-  return GSX_OK;
+  return sort_pairs_public<uint64_t>(keys_in, keys_out, vals_in, vals_out, n, n_dev, key_bits, workspace, workspace_bytes,
+                                     (cudaStream_t)stream);
 }
 
 int gsx_sort_pairs_u32(uint32_t *keys_in, uint32_t *keys_out, uint32_t *vals_in, uint32_t *vals_out, long long n,
                        const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, void *stream) {
   GSX_REQUIRE_DEV(keys_in); GSX_REQUIRE_DEV(keys_out); GSX_REQUIRE_DEV(vals_in); GSX_REQUIRE_DEV(vals_out);
   GSX_REQUIRE_DEV(workspace);
-  int in_b = 0;
-  int rc = sort_pairs_u32_impl(keys_in, keys_out, vals_in, vals_out, n, n_dev, key_bits, workspace, workspace_bytes,
-                               (cudaStream_t)stream, &in_b, 0);
-  if (rc != GSX_OK) return rc;
-  if (!in_b && n > 0) {   // even number of passes: result is in keys_in -> copy to the documented output
-    GSX_CUDA(cudaMemcpyAsync(keys_out, keys_in, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
-    GSX_CUDA(cudaMemcpyAsync(vals_out, vals_in, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
-  }
-  return GSX_OK;
+  return sort_pairs_public<uint32_t>(keys_in, keys_out, vals_in, vals_out, n, n_dev, key_bits, workspace, workspace_bytes,
+                                     (cudaStream_t)stream);
 }
 
 int gsx_tile_ranges(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,

@@ -369,18 +369,17 @@ def main():
     fp32_peak = Hh.measure_fp32_tflops()
     # algorithmic work per launch (SURVEY 8d / BASELINE.md section 5)
     PB_ = 44 + 4 * D                                                # parameter / gradient bytes per Gaussian (236 at deg 3)
-    bin_v1 = os.environ.get("GSX_BIN", "v2") == "v1"
+    fused_hist = not os.environ.get("GSX_NO_FUSED_HIST")
     alg = {
         # batch kernels (one launch per batch of nv views): parameters once + per-view records / packed gradients
-        # (+ the 64-byte binning record of every Gaussian with instances, round 2)
-        "preprocess_fwd": ("hbm", PB_ * N + nv * (74 * P + 5 * (N - P) + (0 if bin_v1 else 64 * Pt))),
+        "preprocess_fwd": ("hbm", PB_ * N + nv * (74 * P + 5 * (N - P))),
         "preprocess_bwd": ("hbm", PB_ * N + nv * (4 * N + 96 * Pt) + PB_ * N),
         # over the P' Gaussians that touch a tile (compacted by the per-Gaussian kernel): 4-pass depth sort (4 + 4*16), tie
-        # fix-up (8), then v2: permutation read (4) + one 64-byte record gather per Gaussian + 8 B written per instance;
-        # v1: scan through the permutation (20) + three gathers (8 + 32) + 8 B per instance
-        "scan_emit": ("hbm", (136 * Pt + 8 * K) if bin_v1 else (144 * Pt + 8 * K)),
-        # tile sort: passes * (8 B in + 8 B out); v1 adds the histogram read (v2: accumulated by the emission kernel)
-        "sort": ("hbm", ((4 if bin_v1 else 0) + 16 * passes) * K),
+        # fix-up (8), scan through the permutation (20), emission in depth order (8 + 32) + 8 B per instance
+        "scan_emit": ("hbm", 136 * Pt + 8 * K),
+        # tile sort: passes * (8 B in + 8 B out); the digit histograms are accumulated by the emission kernel (round 2),
+        # otherwise + 4 B per key for the histogram pass
+        "sort": ("hbm", ((0 if fused_hist else 4) + 16 * passes) * K),
         "ranges": ("hbm", 4 * K + 4 * (T + 1)),
         "composite_fwd": ("fp32", 18 * Sx),
         "composite_bwd": ("fp32", 10 * Sx + 46 * Sp),
@@ -531,9 +530,9 @@ def main():
                   f"gradients (SH gradients rebuilt locally; plain allreduce would be {flat.numel() * 4 / 1e6:.0f} MB)")
     else:
         xbytes = "none (single GPU)"
-    # depth sort: histogram, digit scan, onesweep x4, tie fix-up; fused scan + emission; tile sort: digit scan, onesweep x passes;
-    # ranges; compositing x2   (v1: + 3 scan kernels + 1 histogram)
-    launches_per_view = 2 + 4 + 1 + 1 + 1 + passes + 1 + 2 + (4 if bin_v1 else 0)
+    # depth sort: histogram, digit scan, onesweep x4, tie fix-up; scan x3; emission (+ tile-sort histograms); tile sort: digit
+    # scan, onesweep x passes; ranges; compositing x2
+    launches_per_view = 2 + 4 + 1 + 3 + 1 + 1 + passes + 1 + 2 + (0 if fused_hist else 1)
     out = {
         "metric": METRIC, "value": views_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
