@@ -22,8 +22,13 @@
 //     consecutive floats of the Gaussian's packed gradient row (36 bytes, 1-2 L2 sectors): no CAS loop, no per-batch
 //     zeroing, no flush pass, no CTA barrier on the reduction path.
 // Bound: FP32 issue (no tensor cores: the path has no dense contraction).  Algorithmic work per SURVEY 8d.
+#include <stdlib.h>
+
 #include "gsx_common.cuh"
 
+#ifndef GSX_C3_DEFAULT_CTA
+#define GSX_C3_DEFAULT_CTA 128
+#endif
 #ifndef GSX_C3_BWD_MINB
 #define GSX_C3_BWD_MINB 8
 #endif
@@ -36,7 +41,6 @@ namespace {
 
 constexpr float ALPHA_MIN = 0.00392156862f;   // render.cu:74, render_backward.cu:123
 constexpr float LOG2E = 1.4426950408889634f;
-constexpr int CT = 128;                        // threads per CTA == staged entries per batch
 
 __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
 __device__ __forceinline__ float2 mul2(float2 a, float2 b) { return __fmul2_rn(a, b); }
@@ -59,11 +63,22 @@ __device__ __forceinline__ void cp_commit() { asm volatile("cp.async.commit_grou
 template <int N>
 __device__ __forceinline__ void cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-struct Ring {   // two stages of 128 records
-  float4 r0[2][CT], r1[2][CT], r2[2][CT];
+template <int NT>
+struct Ring {   // two stages of NT records (one per thread of the CTA)
+  float4 r0[2][NT], r1[2][NT], r2[2][NT];
 };
+// NT = 128: one CTA per 16x16 tile, four warps share the staged batches (CTA barriers around each batch).
+// NT = 32: one single-warp CTA per 8x8 pixel block: the warp stages its own batches of 32 records (the tile's list is then
+// fetched four times, from L2), needs no CTA barrier, terminates and retires on its own -- the scheduler back-fills the
+// slot instead of holding three idle warps until the slowest warp of the tile is done (ncu r2a: 1.35-1.45 barrier stall
+// cycles per issued instruction, warps_active 47-53 %).
+template <int NT>
+__device__ __forceinline__ void cta_sync() { if (NT == 32) __syncwarp(); else __syncthreads(); }
+template <int NT>
+__device__ __forceinline__ bool cta_all(bool p) { return NT == 32 ? p : (__syncthreads_and(p) != 0); }
 
-__device__ __forceinline__ void stage(Ring &s, int buf, int tid, int g, const float4 *__restrict__ r0,
+template <int NT>
+__device__ __forceinline__ void stage(Ring<NT> &s, int buf, int tid, int g, const float4 *__restrict__ r0,
                                       const float4 *__restrict__ r1, const float4 *__restrict__ r2) {
   if (g >= 0) {
     cp_async16(&s.r0[buf][tid], r0 + g);
@@ -85,13 +100,15 @@ __device__ __forceinline__ Quad quad_of(float dx, float a, float b, float c) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------- forward
-__global__ void __launch_bounds__(CT, GSX_C3_FWD_MINB)
+template <int NT>
+__global__ void __launch_bounds__(NT, (NT == 32 ? 32 : GSX_C3_FWD_MINB))
 k_composite_fwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, const float4 *__restrict__ r2,
                  const int *__restrict__ sorted, const int *__restrict__ ranges, int ntx, int W, int H, float bg,
                  int *__restrict__ splats_per_pixel, float *__restrict__ weight_per_pixel, float *__restrict__ image) {
-  __shared__ Ring s;
-  const int tile = blockIdx.x;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int CT = NT;
+  __shared__ Ring<NT> s;
+  const int tile = NT == 32 ? blockIdx.x >> 2 : blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = NT == 32 ? (blockIdx.x & 3) : (tid >> 5);
   const int X0 = (tile % ntx) * 16 + (warp & 1) * 8, Y0 = (tile / ntx) * 16 + (warp >> 1) * 8;
   const int px = X0 + (lane & 7), py0 = Y0 + (lane >> 3);
   const float fpx = (float)px;
@@ -117,7 +134,7 @@ k_composite_fwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, c
     stage(s, buf ^ 1, tid, b + 1 < nbatch ? id_next : -1, r0, r1, r2);
     id_next = base + 2 * CT + tid < total ? sorted[start + base + 2 * CT + tid] : -1;
     cp_wait<1>();
-    __syncthreads();
+    cta_sync<NT>();
     const int nb = min(CT, total - base);
     if (!warp_done) {
       for (int c = 0; c < nb; c += 32) {
@@ -152,7 +169,7 @@ k_composite_fwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, c
         if (__ballot_sync(0xffffffffu, !(done0 && done1)) == 0) { warp_done = true; break; }
       }
     }
-    if (__syncthreads_and(warp_done)) break;
+    if (cta_all<NT>(warp_done)) break;
   }
   cp_wait<0>();   // nothing may still be landing in shared memory when the CTA retires
   if (in0) {
@@ -170,17 +187,18 @@ k_composite_fwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, c
 // ---------------------------------------------------------------------------------------------------------------- backward
 // STATS: counts warp-hits (extent-box survivors inside the warp's range) and contributing warp-hits instead of writing
 // gradients (diagnostics for the roofline arithmetic, gsx_ctx_count_hits).
-template <bool STATS>
-__global__ void __launch_bounds__(CT, GSX_C3_BWD_MINB)
+template <bool STATS, int NT>
+__global__ void __launch_bounds__(NT, (NT == 32 ? 32 : GSX_C3_BWD_MINB))
 k_composite_bwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, const float4 *__restrict__ r2,
                  const int *__restrict__ sorted, const int *__restrict__ ranges, int ntx, int W, int H, float bg,
                  const int *__restrict__ splats_per_pixel, const float *__restrict__ weight_per_pixel,
                  const float *__restrict__ grad_image, float *__restrict__ packed, unsigned long long *__restrict__ stats) {
-  __shared__ Ring s;
+  constexpr int CT = NT;
+  __shared__ Ring<NT> s;
   __shared__ int s_ids[2][CT];
   __shared__ int s_max;
-  const int tile = blockIdx.x;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tile = NT == 32 ? blockIdx.x >> 2 : blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = NT == 32 ? (blockIdx.x & 3) : (tid >> 5);
   const int X0 = (tile % ntx) * 16 + (warp & 1) * 8, Y0 = (tile / ntx) * 16 + (warp >> 1) * 8;
   const int px = X0 + (lane & 7), py0 = Y0 + (lane >> 3);
   const float fpx = (float)px;
@@ -211,11 +229,14 @@ k_composite_bwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, c
   }
   float2 sacc = bc(0.0f);   // sum_c (colour accumulated behind the current entry)_c * g_c
   const int warp_max = __reduce_max_sync(0xffffffffu, max(count0, count1));
-  if (tid == 0) s_max = 0;
-  __syncthreads();
-  if (lane == 0 && warp_max > 0) atomicMax(&s_max, warp_max);
-  __syncthreads();
-  const int cta_max = s_max;   // render_backward.cu:74 (start index = max count - 1)
+  int cta_max = warp_max;   // render_backward.cu:74 (start index = max count - 1); a lone warp starts at its own maximum
+  if (NT != 32) {
+    if (tid == 0) s_max = 0;
+    __syncthreads();
+    if (lane == 0 && warp_max > 0) atomicMax(&s_max, warp_max);
+    __syncthreads();
+    cta_max = s_max;
+  }
 
   // after the butterfly, lane (lane & 3) == 0 holds value k = 4 b4 + 2 b3 + b2 of {r, g, b, u, v, ca, cb, cc} and lane 2 the
   // ninth (opacity); their places in the packed row {r,g,b,opa}{u,v,ca,cb}{cc}
@@ -240,7 +261,7 @@ k_composite_bwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, c
     stage(s, buf ^ 1, tid, b + 1 < nbatch ? id_next : -1, r0, r1, r2);
     id_next = id_of(b + 2);
     cp_wait<1>();
-    __syncthreads();
+    cta_sync<NT>();
     const int hi = min(top, warp_max);
     for (int chi = hi; chi > lo; chi -= 32) {
       const int j = chi - 1 - lane;   // lane 0 = farthest entry first (back to front)
@@ -330,7 +351,7 @@ k_composite_bwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, c
         if (red_lane && q2.w != 0.0f) atomicAdd(packed + (size_t)s_ids[buf][e] * 12 + red_off, a1);
       }
     }
-    __syncthreads();   // the stage is free for batch b+2
+    cta_sync<NT>();   // the stage is free for batch b+2
   }
   cp_wait<0>();
   if (STATS) {
@@ -340,10 +361,19 @@ k_composite_bwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, c
 
 }  // namespace
 
+// GSX_COMPOSITE_CTA=32 selects the single-warp CTAs (one per 8x8 pixel block), 128 the tile-per-CTA kernels
+static int cta_threads() {
+  static const int v = [] { const char *e = getenv("GSX_COMPOSITE_CTA"); const int x = e ? atoi(e) : GSX_C3_DEFAULT_CTA; return x == 32 ? 32 : 128; }();
+  return v;
+}
+
 int composite_fwd3_launch(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges, int W,
                           int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st) {
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
-  k_composite_fwd3<<<ntx * nty, CT, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, image);
+  if (cta_threads() == 32)
+    k_composite_fwd3<32><<<ntx * nty * 4, 32, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, image);
+  else
+    k_composite_fwd3<128><<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, image);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -352,8 +382,12 @@ int composite_bwd3_launch(const float4 *r0, const float4 *r1, const float4 *r2, 
                           int H, float bg, const int *spp, const float *wpp, const float *grad_image, float *packed_grads,
                           cudaStream_t st) {
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
-  k_composite_bwd3<false><<<ntx * nty, CT, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, grad_image,
-                                                    packed_grads, nullptr);
+  if (cta_threads() == 32)
+    k_composite_bwd3<false, 32><<<ntx * nty * 4, 32, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, grad_image,
+                                                            packed_grads, nullptr);
+  else
+    k_composite_bwd3<false, 128><<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, grad_image,
+                                                            packed_grads, nullptr);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -363,8 +397,8 @@ int composite_hits_launch(const float4 *r0, const float4 *r1, const float4 *r2, 
                           int H, const int *spp, const float *wpp, const float *grad_image, unsigned long long *out_dev,
                           cudaStream_t st) {
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
-  k_composite_bwd3<true><<<ntx * nty, CT, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, 0.0f, spp, wpp, grad_image, nullptr,
-                                                   out_dev);
+  k_composite_bwd3<true, 128><<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, 0.0f, spp, wpp, grad_image, nullptr,
+                                                         out_dev);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
