@@ -29,11 +29,13 @@
 #ifndef GSX_C3_DEFAULT_CTA
 #define GSX_C3_DEFAULT_CTA 128
 #endif
+// resident CTAs per SM the register allocation is capped for (measured on B200, profiles/r2c_*: backward 8 -> 10 CTAs
+// (59 -> 48 registers, 4 bytes spilled) 0.540 -> 0.518 ms, 9 CTAs 0.554; forward 8 -> 12 CTAs (50 -> 40 registers) 0.262 -> 0.260)
 #ifndef GSX_C3_BWD_MINB
-#define GSX_C3_BWD_MINB 8
+#define GSX_C3_BWD_MINB 10
 #endif
 #ifndef GSX_C3_FWD_MINB
-#define GSX_C3_FWD_MINB 8
+#define GSX_C3_FWD_MINB 12
 #endif
 
 namespace gsx {
@@ -68,10 +70,11 @@ struct Ring {   // two stages of NT records (one per thread of the CTA)
   float4 r0[2][NT], r1[2][NT], r2[2][NT];
 };
 // NT = 128: one CTA per 16x16 tile, four warps share the staged batches (CTA barriers around each batch).
-// NT = 32: one single-warp CTA per 8x8 pixel block: the warp stages its own batches of 32 records (the tile's list is then
-// fetched four times, from L2), needs no CTA barrier, terminates and retires on its own -- the scheduler back-fills the
-// slot instead of holding three idle warps until the slowest warp of the tile is done (ncu r2a: 1.35-1.45 barrier stall
-// cycles per issued instruction, warps_active 47-53 %).
+// NT = 32 (GSX_COMPOSITE_CTA=32, kept for A/B): one single-warp CTA per 8x8 pixel block: the warp stages its own batches of
+// 32 records (the tile's list is then fetched four times, from L2), needs no CTA barrier, terminates and retires on its
+// own.  Measured on B200 (profiles/r2c_*): the barrier stalls disappear (1.35 -> 0 cycles per issued instruction) but the
+// kernel executes 5 % more instructions at the same 3.1 instructions / cycle / SM: backward 0.540 -> 0.555 ms, forward
+// 0.262 -> 0.270 ms.  The tile-per-CTA shape stays the default: the kernels are bound by issue slots, not by barriers.
 template <int NT>
 __device__ __forceinline__ void cta_sync() { if (NT == 32) __syncwarp(); else __syncthreads(); }
 template <int NT>

@@ -369,7 +369,7 @@ def main():
     fp32_peak = Hh.measure_fp32_tflops()
     # algorithmic work per launch (SURVEY 8d / BASELINE.md section 5)
     PB_ = 44 + 4 * D                                                # parameter / gradient bytes per Gaussian (236 at deg 3)
-    fused_hist = not os.environ.get("GSX_NO_FUSED_HIST")
+    fused_hist = bool(os.environ.get("GSX_FUSED_HIST"))
     alg = {
         # batch kernels (one launch per batch of nv views): parameters once + per-view records / packed gradients
         "preprocess_fwd": ("hbm", PB_ * N + nv * (74 * P + 5 * (N - P))),
@@ -589,7 +589,7 @@ def main():
                 gref = dict(xyz=gd.xyz, scale=gd.scale, quaternion=gd.quaternion, opacity=gd.opacity, band0=gd.band0,
                             sh=(gd.sh.view(N, -1, 3) if gd.sh_stride else None))
                 out["ref_cuda_baseline"] = RC.replay_view(gref, cams[0], W, H, l_max, S.NEAR_THRESH, S.CULL_PADDING, S.MH_DIST,
-                                                          gi_dev, reps=2)
+                                                          gi_dev, reps=3)
                 b1 = out["ref_cuda_baseline"]
                 if "ms_per_view" in b1:
                     b1["speedup_of_this_repo"] = round(b1["ms_per_view"] / (ms_total / args.steps / N_VIEWS), 2)

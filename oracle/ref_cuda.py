@@ -263,11 +263,19 @@ def replay_view(g, cam, W, H, l_max, near, pad, mh, grad_image, reps=2):
            "sh_degree": deg, "sh": "sphericart CUDA backend (NVRTC)" if use_sh else "band 0 via torch (sphericart backend not loadable)"}
     try:
         one_view({})                                               # warm-up (NVRTC JIT, allocator)
-        acc = {}
+        runs = []
         for _ in range(reps):
+            acc = {}
             P, Cc, K = one_view(acc)
-        st = {k: round(v / reps, 4) for k, v in acc.items()}
-        out.update(P=P, coarse_pairs_C=Cc, instances_K=K, stage_ms=st, ms_per_view=round(sum(st.values()), 3),
+            runs.append(acc)
+        # the reference allocates GBs of thrust temporaries inside F7 (96 M coarse pairs) and a sphericart object per SH
+        # call: its times swing with the allocator's state, so the FASTEST replay is reported (in its favour) and the
+        # spread beside it
+        tot = [sum(r.values()) for r in runs]
+        best = runs[int(min(range(reps), key=lambda i: tot[i]))]
+        st = {k: round(v, 4) for k, v in best.items()}
+        out.update(P=P, coarse_pairs_C=Cc, instances_K=K, stage_ms=st, ms_per_view=round(min(tot), 3), replays=reps,
+                   ms_per_view_all_replays=[round(t, 3) for t in tot],
                    ms_per_view_kernels_only=round(sum(v for k, v in st.items() if not k.startswith("compaction")), 3))
     except Exception as e:                                         # e.g. out of memory in the coarse pair list
         out["error"] = repr(e)[:300]
