@@ -26,6 +26,12 @@
 
 #include "gsx_common.cuh"
 
+#ifndef GSX_C4_BWD_MINB
+#define GSX_C4_BWD_MINB 6
+#endif
+#ifndef GSX_C4_DEFAULT
+#define GSX_C4_DEFAULT 0   // measured before it becomes the default
+#endif
 #ifndef GSX_C3_DEFAULT_CTA
 #define GSX_C3_DEFAULT_CTA 128
 #endif
@@ -362,12 +368,213 @@ k_composite_bwd3(const float4 *__restrict__ r0, const float4 *__restrict__ r1, c
   }
 }
 
+
+// ------------------------------------------------------------------------------------------ backward, two-phase reduction
+// k_composite_bwd3 spends 55 of its 127 instructions per contributing warp-hit on turning 64 per-pixel partials into 9
+// per-entry sums: the moment products, a 12-shuffle / 16-select / 15-add transposing butterfly and the linear map to the
+// gradients.  Everything the 9 sums need from a pixel is TWO scalars, w = alpha T (colour gradient) and gp = dL/dpower
+// (geometry gradients); the rest are per-pixel constants (image gradient, pixel coordinates).  So:
+//   phase 1 (lane = pixel pair, per contributing hit): evaluate the entry as before, store the lane's (w, gp) pairs and the
+//            entry's 8 parameters into a per-warp shared-memory buffer of HB hits -- no cross-lane traffic at all;
+//   phase 2 (lane = (buffered hit h, pixel-row pair g), once per HB hits): the lane runs over the 8 columns of its two
+//            pixel rows accumulating sum w g_c (3), sum gp, sum gp cx, sum gp cx^2 with packed FMAs against per-pixel
+//            constants (cx = column, compile-time; cy = row, a per-lane constant, so the y-moments follow from the
+//            x-moments by three multiplies); two shuffle steps merge the four row pairs; the moments about the block origin
+//            are shifted to the entry's centre (dx = (u - X0) - cx), mapped to the gradients (render_backward.cu:154-197)
+//            and leave as two red.global.add.v4.f32 + one scalar RED per hit, 8 hits per instruction.
+// Instructions per contributing warp-hit: ~65 + ~22 instead of 127; shared memory 5.3 KB per warp.
+constexpr int HB = 8;             // buffered hits per flush (lanes: 8 hits x 4 row pairs)
+constexpr int HROW = 66;          // floats per buffered hit row: 64 + 2 -> the 8 hits of a 16-lane phase hit distinct banks
+struct WarpBuf {
+  float w[HB][HROW], gp[HB][HROW];   // [hit][2 * source lane + pixel]
+  float4 meta[HB][2];                // {u, v, conic a, b} {conic c, opa, opa (1 - opa), Gaussian id (int bits)}
+  float g[32][6];                    // per source lane: gx.x, gx.y, gy.x, gy.y, gz.x, gz.y (image gradient of its two pixels)
+};
+
+__device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+// phase 2: reduce the nbuf buffered hits of this warp and add them to the packed gradient rows
+__device__ __forceinline__ void flush_hits(WarpBuf &wb, int nbuf, int lane, float X0f, float Y0f, float half_w, float half_h,
+                                           float *__restrict__ packed) {
+  __syncwarp();
+  const int h = lane & 7, g = lane >> 3;             // buffered hit, row pair (pixel rows g and g + 4 of the 8x8 block)
+  const float2 cy = make_float2((float)g, (float)(g + 4));
+  float2 R = bc(0.f), G = bc(0.f), B = bc(0.f), S0 = bc(0.f), Sx = bc(0.f), Sxx = bc(0.f);
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {                      // source lane j = 8 g + c: column c, rows g and g + 4
+    const int j = 8 * g + c;
+    const float2 w2 = *reinterpret_cast<const float2 *>(&wb.w[h][2 * j]);
+    const float2 p2 = *reinterpret_cast<const float2 *>(&wb.gp[h][2 * j]);
+    const float2 gx = *reinterpret_cast<const float2 *>(&wb.g[j][0]);
+    const float2 gy = *reinterpret_cast<const float2 *>(&wb.g[j][2]);
+    const float2 gz = *reinterpret_cast<const float2 *>(&wb.g[j][4]);
+    R = fma2(w2, gx, R); G = fma2(w2, gy, G); B = fma2(w2, gz, B);
+    S0 = add2(S0, p2);
+    if (c > 0) { Sx = fma2(p2, bc((float)c), Sx); Sxx = fma2(p2, bc((float)(c * c)), Sxx); }
+  }
+  // the lane's two rows -> scalars (cy is constant along a row: the y-moments follow from S0 and Sx)
+  float v[9];
+  v[0] = R.x + R.y; v[1] = G.x + G.y; v[2] = B.x + B.y;
+  v[3] = S0.x + S0.y;                                 // S0
+  v[4] = Sx.x + Sx.y;                                 // Sx
+  v[5] = Sxx.x + Sxx.y;                               // Sxx
+  v[6] = cy.x * S0.x + cy.y * S0.y;                   // Sy
+  v[7] = cy.x * Sx.x + cy.y * Sx.y;                   // Sxy
+  v[8] = (cy.x * cy.x) * S0.x + (cy.y * cy.y) * S0.y; // Syy
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {                       // sum over the four row pairs (lanes h, h + 8, h + 16, h + 24)
+    v[k] += __shfl_xor_sync(0xffffffffu, v[k], 8);
+    v[k] += __shfl_xor_sync(0xffffffffu, v[k], 16);
+  }
+  if (g == 0 && h < nbuf) {
+    const float4 m0 = wb.meta[h][0], m1 = wb.meta[h][1];
+    if (m1.z != 0.0f) {   // Q7 (render_backward.cu:170): opa (1 - opa) underflowed -> the reference drops the entry
+      const float A = m0.x - X0f, Bc = m0.y - Y0f;    // entry centre relative to the block origin: dx = A - cx, dy = Bc - cy
+      const float S0_ = v[3], Sx_ = v[4], Sxx_ = v[5], Sy_ = v[6], Sxy_ = v[7], Syy_ = v[8];
+      const float gdx = A * S0_ - Sx_, gdy = Bc * S0_ - Sy_;                       // sum gp dx, sum gp dy
+      const float gdxx = A * (A * S0_ - 2.0f * Sx_) + Sxx_;                         // sum gp dx^2
+      const float gdyy = Bc * (Bc * S0_ - 2.0f * Sy_) + Syy_;                       // sum gp dy^2
+      const float gdxy = A * (Bc * S0_ - Sy_) - Bc * Sx_ + Sxy_;                    // sum gp dx dy
+      float *o = packed + (size_t)__float_as_int(m1.w) * 12;
+      red_add_v4(o, v[0], v[1], v[2], S0_ * (1.0f - m1.y));
+      red_add_v4(o + 4, (m0.z * gdx + m0.w * gdy) * -half_w, (m1.x * gdy + m0.w * gdx) * -half_h, -0.5f * gdxx, -gdxy);
+      atomicAdd(o + 8, -0.5f * gdyy);
+    }
+  }
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(128, GSX_C4_BWD_MINB)
+k_composite_bwd4(const float4 *__restrict__ r0, const float4 *__restrict__ r1, const float4 *__restrict__ r2,
+                 const int *__restrict__ sorted, const int *__restrict__ ranges, int ntx, int W, int H, float bg,
+                 const int *__restrict__ splats_per_pixel, const float *__restrict__ weight_per_pixel,
+                 const float *__restrict__ grad_image, float *__restrict__ packed) {
+  constexpr int CT = 128;
+  __shared__ Ring<CT> s;
+  __shared__ int s_ids[2][CT];
+  __shared__ int s_max;
+  __shared__ __align__(16) WarpBuf s_wb[4];
+  const int tile = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int X0 = (tile % ntx) * 16 + (warp & 1) * 8, Y0 = (tile / ntx) * 16 + (warp >> 1) * 8;
+  const int px = X0 + (lane & 7), py0 = Y0 + (lane >> 3);
+  const float fpx = (float)px;
+  const float2 nfpy = make_float2(-(float)py0, -(float)(py0 + 4));
+  const float bx0 = (float)X0, bx1 = (float)(X0 + 7), by0 = (float)Y0, by1 = (float)(Y0 + 7);
+  const int start = ranges[tile];
+  const float half_w = 0.5f * (float)W, half_h = 0.5f * (float)H;
+  WarpBuf &wb = s_wb[warp];
+
+  int count0 = 0, count1 = 0;
+  float2 T = bc(0.0f), gx = bc(0.0f), gy = bc(0.0f), gz = bc(0.0f);
+  if (px < W && py0 < H) {
+    const size_t q = (size_t)py0 * W + px;
+    count0 = splats_per_pixel[q]; T.x = weight_per_pixel[q];
+    gx.x = grad_image[3 * q]; gy.x = grad_image[3 * q + 1]; gz.x = grad_image[3 * q + 2];
+  }
+  if (px < W && py0 + 4 < H) {
+    const size_t q = (size_t)(py0 + 4) * W + px;
+    count1 = splats_per_pixel[q]; T.y = weight_per_pixel[q];
+    gx.y = grad_image[3 * q]; gy.y = grad_image[3 * q + 1]; gz.y = grad_image[3 * q + 2];
+  }
+  wb.g[lane][0] = gx.x; wb.g[lane][1] = gx.y; wb.g[lane][2] = gy.x; wb.g[lane][3] = gy.y; wb.g[lane][4] = gz.x; wb.g[lane][5] = gz.y;
+  float2 tb;   // -T_final * (bg gx + bg gy + bg gz), render_backward.cu:149-152
+  {
+    float b0 = 0.0f, b1 = 0.0f;
+    b0 += bg * gx.x; b0 += bg * gy.x; b0 += bg * gz.x;
+    b1 += bg * gx.y; b1 += bg * gy.y; b1 += bg * gz.y;
+    tb = make_float2(-T.x * b0, -T.y * b1);
+  }
+  float2 sacc = bc(0.0f);
+  const int warp_max = __reduce_max_sync(0xffffffffu, max(count0, count1));
+  if (tid == 0) s_max = 0;
+  __syncthreads();
+  if (lane == 0 && warp_max > 0) atomicMax(&s_max, warp_max);
+  __syncthreads();
+  const int cta_max = s_max;   // render_backward.cu:74
+  int nbuf = 0;                // buffered contributing hits of this warp (warp-uniform)
+
+  const int nbatch = (cta_max + CT - 1) / CT;
+  auto id_of = [&](int j) {
+    const int top = cta_max - j * CT, lo = max(0, top - CT);
+    return (j < nbatch && tid < top - lo) ? sorted[start + lo + tid] : -1;
+  };
+  int id_next = id_of(0);
+  if (nbatch > 0) { if (id_next >= 0) s_ids[0][tid] = id_next; stage(s, 0, tid, id_next, r0, r1, r2); }
+  id_next = id_of(1);
+  for (int b = 0; b < nbatch; ++b) {
+    const int buf = b & 1;
+    const int top = cta_max - b * CT, lo = max(0, top - CT);
+    if (b + 1 < nbatch && id_next >= 0) s_ids[buf ^ 1][tid] = id_next;
+    stage(s, buf ^ 1, tid, b + 1 < nbatch ? id_next : -1, r0, r1, r2);
+    id_next = id_of(b + 2);
+    cp_wait<1>();
+    __syncthreads();
+    const int hi = min(top, warp_max);
+    for (int chi = hi; chi > lo; chi -= 32) {
+      const int j = chi - 1 - lane;   // lane 0 = farthest entry first (back to front)
+      bool hit = false;
+      if (j >= lo) {
+        const float4 q = s.r0[buf][j - lo];
+        hit = !(q.x + q.z < bx0 || q.x - q.z > bx1 || q.y + q.w < by0 || q.y - q.w > by1);
+      }
+      unsigned m = __ballot_sync(0xffffffffu, hit);
+      while (m) {
+        const int idx = chi - 1 - (__ffs(m) - 1);
+        m &= m - 1;
+        const int e = idx - lo;
+        const float2 uv = *reinterpret_cast<const float2 *>(&s.r0[buf][e]);
+        const float4 q1 = s.r1[buf][e];
+        const float dx = uv.x - fpx;
+        const Quad q = quad_of(dx, q1.x, q1.y, q1.z);
+        const float2 dy = add2(bc(uv.y), nfpy);
+        const float2 p2 = fma2(dy, fma2(bc(q.hc), dy, bc(q.B)), bc(q.A));
+        const float2 au = mul2(bc(q1.w), make_float2(ex2(fminf(0.0f, p2.x)), ex2(fminf(0.0f, p2.y))));   // opa * G
+        const bool v0 = au.x >= ALPHA_MIN && idx < count0, v1 = au.y >= ALPHA_MIN && idx < count1;
+        if (!__any_sync(0xffffffffu, v0 || v1)) continue;
+        const float4 q2 = s.r2[buf][e];
+        const float2 aum = make_float2(v0 ? au.x : 0.0f, v1 ? au.y : 0.0f);
+        const float2 al = make_float2(fminf(0.99f, aum.x), fminf(0.99f, aum.y));
+        const float2 om = add2(bc(1.0f), make_float2(-al.x, -al.y));
+        const float2 iom = make_float2(rcp(om.x), rcp(om.y));
+        T = mul2(T, iom);
+        const float2 w = mul2(al, T);
+        const float2 cgd = fma2(bc(q2.z), gz, fma2(bc(q2.y), gy, mul2(bc(q2.x), gx)));
+        const float2 ga = fma2(tb, iom, mul2(add2(cgd, make_float2(-sacc.x, -sacc.y)), T));
+        sacc = fma2(om, sacc, mul2(al, cgd));
+        const float2 gp = mul2(aum, ga);
+        // phase 1 ends here: park the lane's (w, gp) pairs and the entry's parameters
+        *reinterpret_cast<float2 *>(&wb.w[nbuf][2 * lane]) = w;
+        *reinterpret_cast<float2 *>(&wb.gp[nbuf][2 * lane]) = gp;
+        if (lane < 2) wb.meta[nbuf][lane] = lane == 0 ? make_float4(uv.x, uv.y, q1.x, q1.y)
+                                                      : make_float4(q1.z, q1.w, q2.w, __int_as_float(s_ids[buf][e]));
+        if (++nbuf == HB) { flush_hits(wb, HB, lane, (float)X0, (float)Y0, half_w, half_h, packed); nbuf = 0; }
+      }
+    }
+    __syncthreads();   // the stage is free for batch b+2
+  }
+  cp_wait<0>();
+  if (nbuf > 0) flush_hits(wb, nbuf, lane, (float)X0, (float)Y0, half_w, half_h, packed);
+}
+
 }  // namespace
 
 // GSX_COMPOSITE_CTA=32 selects the single-warp CTAs (one per 8x8 pixel block), 128 the tile-per-CTA kernels
 static int cta_threads() {
   static const int v = [] { const char *e = getenv("GSX_COMPOSITE_CTA"); const int x = e ? atoi(e) : GSX_C3_DEFAULT_CTA; return x == 32 ? 32 : 128; }();
   return v;
+}
+
+// GSX_COMPOSITE_BWD=butterfly selects k_composite_bwd3 (per-hit shuffle reduction), two_phase k_composite_bwd4
+static bool bwd_two_phase() {
+  static const int v = [] {
+    const char *e = getenv("GSX_COMPOSITE_BWD");
+    if (!e) return GSX_C4_DEFAULT;
+    return e[0] == 't' ? 1 : 0;
+  }();
+  return v != 0;
 }
 
 int composite_fwd3_launch(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges, int W,
@@ -385,6 +592,11 @@ int composite_bwd3_launch(const float4 *r0, const float4 *r1, const float4 *r2, 
                           int H, float bg, const int *spp, const float *wpp, const float *grad_image, float *packed_grads,
                           cudaStream_t st) {
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
+  if (bwd_two_phase()) {
+    k_composite_bwd4<<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, grad_image, packed_grads);
+    GSX_LAUNCH_CHECK();
+    return GSX_OK;
+  }
   if (cta_threads() == 32)
     k_composite_bwd3<false, 32><<<ntx * nty * 4, 32, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, grad_image,
                                                             packed_grads, nullptr);
