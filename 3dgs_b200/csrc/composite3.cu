@@ -30,7 +30,7 @@
 #define GSX_C4_BWD_MINB 6
 #endif
 #ifndef GSX_C4_DEFAULT
-#define GSX_C4_DEFAULT 0   // measured before it becomes the default
+#define GSX_C4_DEFAULT 1   // B200, C4 (profiles/r2d_*): 453 M -> 356 M warp instructions, 0.518 -> 0.484 ms per view
 #endif
 #ifndef GSX_C3_DEFAULT_CTA
 #define GSX_C3_DEFAULT_CTA 128
@@ -401,19 +401,23 @@ __device__ __forceinline__ void flush_hits(WarpBuf &wb, int nbuf, int lane, floa
   __syncwarp();
   const int h = lane & 7, g = lane >> 3;             // buffered hit, row pair (pixel rows g and g + 4 of the 8x8 block)
   const float2 cy = make_float2((float)g, (float)(g + 4));
-  float2 R = bc(0.f), G = bc(0.f), B = bc(0.f), S0 = bc(0.f), Sx = bc(0.f), Sxx = bc(0.f);
+  // two independent accumulator sets (even / odd columns): the six chains are otherwise 8 dependent FMAs long each
+  float2 Ra[2] = {bc(0.f), bc(0.f)}, Ga[2] = {bc(0.f), bc(0.f)}, Ba[2] = {bc(0.f), bc(0.f)};
+  float2 S0a[2] = {bc(0.f), bc(0.f)}, Sxa[2] = {bc(0.f), bc(0.f)}, Sxxa[2] = {bc(0.f), bc(0.f)};
 #pragma unroll
   for (int c = 0; c < 8; ++c) {                      // source lane j = 8 g + c: column c, rows g and g + 4
-    const int j = 8 * g + c;
+    const int j = 8 * g + c, a = c & 1;
     const float2 w2 = *reinterpret_cast<const float2 *>(&wb.w[h][2 * j]);
     const float2 p2 = *reinterpret_cast<const float2 *>(&wb.gp[h][2 * j]);
     const float2 gx = *reinterpret_cast<const float2 *>(&wb.g[j][0]);
     const float2 gy = *reinterpret_cast<const float2 *>(&wb.g[j][2]);
     const float2 gz = *reinterpret_cast<const float2 *>(&wb.g[j][4]);
-    R = fma2(w2, gx, R); G = fma2(w2, gy, G); B = fma2(w2, gz, B);
-    S0 = add2(S0, p2);
-    if (c > 0) { Sx = fma2(p2, bc((float)c), Sx); Sxx = fma2(p2, bc((float)(c * c)), Sxx); }
+    Ra[a] = fma2(w2, gx, Ra[a]); Ga[a] = fma2(w2, gy, Ga[a]); Ba[a] = fma2(w2, gz, Ba[a]);
+    S0a[a] = add2(S0a[a], p2);
+    if (c > 0) { Sxa[a] = fma2(p2, bc((float)c), Sxa[a]); Sxxa[a] = fma2(p2, bc((float)(c * c)), Sxxa[a]); }
   }
+  const float2 R = add2(Ra[0], Ra[1]), G = add2(Ga[0], Ga[1]), B = add2(Ba[0], Ba[1]);
+  const float2 S0 = add2(S0a[0], S0a[1]), Sx = add2(Sxa[0], Sxa[1]), Sxx = add2(Sxxa[0], Sxxa[1]);
   // the lane's two rows -> scalars (cy is constant along a row: the y-moments follow from S0 and Sx)
   float v[9];
   v[0] = R.x + R.y; v[1] = G.x + G.y; v[2] = B.x + B.y;
