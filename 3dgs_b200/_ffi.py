@@ -32,7 +32,7 @@ SYMBOLS = [
     "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers", "gsx_adam_step", "gsx_adam_step_fused",
     "gsx_fused_loss_workspace_bytes", "gsx_fused_loss",
     "gsx_compute_morton_codes", "gsx_morton_order_workspace_bytes", "gsx_morton_order", "gsx_gather_rows", "gsx_gather_rows_multi",
-    "gsx_dp_unique_id", "gsx_dp_init", "gsx_dp_destroy", "gsx_dp_grads", "gsx_dp_step", "gsx_dp_render_host", "gsx_dp_allreduce",
+    "gsx_dp_unique_id", "gsx_dp_init", "gsx_dp_destroy", "gsx_dp_grads", "gsx_dp_step", "gsx_dp_render_host", "gsx_dp_render_host_async", "gsx_dp_allreduce",
     "gsx_dp_enable_timing", "gsx_dp_timing",
     "gsx_clone_gaussians", "gsx_split_gaussians", "gsx_densify_workspace_bytes", "gsx_densify_plan", "gsx_densify_apply",
 ]

@@ -104,6 +104,7 @@ struct gsx_dp {
   float *grad_stage[GSX_MAX_VIEWS] = {};
   float *img_stage[2] = {nullptr, nullptr};
   size_t img_bytes = 0;
+  bool dl_pending[2] = {false, false};             // a download from image stage i is (or may be) in flight
   std::vector<float> campos_slots;                 // camera positions in gather-buffer slot order
 };
 
@@ -227,7 +228,7 @@ int gsx_dp_allreduce(gsx_dp_t *d, float *buf, size_t n_floats, void *stream) {
 
 static int dp_step_impl(gsx_dp_t *d, const gsx_view_t *views_all, const gsx_params_t *p, const float *const *grad_images_dev,
                         const float *const *grad_images_host, float *const *images_host, const gsx_adam_epilogue_t *adam,
-                        cudaStream_t st) {
+                        cudaStream_t st, bool sync) {
   NvtxRange nvtx_("gsx_dp_step");
   gsx_ctx_t *c = d->ctx;
   const int N = d->N, nv = d->vpr, W = d->world;
@@ -269,7 +270,7 @@ static int dp_step_impl(gsx_dp_t *d, const gsx_view_t *views_all, const gsx_para
   if (rc != GSX_OK) return rc;
   gsx_state_t state;
   for (int k = 0; k < nv; ++k) {
-    if (host && k >= 2 && images_host && images_host[k - 2]) GSX_CUDA(cudaStreamWaitEvent(st, d->ev_dl[k & 1], 0));   // image stage k & 1 is free again
+    if (host && d->dl_pending[k & 1]) { GSX_CUDA(cudaStreamWaitEvent(st, d->ev_dl[k & 1], 0)); d->dl_pending[k & 1] = false; }   // image stage k & 1 is free again (a download of this or of the previous step)
     rc = gsx_batch_forward_view(c, k, st);
     if (rc != GSX_OK) return rc;
     if (host && images_host && images_host[k]) {   // view k's image goes back to the host while its backward runs
@@ -280,6 +281,7 @@ static int dp_step_impl(gsx_dp_t *d, const gsx_view_t *views_all, const gsx_para
       GSX_CUDA(cudaStreamWaitEvent(d->cs_out, d->ev_img, 0));
       GSX_CUDA(cudaMemcpyAsync(images_host[k], d->img_stage[k & 1], bytes, cudaMemcpyDeviceToHost, d->cs_out));
       GSX_CUDA(cudaEventRecord(d->ev_dl[k & 1], d->cs_out));
+      d->dl_pending[k & 1] = true;
     }
     const float *gi = host ? d->grad_stage[k] : grad_images_dev[k];
     if (host) GSX_CUDA(cudaStreamWaitEvent(st, d->ev_in[k], 0));
@@ -335,9 +337,13 @@ static int dp_step_impl(gsx_dp_t *d, const gsx_view_t *views_all, const gsx_para
     if (rc != GSX_OK) return rc;
   }
   if (d->timing) GSX_CUDA(cudaEventRecord(d->tm[7], st));
-  if (host) {   // never return with copies in flight
+  if (host && sync) {   // never return with copies in flight
     cudaStreamSynchronize(d->cs_in); cudaStreamSynchronize(d->cs_out);
     GSX_CUDA(cudaStreamSynchronize(st));
+    d->dl_pending[0] = d->dl_pending[1] = false;
+  } else if (host) {    // asynchronous form: the caller's stream joins the downloads, so synchronising it covers them
+    for (int i = 0; i < 2; ++i)
+      if (d->dl_pending[i]) GSX_CUDA(cudaStreamWaitEvent(st, d->ev_dl[i], 0));
   }
   return GSX_OK;
 }
@@ -345,14 +351,24 @@ static int dp_step_impl(gsx_dp_t *d, const gsx_view_t *views_all, const gsx_para
 int gsx_dp_step(gsx_dp_t *d, const gsx_view_t *views_all_host, const gsx_params_t *params, const float *const *grad_images_dev,
                 const gsx_adam_epilogue_t *adam, void *stream) {
   if (!d || !views_all_host || !params || !grad_images_dev) { set_error("null argument"); return GSX_E_NULL; }
-  return dp_step_impl(d, views_all_host, params, grad_images_dev, nullptr, nullptr, adam, (cudaStream_t)stream);
+  return dp_step_impl(d, views_all_host, params, grad_images_dev, nullptr, nullptr, adam, (cudaStream_t)stream, false);
 }
 
 int gsx_dp_render_host(gsx_dp_t *d, const gsx_view_t *views_all_host, const gsx_params_t *params,
                        const float *const *grad_images_host, float *const *images_host, const gsx_adam_epilogue_t *adam,
                        void *stream) {
   if (!d || !views_all_host || !params || !grad_images_host) { set_error("null argument"); return GSX_E_NULL; }
-  return dp_step_impl(d, views_all_host, params, nullptr, grad_images_host, images_host, adam, (cudaStream_t)stream);
+  return dp_step_impl(d, views_all_host, params, nullptr, grad_images_host, images_host, adam, (cudaStream_t)stream, true);
+}
+
+// The same without the final synchronisation: everything (uploads, step, downloads) is enqueued and `stream` is made to
+// wait for the downloads, so consecutive steps pipeline and one synchronisation of `stream` by the caller covers all of
+// them.  The host buffers must stay untouched until then.
+int gsx_dp_render_host_async(gsx_dp_t *d, const gsx_view_t *views_all_host, const gsx_params_t *params,
+                             const float *const *grad_images_host, float *const *images_host, const gsx_adam_epilogue_t *adam,
+                             void *stream) {
+  if (!d || !views_all_host || !params || !grad_images_host) { set_error("null argument"); return GSX_E_NULL; }
+  return dp_step_impl(d, views_all_host, params, nullptr, grad_images_host, images_host, adam, (cudaStream_t)stream, false);
 }
 
 }  // extern "C"

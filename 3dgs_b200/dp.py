@@ -209,13 +209,16 @@ class DpNative:
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
         check(lib().gsx_dp_step(self.h, self.views, C.byref(p), arr, C.byref(adam) if adam is not None else None, st))
 
-    def render_host(self, grad_images_host, images_host, adam=None):
-        """pinned host loss-gradient images in, pinned host rendered images out (synchronises)"""
+    def render_host(self, grad_images_host, images_host, adam=None, sync=True):
+        """pinned host loss-gradient images in, pinned host rendered images out.  sync=False: everything is enqueued and the
+        current stream joins the downloads (gsx_dp_render_host_async): consecutive steps pipeline, the caller synchronises
+        the stream once and leaves the host buffers alone until then."""
         gi = (C.c_void_p * self.nv_local)(*[t.data_ptr() for t in grad_images_host])
         io = (C.c_void_p * self.nv_local)(*[t.data_ptr() for t in images_host])
         p = self.g.params()
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
-        check(lib().gsx_dp_render_host(self.h, self.views, C.byref(p), gi, io, C.byref(adam) if adam is not None else None, st))
+        fn = lib().gsx_dp_render_host if sync else lib().gsx_dp_render_host_async
+        check(fn(self.h, self.views, C.byref(p), gi, io, C.byref(adam) if adam is not None else None, st))
 
     def allreduce(self, buf):
         st = C.c_void_p(torch.cuda.current_stream().cuda_stream)

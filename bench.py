@@ -250,7 +250,10 @@ def main():
             r.batch_render_host(vstructs, gd, gi_host, img_host, flags=OVER)
             return
         if native:
-            nat.render_host(gi_host, img_host)                     # the library pipelines the copies (gsx_dp_render_host)
+            # the library pipelines the copies; the asynchronous form lets consecutive steps overlap their launch overhead
+            # (a rank with one 2 ms view per step is otherwise idle while the host enqueues the next step) -- the timed
+            # region ends with a device synchronisation, which covers every download
+            nat.render_host(gi_host, img_host, sync=False)
             return
         # host buffers in / out around the same exchange: per view H2D of the loss gradient, D2H of the image, on two copy
         # streams (uploads under the per-Gaussian forward, view k's download under its backward) like the library's

@@ -374,6 +374,11 @@ int gsx_dp_step(gsx_dp_t *dp, const gsx_view_t *views_all_host, const gsx_params
 int gsx_dp_render_host(gsx_dp_t *dp, const gsx_view_t *views_all_host, const gsx_params_t *params,
                        const float *const *grad_images_host, float *const *images_host, const gsx_adam_epilogue_t *adam,
                        void *stream);
+/* gsx_dp_render_host without the final synchronisation: `stream` is made to wait for the image downloads, so consecutive
+ * steps pipeline and one synchronisation of `stream` covers them; the host buffers must stay untouched until then. */
+int gsx_dp_render_host_async(gsx_dp_t *dp, const gsx_view_t *views_all_host, const gsx_params_t *params,
+                             const float *const *grad_images_host, float *const *images_host, const gsx_adam_epilogue_t *adam,
+                             void *stream);
 int gsx_dp_allreduce(gsx_dp_t *dp, float *buf, size_t n_floats, void *stream);
 int gsx_dp_enable_timing(gsx_dp_t *dp, int on);
 /* ms_out[6] = views phase, gather tail after the last view, per-Gaussian backward, allreduce, SH rebuild (+ waits,
