@@ -27,7 +27,7 @@ SYMBOLS = [
     "gsx_ctx_create", "gsx_ctx_destroy", "gsx_forward", "gsx_backward", "gsx_ctx_stats", "gsx_ctx_reserve", "gsx_ctx_overflow",
     "gsx_ctx_state", "gsx_render_view_host", "gsx_ctx_enable_timing", "gsx_ctx_timing", "gsx_ctx_count_work", "gsx_ctx_count_hits", "gsx_measure_fp32_tflops",
     "gsx_batch_reserve", "gsx_batch_forward_params", "gsx_batch_forward_view", "gsx_batch_backward_view",
-    "gsx_batch_backward_params", "gsx_batch_render_host", "gsx_batch_extract_view_rgb_grad",
+    "gsx_batch_backward_params", "gsx_batch_render_host", "gsx_batch_graph_capture", "gsx_graph_launch", "gsx_graph_destroy", "gsx_batch_extract_view_rgb_grad",
     "gsx_sh_grads_from_view_rgb", "gsx_ctx_build_sorted_keys", "gsx_batch_extract_view_rgb_grad_peers",
     "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers", "gsx_adam_step", "gsx_adam_step_fused",
     "gsx_fused_loss_workspace_bytes", "gsx_fused_loss",

@@ -829,6 +829,91 @@ int gsx_ctx_build_sorted_keys(gsx_ctx_t *c, const uint64_t **out) {
   return GSX_OK;
 }
 
+// ---- CUDA-graph replay of a whole batch step ("persistent workspace, CUDA-graph replay") ---------------
+// The ~20 launches per view of the batch path (latency-bound sort / scan kernels, side streams, events) are captured once
+// -- forward of every view, the loss gradient of each view (given, or computed in the graph from a ground-truth image by
+// gsx_fused_loss), backward, parameter gradients -- and replayed with one cudaGraphLaunch per training step.  Everything the
+// step reads is behind fixed device pointers (parameters, ground truth / loss gradients, gradients), so the caller only
+// updates their contents between launches.  The view set and N are baked in: capture again when they change (or when
+// gsx_ctx_reserve re-allocated the instance buffers).
+struct gsx_graph {
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t exec = nullptr;
+  void *loss_ws = nullptr;
+  float *loss_dev = nullptr;
+};
+
+int gsx_graph_destroy(gsx_graph_t *g) {
+  if (!g) return GSX_OK;
+  if (g->exec) cudaGraphExecDestroy(g->exec);
+  if (g->graph) cudaGraphDestroy(g->graph);
+  cudaFree(g->loss_ws); cudaFree(g->loss_dev);
+  delete g;
+  return GSX_OK;
+}
+
+int gsx_graph_launch(gsx_graph_t *g, void *stream) {
+  if (!g || !g->exec) { set_error("null graph"); return GSX_E_NULL; }
+  GSX_CUDA(cudaGraphLaunch(g->exec, (cudaStream_t)stream));
+  return GSX_OK;
+}
+
+int gsx_batch_graph_capture(gsx_ctx_t *c, const gsx_view_t *views, int n_views, const gsx_params_t *p, int N,
+                            const float *const *grad_images_dev, const float *const *gt_images_dev, float ssim_weight,
+                            float *const *images_out_dev, float *losses_dev, const gsx_grads_t *g, int flags, void *stream,
+                            gsx_graph_t **out) {
+  if (!c || !views || !p || !g || !out) { set_error("null argument"); return GSX_E_NULL; }
+  if (!grad_images_dev && !gt_images_dev) { set_error("either loss-gradient images or ground-truth images are needed"); return GSX_E_NULL; }
+  if (n_views < 1 || n_views > c->n_slots) { set_error("n_views %d exceeds the reserved slots (%d)", n_views, c->n_slots); return GSX_E_ARG; }
+  if (c->timing) { set_error("stage timing must be off while capturing"); return GSX_E_ARG; }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (st == nullptr) { set_error("capture needs a non-default stream"); return GSX_E_ARG; }
+  gsx_graph *gr = new gsx_graph();
+  size_t lws = 0;
+  if (gt_images_dev) {
+    for (int k = 0; k < n_views; ++k) lws = std::max(lws, gsx_fused_loss_workspace_bytes(views[k].height, views[k].width));
+    if (cudaMalloc(&gr->loss_ws, lws) != cudaSuccess || cudaMalloc(&gr->loss_dev, sizeof(float)) != cudaSuccess) {
+      gsx_graph_destroy(gr); set_error("cannot allocate the loss workspace"); return GSX_E_CUDA;
+    }
+  }
+  // one eager step first: creates the side streams / events lazily created by the batch path, sizes nothing new inside
+  int rc = gsx_batch_forward_params(c, views, n_views, p, N, stream);
+  for (int k = 0; k < n_views && rc == GSX_OK; ++k) rc = gsx_batch_forward_view(c, k, stream);
+  if (rc == GSX_OK) rc = drain_async(c, st);
+  if (rc != GSX_OK) { gsx_graph_destroy(gr); return rc; }
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e == cudaSuccess) e = cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed);
+  if (e != cudaSuccess) { gsx_graph_destroy(gr); set_error("cudaStreamBeginCapture -> %s", cudaGetErrorString(e)); return GSX_E_CUDA; }
+  rc = gsx_batch_forward_params(c, views, n_views, p, N, stream);
+  for (int k = 0; k < n_views && rc == GSX_OK; ++k) {
+    rc = gsx_batch_forward_view(c, k, stream);
+    if (rc != GSX_OK) break;
+    const size_t bytes = (size_t)views[k].width * views[k].height * 3 * sizeof(float);
+    if (images_out_dev && images_out_dev[k] &&
+        cudaMemcpyAsync(images_out_dev[k], c->image, bytes, cudaMemcpyDeviceToDevice, st) != cudaSuccess) { rc = GSX_E_CUDA; break; }
+    const float *gi = grad_images_dev ? grad_images_dev[k] : c->grad_image;
+    if (gt_images_dev) {
+      rc = gsx_fused_loss(c->image, gt_images_dev[k], views[k].height, views[k].width, ssim_weight, c->grad_image, gr->loss_ws, lws,
+                          losses_dev ? losses_dev + k : gr->loss_dev, nullptr, stream);
+      if (rc != GSX_OK) break;
+    }
+    rc = gsx_batch_backward_view(c, k, gi, stream);
+  }
+  if (rc == GSX_OK) rc = gsx_batch_backward_params(c, p, N, g, flags, stream);
+  e = cudaStreamEndCapture(st, &gr->graph);   // always end the capture, error or not
+  if (rc == GSX_OK && e != cudaSuccess) { set_error("cudaStreamEndCapture -> %s", cudaGetErrorString(e)); rc = GSX_E_CUDA; }
+  if (rc == GSX_OK) {
+    e = cudaGraphInstantiate(&gr->exec, gr->graph, 0);
+    if (e != cudaSuccess) { set_error("cudaGraphInstantiate -> %s", cudaGetErrorString(e)); rc = GSX_E_CUDA; }
+  }
+  // the capture enqueued nothing: the bookkeeping of work "in flight" on the side streams must not outlive it
+  for (int k = 0; k < c->n_slots; ++k) c->slot[k].pre_async = c->slot[k].bin_async = false;
+  for (BinSet &b : c->bset) b.owner = -1;
+  if (rc != GSX_OK) { cudaGetLastError(); gsx_graph_destroy(gr); return rc; }
+  *out = gr;
+  return GSX_OK;
+}
+
 int gsx_render_view_host(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N,
                          const float *grad_image_host, float *image_host, const gsx_grads_t *g, void *stream) {
   if (!c || !v || !p) { set_error("null argument"); return GSX_E_NULL; }

@@ -578,6 +578,34 @@ class Rasterizer:
             self.batch_backward_view(k, gi)
         self.batch_backward_params(g, flags)
 
+    def batch_graph_capture(self, views, g, grad_images=None, gt_images=None, ssim_weight=0.2, images_out=None, losses=None,
+                            flags=_ffi.GSX_GRAD_OVERWRITE, stream=None):
+        """The whole batch step as ONE CUDA graph (gsx_batch_graph_capture).  grad_images: per-view device tensors the caller
+        refreshes between launches, or gt_images: the loss gradient is computed in the graph (L1 + SSIM).  Returns a handle
+        for graph_launch(); capture happens on `stream` (a non-default torch stream; one is created when None)."""
+        if g.grads is None:
+            g.zero_grads()
+        self._gstream = stream if stream is not None else torch.cuda.Stream()
+        arr = (GsxView * len(views))(*views)
+        self._bviews, self._n = arr, g.N
+        self._view = arr[len(views) - 1]
+        gs_, p = g.grads_struct(), g.params()
+        mk = lambda ts: (C.c_void_p * len(views))(*[t.data_ptr() for t in ts]) if ts is not None else None
+        h = C.c_void_p()
+        self._gkeep = (grad_images, gt_images, images_out, losses)
+        check(lib().gsx_batch_graph_capture(self.h, arr, len(views), C.byref(p), g.N, mk(grad_images), mk(gt_images), f32(ssim_weight),
+                                            mk(images_out), _ptr(losses), C.byref(gs_), int(flags),
+                                            C.c_void_p(self._gstream.cuda_stream), C.byref(h)))
+        return h
+
+    def graph_launch(self, h, stream=None):
+        st = stream if stream is not None else self._gstream
+        check(lib().gsx_graph_launch(h, C.c_void_p(st.cuda_stream)))
+
+    @staticmethod
+    def graph_destroy(h):
+        lib().gsx_graph_destroy(h)
+
     def batch_render_host(self, views, g, grad_images_host, images_host, flags=_ffi.GSX_GRAD_OVERWRITE):
         """Host-buffer batch step: pinned host grad images in, pinned host images out (synchronises)."""
         if g.grads is None:

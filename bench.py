@@ -523,6 +523,57 @@ def main():
         except Exception as e:
             next_rows["density_rows_error"] = repr(e)[:300]
 
+    # ---- next row: the same batch step replayed as ONE CUDA graph (gsx_batch_graph_capture) ----------
+    if world == 1:
+        try:
+            def timed_pair(rr, vs, gg, gi_list, reps_g=10):
+                ev = lambda: torch.cuda.Event(enable_timing=True)
+                gstream = torch.cuda.Stream()
+                h_ = rr.batch_graph_capture(vs, gg, grad_images=gi_list, stream=gstream)
+                with torch.cuda.stream(gstream):
+                    for _ in range(2):
+                        rr.graph_launch(h_, gstream)
+                    a_, b_ = ev(), ev()
+                    a_.record(gstream)
+                    for _ in range(reps_g):
+                        rr.graph_launch(h_, gstream)
+                    b_.record(gstream)
+                torch.cuda.synchronize()
+                ms_graph = a_.elapsed_time(b_) / reps_g
+                gsx_h.Rasterizer.graph_destroy(h_)
+                for _ in range(2):
+                    rr.batch_step(vs, gg, gi_list, flags=OVER)
+                a_, b_ = ev(), ev()
+                a_.record()
+                for _ in range(reps_g):
+                    rr.batch_step(vs, gg, gi_list, flags=OVER)
+                b_.record()
+                torch.cuda.synchronize()
+                return ms_graph, a_.elapsed_time(b_) / reps_g
+            gsx_h = Hh
+            mg, me = timed_pair(r, vstructs, gd, [gi_dev] * nv)
+            # a small scene, where the ~20 launches per view are not hidden behind long kernels
+            Ns, Ws, Hs = 200_000, 480, 270
+            gsm = S.synthetic_gaussians(Ns, l_max=l_max, seed=0x3D65 + 9)
+            gds = Hh.Gaussians(gsm["xyz"], gsm["scale"], gsm["quaternion"], gsm["opacity"], gsm["band0"], gsm["sh"], device=dev)
+            gds.zero_grads()
+            rs_ = Hh.Rasterizer(Ns, Ws, Hs, instance_capacity=16 * Ns)
+            rs_.batch_reserve(N_VIEWS)
+            cams_s = [S.orbit_camera(Ws, Hs, azimuth_deg=45.0 * k) for k in range(N_VIEWS)]
+            vs_s = [Hh.make_view(c_["view"], c_["proj"], c_["campos"], c_["fx"], c_["fy"], Ws, Hs, near_thresh=S.NEAR_THRESH,
+                                 cull_padding=S.CULL_PADDING, mh_dist=S.MH_DIST, background=0.0, l_max=l_max) for c_ in cams_s]
+            for v_ in vs_s:
+                assert not rs_.forward_checked(v_, gds)["overflow"]
+            gis_s = torch.as_tensor(S.grad_image(Ws, Hs)).to(dev)
+            mgs, mes = timed_pair(rs_, vs_s, gds, [gis_s] * N_VIEWS)
+            rs_.close()
+            next_rows["graph_replay"] = {
+                "c4_batch_ms": {"graph": round(mg, 3), "eager": round(me, 3)},
+                "small_scene_batch_ms": {"graph": round(mgs, 3), "eager": round(mes, 3), "scene": f"{Ns} Gaussians, {Ws}x{Hs}, 8 views"},
+                "what": "one cudaGraphLaunch per batch step (gsx_batch_graph_capture: per-Gaussian forward, 8 x (bin + sort + composite + backward), per-Gaussian backward; side streams captured) vs the same step enqueued call by call"}
+        except Exception as e:
+            next_rows["graph_replay_error"] = repr(e)[:300]
+
     views_per_s = N_VIEWS * args.steps / (ms_total * 1e-3)
     if world > 1:
         transport = "nccl from C++ (gsx_dp_step)" if native else vp.ex.transport

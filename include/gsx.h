@@ -228,6 +228,22 @@ int gsx_batch_forward_view(gsx_ctx_t *ctx, int slot, void *stream);
 int gsx_batch_backward_view(gsx_ctx_t *ctx, int slot, const float *grad_image, void *stream);
 int gsx_batch_backward_params(gsx_ctx_t *ctx, const gsx_params_t *params, int N, const gsx_grads_t *grads, int flags,
                               void *stream);
+/* ---- CUDA-graph replay of a whole batch step.  gsx_batch_graph_capture records the batch protocol above
+ *      -- per-Gaussian forward, then per view: bin + sort + composite, the view's loss gradient, compositing backward; then the
+ *      per-Gaussian backward -- into a CUDA graph, side streams included; gsx_graph_launch replays it with one call per
+ *      training step.  Loss gradients: grad_images_dev[k] (fixed device buffers whose CONTENTS the caller updates between
+ *      launches), or, when gt_images_dev is given instead, computed inside the graph from each rendered image by
+ *      gsx_fused_loss(image, gt_images_dev[k], ssim_weight) (mean loss of view k -> losses_dev[k] when non-NULL).
+ *      images_out_dev[k] (optional) receives view k's rendered image.  `stream` must be a non-default stream; views, N and
+ *      every pointer are baked in (capture again after gsx_ctx_reserve or when the views change). ------------------------ */
+typedef struct gsx_graph gsx_graph_t;
+int gsx_batch_graph_capture(gsx_ctx_t *ctx, const gsx_view_t *views_host, int n_views, const gsx_params_t *params, int N,
+                            const float *const *grad_images_dev, const float *const *gt_images_dev, float ssim_weight,
+                            float *const *images_out_dev, float *losses_dev, const gsx_grads_t *grads, int flags, void *stream,
+                            gsx_graph_t **graph_out);
+int gsx_graph_launch(gsx_graph_t *graph, void *stream);
+int gsx_graph_destroy(gsx_graph_t *graph);
+
 /* ---- view-parallel multi-GPU exchange.  A view's SH coefficient gradient is rank 1:
  *      d sh[k][c] = d rgb_c * Y_k(dir_view) (cuda/spherical_harmonics_backward.cu:100-104), so instead of allreducing the
  *      192 B/Gaussian band-0 + SH gradient, ranks all-gather the 12 B/Gaussian d rgb of each view and every rank rebuilds

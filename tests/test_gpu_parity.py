@@ -853,6 +853,64 @@ def test_capacity_overflow_is_safe_and_reported_for_every_view(B, monkeypatch):
     assert int(kdev.item()) == full["K"] and not ranges.any().item() and (srt == -1).all().item()
 
 
+def test_batch_graph_replay_matches_eager(B):
+    """gsx_batch_graph_capture / gsx_graph_launch (CUDA-graph replay): the whole batch step -- side streams
+    included -- captured once and replayed must give the eager path's images and gradients; with ground-truth images the loss
+    gradient of every view is computed inside the graph (gsx_fused_loss) and must equal forward -> fused_loss -> backward."""
+    import torch
+    W, H, N, l_max = 224, 160, 12000, 2
+    cams = [S.orbit_camera(W, H, azimuth_deg=a) for a in (15.0, 135.0, 255.0)]
+    g = S.synthetic_gaussians(N, l_max=l_max, seed=49)
+    Hh = gs.host
+    gd = Hh.Gaussians(g["xyz"], g["scale"], g["quaternion"], g["opacity"], g["band0"], g["sh"])
+    views = [util.gsx_view(c, l_max, 0.2) for c in cams]
+    gis = [torch.as_tensor(S.grad_image(W, H, seed=60 + k) * 1e3).cuda() for k in range(3)]
+    r = Hh.Rasterizer(N, W, H, instance_capacity=8 * N)
+    r.batch_reserve(3)
+    imgs = []
+    r.batch_step(views, gd, gis, flags=2, on_image=lambda k: imgs.append(r.state_image().clone()))
+    torch.cuda.synchronize()
+    want = {k: t.clone() for k, t in gd.grads.items()}
+    # ---- given loss gradients
+    out_imgs = [torch.zeros((H, W, 3), device="cuda") for _ in range(3)]
+    h = r.batch_graph_capture(views, gd, grad_images=gis, images_out=out_imgs)
+    for rep in range(2):
+        for t in gd.grads.values():
+            t.fill_(5.0)
+        r.graph_launch(h)
+        torch.cuda.synchronize()
+        for k in range(3):
+            assert torch.equal(out_imgs[k], imgs[k]), f"replay {rep}: image {k}"
+        for k in want:
+            util.assert_grad_close(gd.grads[k].cpu().numpy(), want[k].cpu().numpy(), f"replay {rep}: d {k}")
+    # the caller refreshes the CONTENTS of the gradient images between launches
+    for t in gis:
+        t.mul_(2.0)
+    r.graph_launch(h)
+    torch.cuda.synchronize()
+    util.assert_grad_close(gd.grads["xyz"].cpu().numpy(), 2.0 * want["xyz"].cpu().numpy(), "replay with refreshed loss gradients")
+    Hh.Rasterizer.graph_destroy(h)
+    assert r.overflow() == 0
+    # ---- loss inside the graph
+    gts = [(im + 0.05 * torch.randn_like(im)).clamp_(0, 1) for im in imgs]
+    losses = torch.zeros(3, device="cuda")
+    h2 = r.batch_graph_capture(views, gd, gt_images=gts, ssim_weight=0.2, losses=losses)
+    r.graph_launch(h2)
+    torch.cuda.synchronize()
+    got = {k: t.clone() for k, t in gd.grads.items()}
+    gis2, ls = [], []
+    for im, gt in zip(imgs, gts):
+        l_, gi_ = Hh.fused_loss(im, gt, 0.2)
+        ls.append(l_); gis2.append(gi_)
+    r.batch_step(views, gd, gis2, flags=2)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(losses.cpu().numpy(), ls, rtol=1e-6, atol=1e-7)
+    for k in got:
+        util.assert_grad_close(got[k].cpu().numpy(), gd.grads[k].cpu().numpy(), f"loss-in-graph d {k}")
+    Hh.Rasterizer.graph_destroy(h2)
+    r.close()
+
+
 # ------------------------------------------------------------------------------------------ optimiser (SURVEY 8f rank 2)
 _ADAM = dict(b1=0.9, b2=0.999, eps=1e-8)
 # float tolerance of the Adam step: the device contracts b*m + (1-b)*g into a fused multiply-add, the oracle
