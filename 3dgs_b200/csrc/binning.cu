@@ -28,6 +28,9 @@ int sort_pairs_u32_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, ui
                         const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
                         int *result_in_b, int flags);
 int sort_prepare_impl(long long n, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st);
+int sort_tiles_with_ranges_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                                const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
+                                size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags);
 unsigned *sort_hist_impl(void *workspace);
 int tile_ranges_impl(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
                      cudaStream_t st);
@@ -407,6 +410,18 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
     GSX_LAUNCH_CHECK();
   }
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
+  // tile ranges: extracted by the last scatter of the tile sort (round 2; GSX_RANGES=separate: the stand-alone kernel that
+  // re-reads the 4 K bytes of sorted tile ids)
+  static const bool fused_ranges = [] { const char *e = getenv("GSX_RANGES"); return !(e && e[0] == 's'); }();
+  if (fused_ranges) {
+    rc = sort_tiles_with_ranges_impl(ka, kb, va, vb, capacity, pb.total + 1, key_bits, ntx * nty, ranges, ws + L.sort_ws,
+                                     L.sort_ws_bytes, st, &in_b, (N > 0 && fuse_hist) ? 1 : 0);
+    if (rc != GSX_OK) return rc;
+    *sorted_tiles = in_b ? kb : ka;
+    *sorted_vals = in_b ? vb : va;
+    if (ev) { GSX_CUDA(cudaEventRecord(ev[1], st)); GSX_CUDA(cudaEventRecord(ev[2], st)); }
+    return GSX_OK;
+  }
   rc = sort_pairs_u32_impl(ka, kb, va, vb, capacity, pb.total + 1, key_bits, ws + L.sort_ws, L.sort_ws_bytes, st, &in_b,
                            (N > 0 && fuse_hist) ? 1 : 0);
   if (rc != GSX_OK) return rc;

@@ -14,6 +14,7 @@
 // (n_dev) so the view-level path never syncs with the host.
 // The kernels are templated on the key type: the view-level path sorts 32-bit keys twice (depth per Gaussian, then
 // tile id per instance, binning.cu) instead of one 64-bit tile|depth key per instance.
+#include <limits.h>
 #include <stdlib.h>
 
 #include <algorithm>
@@ -104,7 +105,10 @@ __global__ void __launch_bounds__(THREADS, (THREADS <= 256 ? (sizeof(KeyT) == 8 
 k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
            uint32_t *__restrict__ vals_out, long long n_host, const int *__restrict__ n_dev, int shift, int bits,
            const unsigned int *__restrict__ digit_base /*[256] exclusive*/, unsigned int *__restrict__ status,
-           unsigned int *__restrict__ ticket) {
+           unsigned int *__restrict__ ticket, int *__restrict__ first_of_key, int key_clamp) {
+  // first_of_key (last pass of the tile sort only, else null): first_of_key[k] = smallest output index holding key k
+  // (keys clamped to key_clamp) -- the tile-range extraction fused into the scatter: a run of equal keys
+  // is contiguous in the re-ordered tile, so only run starts issue an atomicMin; k_ranges_from_first turns it into ranges
   constexpr int WARPS = THREADS / 32, TILE = THREADS * IPT;
   static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit for the digit-parallel steps");
   extern __shared__ __align__(16) unsigned char s_dyn[];
@@ -245,6 +249,10 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
       const unsigned d = (unsigned)(kk >> shift) & mask;
       gidx[k] = s_gbase[d] + slot;
       keys_out[gidx[k]] = kk;
+      if (first_of_key) {   // the keys of a digit run are sorted (earlier passes), so equal keys are adjacent slots
+        const bool run_start = slot == 0 || s_keys[slot - 1] != kk;
+        if (run_start) atomicMin(first_of_key + (int)min((unsigned long long)kk, (unsigned long long)key_clamp), gidx[k]);
+      }
     }
   }
   __syncthreads();
@@ -305,14 +313,15 @@ SortLayout sort_layout(long long n) {
 template <typename KeyT, int THREADS, int IPT>
 static int launch_onesweep(int tiles, const KeyT *kin, KeyT *kout, const uint32_t *vin, uint32_t *vout, long long n,
                            const int *n_dev, int shift, int bits, const unsigned *base, unsigned *status, unsigned *ticket,
-                           cudaStream_t st) {
+                           cudaStream_t st, int *first_of_key, int key_clamp) {
   const size_t dyn = sizeof(KeyT) * (size_t)THREADS * IPT;
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
     GSX_CUDA(cudaFuncSetAttribute(k_onesweep<KeyT, THREADS, IPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
     attr_set = true;
   }
-  k_onesweep<KeyT, THREADS, IPT><<<tiles, THREADS, dyn, st>>>(kin, kout, vin, vout, n, n_dev, shift, bits, base, status, ticket);
+  k_onesweep<KeyT, THREADS, IPT><<<tiles, THREADS, dyn, st>>>(kin, kout, vin, vout, n, n_dev, shift, bits, base, status, ticket,
+                                                              first_of_key, key_clamp);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -326,7 +335,7 @@ static int launch_onesweep(int tiles, const KeyT *kin, KeyT *kout, const uint32_
 template <typename KeyT>
 static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n, const int *n_dev,
                         int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags,
-                        KeyT *first_k = nullptr, uint32_t *first_v = nullptr) {
+                        KeyT *first_k = nullptr, uint32_t *first_v = nullptr, int *first_of_key = nullptr, int key_clamp = 0) {
   if (key_bits < 1 || key_bits > (int)sizeof(KeyT) * 8) { set_error("key_bits %d out of range", key_bits); return GSX_E_ARG; }
   const int passes = (key_bits + 7) / 8;
   // With an even number of passes the ping-pong a -> b -> a ends in a.  first_k / first_v (a third buffer): the first pass
@@ -356,12 +365,13 @@ static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *
   for (int p = 0; p < passes; ++p) {
     const int bits = std::min(8, key_bits - 8 * p);
     unsigned *stp = status + (size_t)p * tiles * RADIX;
+    int *fk = p == passes - 1 ? first_of_key : nullptr;
     int rc;
     switch (cfg) {
-      case 1: rc = launch_onesweep<KeyT, 512, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st); break;
-      case 2: rc = launch_onesweep<KeyT, 384, 20>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st); break;
-      case 3: rc = launch_onesweep<KeyT, 512, 12>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st); break;
-      default: rc = launch_onesweep<KeyT, 256, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st); break;
+      case 1: rc = launch_onesweep<KeyT, 512, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp); break;
+      case 2: rc = launch_onesweep<KeyT, 384, 20>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp); break;
+      case 3: rc = launch_onesweep<KeyT, 512, 12>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp); break;
+      default: rc = launch_onesweep<KeyT, 256, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp); break;
     }
     if (rc != GSX_OK) return rc;
     if (via_third && p == 0) { kin = first_k; vin = first_v; kout = keys_b; vout = vals_b; }
@@ -392,6 +402,51 @@ int sort_pairs_u32_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, ui
                         const int *n_dev, int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st,
                         int *result_in_b, int flags) {
   return sort_pairs_t<uint32_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b, flags);
+}
+
+// ---- tile sort with the range extraction fused into its last scatter: ranges[t] = first i with tile(i) >= t, ranges[T] = n
+namespace {
+__global__ void __launch_bounds__(1024) k_ranges_init(int *__restrict__ ranges, int n_tiles) {
+  for (int t = blockIdx.x * 1024 + threadIdx.x; t <= n_tiles; t += gridDim.x * 1024) ranges[t] = INT_MAX;
+}
+// suffix minimum over first_of_key (in place): empty tiles take the first index of the next non-empty one, the end is n
+__global__ void __launch_bounds__(1024) k_ranges_from_first(int *__restrict__ ranges, int n_tiles, long long n_host,
+                                                            const int *__restrict__ n_dev) {
+  __shared__ int s_min[1024];
+  const int n = (int)live_count(n_dev, n_host);
+  const int per = (n_tiles + 1 + 1023) / 1024;               // contiguous chunk of tiles per thread
+  const int t0 = threadIdx.x * per, t1 = min(t0 + per, n_tiles + 1);
+  int m = INT_MAX;
+  for (int t = t1 - 1; t >= t0; --t) m = min(m, t == n_tiles ? n : ranges[t]);
+  s_min[threadIdx.x] = m;
+  __syncthreads();
+  // suffix minimum across the chunks (inclusive), sequential part: 1024 values
+  for (int off = 1; off < 1024; off <<= 1) {
+    const int o = threadIdx.x + off < 1024 ? s_min[threadIdx.x + off] : INT_MAX;
+    __syncthreads();
+    s_min[threadIdx.x] = min(s_min[threadIdx.x], o);
+    __syncthreads();
+  }
+  int run = threadIdx.x + 1 < 1024 ? s_min[threadIdx.x + 1] : INT_MAX;   // minimum over all later chunks
+  run = min(run, n);
+  for (int t = t1 - 1; t >= t0; --t) {
+    run = min(run, t == n_tiles ? n : ranges[t]);
+    ranges[t] = run;
+  }
+}
+}  // namespace
+
+int sort_tiles_with_ranges_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                                const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
+                                size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags) {
+  k_ranges_init<<<std::max(1, std::min(8, (n_tiles + 1024) / 1024)), 1024, 0, st>>>(ranges, n_tiles);
+  GSX_LAUNCH_CHECK();
+  int rc = sort_pairs_t<uint32_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b, flags,
+                                  nullptr, nullptr, ranges, n_tiles - 1);
+  if (rc != GSX_OK) return rc;
+  k_ranges_from_first<<<1, 1024, 0, st>>>(ranges, n_tiles, n, n_dev);
+  GSX_LAUNCH_CHECK();
+  return GSX_OK;
 }
 
 static int ranges_grid(long long n, int n_tiles) {

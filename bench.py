@@ -388,6 +388,8 @@ def main():
         "composite_bwd": ("fp32", 10 * Sx + 46 * Sp),
     }
     stages = {}
+    if launch_ms.get("ranges", 1.0) < 0.005:                       # tile ranges come out of the last sort pass (default): no stage
+        alg.pop("ranges")
     for k_, (bound, w) in alg.items():
         t = launch_ms[k_] * 1e-3
         if bound == "hbm":
@@ -586,7 +588,7 @@ def main():
         xbytes = "none (single GPU)"
     # depth sort: histogram, digit scan, onesweep x4, tie fix-up; scan x3; emission (+ tile-sort histograms); tile sort: digit
     # scan, onesweep x passes; ranges; compositing x2
-    launches_per_view = 2 + 4 + 1 + 3 + 1 + 1 + passes + 1 + 2 + (0 if fused_hist else 1)
+    launches_per_view = 2 + 4 + 1 + 3 + 1 + 1 + passes + 2 + 2 + (0 if fused_hist else 1)   # ranges: init + suffix-min fix-up
     out = {
         "metric": METRIC, "value": views_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
