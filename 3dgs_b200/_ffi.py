@@ -30,7 +30,7 @@ SYMBOLS = [
     "gsx_batch_backward_params", "gsx_batch_render_host", "gsx_batch_graph_capture", "gsx_graph_launch", "gsx_graph_destroy", "gsx_batch_extract_view_rgb_grad",
     "gsx_sh_grads_from_view_rgb", "gsx_ctx_build_sorted_keys", "gsx_batch_extract_view_rgb_grad_peers",
     "gsx_allreduce_multimem_f32", "gsx_push_view_rgb_peers", "gsx_adam_step", "gsx_adam_step_fused",
-    "gsx_fused_loss_workspace_bytes", "gsx_fused_loss",
+    "gsx_fused_loss_workspace_bytes", "gsx_fused_loss", "gsx_fused_loss_static",
     "gsx_compute_morton_codes", "gsx_morton_order_workspace_bytes", "gsx_morton_order", "gsx_gather_rows", "gsx_gather_rows_multi",
     "gsx_dp_unique_id", "gsx_dp_init", "gsx_dp_destroy", "gsx_dp_grads", "gsx_dp_step", "gsx_dp_render_host", "gsx_dp_render_host_async", "gsx_dp_allreduce",
     "gsx_dp_enable_timing", "gsx_dp_timing",

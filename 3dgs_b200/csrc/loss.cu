@@ -12,6 +12,8 @@
 // the symmetric taps paired like the reference, so the two agree to rounding; derivative maps are stored PLANAR
 // ([map][channel][H][W]) so the second kernel's loads coalesce.  Bytes per pixel: 24 read + 36 written, then 36 + 24
 // read + 12 written = 132 B (274 MB at 1920x1080, mostly L2-resident between the two kernels).
+#include <mutex>
+
 #include "gsx_common.cuh"
 
 namespace gsx {
@@ -254,6 +256,33 @@ __global__ void __launch_bounds__(kThreads) k_loss_bwd(int H, int W, float ssim_
   }
 }
 
+// ---- scratch of gsx_fused_loss_static: file-scope device memory, so that entry point never allocates --------------------
+// Same carve-up as the caller workspace of gsx_fused_loss: float [0] = loss sum, float [1] = mean when the caller passes no
+// loss_dev, +256 bytes: the nine planar derivative maps.  Every GPU that loads libgsx.so holds these 36 MiB + 256 B until the
+// process exits.  In HOST code the name below is only a stand-in for the symbol, not a device address: static_scratch()
+// asks the runtime for the address (once per device, with that device current) and the kernels are handed that pointer.
+constexpr size_t kStaticScratchBytes = 256 + (size_t)9 * GSX_FUSED_LOSS_STATIC_MAX_PIXELS * sizeof(float);
+static __device__ __align__(256) unsigned char g_loss_static_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void *g_static_ptr[kMaxDevices] = {};   // device address of g_loss_static_scratch on device d (each device has its own copy)
+
+int static_scratch(char **out) {
+  int dev = -1;
+  GSX_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) { set_error("device ordinal %d outside [0, %d)", dev, kMaxDevices); return GSX_E_ARG; }
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ptr[dev]) {
+    void *p = nullptr;
+    GSX_CUDA(cudaGetSymbolAddress(&p, g_loss_static_scratch));
+    if (!p) { set_error("cudaGetSymbolAddress returned a null address on device %d", dev); return GSX_E_CUDA; }
+    g_static_ptr[dev] = p;
+  }
+  *out = static_cast<char *>(g_static_ptr[dev]);
+  return GSX_OK;
+}
+
 }  // namespace
 }  // namespace gsx
 
@@ -287,6 +316,39 @@ int gsx_fused_loss(const float *predicted, const float *gt, int rows, int cols, 
   k_loss_bwd<<<grid, block, 0, st>>>(rows, cols, ssim_weight, predicted, gt, maps, image_grad, sum, mean);
   GSX_LAUNCH_CHECK();
   if (loss_host) {   // the reference's behaviour: the call returns the loss (one synchronisation)
+    GSX_CUDA(cudaMemcpyAsync(loss_host, mean, sizeof(float), cudaMemcpyDeviceToHost, st));
+    GSX_CUDA(cudaStreamSynchronize(st));
+  }
+  return GSX_OK;
+}
+
+// The same two kernels over the library's static device scratch: no cudaMalloc / cudaFree / allocating call on any path.
+int gsx_fused_loss_static(const float *predicted, const float *gt, int rows, int cols, float ssim_weight, float *image_grad,
+                          float *loss_dev, float *loss_host, void *stream) {
+  GSX_REQUIRE_DEV(predicted); GSX_REQUIRE_DEV(gt); GSX_REQUIRE_DEV(image_grad);
+  if (loss_dev) GSX_REQUIRE_DEV(loss_dev);
+  if (rows <= 0 || cols <= 0) { set_error("image %d x %d", cols, rows); return GSX_E_ARG; }
+  if ((long long)rows * cols > (long long)GSX_FUSED_LOSS_STATIC_MAX_PIXELS) {
+    set_error("gsx_fused_loss_static: image %d x %d = %lld pixels exceeds the static scratch's maximum of %d pixels "
+              "(use gsx_fused_loss with a caller workspace)", cols, rows, (long long)rows * cols,
+              (int)GSX_FUSED_LOSS_STATIC_MAX_PIXELS);
+    return GSX_E_WORKSPACE;
+  }
+  char *scratch = nullptr;
+  if (int rc = static_scratch(&scratch)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  float *sum = reinterpret_cast<float *>(scratch);
+  float *mean = loss_dev ? loss_dev : sum + 1;
+  float *maps = reinterpret_cast<float *>(scratch + 256);
+  // the array keeps the previous call's contents: the loss sum must start at zero (the maps are fully overwritten for
+  // every pixel inside rows x cols before the second kernel reads them, and it reads nothing outside)
+  GSX_CUDA(cudaMemsetAsync(sum, 0, sizeof(float), st));
+  const dim3 block(kBX, kBY), grid(ceil_div(cols, kTX), ceil_div(rows, kTY));
+  k_loss_fwd<<<grid, block, 0, st>>>(rows, cols, ssim_weight, predicted, gt, maps, sum);
+  GSX_LAUNCH_CHECK();
+  k_loss_bwd<<<grid, block, 0, st>>>(rows, cols, ssim_weight, predicted, gt, maps, image_grad, sum, mean);
+  GSX_LAUNCH_CHECK();
+  if (loss_host) {
     GSX_CUDA(cudaMemcpyAsync(loss_host, mean, sizeof(float), cudaMemcpyDeviceToHost, st));
     GSX_CUDA(cudaStreamSynchronize(st));
   }

@@ -331,6 +331,20 @@ int gsx_adam_step_fused(const gsx_adam_group_t *groups_host, int n_groups, const
 size_t gsx_fused_loss_workspace_bytes(int rows, int cols);
 int gsx_fused_loss(const float *predicted, const float *gt, int rows, int cols, float ssim_weight, float *image_grad,
                    void *workspace, size_t workspace_bytes, float *loss_dev, float *loss_host, void *stream);
+/* gsx_fused_loss_static: NO counterpart in the reference -- added for callers that
+ * cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same kernels,
+ * arguments and results as gsx_fused_loss, but the workspace (loss sum + nine derivative maps) is a file-scope static
+ * __device__ array inside libgsx.so instead of a caller buffer: the call performs no cudaMalloc, cudaFree or other
+ * allocating call.  Limit: rows * cols <= GSX_FUSED_LOSS_STATIC_MAX_PIXELS (1 Mi pixels, e.g. 1280x720 or 1024x1024; the
+ * array is 36 MiB + 256 B, held by every GPU that loads the library until the process exits); larger images are rejected
+ * with GSX_E_WORKSPACE and a message -- use gsx_fused_loss.  All calls on a device share the one array, which keeps the
+ * previous call's contents (the entry point clears the loss accumulator itself): calls that overlap on the GPU -- different
+ * streams without an ordering between them -- race, so serialise them.  loss_host != NULL synchronises the stream (leave it
+ * NULL under capture).  The first call on each device resolves the array's device address (cudaGetSymbolAddress); make it
+ * outside stream capture. */
+#define GSX_FUSED_LOSS_STATIC_MAX_PIXELS (1 << 20)
+int gsx_fused_loss_static(const float *predicted, const float *gt, int rows, int cols, float ssim_weight, float *image_grad,
+                          float *loss_dev, float *loss_host, void *stream);
 
 /* ---- SURVEY 8f rank 4 (first half): Morton re-layout of the Gaussian arrays ----
  * gsx_compute_morton_codes replaces compute_morton_codes (include/gsplat_cuda/cuda_forward.cuh:186, cuda/culling.cu:42-68,
