@@ -144,6 +144,14 @@ __global__ void k_compose_keys(const uint32_t *__restrict__ tiles, const uint32_
     out[i] = ((uint64_t)tiles[i] << 32) | float_sort_bits(depth[ids[i]]);
 }
 
+// same when the per-instance tile ids do not exist (direct tile binning): one warp per tile walks its range
+__global__ void k_compose_keys_ranges(const int *__restrict__ ranges, int n_tiles, const uint32_t *__restrict__ ids,
+                                      const float *__restrict__ depth, uint64_t *__restrict__ out) {
+  const int lane = threadIdx.x & 31, warps = (gridDim.x * blockDim.x) >> 5;
+  for (int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < n_tiles; t += warps)
+    for (int i = ranges[t] + lane; i < ranges[t + 1]; i += 32) out[i] = ((uint64_t)t << 32) | float_sort_bits(depth[ids[i]]);
+}
+
 __global__ void k_count_mask(const uint8_t *__restrict__ mask, int N, int *__restrict__ out) {
   int c = 0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) c += mask[i] ? 1 : 0;
@@ -813,7 +821,7 @@ int gsx_ctx_state(gsx_ctx_t *c, gsx_state_t *o) {
 int gsx_ctx_build_sorted_keys(gsx_ctx_t *c, const uint64_t **out) {
   if (!c || !out) return GSX_E_NULL;
   *out = nullptr;
-  if (!c->sorted_tiles) return GSX_OK;
+  if (!c->sorted_vals) return GSX_OK;
   if (c->key64_cap < c->capacity) {
     if (c->key64) cudaFree(c->key64);
     c->key64 = nullptr; c->key64_cap = 0;
@@ -821,8 +829,12 @@ int gsx_ctx_build_sorted_keys(gsx_ctx_t *c, const uint64_t **out) {
     c->key64_cap = c->capacity;
   }
   GSX_CUDA(cudaDeviceSynchronize());
-  k_compose_keys<<<kNumSMs * 8, 256>>>(c->sorted_tiles, c->sorted_vals, c->slot[c->cur].p.depth,
-                                       c->cur_total + 1, c->capacity, c->key64);
+  if (c->sorted_tiles)
+    k_compose_keys<<<kNumSMs * 8, 256>>>(c->sorted_tiles, c->sorted_vals, c->slot[c->cur].p.depth,
+                                         c->cur_total + 1, c->capacity, c->key64);
+  else
+    k_compose_keys_ranges<<<kNumSMs * 8, 256>>>(c->ranges, ((c->last_w + 15) / 16) * ((c->last_h + 15) / 16), c->sorted_vals,
+                                                c->slot[c->cur].p.depth, c->key64);
   GSX_LAUNCH_CHECK();
   GSX_CUDA(cudaDeviceSynchronize());
   *out = c->key64;

@@ -393,6 +393,25 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
   uint32_t *ka = (uint32_t *)(ws + L.keys_a), *kb = (uint32_t *)(ws + L.keys_b);
   uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
   int in_b = 0, rc;
+  // Direct tile binning (round 2, tilebin.cu, GSX_BINNING=direct): the instance ids go straight to their final place by one
+  // stable counting sort on the tile id; its count matrices live in the key buffers the sort path would use.  Bit-identical
+  // lists (tests), but measured SLOWER at C4 on B200 (profiles/r2i_*): count pass 0.57 ms + ordered emission 0.83 ms against
+  // 0.23 + 0.07 + 0.33 ms for emission + histogram + two radix passes -- the exact SAT enumeration runs twice (152 M + 279 M warp
+  // instructions at 17 % occupancy: one CTA of 11 warps per SM holds the 16-bit tile counters), and the scattered 4-byte
+  // stores do not merge in L2 (433 MB of DRAM writes + as much read-for-fill for 84 MB of ids).  So emission + radix sort stays
+  // the default; the direct path is kept as the measured alternative.
+  {
+    const char *e = getenv("GSX_BINNING");
+    TileBinPlan plan;
+    if (e && e[0] == 'd' && N > 0 && tilebin_plan(ntx, nty, N, capacity, L.vals_a - L.keys_a, &plan)) {
+      rc = tilebin_run(plan, uv, uv_stride, radius, pb.dkeys, pb.perm, pb.offsets, N, pb.count, pb.total, ntx, nty,
+                       (tight && uv_stride == 4) ? 1 : 0, ws + L.keys_a, ranges, va, st, ev);
+      if (rc != GSX_OK) return rc;
+      *sorted_tiles = nullptr;
+      *sorted_vals = va;
+      return GSX_OK;
+    }
+  }
   const int key_bits = tile_key_bits(ntx * nty) - 32;
   // Measured on B200 (profiles/r2c_*): the sort loses its 0.057 ms histogram pass, the emission kernel gains 0.050 ms of
   // shared-memory atomics (20.9 M instances): a wash, so the separate histogram pass stays the default (GSX_FUSED_HIST=1).

@@ -78,4 +78,21 @@ struct PreBin {
   const int *count = nullptr;                          // device count of sorted entries (compact mode) or null
 };
 
+// direct tile binning (tilebin.cu): one stable counting sort on the tile id instead of emission + two radix passes
+struct TileBinPlan {
+  int warps = 0;            // warps per CTA = segments per CTA
+  int ctas = 0;             // G
+  int bands = 0;            // tile-row bands (grid.y)
+  int rows_per_band = 0;    // tile rows per band
+  int tb = 0;               // tiles per band (rows_per_band * ntx, rounded up to even)
+  size_t smem_count = 0, smem_emit = 0;
+  size_t off_W = 0;         // byte offset of the u16 matrix inside the region (the u32 matrix C is at 0)
+  size_t off_seg = 0;       // segment starts [rows + 1]
+  size_t bytes = 0;
+};
+bool tilebin_plan(int ntx, int nty, int n_max, long long capacity, size_t region_bytes, TileBinPlan *p);
+int tilebin_run(const TileBinPlan &p, const float *uv, int uv_stride, const float4 *radius, const uint32_t *dkeys,
+                const uint32_t *perm, const int *offsets, int n_host, const int *n_dev, const int *total, int ntx, int nty,
+                int tight, char *region, int *ranges, uint32_t *out_ids, cudaStream_t st, cudaEvent_t *ev);
+
 }  // namespace gsx

@@ -150,6 +150,37 @@ def test_sorted_list_bit_exact(B):
     assert e["K"] == 0 and not e["ranges"].any()
 
 
+@pytest.mark.parametrize("W,H,N,n_huge", [(333, 250, 30000, 40), (1920, 1080, 200_000, 200), (3840, 2160, 120_000, 300),
+                                           (160, 16, 3000, 5)])
+def test_direct_tile_binning_equals_sort_path_and_oracle(B, monkeypatch, W, H, N, n_huge):
+    """The two second-level binning paths -- emission + radix sort (default) and the direct counting sort on the tile id
+    (tilebin.cu, GSX_BINNING=direct) -- give the SAME list and ranges, bit for bit, and both equal the oracle's.  Cases: ragged tiles,
+    screen-filling Gaussians (expanded by the whole warp in the middle of a chunk), equal depths, a 4K view (tile-row bands:
+    more tiles than 16-bit counters per warp fit shared memory), a single tile row."""
+    rng = np.random.default_rng(W * 7 + N)
+    ntx, nty = (W + 15) // 16, (H + 15) // 16
+    uv = np.stack([rng.uniform(-120, W + 120, N), rng.uniform(-120, H + 120, N)], 1).astype(np.float32)
+    z = rng.uniform(0.3, 9.0, N).astype(np.float32)
+    z[::5] = 2.5                                      # equal-depth ties (ascending id inside a tile)
+    xyz = np.stack([np.zeros(N), np.zeros(N), z], 1).astype(np.float32)
+    rmaj = np.ceil(rng.exponential(8.0, N) + 1).astype(np.float32)
+    huge = rng.choice(N, n_huge, replace=False)
+    rmaj[huge] = np.ceil(rng.uniform(60, 0.6 * max(W, H), n_huge)).astype(np.float32)
+    rmin = np.ceil(rmaj * rng.uniform(0.1, 1.0, N)).astype(np.float32)
+    th = rng.uniform(-np.pi / 2, np.pi / 2, N)
+    rad = np.stack([rmaj, rmin, np.sin(th), np.cos(th)], 1).astype(np.float32)
+    monkeypatch.delenv("GSX_BINNING", raising=False)
+    a = B.sorted_list(uv, xyz, rad, ntx, nty)
+    monkeypatch.setenv("GSX_BINNING", "direct")
+    d = B.sorted_list(uv, xyz, rad, ntx, nty)
+    o = G.sorted_list(uv, xyz, rad, ntx, nty)
+    assert a["K"] == d["K"] == o["K"] and d["K"] > 0
+    np.testing.assert_array_equal(d["ranges"], o["ranges"])
+    np.testing.assert_array_equal(d["sorted"], o["sorted"])
+    np.testing.assert_array_equal(a["ranges"], d["ranges"])
+    np.testing.assert_array_equal(a["sorted"], d["sorted"])
+
+
 # ------------------------------------------------------------------------------------------ compositing
 def _comp_inputs(N=4000, W=150, H=100, seed=2, big=False):
     rng = np.random.default_rng(seed)
@@ -466,8 +497,10 @@ def test_view_parallel_split_exchange_matches_fused(B, l_max, sh_alloc):
     r.close()
 
 
-def test_view_sorted_list_depth_ties_canonical(B):
-    """Every Gaussian three times (identical depth bits): the compacted depth keys arrive unordered, so the canonical
+@pytest.mark.parametrize("binning", ["sort", "direct"])
+def test_view_sorted_list_depth_ties_canonical(B, monkeypatch, binning):
+    """(both second-level binning paths: emission + radix sort, and the direct counting sort of tilebin.cu)
+    Every Gaussian three times (identical depth bits): the compacted depth keys arrive unordered, so the canonical
     tie order (ascending Gaussian id) exercises k_fix_ties.  Bit-exact against the oracle's list."""
     W, H = 160, 128
     cam = S.orbit_camera(W, H, azimuth_deg=70.0)
@@ -476,6 +509,7 @@ def test_view_sorted_list_depth_ties_canonical(B):
     g = {k: rep(v) for k, v in g0.items()}
     perm = np.random.default_rng(5).permutation(g["xyz"].shape[0])            # interleave the copies
     g = {k: (None if v is None else np.ascontiguousarray(v[perm])) for k, v in g.items()}
+    monkeypatch.setenv("GSX_BINNING", binning)
     Hh, gd, r, v, stats = _run_view(cam, g, 0, 0.0)
     st = {k: (t.cpu().numpy() if hasattr(t, "cpu") else t) for k, t in r.state().items()}
     N = g["xyz"].shape[0]
