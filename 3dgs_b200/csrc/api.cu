@@ -44,7 +44,7 @@ int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, in
 int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, const int *touched, int ntx, int nty, int N,
                        long long capacity, char *ws, const BinLayout &L, const PreBin &pb, int *ranges,
                        const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
-                       int tight);
+                       int tight, const uint2 *trec, const uint16_t *tlist);
 size_t prebin_sort_ws_bytes(int N);
 size_t prebin_block_sums_count(int N);
 int batch_fwd_launch(const BatchConst &bc, const gsx_params_t &p, int N, int l_max, cudaStream_t st);
@@ -115,7 +115,9 @@ struct gsx_ctx {
   int *h_over = nullptr;            // pinned + mapped: largest K that exceeded the capacity since the last reserve (0: none)
   int *d_P = nullptr;
   unsigned long long *d_work = nullptr;   // gsx_ctx_count_work's two counters
-  int *d_ccount = nullptr;          // [GSX_MAX_BATCH] compacted-Gaussian counters of the slots
+  int *d_ccount = nullptr;          // [GSX_MAX_BATCH] compacted-Gaussian counters of the slots, [GSX_MAX_BATCH] = tile-list cursor
+  uint16_t *tlist = nullptr;        // tile ids of every (view, Gaussian, tile) instance of the current batch, as the per-Gaussian
+  unsigned tl_cap = 0;              // forward enumerated them (batch.cu); tl_cap entries, re-sized with the instance capacity
   // optional stage timing (gsx_ctx_enable_timing): 0,1 per-Gaussian forward; 2 view start, 3 emit, 4 sort, 5 ranges,
   // 6 compositing forward; 7,8 compositing backward; 9,10 per-Gaussian backward
   bool timing = false;
@@ -159,6 +161,24 @@ __global__ void k_count_mask(const uint8_t *__restrict__ mask, int N, int *__res
   if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
 }
 
+static bool lists_enabled() { const char *e = getenv("GSX_TILE_LISTS"); return !(e && e[0] == '0'); }
+
+// The batch's tile-list buffer (tile ids of the rectangles of more than COOP_CELLS cells; each reserves its cell count):
+// room for the instance capacity of every reserved slot.  A rectangle that does not fit gets no list and the emission
+// falls back to the SAT for it.  GSX_TILE_LISTS=0: the emission kernel enumerates everything itself (round-1 behaviour).
+static int ensure_tile_lists(gsx_ctx *c) {
+  const bool off = !lists_enabled() || c->n_px_tiles > 65536;   // 16-bit tile ids
+  unsigned long long want = off ? 0ull : std::min<unsigned long long>(0xffffff00ull,
+      (unsigned long long)c->capacity * (unsigned long long)std::max(1, c->n_slots));
+  if (const char *cap = getenv("GSX_TILE_LISTS_CAP")) want = std::min<unsigned long long>(want, strtoull(cap, nullptr, 10));   // tests: force the fallback
+  if (want <= c->tl_cap && !(off && c->tlist)) return GSX_OK;
+  if (c->tlist) { cudaFree(c->tlist); c->tlist = nullptr; c->tl_cap = 0; }
+  if (want == 0) return GSX_OK;
+  GSX_CUDA(cudaMalloc(&c->tlist, want * sizeof(uint16_t)));
+  c->tl_cap = (unsigned)want;
+  return GSX_OK;
+}
+
 static int alloc_bin(gsx_ctx *c, long long capacity) {
   for (BinSet &b : c->bset) {
     if (b.ws) { cudaFree(b.ws); b.ws = nullptr; }
@@ -176,7 +196,7 @@ static int alloc_bin(gsx_ctx *c, long long capacity) {
     if (!c->bset[i].ranges) GSX_CUDA(cudaMalloc(&c->bset[i].ranges, sizeof(int) * (size_t)(c->n_px_tiles + 1)));
   }
   c->bin_ws = c->bset[0].ws; c->ranges = c->bset[0].ranges;
-  return GSX_OK;
+  return ensure_tile_lists(c);
 }
 
 static void release_slot(gsx_slot &s);
@@ -200,6 +220,7 @@ static int alloc_slot_buffers(gsx_ctx *c, int k) {
   GSX_CUDA(cudaMalloc(&s.p.gacc, n * 12 * sizeof(float)));
   GSX_CUDA(cudaMalloc(&s.p.ckey, n * sizeof(uint32_t)));
   GSX_CUDA(cudaMalloc(&s.p.cid, n * sizeof(uint32_t)));
+  GSX_CUDA(cudaMalloc(&s.p.trec, n * sizeof(uint2)));
   s.p.ccount = c->d_ccount + k;
   s.pb.key_a = s.p.ckey; s.pb.val_a = s.p.cid;
   s.pb.over_flag = c->h_over;
@@ -222,7 +243,7 @@ static int alloc_slot_buffers(gsx_ctx *c, int k) {
 }
 static void release_slot(gsx_slot &s) {   // cudaFree(nullptr) is a no-op
   cudaFree(s.p.r0); cudaFree(s.p.r1); cudaFree(s.p.r2); cudaFree(s.p.radius); cudaFree(s.p.depth); cudaFree(s.p.mask);
-  cudaFree(s.p.touched); cudaFree(s.p.gacc); cudaFree(s.p.ckey); cudaFree(s.p.cid);
+  cudaFree(s.p.touched); cudaFree(s.p.gacc); cudaFree(s.p.ckey); cudaFree(s.p.cid); cudaFree(s.p.trec);
   cudaFree(s.pb.key_b); cudaFree(s.pb.val_b); cudaFree(s.pb.offsets); cudaFree(s.pb.block_sums); cudaFree(s.pb.total);
   cudaFree(s.pb.sort_ws);
   if (s.ev_pre) cudaEventDestroy(s.ev_pre);
@@ -245,6 +266,11 @@ static int drain_async(gsx_ctx *c, cudaStream_t st) {
   return GSX_OK;
 }
 
+// the batch's tile-list buffer (GSX_TILE_LISTS=0: none -- the emission then repeats the SAT, the round-1 behaviour)
+static void set_tile_lists(gsx_ctx *c, BatchConst *bc) {
+  bc->tlist = c->tlist; bc->tcursor = (unsigned *)(c->d_ccount + GSX_MAX_BATCH); bc->tl_cap = c->tlist ? c->tl_cap : 0;
+}
+
 // emission + tile sort + ranges of slot k's view into instance-buffer set k & 1, on stream `st`
 static int issue_emit_sort(gsx_ctx *c, int k, int N, cudaStream_t st, cudaEvent_t *ev) {
   gsx_slot &s = c->slot[k];
@@ -253,7 +279,8 @@ static int issue_emit_sort(gsx_ctx *c, int k, int N, cudaStream_t st, cudaEvent_
   const int ntx = (v.width + 15) / 16, nty = (v.height + 15) / 16;
   b.owner = k;
   return bin_emit_sort_impl((const float *)s.p.r0, 4, s.p.radius, s.p.touched, ntx, nty, N, c->capacity, b.ws, c->L, s.pb, b.ranges,
-                            &b.sorted_tiles, &b.sorted_vals, st, ev, (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0);
+                            &b.sorted_tiles, &b.sorted_vals, st, ev, (v.flags & GSX_LISTS_CONTRIBUTING) ? 1 : 0,
+                            (lists_enabled() && c->n_px_tiles <= 65536) ? s.p.trec : nullptr, c->tlist);
 }
 
 // view k+... binned ahead on the binning stream: after its pre-binning and after everything queued so far on `st` (the
@@ -346,8 +373,8 @@ int gsx_ctx_create(gsx_ctx_t **out, int max_gaussians, int max_width, int max_he
   const size_t px = (size_t)max_width * max_height;
   const int T = ((max_width + 15) / 16) * ((max_height + 15) / 16);
   if (instance_capacity >= (1LL << 30)) { set_error("instance capacity %lld >= 2^30", instance_capacity); delete c; return GSX_E_ARG; }
-  GSX_CUDA(cudaMalloc(&c->d_ccount, GSX_MAX_BATCH * sizeof(int)));
-  GSX_CUDA(cudaMemset(c->d_ccount, 0, GSX_MAX_BATCH * sizeof(int)));
+  GSX_CUDA(cudaMalloc(&c->d_ccount, (GSX_MAX_BATCH + 1) * sizeof(int)));
+  GSX_CUDA(cudaMemset(c->d_ccount, 0, (GSX_MAX_BATCH + 1) * sizeof(int)));
   GSX_CUDA(cudaHostAlloc(&c->h_over, 4 * sizeof(int), cudaHostAllocMapped));
   c->h_over[0] = 0;
   GSX_CUDA(cudaMalloc(&c->d_work, 2 * sizeof(unsigned long long)));
@@ -389,7 +416,7 @@ int gsx_ctx_destroy(gsx_ctx_t *c) {
   if (c->ev_free) cudaEventDestroy(c->ev_free);
   if (c->cs_in) cudaStreamDestroy(c->cs_in);
   if (c->cs_out) cudaStreamDestroy(c->cs_out);
-  cudaFree(c->grad_image); cudaFree(c->d_P); cudaFree(c->d_ccount); cudaFreeHost(c->h_stats);
+  cudaFree(c->grad_image); cudaFree(c->d_P); cudaFree(c->d_ccount); cudaFree(c->tlist); cudaFreeHost(c->h_stats);
   cudaFree(c->d_work); cudaFreeHost(c->h_over);
   delete c;
   return GSX_OK;
@@ -418,8 +445,10 @@ int gsx_forward(gsx_ctx_t *c, const gsx_view_t *v, const gsx_params_t *p, int N,
   c->batch_n = N; c->batch_nv = 1; c->batch_lmax = v->l_max;
   BatchConst bc;
   bc.nv = 1; bc.v[0] = make_view_const(*v); bc.s[0] = c->slot[0].p;
+  set_tile_lists(c, &bc);
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
   GSX_CUDA(cudaMemsetAsync(c->d_ccount, 0, sizeof(int), st));
+  GSX_CUDA(cudaMemsetAsync(c->d_ccount + GSX_MAX_BATCH, 0, sizeof(int), st));
   rc = batch_fwd_launch(bc, *p, N, v->l_max, st);
   if (rc != GSX_OK) return rc;
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[1], st));
@@ -463,10 +492,11 @@ int gsx_batch_reserve(gsx_ctx_t *c, int n_slots) {
     GSX_CUDA(cudaMalloc(&c->bset[1].ws, c->L.bytes));
     GSX_CUDA(cudaMalloc(&c->bset[1].ranges, sizeof(int) * (size_t)(c->n_px_tiles + 1)));
   }
-  return GSX_OK;
+  return ensure_tile_lists(c);
 }
 
 static int fill_batch_const(gsx_ctx *c, int nv, BatchConst *bc) {
+  set_tile_lists(c, bc);
   bc->nv = nv;
   for (int k = 0; k < nv; ++k) { bc->v[k] = make_view_const(c->slot[k].view); bc->s[k] = c->slot[k].p; }
   return GSX_OK;
@@ -492,7 +522,7 @@ int gsx_batch_forward_params(gsx_ctx_t *c, const gsx_view_t *views, int n_views,
     if (rcd != GSX_OK) return rcd;
   }
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[0], st));
-  GSX_CUDA(cudaMemsetAsync(c->d_ccount, 0, GSX_MAX_BATCH * sizeof(int), st));
+  GSX_CUDA(cudaMemsetAsync(c->d_ccount, 0, (GSX_MAX_BATCH + 1) * sizeof(int), st));
   int rc = batch_fwd_launch(bc, *p, N, views[0].l_max, st);
   if (c->timing) GSX_CUDA(cudaEventRecord(c->ev[1], st));
   if (rc != GSX_OK) return rc;

@@ -181,21 +181,53 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
       sp.mask[gi] = 1;
       zc = pc.z;
     }
-    // exact tile count (F7 window + SAT): small rectangles per thread, large ones by the whole warp
+    // exact tile count (F7 window + SAT): small rectangles per thread, large ones by the whole warp.  What the enumeration
+    // finds is kept for the emission kernel (binning.cu k_emit_lists), which then needs neither the SAT nor the screen-space
+    // records: a small rectangle leaves its 16-bit hit mask (cells tx-major, as enumerated) + origin tile + row count in an
+    // 8-byte record; a large one reserves its cell count in the batch's tile-list buffer and writes its tile ids there.
     const bool big = active && rect_cells(tr) > COOP_CELLS;
+    unsigned hitmask = 0;
     if (active && !big) {
+      int b = 0;
       for (int tx = tr.x0; tx <= tr.x1; ++tx) {
         const SatCol col = sat_col(so, tx);
-        for (int ty = tr.y0; ty <= tr.y1; ++ty) cnt += sat_cell(so, col, ty) ? 1 : 0;
+        for (int ty = tr.y0; ty <= tr.y1; ++ty, ++b) hitmask |= (sat_cell(so, col, ty) ? 1u : 0u) << b;
       }
+      cnt = __popc(hitmask);
+      if (cnt > 0) sp.trec[gi] = make_uint2((unsigned)(tr.y0 * vc.ntx + tr.x0) | ((unsigned)(tr.y1 - tr.y0 + 1) << 16), hitmask);
     }
     unsigned bm = __ballot_sync(0xffffffffu, big);
+    // room for the large rectangles of this warp step: one atomic for all of them (a same-address atomic per rectangle, with
+    // its return value on the critical path, cost 8 % of the kernel's stall samples)
+    unsigned mybase = 0xffffffffu;   // 0xffffffff: no room in the list buffer -> the emission repeats the SAT for this one
+    if (bm && bc.tl_cap) {
+      const unsigned need = big ? (unsigned)rect_cells(tr) : 0u;
+      unsigned incl = need;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const unsigned x = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += x;
+      }
+      unsigned at = 0;
+      if (lane == 31) at = atomicAdd(bc.tcursor, incl);
+      at = __shfl_sync(0xffffffffu, at, 31) + incl - need;
+      if (big && (unsigned long long)at + need <= (unsigned long long)bc.tl_cap) mybase = at;
+    }
     while (bm) {
       const int leader = __ffs(bm) - 1;
       bm &= bm - 1;
       int c = 0;
-      coop_tile_rect(leader, so, tr, [&](bool, unsigned ballot, int, int) { c += __popc(ballot); });
-      if (lane == leader) cnt = c;
+      unsigned lbase = mybase;
+      lbase = __shfl_sync(0xffffffffu, lbase, leader);
+      const int lntx = __shfl_sync(0xffffffffu, vc.ntx, leader);
+      coop_tile_rect(leader, so, tr, [&](bool hit, unsigned ballot, int tx, int ty) {
+        if (hit && lbase != 0xffffffffu) bc.tlist[lbase + c + __popc(ballot & ((1u << lane) - 1u))] = (uint16_t)(ty * lntx + tx);
+        c += __popc(ballot);
+      });
+      if (lane == leader) {
+        cnt = c;
+        if (c > 0) sp.trec[gi] = make_uint2(lbase, 0x80000000u | (unsigned)c);
+      }
     }
     if (active) sp.touched[gi] = cnt;
     // Gaussians with instances are appended (warp-aggregated, unordered) to the view's compact depth-key list: the

@@ -185,6 +185,86 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
   flush_hist();
 }
 
+// Emission from what the exact tile count of the per-Gaussian forward left (batch.cu): no SAT, no gathers of the
+// screen-space records, one 8-byte record per Gaussian -- the hit mask of a small rectangle, or where a large one's tile ids
+// are.  A warp owns 32 consecutive depth ranks; their instances are one contiguous output range [o_0, o_31 + cnt_31), which
+// the warp fills 32 entries per step, coalesced: each lane finds the Gaussian its output position belongs to by a 5-step
+// search over the 32 offsets (shuffles) and produces that Gaussian's k-th tile (the k-th set bit of the mask, or the k-th
+// entry of its list).  A large rectangle without a list (the buffer was full) is enumerated with the SAT as k_emit does.
+// Compact mode only (every entry has instances).
+__device__ __forceinline__ unsigned nth_set_bit16(unsigned m, unsigned k) {   // position of the k-th (0-based) set bit of a 16-bit mask
+  unsigned r = 0;
+  unsigned c = __popc(m & 0xffu);
+  if (k >= c) { k -= c; r += 8; m >>= 8; }
+  c = __popc(m & 0xfu);
+  if (k >= c) { k -= c; r += 4; m >>= 4; }
+  c = __popc(m & 0x3u);
+  if (k >= c) { k -= c; r += 2; m >>= 2; }
+  if (k >= (m & 1u)) r += 1;
+  return r;
+}
+
+__global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__ uv, int uv_stride,
+                                                       const float4 *__restrict__ radius, const uint32_t *__restrict__ perm,
+                                                       const int *__restrict__ offsets, const uint2 *__restrict__ trec,
+                                                       const uint16_t *__restrict__ tlist, int ntx, int nty, int N_host,
+                                                       const int *__restrict__ n_dev, const int *__restrict__ total,
+                                                       uint32_t *__restrict__ tiles, uint32_t *__restrict__ vals, int tight) {
+  if (total[1] == 0) return;   // empty view or K beyond the capacity: nothing is emitted (block-uniform)
+  const int n = min(*n_dev, N_host);
+  const int j = blockIdx.x * kBlock + threadIdx.x, lane = threadIdx.x & 31;
+  const bool live = j < n;
+  if (!__any_sync(0xffffffffu, live)) return;
+  int i = 0, cnt = 0, o = INT_MAX;
+  uint2 rec = make_uint2(0u, 0u);
+  if (live) {
+    i = (int)perm[j];
+    o = offsets[j];
+    rec = trec[i];
+    cnt = (rec.y & 0x80000000u) ? (int)(rec.y & 0x7fffffffu) : __popc(rec.y);
+  }
+  const bool is_big = (rec.y & 0x80000000u) != 0u;
+  if (live && is_big && rec.x == 0xffffffffu) {   // no list: the SAT enumeration of k_emit, serially (rare)
+    const float u = uv[(size_t)i * uv_stride], v = uv[(size_t)i * uv_stride + 1];
+    const float4 r = radius[i];
+    const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
+    TileRange tr = sat_aabb_range(s, candidate_window(u, v, r.x, ntx, nty));
+    if (tight) clip_range_to_extent(tr, u, v, uv[(size_t)i * uv_stride + 2], uv[(size_t)i * uv_stride + 3]);
+    long long w = o;
+    for (int tx = tr.x0; tx <= tr.x1; ++tx) {
+      const SatCol col = sat_col(s, tx);
+      for (int ty = tr.y0; ty <= tr.y1; ++ty)
+        if (sat_cell(s, col, ty)) { tiles[w] = (uint32_t)(ty * ntx + tx); vals[w] = (uint32_t)i; ++w; }
+    }
+  }
+  const int nlive = __popc(__ballot_sync(0xffffffffu, live));
+  const int first = __shfl_sync(0xffffffffu, o, 0);
+  const int end = __shfl_sync(0xffffffffu, o + cnt, nlive - 1);
+  for (int p0 = first; p0 < end; p0 += 32) {
+    const int p = p0 + lane;
+    int own = 0;   // the last lane whose offset is <= p (offsets ascend; dead lanes hold INT_MAX)
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+      const int cand = own + step;
+      const int oc = __shfl_sync(0xffffffffu, o, cand & 31);
+      if (cand < 32 && oc <= p) own = cand;
+    }
+    const unsigned k = (unsigned)(p - __shfl_sync(0xffffffffu, o, own));
+    const unsigned rx = __shfl_sync(0xffffffffu, rec.x, own), ry = __shfl_sync(0xffffffffu, rec.y, own);
+    const uint32_t oi = (uint32_t)__shfl_sync(0xffffffffu, i, own);
+    if (p < end) {
+      if (ry & 0x80000000u) {
+        if (rx != 0xffffffffu) { tiles[p] = tlist[rx + k]; vals[p] = oi; }
+      } else {
+        const unsigned b = nth_set_bit16(ry, k), ny = rx >> 16;
+        const unsigned cx = (unsigned)(((float)b + 0.5f) * __frcp_rn((float)ny));   // b / ny for b < 16, ny <= 16
+        tiles[p] = (rx & 0xffffu) + (b - cx * ny) * (unsigned)ntx + cx;
+        vals[p] = oi;
+      }
+    }
+  }
+}
+
 // Compacted depth keys arrive in nondeterministic order (atomic append, batch.cu), so Gaussians with EQUAL depth bits
 // leave the stable sort in that order; the canonical order breaks depth ties by ascending Gaussian id.
 // Runs of equal keys are short (a few per million): the thread at the start of a run insertion-sorts its ids.
@@ -389,7 +469,7 @@ int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, in
 int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, const int *touched, int ntx, int nty, int N,
                        long long capacity, char *ws, const BinLayout &L, const PreBin &pb, int *ranges,
                        const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
-                       int tight) {
+                       int tight, const uint2 *trec, const uint16_t *tlist) {
   uint32_t *ka = (uint32_t *)(ws + L.keys_a), *kb = (uint32_t *)(ws + L.keys_b);
   uint32_t *va = (uint32_t *)(ws + L.vals_a), *vb = (uint32_t *)(ws + L.vals_b);
   int in_b = 0, rc;
@@ -422,6 +502,10 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
       rc = sort_prepare_impl(capacity, key_bits, ws + L.sort_ws, L.sort_ws_bytes, st);
       if (rc != GSX_OK) return rc;
     }
+    if (trec && pb.count && !fuse_hist)
+      k_emit_lists<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.offsets, trec, tlist, ntx, nty, N,
+                                                         pb.count, pb.total, ka, va, (tight && uv_stride == 4) ? 1 : 0);
+    else
     k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, pb.dkeys, pb.perm, touched, pb.offsets, ntx, nty, N,
                                                    pb.count, pb.total, capacity, ka, va, (tight && uv_stride == 4) ? 1 : 0,
                                                    fuse_hist ? sort_hist_impl(ws + L.sort_ws) : nullptr, std::min(key_bits, 8),
@@ -464,7 +548,7 @@ int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_
   int rc = bin_prebin_impl(depth, depth_stride, touched, N, false, nullptr, &pb, st, capacity);
   if (rc != GSX_OK) return rc;
   return bin_emit_sort_impl(uv, uv_stride, radius, touched, ntx, nty, N, capacity, ws, L, pb, ranges, sorted_tiles, sorted_vals, st,
-                            nullptr, 0);
+                            nullptr, 0, nullptr, nullptr);
 }
 
 size_t prebin_sort_ws_bytes(int N) { return sort_workspace_bytes_impl(N); }

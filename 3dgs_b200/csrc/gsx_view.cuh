@@ -41,12 +41,20 @@ struct SlotPtrs {
   float4 *gacc;   // [N][3] float4
   uint32_t *ckey, *cid;   // [N] depth bits / ids of the Gaussians touching a tile, compacted (unordered)
   int *ccount;            // device int: how many
+  uint2 *trec;            // [N] what the exact tile count found, for the emission (batch.cu / binning.cu k_emit_lists):
+                          //   small rectangle: x = origin tile | rows << 16, y = hit mask over its <= 16 cells (tx-major)
+                          //   large rectangle: x = start of its tile ids in BatchConst::tlist (0xffffffff: none), y = 1 << 31 | count
 };
 
 struct BatchConst {
   ViewConst v[GSX_MAX_BATCH];
   SlotPtrs s[GSX_MAX_BATCH];
   int nv;
+  // Tile ids (16-bit) of the LARGE rectangles (> COOP_CELLS cells) of every view of the batch, append-only; small ones
+  // travel as hit masks in SlotPtrs::trec.  tl_cap == 0: no buffer (large rectangles are re-enumerated by the emission).
+  uint16_t *tlist;
+  unsigned *tcursor;      // device counter: entries handed out so far
+  unsigned tl_cap;        // entries in tlist
 };
 
 }  // namespace gsx

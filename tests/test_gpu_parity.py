@@ -497,9 +497,11 @@ def test_view_parallel_split_exchange_matches_fused(B, l_max, sh_alloc):
     r.close()
 
 
-@pytest.mark.parametrize("binning", ["sort", "direct"])
+@pytest.mark.parametrize("binning", ["sort", "direct", "sort-nolists", "sort-shortlists"])
 def test_view_sorted_list_depth_ties_canonical(B, monkeypatch, binning):
-    """(both second-level binning paths: emission + radix sort, and the direct counting sort of tilebin.cu)
+    """(both second-level binning paths: emission + radix sort, and the direct counting sort of tilebin.cu; the emission
+    from the per-Gaussian forward's tile lists, without them (GSX_TILE_LISTS=0: SAT in the emission kernel), and with a list
+    buffer that only holds 3000 entries, so that most Gaussians take the SAT fallback inside k_emit_lists)
     Every Gaussian three times (identical depth bits): the compacted depth keys arrive unordered, so the canonical
     tie order (ascending Gaussian id) exercises k_fix_ties.  Bit-exact against the oracle's list."""
     W, H = 160, 128
@@ -509,7 +511,11 @@ def test_view_sorted_list_depth_ties_canonical(B, monkeypatch, binning):
     g = {k: rep(v) for k, v in g0.items()}
     perm = np.random.default_rng(5).permutation(g["xyz"].shape[0])            # interleave the copies
     g = {k: (None if v is None else np.ascontiguousarray(v[perm])) for k, v in g.items()}
-    monkeypatch.setenv("GSX_BINNING", binning)
+    monkeypatch.setenv("GSX_BINNING", binning.split("-")[0])
+    if binning == "sort-nolists":
+        monkeypatch.setenv("GSX_TILE_LISTS", "0")
+    if binning == "sort-shortlists":
+        monkeypatch.setenv("GSX_TILE_LISTS_CAP", "3000")
     Hh, gd, r, v, stats = _run_view(cam, g, 0, 0.0)
     st = {k: (t.cpu().numpy() if hasattr(t, "cpu") else t) for k, t in r.state().items()}
     N = g["xyz"].shape[0]
