@@ -40,7 +40,7 @@ int check_device_ptr(const void *p, const char *name) {
 // from binning.cu / composite.cu / batch.cu
 BinLayout bin_layout(int N, long long capacity);
 int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, int N, bool compact, const int *ccount,
-                    PreBin *pb, cudaStream_t st, long long capacity);
+                    PreBin *pb, cudaStream_t st, long long capacity, const uint2 *trec);
 int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, const int *touched, int ntx, int nty, int N,
                        long long capacity, char *ws, const BinLayout &L, const PreBin &pb, int *ranges,
                        const uint32_t **sorted_tiles, const uint32_t **sorted_vals, cudaStream_t st, cudaEvent_t *ev,
@@ -227,6 +227,7 @@ static int alloc_slot_buffers(gsx_ctx *c, int k) {
   GSX_CUDA(cudaMalloc(&s.pb.key_b, n * sizeof(uint32_t)));
   GSX_CUDA(cudaMalloc(&s.pb.val_b, n * sizeof(uint32_t)));
   GSX_CUDA(cudaMalloc(&s.pb.offsets, n * sizeof(int)));
+  GSX_CUDA(cudaMalloc(&s.pb.srec, n * sizeof(uint2)));
   GSX_CUDA(cudaMalloc(&s.pb.block_sums, prebin_block_sums_count(c->max_n) * sizeof(int)));
   GSX_CUDA(cudaMalloc(&s.pb.total, 4 * sizeof(int)));
   GSX_CUDA(cudaMemset(s.pb.total, 0, 4 * sizeof(int)));
@@ -244,7 +245,7 @@ static int alloc_slot_buffers(gsx_ctx *c, int k) {
 static void release_slot(gsx_slot &s) {   // cudaFree(nullptr) is a no-op
   cudaFree(s.p.r0); cudaFree(s.p.r1); cudaFree(s.p.r2); cudaFree(s.p.radius); cudaFree(s.p.depth); cudaFree(s.p.mask);
   cudaFree(s.p.touched); cudaFree(s.p.gacc); cudaFree(s.p.ckey); cudaFree(s.p.cid); cudaFree(s.p.trec);
-  cudaFree(s.pb.key_b); cudaFree(s.pb.val_b); cudaFree(s.pb.offsets); cudaFree(s.pb.block_sums); cudaFree(s.pb.total);
+  cudaFree(s.pb.key_b); cudaFree(s.pb.val_b); cudaFree(s.pb.offsets); cudaFree(s.pb.srec); cudaFree(s.pb.block_sums); cudaFree(s.pb.total);
   cudaFree(s.pb.sort_ws);
   if (s.ev_pre) cudaEventDestroy(s.ev_pre);
   if (s.ev_bin) cudaEventDestroy(s.ev_bin);
@@ -339,7 +340,8 @@ static int forward_view(gsx_ctx *c, int k, int N, cudaStream_t st) {
 
 // depth sort (+ tie fix-up) of the slot's compacted list and the scan of the tile counts in depth order
 static int prebin(gsx_ctx *c, gsx_slot &s, int N, cudaStream_t st) {
-  return bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, st, c->capacity);
+  return bin_prebin_impl(nullptr, 0, s.p.touched, N, true, s.p.ccount, &s.pb, st, c->capacity,
+                         (lists_enabled() && c->n_px_tiles <= 65536) ? s.p.trec : nullptr);
 }
 
 static int check_view(gsx_ctx *c, const gsx_view_t *v, const gsx_params_t *p, int N) {

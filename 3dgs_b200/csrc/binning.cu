@@ -31,6 +31,9 @@ int sort_prepare_impl(long long n, int key_bits, void *workspace, size_t workspa
 int sort_tiles_with_ranges_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
                                 const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
                                 size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags);
+int sort_tiles_with_ranges_u16_impl(uint16_t *keys_a, uint16_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                                    const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
+                                    size_t workspace_bytes, cudaStream_t st, int *result_in_b);
 unsigned *sort_hist_impl(void *workspace);
 int tile_ranges_impl(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
                      cudaStream_t st);
@@ -192,6 +195,7 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
 // search over the 32 offsets (shuffles) and produces that Gaussian's k-th tile (the k-th set bit of the mask, or the k-th
 // entry of its list).  A large rectangle without a list (the buffer was full) is enumerated with the SAT as k_emit does.
 // Compact mode only (every entry has instances).
+__device__ __forceinline__ int rec_count(uint2 r) { return (r.y & 0x80000000u) ? (int)(r.y & 0x7fffffffu) : __popc(r.y); }
 __device__ __forceinline__ unsigned nth_set_bit16(unsigned m, unsigned k) {   // position of the k-th (0-based) set bit of a 16-bit mask
   unsigned r = 0;
   unsigned c = __popc(m & 0xffu);
@@ -204,62 +208,92 @@ __device__ __forceinline__ unsigned nth_set_bit16(unsigned m, unsigned k) {   //
   return r;
 }
 
+// Record mode: a block owns one scan tile of SCAN_TILE consecutive depth ranks (warp w: 8 sub-chunks of 32), rebuilds their
+// output offsets from the scanned block sums + its own prefix over the counts, and emits sub-chunk by sub-chunk.
+template <typename TileT>   // uint16_t when the tile sort that follows runs on 16-bit keys
 __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__ uv, int uv_stride,
                                                        const float4 *__restrict__ radius, const uint32_t *__restrict__ perm,
-                                                       const int *__restrict__ offsets, const uint2 *__restrict__ trec,
+                                                       const uint2 *__restrict__ srec, const int *__restrict__ block_sums,
                                                        const uint16_t *__restrict__ tlist, int ntx, int nty, int N_host,
                                                        const int *__restrict__ n_dev, const int *__restrict__ total,
-                                                       uint32_t *__restrict__ tiles, uint32_t *__restrict__ vals, int tight) {
+                                                       TileT *__restrict__ tiles, uint32_t *__restrict__ vals, int tight) {
+  static_assert(SCAN_TILE == kBlock * SCAN_IPT && SCAN_IPT == 8, "a warp owns 8 sub-chunks of 32 entries");
+  __shared__ int s_w[kBlock / 32];
   if (total[1] == 0) return;   // empty view or K beyond the capacity: nothing is emitted (block-uniform)
   const int n = min(*n_dev, N_host);
-  const int j = blockIdx.x * kBlock + threadIdx.x, lane = threadIdx.x & 31;
-  const bool live = j < n;
-  if (!__any_sync(0xffffffffu, live)) return;
-  int i = 0, cnt = 0, o = INT_MAX;
-  uint2 rec = make_uint2(0u, 0u);
-  if (live) {
-    i = (int)perm[j];
-    o = offsets[j];
-    rec = trec[i];
-    cnt = (rec.y & 0x80000000u) ? (int)(rec.y & 0x7fffffffu) : __popc(rec.y);
-  }
-  const bool is_big = (rec.y & 0x80000000u) != 0u;
-  if (live && is_big && rec.x == 0xffffffffu) {   // no list: the SAT enumeration of k_emit, serially (rare)
-    const float u = uv[(size_t)i * uv_stride], v = uv[(size_t)i * uv_stride + 1];
-    const float4 r = radius[i];
-    const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
-    TileRange tr = sat_aabb_range(s, candidate_window(u, v, r.x, ntx, nty));
-    if (tight) clip_range_to_extent(tr, u, v, uv[(size_t)i * uv_stride + 2], uv[(size_t)i * uv_stride + 3]);
-    long long w = o;
-    for (int tx = tr.x0; tx <= tr.x1; ++tx) {
-      const SatCol col = sat_col(s, tx);
-      for (int ty = tr.y0; ty <= tr.y1; ++ty)
-        if (sat_cell(s, col, ty)) { tiles[w] = (uint32_t)(ty * ntx + tx); vals[w] = (uint32_t)i; ++w; }
-    }
-  }
-  const int nlive = __popc(__ballot_sync(0xffffffffu, live));
-  const int first = __shfl_sync(0xffffffffu, o, 0);
-  const int end = __shfl_sync(0xffffffffu, o + cnt, nlive - 1);
-  for (int p0 = first; p0 < end; p0 += 32) {
-    const int p = p0 + lane;
-    int own = 0;   // the last lane whose offset is <= p (offsets ascend; dead lanes hold INT_MAX)
+  const int base = blockIdx.x * SCAN_TILE;
+  if (base >= n) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wj0 = base + warp * (32 * SCAN_IPT);
+  int ex[SCAN_IPT];   // exclusive prefix of the counts inside the warp's 256 entries
+  int run = 0;
 #pragma unroll
-    for (int step = 16; step > 0; step >>= 1) {
-      const int cand = own + step;
-      const int oc = __shfl_sync(0xffffffffu, o, cand & 31);
-      if (cand < 32 && oc <= p) own = cand;
+  for (int c = 0; c < SCAN_IPT; ++c) {
+    const int j = wj0 + c * 32 + lane;
+    const int cnt = j < n ? rec_count(srec[j]) : 0;
+    int incl = cnt;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int x = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += x;
     }
-    const unsigned k = (unsigned)(p - __shfl_sync(0xffffffffu, o, own));
-    const unsigned rx = __shfl_sync(0xffffffffu, rec.x, own), ry = __shfl_sync(0xffffffffu, rec.y, own);
-    const uint32_t oi = (uint32_t)__shfl_sync(0xffffffffu, i, own);
-    if (p < end) {
-      if (ry & 0x80000000u) {
-        if (rx != 0xffffffffu) { tiles[p] = tlist[rx + k]; vals[p] = oi; }
-      } else {
-        const unsigned b = nth_set_bit16(ry, k), ny = rx >> 16;
-        const unsigned cx = (unsigned)(((float)b + 0.5f) * __frcp_rn((float)ny));   // b / ny for b < 16, ny <= 16
-        tiles[p] = (rx & 0xffffu) + (b - cx * ny) * (unsigned)ntx + cx;
-        vals[p] = oi;
+    ex[c] = run + incl - cnt;
+    run += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  if (lane == 0) s_w[warp] = run;
+  __syncthreads();
+  int wbase = block_sums[blockIdx.x];
+  for (int w = 0; w < warp; ++w) wbase += s_w[w];
+#pragma unroll 1
+  for (int c = 0; c < SCAN_IPT; ++c) {
+    const int j = wj0 + c * 32 + lane;
+    const bool live = j < n;
+    if (!__any_sync(0xffffffffu, live)) break;
+    int i = 0, cnt = 0, o = INT_MAX;
+    uint2 rec = make_uint2(0u, 0u);
+    if (live) {
+      rec = srec[j];
+      i = (int)perm[j];
+      cnt = rec_count(rec);
+      o = wbase + ex[c];
+    }
+    if (live && (rec.y & 0x80000000u) && rec.x == 0xffffffffu) {   // large rectangle without a list: the SAT, serially (rare)
+      const float u = uv[(size_t)i * uv_stride], v = uv[(size_t)i * uv_stride + 1];
+      const float4 r = radius[i];
+      const ObbSat s = obb_sat_setup(compute_obb(u, v, r.x, r.y, r.z, r.w));
+      TileRange tr = sat_aabb_range(s, candidate_window(u, v, r.x, ntx, nty));
+      if (tight) clip_range_to_extent(tr, u, v, uv[(size_t)i * uv_stride + 2], uv[(size_t)i * uv_stride + 3]);
+      long long w = o;
+      for (int tx = tr.x0; tx <= tr.x1; ++tx) {
+        const SatCol col = sat_col(s, tx);
+        for (int ty = tr.y0; ty <= tr.y1; ++ty)
+          if (sat_cell(s, col, ty)) { tiles[w] = (TileT)(ty * ntx + tx); vals[w] = (uint32_t)i; ++w; }
+      }
+    }
+    const int nlive = __popc(__ballot_sync(0xffffffffu, live));
+    const int first = __shfl_sync(0xffffffffu, o, 0);
+    const int end = __shfl_sync(0xffffffffu, o + cnt, nlive - 1);
+    for (int p0 = first; p0 < end; p0 += 32) {
+      const int p = p0 + lane;
+      int own = 0;   // the last lane whose offset is <= p (offsets ascend; dead lanes hold INT_MAX)
+#pragma unroll
+      for (int step = 16; step > 0; step >>= 1) {
+        const int cand = own + step;
+        const int oc = __shfl_sync(0xffffffffu, o, cand & 31);
+        if (cand < 32 && oc <= p) own = cand;
+      }
+      const unsigned k = (unsigned)(p - __shfl_sync(0xffffffffu, o, own));
+      const unsigned rx = __shfl_sync(0xffffffffu, rec.x, own), ry = __shfl_sync(0xffffffffu, rec.y, own);
+      const uint32_t oi = (uint32_t)__shfl_sync(0xffffffffu, i, own);
+      if (p < end) {
+        if (ry & 0x80000000u) {
+          if (rx != 0xffffffffu) { tiles[p] = tlist[rx + k]; vals[p] = oi; }
+        } else {
+          const unsigned b = nth_set_bit16(ry, k), ny = rx >> 16;
+          const unsigned cx = (unsigned)(((float)b + 0.5f) * __frcp_rn((float)ny));   // b / ny for b < 16, ny <= 16
+          tiles[p] = (TileT)((rx & 0xffffu) + (b - cx * ny) * (unsigned)ntx + cx);
+          vals[p] = oi;
+        }
       }
     }
   }
@@ -317,6 +351,28 @@ __global__ void __launch_bounds__(kBlock) k_scan_reduce(const int *__restrict__ 
   for (int k = 0; k < SCAN_IPT; ++k) {
     const long long i = base + k * kBlock + threadIdx.x;
     if (i < N) v += scan_value(in, perm, dkeys, i);
+  }
+  const int t = block_reduce_sum(v, s_tmp);
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = t;
+}
+
+// record mode: the tile count of entry j is in the 8-byte record of Gaussian perm[j] (batch.cu); the record is gathered
+// once, here, and left in depth order for the emission kernel
+__global__ void __launch_bounds__(kBlock) k_scan_reduce_rec(const uint32_t *__restrict__ perm, const uint2 *__restrict__ trec,
+                                                            int N_host, const int *__restrict__ n_dev, uint2 *__restrict__ srec,
+                                                            int *__restrict__ block_sums) {
+  __shared__ int s_tmp[kBlock / 32];
+  const int N = min(*n_dev, N_host);
+  const long long base = (long long)blockIdx.x * SCAN_TILE;
+  int v = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_IPT; ++k) {
+    const long long j = base + k * kBlock + threadIdx.x;
+    if (j < N) {
+      const uint2 r = trec[perm[j]];
+      srec[j] = r;
+      v += rec_count(r);
+    }
   }
   const int t = block_reduce_sum(v, s_tmp);
   if (threadIdx.x == 0) block_sums[blockIdx.x] = t;
@@ -440,9 +496,9 @@ BinLayout bin_layout(int N, long long capacity) {
 // compact mode (ckey given): key_a / val_a are the slot's compacted, unordered depth keys + ids (*ccount entries) written
 // by the per-Gaussian kernel, so everything here runs over P' entries; otherwise keys are derived from depth[] over N.
 int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, int N, bool compact, const int *ccount,
-                    PreBin *pb, cudaStream_t st, long long capacity) {
+                    PreBin *pb, cudaStream_t st, long long capacity, const uint2 *trec) {
   int in_b = 0, rc;
-  pb->perm = nullptr; pb->dkeys = nullptr; pb->count = nullptr;
+  pb->perm = nullptr; pb->dkeys = nullptr; pb->count = nullptr; pb->rec_mode = false;
   if (N > 0) {
     if (compact) {
       pb->count = ccount;
@@ -458,6 +514,18 @@ int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, in
       GSX_LAUNCH_CHECK();
     }
     pb->perm = sv; pb->dkeys = sk;
+  }
+  // record mode: one gather of the 8-byte tile records (left in depth order), block sums, totals; the emission kernel
+  // rebuilds the offsets itself.  The direct-binning experiment (GSX_BINNING=direct) needs the offsets array: full scan.
+  const char *e = getenv("GSX_BINNING");
+  if (compact && trec && pb->srec && N > 0 && !(e && e[0] == 'd')) {
+    const int nb = std::max(1, ceil_div(N, SCAN_TILE));
+    k_scan_reduce_rec<<<nb, kBlock, 0, st>>>(pb->perm, trec, N, pb->count, pb->srec, pb->block_sums);
+    GSX_LAUNCH_CHECK();
+    k_scan_block_sums<<<1, 1024, 0, st>>>(pb->block_sums, nb, pb->total, capacity, pb->over_flag);
+    GSX_LAUNCH_CHECK();
+    pb->rec_mode = true;
+    return GSX_OK;
   }
   return exclusive_scan_i32(touched, pb->perm, pb->dkeys, N, pb->count, pb->offsets, pb->block_sums, pb->total, st, capacity,
                             pb->over_flag);
@@ -496,15 +564,26 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
   // Measured on B200 (profiles/r2c_*): the sort loses its 0.057 ms histogram pass, the emission kernel gains 0.050 ms of
   // shared-memory atomics (20.9 M instances): a wash, so the separate histogram pass stays the default (GSX_FUSED_HIST=1).
   const bool fuse_hist = key_bits <= 16 && getenv("GSX_FUSED_HIST") != nullptr;
+  // tile ranges: extracted by the last scatter of the tile sort (round 2; GSX_RANGES=separate: the stand-alone kernel that
+  // re-reads the 4 K bytes of sorted tile ids)
+  static const bool fused_ranges = [] { const char *e = getenv("GSX_RANGES"); return !(e && e[0] == 's'); }();
+  // record mode + fused ranges: nobody needs 32-bit tile keys -- emission and sort run on 16-bit ones (GSX_KEYS16=0: A/B)
+  const bool keys16 = pb.rec_mode && !fuse_hist && fused_ranges && key_bits <= 16 && N > 0 &&
+                      !(getenv("GSX_KEYS16") && getenv("GSX_KEYS16")[0] == '0');
   if (N > 0) {
     // the tile sort's digit histograms are accumulated by the emission kernel (tile ids of up to 16 bits: 65536 tiles)
     if (fuse_hist) {
       rc = sort_prepare_impl(capacity, key_bits, ws + L.sort_ws, L.sort_ws_bytes, st);
       if (rc != GSX_OK) return rc;
     }
-    if (trec && pb.count && !fuse_hist)
-      k_emit_lists<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.offsets, trec, tlist, ntx, nty, N,
-                                                         pb.count, pb.total, ka, va, (tight && uv_stride == 4) ? 1 : 0);
+    if (pb.rec_mode && !fuse_hist && keys16)
+      k_emit_lists<uint16_t><<<ceil_div(N, SCAN_TILE), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.srec, pb.block_sums, tlist,
+                                                                      ntx, nty, N, pb.count, pb.total, (uint16_t *)ka, va,
+                                                                      (tight && uv_stride == 4) ? 1 : 0);
+    else if (pb.rec_mode && !fuse_hist)
+      k_emit_lists<uint32_t><<<ceil_div(N, SCAN_TILE), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.srec, pb.block_sums, tlist,
+                                                                      ntx, nty, N, pb.count, pb.total, ka, va,
+                                                                      (tight && uv_stride == 4) ? 1 : 0);
     else
     k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, pb.dkeys, pb.perm, touched, pb.offsets, ntx, nty, N,
                                                    pb.count, pb.total, capacity, ka, va, (tight && uv_stride == 4) ? 1 : 0,
@@ -513,9 +592,15 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
     GSX_LAUNCH_CHECK();
   }
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
-  // tile ranges: extracted by the last scatter of the tile sort (round 2; GSX_RANGES=separate: the stand-alone kernel that
-  // re-reads the 4 K bytes of sorted tile ids)
-  static const bool fused_ranges = [] { const char *e = getenv("GSX_RANGES"); return !(e && e[0] == 's'); }();
+  if (keys16) {
+    rc = sort_tiles_with_ranges_u16_impl((uint16_t *)ka, (uint16_t *)kb, va, vb, capacity, pb.total + 1, key_bits, ntx * nty, ranges,
+                                         ws + L.sort_ws, L.sort_ws_bytes, st, &in_b);
+    if (rc != GSX_OK) return rc;
+    *sorted_tiles = nullptr;   // never written (gsx_ctx_build_sorted_keys rebuilds the tile from the ranges)
+    *sorted_vals = in_b ? vb : va;
+    if (ev) { GSX_CUDA(cudaEventRecord(ev[1], st)); GSX_CUDA(cudaEventRecord(ev[2], st)); }
+    return GSX_OK;
+  }
   if (fused_ranges) {
     rc = sort_tiles_with_ranges_impl(ka, kb, va, vb, capacity, pb.total + 1, key_bits, ntx * nty, ranges, ws + L.sort_ws,
                                      L.sort_ws_bytes, st, &in_b, (N > 0 && fuse_hist) ? 1 : 0);
@@ -545,7 +630,7 @@ int bin_sort_impl(const float *uv, int uv_stride, const float *depth, int depth_
   pb.val_a = (uint32_t *)(ws + L.dv_a); pb.val_b = (uint32_t *)(ws + L.dv_b);
   pb.offsets = (int *)(ws + L.offsets); pb.block_sums = (int *)(ws + L.block_sums); pb.total = (int *)(ws + L.total);
   pb.sort_ws = ws + L.sort_ws; pb.sort_ws_bytes = L.sort_ws_bytes;
-  int rc = bin_prebin_impl(depth, depth_stride, touched, N, false, nullptr, &pb, st, capacity);
+  int rc = bin_prebin_impl(depth, depth_stride, touched, N, false, nullptr, &pb, st, capacity, nullptr);
   if (rc != GSX_OK) return rc;
   return bin_emit_sort_impl(uv, uv_stride, radius, touched, ntx, nty, N, capacity, ws, L, pb, ranges, sorted_tiles, sorted_vals, st,
                             nullptr, 0, nullptr, nullptr);

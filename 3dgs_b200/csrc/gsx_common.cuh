@@ -76,6 +76,10 @@ struct PreBin {
   size_t sort_ws_bytes = 0;
   const uint32_t *perm = nullptr, *dkeys = nullptr;   // results: ids in depth order and their keys
   const int *count = nullptr;                          // device count of sorted entries (compact mode) or null
+  // record mode (compact mode with the per-Gaussian forward's tile records, binning.cu): the scan gathers each record once
+  // and leaves it in depth order; the emission kernel rebuilds the offsets from block_sums itself (no `offsets` array)
+  uint2 *srec = nullptr;     // [N] buffer for the records in depth order
+  bool rec_mode = false;     // set by the pre-binning when srec / block_sums are what the emission must use
 };
 
 // direct tile binning (tilebin.cu): one stable counting sort on the tile id instead of emission + two radix passes

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS <= 256 ? (sizeof(KeyT) == 8 
 k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
            uint32_t *__restrict__ vals_out, long long n_host, const int *__restrict__ n_dev, int shift, int bits,
            const unsigned int *__restrict__ digit_base /*[256] exclusive*/, unsigned int *__restrict__ status,
-           unsigned int *__restrict__ ticket, int *__restrict__ first_of_key, int key_clamp) {
+           unsigned int *__restrict__ ticket, int *__restrict__ first_of_key, int key_clamp, int write_keys) {
   // first_of_key (last pass of the tile sort only, else null): first_of_key[k] = smallest output index holding key k
   // (keys clamped to key_clamp) -- the tile-range extraction fused into the scatter: a run of equal keys
   // is contiguous in the re-ordered tile, so only run starts issue an atomicMin; k_ranges_from_first turns it into ranges
@@ -248,7 +248,7 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
       const KeyT kk = s_keys[slot];
       const unsigned d = (unsigned)(kk >> shift) & mask;
       gidx[k] = s_gbase[d] + slot;
-      keys_out[gidx[k]] = kk;
+      if (write_keys) keys_out[gidx[k]] = kk;   // the last pass of the tile sort leaves only the values (nobody reads its keys)
       if (first_of_key) {   // the keys of a digit run are sorted (earlier passes), so equal keys are adjacent slots
         const bool run_start = slot == 0 || s_keys[slot - 1] != kk;
         if (run_start) atomicMin(first_of_key + (int)min((unsigned long long)kk, (unsigned long long)key_clamp), gidx[k]);
@@ -313,15 +313,15 @@ SortLayout sort_layout(long long n) {
 template <typename KeyT, int THREADS, int IPT>
 static int launch_onesweep(int tiles, const KeyT *kin, KeyT *kout, const uint32_t *vin, uint32_t *vout, long long n,
                            const int *n_dev, int shift, int bits, const unsigned *base, unsigned *status, unsigned *ticket,
-                           cudaStream_t st, int *first_of_key, int key_clamp) {
-  const size_t dyn = sizeof(KeyT) * (size_t)THREADS * IPT;
+                           cudaStream_t st, int *first_of_key, int key_clamp, int write_keys) {
+  const size_t dyn = std::max(sizeof(KeyT), sizeof(uint32_t)) * (size_t)THREADS * IPT;   // the key tile is reused for the values
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
     GSX_CUDA(cudaFuncSetAttribute(k_onesweep<KeyT, THREADS, IPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
     attr_set = true;
   }
   k_onesweep<KeyT, THREADS, IPT><<<tiles, THREADS, dyn, st>>>(kin, kout, vin, vout, n, n_dev, shift, bits, base, status, ticket,
-                                                              first_of_key, key_clamp);
+                                                              first_of_key, key_clamp, write_keys);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
@@ -335,7 +335,8 @@ static int launch_onesweep(int tiles, const KeyT *kin, KeyT *kout, const uint32_
 template <typename KeyT>
 static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n, const int *n_dev,
                         int key_bits, void *workspace, size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags,
-                        KeyT *first_k = nullptr, uint32_t *first_v = nullptr, int *first_of_key = nullptr, int key_clamp = 0) {
+                        KeyT *first_k = nullptr, uint32_t *first_v = nullptr, int *first_of_key = nullptr, int key_clamp = 0,
+                        bool drop_last_keys = false) {
   if (key_bits < 1 || key_bits > (int)sizeof(KeyT) * 8) { set_error("key_bits %d out of range", key_bits); return GSX_E_ARG; }
   const int passes = (key_bits + 7) / 8;
   // With an even number of passes the ping-pong a -> b -> a ends in a.  first_k / first_v (a third buffer): the first pass
@@ -366,12 +367,13 @@ static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *
     const int bits = std::min(8, key_bits - 8 * p);
     unsigned *stp = status + (size_t)p * tiles * RADIX;
     int *fk = p == passes - 1 ? first_of_key : nullptr;
+    const int wk = (drop_last_keys && p == passes - 1) ? 0 : 1;
     int rc;
     switch (cfg) {
-      case 1: rc = launch_onesweep<KeyT, 512, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp); break;
-      case 2: rc = launch_onesweep<KeyT, 384, 20>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp); break;
-      case 3: rc = launch_onesweep<KeyT, 512, 12>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp); break;
-      default: rc = launch_onesweep<KeyT, 256, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp); break;
+      case 1: rc = launch_onesweep<KeyT, 512, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
+      case 2: rc = launch_onesweep<KeyT, 384, 20>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
+      case 3: rc = launch_onesweep<KeyT, 512, 12>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
+      default: rc = launch_onesweep<KeyT, 256, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
     }
     if (rc != GSX_OK) return rc;
     if (via_third && p == 0) { kin = first_k; vin = first_v; kout = keys_b; vout = vals_b; }
@@ -436,17 +438,32 @@ __global__ void __launch_bounds__(1024) k_ranges_from_first(int *__restrict__ ra
 }
 }  // namespace
 
-int sort_tiles_with_ranges_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
-                                const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
-                                size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags) {
+template <typename KeyT>
+static int sort_tiles_with_ranges_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                                    const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
+                                    size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags, bool drop_last_keys) {
   k_ranges_init<<<std::max(1, std::min(8, (n_tiles + 1024) / 1024)), 1024, 0, st>>>(ranges, n_tiles);
   GSX_LAUNCH_CHECK();
-  int rc = sort_pairs_t<uint32_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b, flags,
-                                  nullptr, nullptr, ranges, n_tiles - 1);
+  int rc = sort_pairs_t<KeyT>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, workspace, workspace_bytes, st, result_in_b, flags,
+                              nullptr, nullptr, ranges, n_tiles - 1, drop_last_keys);
   if (rc != GSX_OK) return rc;
   k_ranges_from_first<<<1, 1024, 0, st>>>(ranges, n_tiles, n, n_dev);
   GSX_LAUNCH_CHECK();
   return GSX_OK;
+}
+int sort_tiles_with_ranges_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                                const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
+                                size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags) {
+  return sort_tiles_with_ranges_t<uint32_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, n_tiles, ranges, workspace,
+                                            workspace_bytes, st, result_in_b, flags, false);
+}
+// 16-bit tile ids (up to 65536 tiles): 2 bytes less per key in the emission's write, the histogram's read and both passes'
+// reads and the first pass's write; the last pass writes no keys at all (the ranges come out of its scatter, fused)
+int sort_tiles_with_ranges_u16_impl(uint16_t *keys_a, uint16_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
+                                    const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
+                                    size_t workspace_bytes, cudaStream_t st, int *result_in_b) {
+  return sort_tiles_with_ranges_t<uint16_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, n_tiles, ranges, workspace,
+                                            workspace_bytes, st, result_in_b, 0, true);
 }
 
 static int ranges_grid(long long n, int n_tiles) {
