@@ -244,7 +244,7 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
   __syncthreads();
   int wbase = block_sums[blockIdx.x];
   for (int w = 0; w < warp; ++w) wbase += s_w[w];
-#pragma unroll 1
+#pragma unroll
   for (int c = 0; c < SCAN_IPT; ++c) {
     const int j = wj0 + c * 32 + lane;
     const bool live = j < n;
@@ -275,13 +275,12 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
     const int end = __shfl_sync(0xffffffffu, o + cnt, nlive - 1);
     for (int p0 = first; p0 < end; p0 += 32) {
       const int p = p0 + lane;
-      int own = 0;   // the last lane whose offset is <= p (offsets ascend; dead lanes hold INT_MAX)
-#pragma unroll
-      for (int step = 16; step > 0; step >>= 1) {
-        const int cand = own + step;
-        const int oc = __shfl_sync(0xffffffffu, o, cand & 31);
-        if (cand < 32 && oc <= p) own = cand;
-      }
+      // owner of output position p = the last lane whose offset is <= p.  Every live entry has instances, so the offsets are
+      // strictly ascending: (lanes that start before p0) + (starts inside [p0, p]) - 1, the latter from one OR-reduction
+      const unsigned before = __popc(__ballot_sync(0xffffffffu, o < p0));
+      const unsigned rel = (unsigned)(o - p0);
+      const unsigned starts = __reduce_or_sync(0xffffffffu, rel < 32u ? (1u << rel) : 0u);
+      const int own = (int)(before + __popc(starts & (0xffffffffu >> (31 - lane)))) - 1;
       const unsigned k = (unsigned)(p - __shfl_sync(0xffffffffu, o, own));
       const unsigned rx = __shfl_sync(0xffffffffu, rec.x, own), ry = __shfl_sync(0xffffffffu, rec.y, own);
       const uint32_t oi = (uint32_t)__shfl_sync(0xffffffffu, i, own);

@@ -373,16 +373,22 @@ def main():
     # algorithmic work per launch (SURVEY 8d / BASELINE.md section 5)
     PB_ = 44 + 4 * D                                                # parameter / gradient bytes per Gaussian (236 at deg 3)
     fused_hist = bool(os.environ.get("GSX_FUSED_HIST"))
+    direct = os.environ.get("GSX_BINNING", "")[:1] == "d"
+    records = os.environ.get("GSX_TILE_LISTS", "1")[:1] != "0" and T <= 65536 and not direct   # emission from the forward's tile records
+    keys16 = (records and not fused_hist and os.environ.get("GSX_KEYS16", "1")[:1] != "0"
+              and os.environ.get("GSX_RANGES", "")[:1] != "s")
     alg = {
         # batch kernels (one launch per batch of nv views): parameters once + per-view records / packed gradients
-        "preprocess_fwd": ("hbm", PB_ * N + nv * (74 * P + 5 * (N - P))),
+        "preprocess_fwd": ("hbm", PB_ * N + nv * (74 * P + 5 * (N - P) + (8 * Pt if records else 0))),
         "preprocess_bwd": ("hbm", PB_ * N + nv * (4 * N + 96 * Pt) + PB_ * N),
         # over the P' Gaussians that touch a tile (compacted by the per-Gaussian kernel): 4-pass depth sort (4 + 4*16), tie
-        # fix-up (8), scan through the permutation (20), emission in depth order (8 + 32) + 8 B per instance
-        "scan_emit": ("hbm", 136 * Pt + 8 * K),
-        # tile sort: passes * (8 B in + 8 B out); the digit histograms are accumulated by the emission kernel (round 2),
-        # otherwise + 4 B per key for the histogram pass
-        "sort": ("hbm", ((0 if fused_hist else 4) + 16 * passes) * K),
+        # fix-up (8), then -- tile records (default) -- one gather of the 8-byte record left in depth order (4 + 8 + 8), emission
+        # from the records (4 + 8) + (2 + 4) B per instance; without them: scan through the permutation (20), emission with
+        # the SAT (8 + 32) + 8 B per instance.  The 2-byte tile ids of large rectangles are not counted.
+        "scan_emit": ("hbm", (108 * Pt + 6 * K) if records else (136 * Pt + 8 * K)),
+        # tile sort on 16-bit keys (default): histogram 2 + per pass (2 + 4) in + (2 + 4) out, the last pass writes no keys;
+        # on 32-bit keys: 4 + passes * (8 in + 8 out)
+        "sort": ("hbm", ((2 + 12 * passes - 2) if keys16 else ((0 if fused_hist else 4) + 16 * passes)) * K),
         "ranges": ("hbm", 4 * K + 4 * (T + 1)),
         "composite_fwd": ("fp32", 18 * Sx),
         "composite_bwd": ("fp32", 10 * Sx + 46 * Sp),
