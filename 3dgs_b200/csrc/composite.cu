@@ -621,18 +621,18 @@ int count_work_launch(const float4 *r0, const float4 *r1, const int *sorted, con
 // composite3.cu: the round-2 kernels (packed fp32x2 arithmetic, cp.async ring, direct per-warp reductions).  Default;
 // GSX_COMPOSITE=v2 in the environment selects the round-1 kernels of this file for A/B measurements.
 int composite_fwd3_launch(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges, int W,
-                          int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st);
+                          int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st, const int *order);
 int composite_bwd3_launch(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges, int W,
                           int H, float bg, const int *spp, const float *wpp, const float *grad_image, float *packed_grads,
-                          cudaStream_t st);
+                          cudaStream_t st, const int *order);
 static bool use_v2() {
   static const int v = [] { const char *e = getenv("GSX_COMPOSITE"); return (e && e[0] == 'v' && e[1] == '2') ? 1 : 0; }();
   return v != 0;
 }
 
 int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
-                         int W, int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st) {
-  if (!use_v2()) return composite_fwd3_launch(r0, r1, r2, sorted, ranges, W, H, bg, spp, wpp, image, st);
+                         int W, int H, float bg, int *spp, float *wpp, float *image, cudaStream_t st, const int *order) {
+  if (!use_v2()) return composite_fwd3_launch(r0, r1, r2, sorted, ranges, W, H, bg, spp, wpp, image, st, order);
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
   k_composite_fwd2<<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, image);
   GSX_LAUNCH_CHECK();
@@ -641,8 +641,8 @@ int composite_fwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, c
 
 int composite_bwd_packed(const float4 *r0, const float4 *r1, const float4 *r2, const int *sorted, const int *ranges,
                          int W, int H, float bg, const int *spp, const float *wpp, const float *grad_image,
-                         float *packed_grads, cudaStream_t st) {
-  if (!use_v2()) return composite_bwd3_launch(r0, r1, r2, sorted, ranges, W, H, bg, spp, wpp, grad_image, packed_grads, st);
+                         float *packed_grads, cudaStream_t st, const int *order) {
+  if (!use_v2()) return composite_bwd3_launch(r0, r1, r2, sorted, ranges, W, H, bg, spp, wpp, grad_image, packed_grads, st, order);
   const int ntx = (W + 15) / 16, nty = (H + 15) / 16;
   k_composite_bwd2<2><<<ntx * nty, 128, 0, st>>>(r0, r1, r2, sorted, ranges, ntx, W, H, bg, spp, wpp, grad_image, packed_grads);
   GSX_LAUNCH_CHECK();
