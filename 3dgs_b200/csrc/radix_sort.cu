@@ -100,50 +100,31 @@ __device__ __forceinline__ void st_volatile(unsigned *p, unsigned v) {
   asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
-template <typename KeyT, int THREADS, int IPT>
-__global__ void __launch_bounds__(THREADS, (THREADS <= 256 ? (sizeof(KeyT) == 8 ? 3 : 4) : (sizeof(KeyT) == 8 ? 1 : 2)))
-k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
-           uint32_t *__restrict__ vals_out, long long n_host, const int *__restrict__ n_dev, int shift, int bits,
-           const unsigned int *__restrict__ digit_base /*[256] exclusive*/, unsigned int *__restrict__ status,
-           unsigned int *__restrict__ ticket, int *__restrict__ first_of_key, int key_clamp, int write_keys) {
-  // first_of_key (last pass of the tile sort only, else null): first_of_key[k] = smallest output index holding key k
-  // (keys clamped to key_clamp) -- the tile-range extraction fused into the scatter (SURVEY 7 step 4): a run of equal keys
-  // is contiguous in the re-ordered tile, so only run starts issue an atomicMin; k_ranges_from_first turns it into ranges
-  constexpr int WARPS = THREADS / 32, TILE = THREADS * IPT;
-  static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit for the digit-parallel steps");
-  extern __shared__ __align__(16) unsigned char s_dyn[];
-  KeyT *s_keys = reinterpret_cast<KeyT *>(s_dyn);           // [TILE], reused for the values
-  __shared__ unsigned int s_warp[WARPS][RADIX + 1];         // per-warp digit counts -> exclusive offsets
-  __shared__ unsigned int s_excl[RADIX + 1];                // block-exclusive offset of each digit
-  __shared__ int s_gbase[RADIX];                            // global base minus local offset
-  __shared__ unsigned int s_scan[RADIX / 32];
-  __shared__ unsigned int s_tile;
-
+// the tile's work after its extent is known; FULL: all THREADS * IPT slots hold keys (every tile but the last), so the bounds
+// predicates and the padding digit of the ranking disappear
+template <typename KeyT, int THREADS, int IPT, bool FULL>
+__device__ __forceinline__ void onesweep_tile(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out,
+                                              const uint32_t *__restrict__ vals_in, uint32_t *__restrict__ vals_out, int shift,
+                                              int bits, const unsigned int *__restrict__ digit_base, unsigned int *__restrict__ status,
+                                              int *__restrict__ first_of_key, int key_clamp, int write_keys, unsigned tile,
+                                              long long base, int valid, unsigned mask, KeyT *s_keys,
+                                              unsigned int (*s_warp)[RADIX + 1], unsigned int *s_excl, int *s_gbase,
+                                              unsigned int *s_scan) {
+  constexpr int WARPS = THREADS / 32;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-  for (int i = tid; i < WARPS * (RADIX + 1); i += THREADS) (&s_warp[0][0])[i] = 0;
-  if (tid < RADIX) s_excl[tid] = 0;
-  __syncthreads();
-  const unsigned tile = s_tile;
-  const long long n = live_count(n_dev, n_host);
-  const long long base = (long long)tile * TILE;
-  if (base >= n) return;
-  const int valid = (int)min((long long)TILE, n - base);
-  const unsigned mask = (1u << bits) - 1u;
-
   KeyT key[IPT];
   unsigned pos[IPT];
 #pragma unroll
   for (int i = 0; i < IPT; ++i) {
     const int li = warp * (IPT * 32) + i * 32 + lane;
-    key[i] = li < valid ? keys_in[base + li] : ~(KeyT)0;
+    key[i] = (FULL || li < valid) ? keys_in[base + li] : ~(KeyT)0;
   }
   // 1. tile histogram first (shared-memory integer atomics) so the tile's aggregate is published BEFORE the ranking:
   //    successors' look-back then never waits on this tile's ranking
 #pragma unroll
   for (int i = 0; i < IPT; ++i) {
     const int li = warp * (IPT * 32) + i * 32 + lane;
-    if (li < valid) atomicAdd(&s_excl[(unsigned)(key[i] >> shift) & mask], 1u);
+    if (FULL || li < valid) atomicAdd(&s_excl[(unsigned)(key[i] >> shift) & mask], 1u);
   }
   __syncthreads();
   const unsigned total = tid < RADIX ? s_excl[tid] : 0u;   // for digit == tid
@@ -153,12 +134,15 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
 #pragma unroll
   for (int i = 0; i < IPT; ++i) {
     const int li = warp * (IPT * 32) + i * 32 + lane;
-    const unsigned d = li < valid ? ((unsigned)(key[i] >> shift) & mask) : (unsigned)RADIX;
+    const unsigned d = (FULL || li < valid) ? ((unsigned)(key[i] >> shift) & mask) : (unsigned)RADIX;
     // peers = lanes holding the same digit: one vote per digit bit (+ one for the padding digit RADIX, bit 8).
     // Measured against match.any on B200: tile sort 0.427 -> 0.399 ms per view.
-    const bool pad = d >> 8;
-    const unsigned vp = __ballot_sync(0xffffffffu, pad);
-    unsigned peers = pad ? vp : ~vp;
+    unsigned peers = 0xffffffffu;
+    if (!FULL) {   // a full tile has no padding items
+      const bool pad = d >> 8;
+      const unsigned vp = __ballot_sync(0xffffffffu, pad);
+      peers = pad ? vp : ~vp;
+    }
 #pragma unroll
     for (int b = 0; b < 8; ++b) {
       if (b < bits) {   // uniform
@@ -232,7 +216,7 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
 #pragma unroll
   for (int i = 0; i < IPT; ++i) {
     const int li = warp * (IPT * 32) + i * 32 + lane;
-    if (li < valid) {   // padding items (digit RADIX) are never written
+    if (FULL || li < valid) {   // padding items (digit RADIX) are never written
       const unsigned d = (unsigned)(key[i] >> shift) & mask;
       pos[i] += s_excl[d] + s_warp[warp][d];
       s_keys[pos[i]] = key[i];
@@ -244,7 +228,7 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
   for (int k = 0; k < IPT; ++k) {
     const int slot = tid + k * THREADS;
     gidx[k] = -1;
-    if (slot < valid) {
+    if (FULL || slot < valid) {
       const KeyT kk = s_keys[slot];
       const unsigned d = (unsigned)(kk >> shift) & mask;
       gidx[k] = s_gbase[d] + slot;
@@ -261,12 +245,50 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
 #pragma unroll
   for (int i = 0; i < IPT; ++i) {
     const int li = warp * (IPT * 32) + i * 32 + lane;
-    if (li < valid) s_vals[pos[i]] = vals_in[base + li];
+    if (FULL || li < valid) s_vals[pos[i]] = vals_in[base + li];
   }
   __syncthreads();
 #pragma unroll
   for (int k = 0; k < IPT; ++k)
     if (gidx[k] >= 0) vals_out[gidx[k]] = s_vals[tid + k * THREADS];
+}
+
+template <typename KeyT, int THREADS, int IPT>
+__global__ void __launch_bounds__(THREADS, (THREADS <= 256 ? (sizeof(KeyT) == 8 ? 3 : 4) : (sizeof(KeyT) == 8 ? 1 : 2)))
+k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const uint32_t *__restrict__ vals_in,
+           uint32_t *__restrict__ vals_out, long long n_host, const int *__restrict__ n_dev, int shift, int bits,
+           const unsigned int *__restrict__ digit_base /*[256] exclusive*/, unsigned int *__restrict__ status,
+           unsigned int *__restrict__ ticket, int *__restrict__ first_of_key, int key_clamp, int write_keys) {
+  // first_of_key (last pass of the tile sort only, else null): first_of_key[k] = smallest output index holding key k
+  // (keys clamped to key_clamp) -- the tile-range extraction fused into the scatter (SURVEY 7 step 4): a run of equal keys
+  // is contiguous in the re-ordered tile, so only run starts issue an atomicMin; k_ranges_from_first turns it into ranges
+  constexpr int WARPS = THREADS / 32, TILE = THREADS * IPT;
+  static_assert(THREADS >= RADIX && THREADS % 32 == 0, "one thread per digit for the digit-parallel steps");
+  extern __shared__ __align__(16) unsigned char s_dyn[];
+  KeyT *s_keys = reinterpret_cast<KeyT *>(s_dyn);           // [TILE], reused for the values
+  __shared__ unsigned int s_warp[WARPS][RADIX + 1];         // per-warp digit counts -> exclusive offsets
+  __shared__ unsigned int s_excl[RADIX + 1];                // block-exclusive offset of each digit
+  __shared__ int s_gbase[RADIX];                            // global base minus local offset
+  __shared__ unsigned int s_scan[RADIX / 32];
+  __shared__ unsigned int s_tile;
+
+  const int tid = threadIdx.x;
+  if (tid == 0) s_tile = atomicAdd(ticket, 1u);
+  for (int i = tid; i < WARPS * (RADIX + 1); i += THREADS) (&s_warp[0][0])[i] = 0;
+  if (tid < RADIX) s_excl[tid] = 0;
+  __syncthreads();
+  const unsigned tile = s_tile;
+  const long long n = live_count(n_dev, n_host);
+  const long long base = (long long)tile * TILE;
+  if (base >= n) return;
+  const int valid = (int)min((long long)TILE, n - base);
+  const unsigned mask = (1u << bits) - 1u;
+  if (valid == TILE)
+    onesweep_tile<KeyT, THREADS, IPT, true>(keys_in, keys_out, vals_in, vals_out, shift, bits, digit_base, status, first_of_key,
+                                            key_clamp, write_keys, tile, base, valid, mask, s_keys, s_warp, s_excl, s_gbase, s_scan);
+  else
+    onesweep_tile<KeyT, THREADS, IPT, false>(keys_in, keys_out, vals_in, vals_out, shift, bits, digit_base, status, first_of_key,
+                                             key_clamp, write_keys, tile, base, valid, mask, s_keys, s_warp, s_excl, s_gbase, s_scan);
 }
 
 // ranges[t] = first i whose tile >= t ; ranges[n_tiles] = n   (reference cuda/culling.cu:302-343; exact integer
