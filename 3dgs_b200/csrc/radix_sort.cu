@@ -28,6 +28,9 @@ namespace {
 // GSX_RS_LATE_AGG=1 (build variant): no tile histogram by shared-memory atomics; the aggregate is published after the
 // ranking from the per-warp digit counts.  Measured on B200 at C4 (r2k): 16 fewer shared atomics per thread, but successors'
 // look-back then waits for the ranking: tile sort 0.356 -> 0.411 ms, depth sort + scan + emission 0.363 -> 0.390 ms.  Stays 0.
+#ifndef GSX_RS_MATCH_ATOMIC
+#define GSX_RS_MATCH_ATOMIC 1
+#endif
 #ifndef GSX_RS_LATE_AGG
 #define GSX_RS_LATE_AGG 0
 #endif
@@ -114,8 +117,8 @@ __device__ __forceinline__ void onesweep_tile(const KeyT *__restrict__ keys_in, 
                                               int bits, const unsigned int *__restrict__ digit_base, unsigned int *__restrict__ status,
                                               int *__restrict__ first_of_key, int key_clamp, int write_keys, unsigned tile,
                                               long long base, int valid, unsigned mask, KeyT *s_keys,
-                                              unsigned int (*s_warp)[RADIX + 1], unsigned int *s_excl, int *s_gbase,
-                                              unsigned int *s_scan) {
+                                              unsigned int (*s_warp)[RADIX + 1], unsigned int (*s_match)[RADIX + 1],
+                                              unsigned int *s_excl, int *s_gbase, unsigned int *s_scan) {
   constexpr int WARPS = THREADS / 32;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   KeyT key[IPT];
@@ -146,6 +149,23 @@ __device__ __forceinline__ void onesweep_tile(const KeyT *__restrict__ keys_in, 
   for (int i = 0; i < IPT; ++i) {
     const int li = warp * (IPT * 32) + i * 32 + lane;
     const unsigned d = (FULL || li < valid) ? ((unsigned)(key[i] >> shift) & mask) : (unsigned)RADIX;
+#if GSX_RS_MATCH_ATOMIC
+    // peers = lanes holding the same digit, found through shared memory: every lane ORs its lane bit into the warp's word of
+    // its digit, the word IS the peer mask; the group's first lane clears it for the next item while it advances the
+    // warp's digit counter.  3 shared-memory operations instead of one vote per digit bit, which cost 9 SASS instructions
+    // each (shift, mask, compare, VOTE, select, and: 72 of the ~130 instructions per item of an 8-bit pass).
+    unsigned *mw = &s_match[warp][d];
+    atomicOr(mw, 1u << lane);
+    __syncwarp();
+    const unsigned peers = *reinterpret_cast<volatile unsigned *>(mw);
+    const unsigned lt = peers & ((1u << lane) - 1u);
+    const unsigned before = s_warp[warp][d];
+    __syncwarp();
+    if (lt == 0) { *mw = 0u; s_warp[warp][d] = before + __popc(peers); }
+    __syncwarp();
+    pos[i] = before + __popc(lt);
+  }
+#else
     // peers = lanes holding the same digit: one vote per digit bit (+ one for the padding digit RADIX, bit 8).
     // Measured against match.any on B200: tile sort 0.427 -> 0.399 ms per view.
     unsigned peers = 0xffffffffu;
@@ -169,6 +189,7 @@ __device__ __forceinline__ void onesweep_tile(const KeyT *__restrict__ keys_in, 
     __syncwarp();
     pos[i] = before + __popc(lt);
   }
+#endif
   __syncthreads();
   // per digit: exclusive scan over warps
   if (tid < RADIX) {
@@ -282,6 +303,7 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
   extern __shared__ __align__(16) unsigned char s_dyn[];
   KeyT *s_keys = reinterpret_cast<KeyT *>(s_dyn);           // [TILE], reused for the values
   __shared__ unsigned int s_warp[WARPS][RADIX + 1];         // per-warp digit counts -> exclusive offsets
+  __shared__ unsigned int s_match[GSX_RS_MATCH_ATOMIC ? WARPS : 1][RADIX + 1];   // per-warp peer masks of the item being ranked
   __shared__ unsigned int s_excl[RADIX + 1];                // block-exclusive offset of each digit
   __shared__ int s_gbase[RADIX];                            // global base minus local offset
   __shared__ unsigned int s_scan[RADIX / 32];
@@ -289,7 +311,10 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
 
   const int tid = threadIdx.x;
   if (tid == 0) s_tile = atomicAdd(ticket, 1u);
-  for (int i = tid; i < WARPS * (RADIX + 1); i += THREADS) (&s_warp[0][0])[i] = 0;
+  for (int i = tid; i < WARPS * (RADIX + 1); i += THREADS) {
+    (&s_warp[0][0])[i] = 0;
+    if (GSX_RS_MATCH_ATOMIC) (&s_match[0][0])[i] = 0;
+  }
   if (tid < RADIX) s_excl[tid] = 0;
   __syncthreads();
   const unsigned tile = s_tile;
@@ -300,10 +325,10 @@ k_onesweep(const KeyT *__restrict__ keys_in, KeyT *__restrict__ keys_out, const 
   const unsigned mask = (1u << bits) - 1u;
   if (valid == TILE)
     onesweep_tile<KeyT, THREADS, IPT, true>(keys_in, keys_out, vals_in, vals_out, shift, bits, digit_base, status, first_of_key,
-                                            key_clamp, write_keys, tile, base, valid, mask, s_keys, s_warp, s_excl, s_gbase, s_scan);
+                                            key_clamp, write_keys, tile, base, valid, mask, s_keys, s_warp, s_match, s_excl, s_gbase, s_scan);
   else
     onesweep_tile<KeyT, THREADS, IPT, false>(keys_in, keys_out, vals_in, vals_out, shift, bits, digit_base, status, first_of_key,
-                                             key_clamp, write_keys, tile, base, valid, mask, s_keys, s_warp, s_excl, s_gbase, s_scan);
+                                             key_clamp, write_keys, tile, base, valid, mask, s_keys, s_warp, s_match, s_excl, s_gbase, s_scan);
 }
 
 // ranges[t] = first i whose tile >= t ; ranges[n_tiles] = n   (reference cuda/culling.cu:302-343; exact integer
