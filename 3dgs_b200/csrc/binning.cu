@@ -46,6 +46,16 @@ namespace {
 constexpr int kBlock = 256;
 constexpr int SCAN_IPT = 8;
 constexpr int SCAN_TILE = kBlock * SCAN_IPT;
+// record mode (k_scan_reduce_rec / k_emit_lists): entries per thread and per block.  Measured on B200 at C4 (r2k): 4 instead
+// of 8 (2600 emission blocks instead of 1300: a fuller last wave) shortens the stage timed alone, 0.364 -> 0.305 ms, but the
+// pipelined step -- where the emission of view k + 1 runs under the compositing of view k and idle issue slots are filled
+// anyway -- gets slower, 575 -> 567 views/s: what counts there is the instruction total, and twice the blocks repeat the
+// per-block prologue.  Stays 8.
+#ifndef GSX_REC_IPT
+#define GSX_REC_IPT 8
+#endif
+constexpr int REC_IPT = GSX_REC_IPT;
+constexpr int REC_TILE = kBlock * REC_IPT;
 
 // exact instance count of one Gaussian (+ its coarse candidate count, what the reference's size query returns)
 __device__ __forceinline__ int count_tiles(float u, float v, float4 r, int ntx, int nty, int *coarse) {
@@ -190,25 +200,13 @@ __global__ void __launch_bounds__(kBlock) k_emit(const float *__restrict__ uv, i
 
 // Emission from what the exact tile count of the per-Gaussian forward left (batch.cu): no SAT, no gathers of the
 // screen-space records, one 8-byte record per Gaussian -- the hit mask of a small rectangle, or where a large one's tile ids
-// are.  A warp owns 32 consecutive depth ranks; their instances are one contiguous output range [o_0, o_31 + cnt_31), which
-// the warp fills 32 entries per step, coalesced: each lane finds the Gaussian its output position belongs to by a 5-step
-// search over the 32 offsets (shuffles) and produces that Gaussian's k-th tile (the k-th set bit of the mask, or the k-th
-// entry of its list).  A large rectangle without a list (the buffer was full) is enumerated with the SAT as k_emit does.
-// Compact mode only (every entry has instances).
+// are.  A warp owns 32 consecutive depth ranks; their instances are one contiguous output range.  Small rectangles: each lane
+// expands its mask into a per-warp shared-memory staging buffer, the warp writes it out 32 entries per step (coalesced).
+// Large rectangles: the warp copies the list.  A large rectangle without a list (the buffer was full) is enumerated with the
+// SAT as k_emit does.  Compact mode only (every entry has instances).
 __device__ __forceinline__ int rec_count(uint2 r) { return (r.y & 0x80000000u) ? (int)(r.y & 0x7fffffffu) : __popc(r.y); }
-__device__ __forceinline__ unsigned nth_set_bit16(unsigned m, unsigned k) {   // position of the k-th (0-based) set bit of a 16-bit mask
-  unsigned r = 0;
-  unsigned c = __popc(m & 0xffu);
-  if (k >= c) { k -= c; r += 8; m >>= 8; }
-  c = __popc(m & 0xfu);
-  if (k >= c) { k -= c; r += 4; m >>= 4; }
-  c = __popc(m & 0x3u);
-  if (k >= c) { k -= c; r += 2; m >>= 2; }
-  if (k >= (m & 1u)) r += 1;
-  return r;
-}
 
-// Record mode: a block owns one scan tile of SCAN_TILE consecutive depth ranks (warp w: 8 sub-chunks of 32), rebuilds their
+// Record mode: a block owns one scan tile of REC_TILE consecutive depth ranks (warp w: REC_IPT sub-chunks of 32), rebuilds their
 // output offsets from the scanned block sums + its own prefix over the counts, and emits sub-chunk by sub-chunk.
 template <typename TileT>   // uint16_t when the tile sort that follows runs on 16-bit keys
 __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__ uv, int uv_stride,
@@ -217,18 +215,20 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
                                                        const uint16_t *__restrict__ tlist, int ntx, int nty, int N_host,
                                                        const int *__restrict__ n_dev, const int *__restrict__ total,
                                                        TileT *__restrict__ tiles, uint32_t *__restrict__ vals, int tight) {
-  static_assert(SCAN_TILE == kBlock * SCAN_IPT && SCAN_IPT == 8, "a warp owns 8 sub-chunks of 32 entries");
+  static_assert(REC_TILE == kBlock * REC_IPT, "a warp owns REC_IPT sub-chunks of 32 entries");
   __shared__ int s_w[kBlock / 32];
+  __shared__ uint16_t s_tile[kBlock / 32][32 * COOP_CELLS];   // per warp: the tiles of a sub-chunk's small rectangles
+  __shared__ uint8_t s_own[kBlock / 32][32 * COOP_CELLS];     // ... and the lane each belongs to
   if (total[1] == 0) return;   // empty view or K beyond the capacity: nothing is emitted (block-uniform)
   const int n = min(*n_dev, N_host);
-  const int base = blockIdx.x * SCAN_TILE;
+  const int base = blockIdx.x * REC_TILE;
   if (base >= n) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int wj0 = base + warp * (32 * SCAN_IPT);
-  int ex[SCAN_IPT];   // exclusive prefix of the counts inside the warp's 256 entries
+  const int wj0 = base + warp * (32 * REC_IPT);
+  int ex[REC_IPT];   // exclusive prefix of the counts inside the warp's 256 entries
   int run = 0;
 #pragma unroll
-  for (int c = 0; c < SCAN_IPT; ++c) {
+  for (int c = 0; c < REC_IPT; ++c) {
     const int j = wj0 + c * 32 + lane;
     const int cnt = j < n ? rec_count(srec[j]) : 0;
     int incl = cnt;
@@ -244,16 +244,20 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
   __syncthreads();
   int wbase = block_sums[blockIdx.x];
   for (int w = 0; w < warp; ++w) wbase += s_w[w];
-#pragma unroll
-  for (int c = 0; c < SCAN_IPT; ++c) {
+  // the (record, id) of sub-chunk c + 1 are requested before sub-chunk c is expanded
+  uint2 rec_n = make_uint2(0u, 0u);
+  int i_n = 0;
+  if (wj0 + lane < n) { rec_n = srec[wj0 + lane]; i_n = (int)perm[wj0 + lane]; }
+#pragma unroll 1
+  for (int c = 0; c < REC_IPT; ++c) {
     const int j = wj0 + c * 32 + lane;
     const bool live = j < n;
     if (!__any_sync(0xffffffffu, live)) break;
-    int i = 0, cnt = 0, o = INT_MAX;
-    uint2 rec = make_uint2(0u, 0u);
+    const uint2 rec = rec_n;
+    const int i = i_n;
+    if (c + 1 < REC_IPT && j + 32 < n) { rec_n = srec[j + 32]; i_n = (int)perm[j + 32]; }
+    int cnt = 0, o = INT_MAX;
     if (live) {
-      rec = srec[j];
-      i = (int)perm[j];
       cnt = rec_count(rec);
       o = wbase + ex[c];
     }
@@ -270,29 +274,57 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
           if (sat_cell(s, col, ty)) { tiles[w] = (TileT)(ty * ntx + tx); vals[w] = (uint32_t)i; ++w; }
       }
     }
-    const int nlive = __popc(__ballot_sync(0xffffffffu, live));
-    const int first = __shfl_sync(0xffffffffu, o, 0);
-    const int end = __shfl_sync(0xffffffffu, o + cnt, nlive - 1);
-    for (int p0 = first; p0 < end; p0 += 32) {
-      const int p = p0 + lane;
-      // owner of output position p = the last lane whose offset is <= p.  Every live entry has instances, so the offsets are
-      // strictly ascending: (lanes that start before p0) + (starts inside [p0, p]) - 1, the latter from one OR-reduction
-      const unsigned before = __popc(__ballot_sync(0xffffffffu, o < p0));
-      const unsigned rel = (unsigned)(o - p0);
-      const unsigned starts = __reduce_or_sync(0xffffffffu, rel < 32u ? (1u << rel) : 0u);
-      const int own = (int)(before + __popc(starts & (0xffffffffu >> (31 - lane)))) - 1;
-      const unsigned k = (unsigned)(p - __shfl_sync(0xffffffffu, o, own));
-      const unsigned rx = __shfl_sync(0xffffffffu, rec.x, own), ry = __shfl_sync(0xffffffffu, rec.y, own);
-      const uint32_t oi = (uint32_t)__shfl_sync(0xffffffffu, i, own);
-      if (p < end) {
-        if (ry & 0x80000000u) {
-          if (rx != 0xffffffffu) { tiles[p] = tlist[rx + k]; vals[p] = oi; }
-        } else {
-          const unsigned b = nth_set_bit16(ry, k), ny = rx >> 16;
-          const unsigned cx = (unsigned)(((float)b + 0.5f) * __frcp_rn((float)ny));   // b / ny for b < 16, ny <= 16
-          tiles[p] = (TileT)((rx & 0xffffu) + (b - cx * ny) * (unsigned)ntx + cx);
-          vals[p] = oi;
+    // small rectangles: every lane expands its hit mask into the warp's staging buffer (tile id + owner lane, at the
+    // exclusive prefix of the small counts), then the warp writes the staged entries out 32 per step: consecutive entries of
+    // one Gaussian go to consecutive output positions, so the stores coalesce, and no lane searches for its owner
+    const bool is_big = (rec.y & 0x80000000u) != 0u;
+    const int sc = (live && !is_big) ? cnt : 0;
+    int incl = sc;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int x = __shfl_up_sync(0xffffffffu, incl, off);
+      if (lane >= off) incl += x;
+    }
+    const int sp = incl - sc, stotal = __shfl_sync(0xffffffffu, incl, 31);
+    if (sc) {
+      const unsigned ny = rec.x >> 16, t00 = rec.x & 0xffffu, colmask = (1u << ny) - 1u;
+      int e = sp;
+      for (unsigned m = rec.y, cx = 0; m; m >>= ny, ++cx) {   // column by column, as the mask was built (batch.cu)
+        unsigned col = m & colmask;
+        while (col) {
+          const unsigned b = (unsigned)__ffs(col) - 1u;
+          col &= col - 1;
+          s_tile[warp][e] = (uint16_t)(t00 + b * (unsigned)ntx + cx);
+          s_own[warp][e] = (uint8_t)lane;
+          ++e;
         }
+      }
+    }
+    __syncwarp();
+    for (int e0 = 0; e0 < stotal; e0 += 32) {
+      const int e = e0 + lane;
+      const bool ok = e < stotal;
+      const int own = ok ? s_own[warp][e] : 0;
+      const unsigned t = ok ? s_tile[warp][e] : 0u;
+      const int oo = __shfl_sync(0xffffffffu, o, own), spo = __shfl_sync(0xffffffffu, sp, own);
+      const uint32_t oi = (uint32_t)__shfl_sync(0xffffffffu, i, own);
+      if (ok) {
+        const int p = oo + e - spo;
+        tiles[p] = (TileT)t;
+        vals[p] = oi;
+      }
+    }
+    __syncwarp();   // the staging buffer is free for the next sub-chunk
+    // large rectangles: the warp copies each list
+    unsigned bm = __ballot_sync(0xffffffffu, live && is_big && rec.x != 0xffffffffu);
+    while (bm) {
+      const int L = __ffs(bm) - 1;
+      bm &= bm - 1;
+      const int oo = __shfl_sync(0xffffffffu, o, L), n_l = __shfl_sync(0xffffffffu, cnt, L);
+      const uint32_t ts = __shfl_sync(0xffffffffu, rec.x, L), oi = (uint32_t)__shfl_sync(0xffffffffu, i, L);
+      for (int k = lane; k < n_l; k += 32) {
+        tiles[oo + k] = (TileT)tlist[ts + (uint32_t)k];
+        vals[oo + k] = oi;
       }
     }
   }
@@ -362,10 +394,10 @@ __global__ void __launch_bounds__(kBlock) k_scan_reduce_rec(const uint32_t *__re
                                                             int *__restrict__ block_sums) {
   __shared__ int s_tmp[kBlock / 32];
   const int N = min(*n_dev, N_host);
-  const long long base = (long long)blockIdx.x * SCAN_TILE;
+  const long long base = (long long)blockIdx.x * REC_TILE;
   int v = 0;
 #pragma unroll
-  for (int k = 0; k < SCAN_IPT; ++k) {
+  for (int k = 0; k < REC_IPT; ++k) {
     const long long j = base + k * kBlock + threadIdx.x;
     if (j < N) {
       const uint2 r = trec[perm[j]];
@@ -466,7 +498,7 @@ int exclusive_scan_i32(const int *in, const uint32_t *perm, const uint32_t *dkey
   GSX_LAUNCH_CHECK();
   return GSX_OK;
 }
-size_t scan_block_sums_count(int N) { return (size_t)std::max(1, ceil_div(N, SCAN_TILE)); }
+size_t scan_block_sums_count(int N) { return (size_t)std::max(1, ceil_div(N, std::min(SCAN_TILE, REC_TILE))); }
 
 // Workspace carve-up shared by the per-function F7 entry point and the view-level context.
 BinLayout bin_layout(int N, long long capacity) {
@@ -518,7 +550,7 @@ int bin_prebin_impl(const float *depth, int depth_stride, const int *touched, in
   // rebuilds the offsets itself.  The direct-binning experiment (GSX_BINNING=direct) needs the offsets array: full scan.
   const char *e = getenv("GSX_BINNING");
   if (compact && trec && pb->srec && N > 0 && !(e && e[0] == 'd')) {
-    const int nb = std::max(1, ceil_div(N, SCAN_TILE));
+    const int nb = std::max(1, ceil_div(N, REC_TILE));
     k_scan_reduce_rec<<<nb, kBlock, 0, st>>>(pb->perm, trec, N, pb->count, pb->srec, pb->block_sums);
     GSX_LAUNCH_CHECK();
     k_scan_block_sums<<<1, 1024, 0, st>>>(pb->block_sums, nb, pb->total, capacity, pb->over_flag);
@@ -576,11 +608,11 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
       if (rc != GSX_OK) return rc;
     }
     if (pb.rec_mode && !fuse_hist && keys16)
-      k_emit_lists<uint16_t><<<ceil_div(N, SCAN_TILE), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.srec, pb.block_sums, tlist,
+      k_emit_lists<uint16_t><<<ceil_div(N, REC_TILE), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.srec, pb.block_sums, tlist,
                                                                       ntx, nty, N, pb.count, pb.total, (uint16_t *)ka, va,
                                                                       (tight && uv_stride == 4) ? 1 : 0);
     else if (pb.rec_mode && !fuse_hist)
-      k_emit_lists<uint32_t><<<ceil_div(N, SCAN_TILE), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.srec, pb.block_sums, tlist,
+      k_emit_lists<uint32_t><<<ceil_div(N, REC_TILE), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.srec, pb.block_sums, tlist,
                                                                       ntx, nty, N, pb.count, pb.total, ka, va,
                                                                       (tight && uv_stride == 4) ? 1 : 0);
     else
