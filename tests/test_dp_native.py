@@ -113,8 +113,13 @@ def test_dp_native_world1_matches_batch_step_and_adam(l_max):
     for (p_ref, _, m_ref, v_ref, _), k in zip(groups, names):
         # the two gradient computations differ in their atomics' summation order (1e-6 relative): the first Adam step is
         # lr * g / (|g| + eps), so only gradients of magnitude ~eps can move visibly -- counted, not ignored
-        assert util.close_frac(par[k].cpu().numpy().reshape(N, -1), p_ref.cpu().numpy(), 2e-6, 1e-7) <= 1e-4, f"adam epilogue {k}"
-        assert util.close_frac(mom[k][0].cpu().numpy().reshape(N, -1), m_ref.cpu().numpy(), 1e-3, 1e-12) <= 1e-4, f"adam epilogue m {k}"
+        assert util.close_frac(par[k].cpu().numpy().reshape(N, -1), p_ref.cpu().numpy(), 2e-6, 1e-7) <= 5e-4, f"adam epilogue {k}"
+        # the first moment is (1 - b1) * g, linear in the gradient: the summation-order noise of g is bounded relative to the
+        # array's scale, not to each element (an element that is a near-cancelling sum may differ by far more than 1e-3 of
+        # itself: a per-element relative bound made this check depend on the run's atomic order)
+        mg, mr = mom[k][0].cpu().numpy().reshape(N, -1).astype(np.float64), m_ref.cpu().numpy().astype(np.float64)
+        assert np.linalg.norm(mg - mr) <= 1e-5 * np.linalg.norm(mr), f"adam epilogue m {k} (norm)"
+        assert util.close_frac(mg, mr, 1e-3, 1e-5 * float(np.abs(mr).max())) == 0.0, f"adam epilogue m {k} (elements)"
     assert all(torch.equal(saved[k], getattr(gd, k)) for k in names)
     nat.close()
     r.close()
