@@ -592,9 +592,9 @@ def main():
                   f"gradients (SH gradients rebuilt locally; plain allreduce would be {flat.numel() * 4 / 1e6:.0f} MB)")
     else:
         xbytes = "none (single GPU)"
-    # depth sort: histogram, digit scan, onesweep x4, tie fix-up; scan x3; emission (+ tile-sort histograms); tile sort: digit
-    # scan, onesweep x passes; ranges; compositing x2
-    launches_per_view = 2 + 4 + 1 + 3 + 1 + 1 + passes + 2 + 2 + (0 if fused_hist else 1)   # ranges: init + suffix-min fix-up
+    # depth sort: histogram, digit scan, onesweep x4, tie fix-up; scan (record mode: gather + block sums; else x3); emission;
+    # tile sort: histogram, digit scan, onesweep x passes; ranges: init + suffix-min fix-up; compositing x2
+    launches_per_view = 2 + 4 + 1 + (2 if records else 3) + 1 + 1 + passes + 2 + 2 + (0 if fused_hist else 1)
     out = {
         "metric": METRIC, "value": views_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
