@@ -185,6 +185,7 @@ k_batch_fwd(const __grid_constant__ BatchConst bc, int N, const float *__restric
     // finds is kept for the emission kernel (binning.cu k_emit_lists), which then needs neither the SAT nor the screen-space
     // records: a small rectangle leaves its 16-bit hit mask (cells tx-major, as enumerated) + origin tile + row count in an
     // 8-byte record; a large one reserves its cell count in the batch's tile-list buffer and writes its tile ids there.
+    static_assert(COOP_CELLS <= 16, "a small rectangle's hit mask shares the record word with the large-rectangle flag and is staged 16 per lane");
     const bool big = active && rect_cells(tr) > COOP_CELLS;
     unsigned hitmask = 0;
     if (active && !big) {

@@ -6,6 +6,10 @@
 //   1. a stable 4-pass radix sort of the N Gaussians on their 32 order-preserving depth bits (ties keep ascending id),
 //   2. emitting each Gaussian's instances in that order (exclusive scan of the counts through the permutation),
 //   3. a stable radix sort of the K instances on the tile id alone: ceil(log2 T) bits = 2 passes up to 65536 tiles.
+// Round 2: steps 2 and 3 of the view-level path run in "record mode" -- the per-Gaussian forward's exact tile count leaves
+// an 8-byte tile record per Gaussian (hit mask of a small rectangle / where a large one's tile ids are, batch.cu), the scan
+// gathers the records once into depth order, the emission expands them without any SAT and writes 16-bit tile ids, and the
+// tile sort runs on 16-bit keys (k_scan_reduce_rec, k_emit_lists below; radix_sort.cu).
 // Per instance this moves 2 x 16 B instead of 6 x 24 B; the 64-bit tile|depth keys are never materialised (they can
 // be rebuilt for inspection, api.cu).  Result is bit-identical to sorting the 64-bit keys.  Replaces the reference's coarse_binning_kernel (run twice) + generate_splats_kernel
 // + thrust temporaries + 4 blocking D2H reads (cuda/culling.cu:197-300, :386-475): the candidate window and the
