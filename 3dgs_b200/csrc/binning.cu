@@ -37,7 +37,7 @@ int sort_tiles_with_ranges_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *va
                                 size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags);
 int sort_tiles_with_ranges_u16_impl(uint16_t *keys_a, uint16_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
                                     const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
-                                    size_t workspace_bytes, cudaStream_t st, int *result_in_b);
+                                    size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags);
 unsigned *sort_hist_impl(void *workspace);
 int tile_ranges_impl(const uint64_t *sorted_keys, long long n, const int *n_dev, int n_tiles, int *ranges,
                      cudaStream_t st);
@@ -218,7 +218,8 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
                                                        const uint2 *__restrict__ srec, const int *__restrict__ block_sums,
                                                        const uint16_t *__restrict__ tlist, int ntx, int nty, int N_host,
                                                        const int *__restrict__ n_dev, const int *__restrict__ total,
-                                                       TileT *__restrict__ tiles, uint32_t *__restrict__ vals, int tight) {
+                                                       TileT *__restrict__ tiles, uint32_t *__restrict__ vals, int tight,
+                                                       unsigned *__restrict__ hist, int bits0, int bits1) {
   static_assert(REC_TILE == kBlock * REC_IPT, "a warp owns REC_IPT sub-chunks of 32 entries");
   __shared__ int s_w[kBlock / 32];
   __shared__ uint16_t s_tile[kBlock / 32][32 * COOP_CELLS];   // per warp: the tiles of a sub-chunk's small rectangles
@@ -228,6 +229,26 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
   const int base = blockIdx.x * REC_TILE;
   if (base >= n) return;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  // hist (optional): the digit histograms of the tile sort that follows ([pass][256], pass p = tile-id bits [8p, 8p + 8)),
+  // accumulated while the tile ids are in registers, so the sort needs no histogram pass over the 2 K bytes of keys.  Low
+  // digit: one shared-memory atomic per entry (neighbouring entries differ).  High digit: the same for long runs of
+  // entries (it changes every 256 / n_tiles_x tile rows), so each run of a 32-entry step adds its length once.
+  __shared__ unsigned s_hist[2 * 256];
+  if (hist) { s_hist[threadIdx.x] = 0u; s_hist[threadIdx.x + 256] = 0u; __syncthreads(); }
+  const unsigned m0 = (1u << bits0) - 1u;
+  auto count_step = [&](bool ok, unsigned t, int nvalid) {   // called by all 32 lanes; lanes [0, nvalid) hold entries
+    if (ok) atomicAdd(&s_hist[t & m0], 1u);
+    if (bits1 > 0) {
+      const unsigned hb = ok ? (t >> 8) : 0xffffffffu;
+      const unsigned prev = __shfl_up_sync(0xffffffffu, hb, 1);
+      const bool head = ok && (lane == 0 || prev != hb);
+      const unsigned heads = __ballot_sync(0xffffffffu, head);
+      if (head) {
+        const unsigned after = lane == 31 ? 0u : (heads & ~((2u << lane) - 1u));
+        atomicAdd(&s_hist[256 + hb], (unsigned)((after ? __ffs(after) - 1 : nvalid) - lane));
+      }
+    }
+  };
   const int wj0 = base + warp * (32 * REC_IPT);
   int ex[REC_IPT];   // exclusive prefix of the counts inside the warp's 256 entries
   int run = 0;
@@ -275,7 +296,11 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
       for (int tx = tr.x0; tx <= tr.x1; ++tx) {
         const SatCol col = sat_col(s, tx);
         for (int ty = tr.y0; ty <= tr.y1; ++ty)
-          if (sat_cell(s, col, ty)) { tiles[w] = (TileT)(ty * ntx + tx); vals[w] = (uint32_t)i; ++w; }
+          if (sat_cell(s, col, ty)) {
+            const unsigned t = (unsigned)(ty * ntx + tx);
+            tiles[w] = (TileT)t; vals[w] = (uint32_t)i; ++w;
+            if (hist) { atomicAdd(&s_hist[t & m0], 1u); if (bits1 > 0) atomicAdd(&s_hist[256 + (t >> 8)], 1u); }
+          }
       }
     }
     // small rectangles: every lane expands its hit mask into the warp's staging buffer (tile id + owner lane, at the
@@ -317,6 +342,7 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
         tiles[p] = (TileT)t;
         vals[p] = oi;
       }
+      if (hist) count_step(ok, t, min(32, stotal - e0));
     }
     __syncwarp();   // the staging buffer is free for the next sub-chunk
     // large rectangles: the warp copies each list
@@ -326,11 +352,22 @@ __global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__
       bm &= bm - 1;
       const int oo = __shfl_sync(0xffffffffu, o, L), n_l = __shfl_sync(0xffffffffu, cnt, L);
       const uint32_t ts = __shfl_sync(0xffffffffu, rec.x, L), oi = (uint32_t)__shfl_sync(0xffffffffu, i, L);
-      for (int k = lane; k < n_l; k += 32) {
-        tiles[oo + k] = (TileT)tlist[ts + (uint32_t)k];
-        vals[oo + k] = oi;
+      for (int k0 = 0; k0 < n_l; k0 += 32) {
+        const int k = k0 + lane;
+        const bool ok = k < n_l;
+        const unsigned t = ok ? tlist[ts + (uint32_t)k] : 0u;
+        if (ok) {
+          tiles[oo + k] = (TileT)t;
+          vals[oo + k] = oi;
+        }
+        if (hist) count_step(ok, t, min(32, n_l - k0));
       }
     }
+  }
+  if (hist) {
+    __syncthreads();
+    if (s_hist[threadIdx.x]) atomicAdd(&hist[threadIdx.x], s_hist[threadIdx.x]);
+    if (bits1 > 0 && s_hist[256 + threadIdx.x]) atomicAdd(&hist[256 + threadIdx.x], s_hist[256 + threadIdx.x]);
   }
 }
 
@@ -605,20 +642,28 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
   // record mode + fused ranges: nobody needs 32-bit tile keys -- emission and sort run on 16-bit ones (GSX_KEYS16=0: A/B)
   const bool keys16 = pb.rec_mode && !fuse_hist && fused_ranges && key_bits <= 16 && N > 0 &&
                       !(getenv("GSX_KEYS16") && getenv("GSX_KEYS16")[0] == '0');
+  // record mode, 16-bit keys: the emission accumulates the tile sort's digit histograms (GSX_EMIT_HIST=0: separate pass)
+  const bool emit_hist = keys16 && !(getenv("GSX_EMIT_HIST") && getenv("GSX_EMIT_HIST")[0] == '0');
   if (N > 0) {
     // the tile sort's digit histograms are accumulated by the emission kernel (tile ids of up to 16 bits: 65536 tiles)
     if (fuse_hist) {
       rc = sort_prepare_impl(capacity, key_bits, ws + L.sort_ws, L.sort_ws_bytes, st);
       if (rc != GSX_OK) return rc;
     }
-    if (pb.rec_mode && !fuse_hist && keys16)
+    if (pb.rec_mode && !fuse_hist && keys16) {
+      if (emit_hist) {
+        rc = sort_prepare_impl(capacity, key_bits, ws + L.sort_ws, L.sort_ws_bytes, st);
+        if (rc != GSX_OK) return rc;
+      }
       k_emit_lists<uint16_t><<<ceil_div(N, REC_TILE), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.srec, pb.block_sums, tlist,
                                                                       ntx, nty, N, pb.count, pb.total, (uint16_t *)ka, va,
-                                                                      (tight && uv_stride == 4) ? 1 : 0);
-    else if (pb.rec_mode && !fuse_hist)
+                                                                      (tight && uv_stride == 4) ? 1 : 0,
+                                                                      emit_hist ? sort_hist_impl(ws + L.sort_ws) : nullptr,
+                                                                      std::min(key_bits, 8), std::max(key_bits - 8, 0));
+    } else if (pb.rec_mode && !fuse_hist)
       k_emit_lists<uint32_t><<<ceil_div(N, REC_TILE), kBlock, 0, st>>>(uv, uv_stride, radius, pb.perm, pb.srec, pb.block_sums, tlist,
                                                                       ntx, nty, N, pb.count, pb.total, ka, va,
-                                                                      (tight && uv_stride == 4) ? 1 : 0);
+                                                                      (tight && uv_stride == 4) ? 1 : 0, nullptr, 8, 0);
     else
     k_emit<<<ceil_div(N, kBlock), kBlock, 0, st>>>(uv, uv_stride, radius, pb.dkeys, pb.perm, touched, pb.offsets, ntx, nty, N,
                                                    pb.count, pb.total, capacity, ka, va, (tight && uv_stride == 4) ? 1 : 0,
@@ -629,7 +674,7 @@ int bin_emit_sort_impl(const float *uv, int uv_stride, const float4 *radius, con
   if (ev) GSX_CUDA(cudaEventRecord(ev[0], st));
   if (keys16) {
     rc = sort_tiles_with_ranges_u16_impl((uint16_t *)ka, (uint16_t *)kb, va, vb, capacity, pb.total + 1, key_bits, ntx * nty, ranges,
-                                         ws + L.sort_ws, L.sort_ws_bytes, st, &in_b);
+                                         ws + L.sort_ws, L.sort_ws_bytes, st, &in_b, emit_hist ? 1 : 0);
     if (rc != GSX_OK) return rc;
     *sorted_tiles = nullptr;   // never written (gsx_ctx_build_sorted_keys rebuilds the tile from the ranges)
     *sorted_vals = in_b ? vb : va;

@@ -523,9 +523,9 @@ int sort_tiles_with_ranges_impl(uint32_t *keys_a, uint32_t *keys_b, uint32_t *va
 // reads and the first pass's write; the last pass writes no keys at all (the ranges come out of its scatter, fused)
 int sort_tiles_with_ranges_u16_impl(uint16_t *keys_a, uint16_t *keys_b, uint32_t *vals_a, uint32_t *vals_b, long long n,
                                     const int *n_dev, int key_bits, int n_tiles, int *ranges, void *workspace,
-                                    size_t workspace_bytes, cudaStream_t st, int *result_in_b) {
+                                    size_t workspace_bytes, cudaStream_t st, int *result_in_b, int flags) {
   return sort_tiles_with_ranges_t<uint16_t>(keys_a, keys_b, vals_a, vals_b, n, n_dev, key_bits, n_tiles, ranges, workspace,
-                                            workspace_bytes, st, result_in_b, 0, true);
+                                            workspace_bytes, st, result_in_b, flags, true);
 }
 
 static int ranges_grid(long long n, int n_tiles) {
