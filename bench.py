@@ -377,6 +377,7 @@ def main():
     records = os.environ.get("GSX_TILE_LISTS", "1")[:1] != "0" and T <= 65536 and not direct   # emission from the forward's tile records
     keys16 = (records and not fused_hist and os.environ.get("GSX_KEYS16", "1")[:1] != "0"
               and os.environ.get("GSX_RANGES", "")[:1] != "s")
+    emit_hist = keys16 and os.environ.get("GSX_EMIT_HIST", "1")[:1] != "0"   # tile-sort histograms accumulated by the emission
     alg = {
         # batch kernels (one launch per batch of nv views): parameters once + per-view records / packed gradients
         "preprocess_fwd": ("hbm", PB_ * N + nv * (74 * P + 5 * (N - P) + (8 * Pt if records else 0))),
@@ -386,9 +387,9 @@ def main():
         # from the records (4 + 8) + (2 + 4) B per instance; without them: scan through the permutation (20), emission with
         # the SAT (8 + 32) + 8 B per instance.  The 2-byte tile ids of large rectangles are not counted.
         "scan_emit": ("hbm", (108 * Pt + 6 * K) if records else (136 * Pt + 8 * K)),
-        # tile sort on 16-bit keys (default): histogram 2 + per pass (2 + 4) in + (2 + 4) out, the last pass writes no keys;
+        # tile sort on 16-bit keys (default): [histogram 2, unless the emission accumulated it] + per pass (2 + 4) in + (2 + 4) out, the last pass writes no keys;
         # on 32-bit keys: 4 + passes * (8 in + 8 out)
-        "sort": ("hbm", ((2 + 12 * passes - 2) if keys16 else ((0 if fused_hist else 4) + 16 * passes)) * K),
+        "sort": ("hbm", (((0 if emit_hist else 2) + 12 * passes - 2) if keys16 else ((0 if fused_hist else 4) + 16 * passes)) * K),
         "ranges": ("hbm", 4 * K + 4 * (T + 1)),
         "composite_fwd": ("fp32", 18 * Sx),
         "composite_bwd": ("fp32", 10 * Sx + 46 * Sp),
@@ -594,7 +595,7 @@ def main():
         xbytes = "none (single GPU)"
     # depth sort: histogram, digit scan, onesweep x4, tie fix-up; scan (record mode: gather + block sums; else x3); emission;
     # tile sort: histogram, digit scan, onesweep x passes; ranges: init + suffix-min fix-up; compositing x2
-    launches_per_view = 2 + 4 + 1 + (2 if records else 3) + 1 + 1 + passes + 2 + 2 + (0 if fused_hist else 1)
+    launches_per_view = 2 + 4 + 1 + (2 if records else 3) + 1 + 1 + passes + 2 + 2 + (0 if (fused_hist or emit_hist) else 1)
     out = {
         "metric": METRIC, "value": views_per_s, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
