@@ -497,7 +497,7 @@ def test_view_parallel_split_exchange_matches_fused(B, l_max, sh_alloc):
     r.close()
 
 
-@pytest.mark.parametrize("binning", ["sort", "direct", "sort-nolists", "sort-shortlists", "sort-keys32"])
+@pytest.mark.parametrize("binning", ["sort", "direct", "sort-nolists", "sort-shortlists", "sort-keys32", "sort-histpass"])
 def test_view_sorted_list_depth_ties_canonical(B, monkeypatch, binning):
     """(both second-level binning paths: emission + radix sort, and the direct counting sort of tilebin.cu; the emission
     from the per-Gaussian forward's tile lists, without them (GSX_TILE_LISTS=0: SAT in the emission kernel), and with a list
@@ -518,6 +518,8 @@ def test_view_sorted_list_depth_ties_canonical(B, monkeypatch, binning):
         monkeypatch.setenv("GSX_TILE_LISTS_CAP", "3000")
     if binning == "sort-keys32":                       # 32-bit tile keys through emission + tile sort (default: 16-bit)
         monkeypatch.setenv("GSX_KEYS16", "0")
+    if binning == "sort-histpass":                     # separate histogram pass over the tile keys (default: the emission's)
+        monkeypatch.setenv("GSX_EMIT_HIST", "0")
     Hh, gd, r, v, stats = _run_view(cam, g, 0, 0.0)
     st = {k: (t.cpu().numpy() if hasattr(t, "cpu") else t) for k, t in r.state().items()}
     N = g["xyz"].shape[0]
