@@ -53,8 +53,11 @@ static int rs_cfg(int key_bytes, long long n) {
     return (v >= 0 && v < 4) ? v : -1;
   }();
   if (forced >= 0) return forced;
-  if (key_bytes == 8) return 0;
-  return n > 6000000 ? 1 : 3;
+  // Round 2, after the ranking moved to shared-memory peer masks (r2m A/B of the whole C4 step, views/s): 256 x 16 for every
+  // sort 582.6, 512 x 16 578.8, 384 x 20 578.9, 512 x 12 571.6 (with the ballot ranking the large shapes had won: 512 x 16
+  // for the 20.9 M instances, 512 x 12 for the 2.7 M depth keys).
+  (void)key_bytes; (void)n;
+  return 0;
 }
 static int rs_tile(int key_bytes, long long n) { const int c = rs_cfg(key_bytes, n); return kRsCfg[c].threads * kRsCfg[c].ipt; }
 
