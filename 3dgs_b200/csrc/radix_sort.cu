@@ -43,21 +43,22 @@ constexpr uint32_t FLAG_AGG = 1u << 30, FLAG_INC = 2u << 30, FLAG_MASK = 3u << 3
 // bandwidth per pass until registers / shared memory cut the occupancy (CUB's sm_100 tuning for 4-byte keys + 4-byte values
 // uses 384-512 threads x ~20 keys, tuning_radix_sort.cuh:92-160).  GSX_RS_CFG=0..3 selects one at run time for A/B runs.
 struct RsCfg { int threads, ipt; };
-constexpr RsCfg kRsCfg[4] = {{256, 16}, {512, 16}, {384, 20}, {512, 12}};
+constexpr RsCfg kRsCfg[6] = {{256, 16}, {512, 16}, {384, 20}, {512, 12}, {256, 20}, {256, 24}};
 // Measured on B200 against CUB Policy1000 on the C4 keys (profiles/r2b_*sort_vs_cub*): 4-byte keys, 20.9 M pairs: 512 x 16
 // is the fastest shape; 2.7 M pairs (one wave of tiles, latency-bound): 512 x 12; 8-byte keys: 256 x 16.
 static int rs_cfg(int key_bytes, long long n) {
   static const int forced = [] {
     const char *e = getenv("GSX_RS_CFG");
     const int v = e ? atoi(e) : -1;
-    return (v >= 0 && v < 4) ? v : -1;
+    return (v >= 0 && v < 6) ? v : -1;
   }();
   if (forced >= 0) return forced;
   // Round 2, after the ranking moved to shared-memory peer masks (r2m A/B of the whole C4 step, views/s): 256 x 16 for every
   // sort 582.6, 512 x 16 578.8, 384 x 20 578.9, 512 x 12 571.6 (with the ballot ranking the large shapes had won: 512 x 16
   // for the 20.9 M instances, 512 x 12 for the 2.7 M depth keys).
-  (void)key_bytes; (void)n;
-  return 0;
+  // 256 x 20 against 256 x 16 / 256 x 24, same A/B: 585.0 / 582.3 / 579.3 (2- and 4-byte keys; 8-byte keys keep 256 x 16)
+  (void)n;
+  return key_bytes == 8 ? 0 : 4;
 }
 static int rs_tile(int key_bytes, long long n) { const int c = rs_cfg(key_bytes, n); return kRsCfg[c].threads * kRsCfg[c].ipt; }
 
@@ -438,6 +439,8 @@ static int sort_pairs_t(KeyT *keys_a, KeyT *keys_b, uint32_t *vals_a, uint32_t *
       case 1: rc = launch_onesweep<KeyT, 512, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
       case 2: rc = launch_onesweep<KeyT, 384, 20>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
       case 3: rc = launch_onesweep<KeyT, 512, 12>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
+      case 4: rc = launch_onesweep<KeyT, 256, 20>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
+      case 5: rc = launch_onesweep<KeyT, 256, 24>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
       default: rc = launch_onesweep<KeyT, 256, 16>(tiles, kin, kout, vin, vout, n, n_dev, 8 * p, bits, hist + p * RADIX, stp, ticket + p, st, fk, key_clamp, wk); break;
     }
     if (rc != GSX_OK) return rc;
