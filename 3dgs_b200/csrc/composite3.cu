@@ -26,8 +26,11 @@
 
 #include "gsx_common.cuh"
 
+// r2n sweep of the whole C4 step (profiles/sweep_c4_minb.sh, views/s): backward cap 5 / 6 / 7 / 8 / 9 CTAs per SM = 575 / 585 / 591 /
+// 583 / 578 (78 -> 71 registers at 7; shared memory still holds 6 CTAs, the gain is the tighter schedule); with the forward
+// at 14 (below): 595
 #ifndef GSX_C4_BWD_MINB
-#define GSX_C4_BWD_MINB 6
+#define GSX_C4_BWD_MINB 7
 #endif
 #ifndef GSX_C4_DEFAULT
 #define GSX_C4_DEFAULT 1   // B200, C4 (profiles/r2d_*): 453 M -> 356 M warp instructions, 0.518 -> 0.484 ms per view
@@ -40,8 +43,9 @@
 #ifndef GSX_C3_BWD_MINB
 #define GSX_C3_BWD_MINB 10
 #endif
+// r2n: forward cap 10 / 12 / 14 / 16 = 577 / 585 / 588 / 588 views/s (32 registers + 8 bytes spilled from 14 on)
 #ifndef GSX_C3_FWD_MINB
-#define GSX_C3_FWD_MINB 12
+#define GSX_C3_FWD_MINB 14
 #endif
 
 namespace gsx {
