@@ -212,8 +212,13 @@ __device__ __forceinline__ int rec_count(uint2 r) { return (r.y & 0x80000000u) ?
 
 // Record mode: a block owns one scan tile of REC_TILE consecutive depth ranks (warp w: REC_IPT sub-chunks of 32), rebuilds their
 // output offsets from the scanned block sums + its own prefix over the counts, and emits sub-chunk by sub-chunk.
+// resident blocks per SM the register allocation is capped for (r2n sweep of the whole C4 step: 4 / 5 / 6 / 8 = 593.7 / 599.1 /
+// 594.5 / 594.0 views/s)
+#ifndef GSX_EMIT_MINB
+#define GSX_EMIT_MINB 5
+#endif
 template <typename TileT>   // uint16_t when the tile sort that follows runs on 16-bit keys
-__global__ void __launch_bounds__(kBlock) k_emit_lists(const float *__restrict__ uv, int uv_stride,
+__global__ void __launch_bounds__(kBlock, GSX_EMIT_MINB) k_emit_lists(const float *__restrict__ uv, int uv_stride,
                                                        const float4 *__restrict__ radius, const uint32_t *__restrict__ perm,
                                                        const uint2 *__restrict__ srec, const int *__restrict__ block_sums,
                                                        const uint16_t *__restrict__ tlist, int ntx, int nty, int N_host,
