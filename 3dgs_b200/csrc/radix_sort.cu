@@ -28,6 +28,9 @@ namespace {
 // GSX_RS_LATE_AGG=1 (build variant): no tile histogram by shared-memory atomics; the aggregate is published after the
 // ranking from the per-warp digit counts.  Measured on B200 at C4 (r2k): 16 fewer shared atomics per thread, but successors'
 // look-back then waits for the ranking: tile sort 0.356 -> 0.411 ms, depth sort + scan + emission 0.363 -> 0.390 ms.  Stays 0.
+#ifndef GSX_RS_LB
+#define GSX_RS_LB 8   // predecessors fetched per look-back round (r2o sweep of the C4 step: 4 / 8 / 16 = 599 / 598 / 587 views/s)
+#endif
 #ifndef GSX_RS_MATCH_ATOMIC
 #define GSX_RS_MATCH_ATOMIC 1
 #endif
@@ -226,7 +229,7 @@ __device__ __forceinline__ void onesweep_tile(const KeyT *__restrict__ keys_in, 
       // windowed: LB predecessors are fetched at once (independent loads in flight) and consumed nearest first up to
       // the first one that is inclusive or not yet published -- with every tile of a small input resident in one wave
       // the walk back is long, and one L2 round trip per hop was the latency of the whole pass
-      constexpr int LB = 8;
+      constexpr int LB = GSX_RS_LB;
       long long t = (long long)tile - 1;
       while (true) {
         unsigned sw[LB];
